@@ -1,0 +1,203 @@
+/*
+ * vectorian_b200.h -- C ABI of the B200-native brute-force sentence search path.
+ *
+ * The reference (poke1024/vectorian) has no C ABI: its boundary for this path is
+ * the pybind11 module `vectorian_core` (vectorian/core/cpp/module.cpp:30-152).
+ * Each entry point below names the reference interface it replaces.  All
+ * pointers are HOST pointers unless the name ends in `_dev`; the library owns
+ * every device allocation until the matching *_destroy.  Every function returns
+ * 0 on success and a nonzero vx_status otherwise; vx_last_error() gives the
+ * message of the last failure on the calling thread.  There is no CPU fallback:
+ * without a usable CUDA device vx_init fails with VX_ERR_NO_DEVICE.
+ */
+#ifndef VECTORIAN_B200_H
+#define VECTORIAN_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+	VX_OK = 0,
+	VX_ERR_INVALID = 1,      /* bad argument (mirrors std::invalid_argument / RuntimeError) */
+	VX_ERR_NO_DEVICE = 2,    /* no CUDA device / wrong architecture                        */
+	VX_ERR_CUDA = 3,         /* a CUDA call failed                                         */
+	VX_ERR_LENGTH = 4,       /* pyalign::exceeded_implementation_length (solver.h:111-130) */
+	VX_ERR_ABORTED = 5       /* Query::abort() (cpp/query.h:183-189)                       */
+} vx_status;
+
+/* pyalign::enums::Locality (pyalign/algorithm/enum.h:27-31) */
+typedef enum { VX_LOCAL = 0, VX_GLOBAL = 1, VX_SEMIGLOBAL = 2 } vx_locality;
+
+/* solver choice made by FactoryCreator::resolve_gap_type (pyalign/algorithm/factory.h:930-965) */
+typedef enum { VX_GAP_LINEAR = 0, VX_GAP_AFFINE = 1, VX_GAP_GENERAL = 2 } vx_gap_kind;
+
+/* Maximum sequence length of the reference solver: int16 index >> 1 (solver.h:488-495). */
+#define VX_MAX_LEN 16383
+
+/*
+ * Alignment options == {'locality', 'gap_cost'} of vectorian.alignment.*.to_args
+ * (vectorian/alignment.py:31-38) after GapCostOptions parsing (factory.h:33-65).
+ *   linear : per-step cost lin_s / lin_t                      (LinearGapCostSolver, solver.h:2738-2848)
+ *   affine : w(k) = aff_ext * k + aff_open for k >= 1, w(0)=0 (AffineCost, solver.h:2850-2873; note the
+ *            (u,v) swap at factory.h:41-52: AffineGapCost(u, v) -> aff_open = u, aff_ext = v)
+ *   general: tables w_s[0..n_w_s), w_t[0..n_w_t) = GapCost.costs(n)  (GeneralGapCostSolver, solver.h:3087-3118);
+ *            n_w_s must be > the longest window, n_w_t > the query length.
+ */
+typedef struct {
+	int32_t locality;   /* vx_locality */
+	int32_t gap_kind;   /* vx_gap_kind */
+	float lin_s, lin_t;
+	float aff_open_s, aff_ext_s;
+	float aff_open_t, aff_ext_t;
+	const float *w_s;
+	int32_t n_w_s;
+	const float *w_t;
+	int32_t n_w_t;
+} vx_align_params;
+
+/*
+ * Query options == kwargs of core.Query.initialize (cpp/query.cpp:32-154) that reach the hot path.
+ *   max_matches, min_score : ResultSet(max_matches, Score(min_score, 1))           cpp/query.cpp:14-15
+ *   submatch_weight        : reference_score                                        cpp/metric/alignment.h:84-106
+ *   tag_weighted != 0      : 'alignment-tag-weighted' -> TagWeightedSlice           cpp/slice/static.h:193-288
+ *       t_weights[T]  = weight of each query token's Penn tag (default 1)          cpp/match/instantiate.cpp:10-38
+ *       t_pos[T]      = universal POS id of each query token
+ *       pos_mismatch_penalty, similarity_threshold
+ */
+typedef struct {
+	int32_t max_matches;
+	float min_score;
+	float submatch_weight;
+	int32_t tag_weighted;
+	const float *t_weights;
+	const int8_t *t_pos;
+	float pos_mismatch_penalty;
+	float similarity_threshold;
+} vx_query_params;
+
+/* One returned match == Match{slice_id, document, Score} (cpp/match/match.h:275-425). */
+typedef struct {
+	float score;       /* Score::value() = (raw / max) * boost   cpp/match/match.h:302-307 */
+	float score_max;   /* Score::max()   = reference_score       cpp/metric/alignment.h:84-106 */
+	int32_t doc;       /* Document::id()                          cpp/document.h:229 */
+	int32_t slice;     /* Match::slice_id()                       cpp/match/match.h:390 */
+} vx_hit;
+
+typedef struct vx_corpus vx_corpus;   /* packed device corpus: replaces core.Document[] + Spans (cpp/document.h) */
+typedef struct vx_embedding vx_embedding; /* replaces StaticEmbedding / Vectors (cpp/embedding/static.h) */
+typedef struct vx_sim vx_sim;         /* replaces SimilarityMatrix (cpp/metric/metric.h:9-52) */
+
+/* ---- library ---- */
+
+/* Select the CUDA device for this process (one process per GPU). Fails loudly without sm_100. */
+int vx_init(int device);
+const char *vx_last_error(void);
+const char *vx_build_info(void);      /* replaces backend_build_time (cpp/module.cpp:20-22) */
+int vx_device_sm_count(void);
+
+/* ---- corpus: replaces core.Document construction + Spans::iterate ---- */
+
+/*
+ * Pack documents once into device-resident arrays for one partition
+ * (level fixed by the caller's choice of span table; window_size / window_step as in
+ * Query::initialize 'partition', cpp/query.cpp:95-113; enumeration follows Spans::iterate,
+ * cpp/document.h:147-169, including the running `token_at`).
+ *   token_id[n_tok]         Token::id of all documents, concatenated       cpp/common.h:34-42
+ *   token_pos[n_tok]        Token::pos or NULL (needed for tag-weighted)
+ *   doc_tok_off[n_doc+1]    token offset of each document in token_id
+ *   span_start/end[n_span]  VariableSpans{start,end} per document, relative to the document's
+ *                           first token, concatenated                      cpp/document.h:58-104
+ *   doc_span_off[n_doc+1]   span offset of each document
+ * Document ids are 0..n_doc-1 (corpus order, vectorian/corpus/corpus.py:370-381).
+ */
+int vx_corpus_create(
+	const int32_t *token_id, const int8_t *token_pos, int64_t n_tok,
+	const int64_t *doc_tok_off, int32_t n_doc,
+	const int32_t *span_start, const int32_t *span_end, const int64_t *doc_span_off,
+	int32_t window_size, int32_t window_step,
+	vx_corpus **out);
+
+/* Same, but token_id_dev / token_pos_dev are DEVICE pointers (corpus generated or already resident on the GPU). */
+int vx_corpus_create_dev(
+	const int32_t *token_id_dev, const int8_t *token_pos_dev, int64_t n_tok,
+	const int64_t *doc_tok_off, int32_t n_doc,
+	const int32_t *span_start, const int32_t *span_end, const int64_t *doc_span_off,
+	int32_t window_size, int32_t window_step,
+	vx_corpus **out);
+
+int vx_corpus_destroy(vx_corpus *c);
+int64_t vx_corpus_n_windows(const vx_corpus *c);   /* windows with len_s >= 1 */
+int64_t vx_corpus_n_tokens(const vx_corpus *c);
+int64_t vx_corpus_n_cells(const vx_corpus *c);     /* sum of len_s over all windows (x T = DP cells) */
+int32_t vx_corpus_max_len(const vx_corpus *c);     /* longest window; Spans::max_len's role */
+
+/*
+ * core.Booster(float32[n_spans]) per document (cpp/document.h:175-187), concatenated in document
+ * order and indexed by slice_id: boost[doc_span_off[d] + slice_id].  NULL clears the booster.
+ */
+int vx_corpus_set_boost(vx_corpus *c, const float *boost, int64_t n);
+
+/*
+ * Contextual per-token vectors X[n_tok x d] (row-major fp32), aligned with token_id.
+ * Replaces Document contextual embeddings + per-document GEMM (cpp/metric/contextual.cpp:26-63).
+ */
+int vx_corpus_set_contextual(vx_corpus *c, const float *x, int64_t n_tok, int32_t d);
+
+/* ---- embedding + similarity matrix: replaces CosineSim.compute + build_static_similarity_matrix ---- */
+
+/* E[V x d] row-major fp32; rows are L2-normalised on the device (Vectors.normalized, embedding/vectors.py:71-86). */
+int vx_embedding_create(const float *e, int64_t v, int32_t d, vx_embedding **out);
+int vx_embedding_destroy(vx_embedding *e);
+
+/*
+ * S[V x T] = clip01(Ehat . Qhat^T); S[q_id[j], j] = 1 where 0 <= q_id[j] < V
+ * (cpp/metric/static.cpp:9-78, vectorian/sim/vector.py:66-78, cpp/metric/metric.h:28-30).
+ * q_vec[T x d] are the UNnormalised query-token vectors.
+ */
+int vx_sim_static(const vx_embedding *e, const int32_t *q_id, const float *q_vec, int32_t t, vx_sim **out);
+
+/* Upload a precomputed S[V x T] (so any Python VectorSim can still supply it; no fix-up, no clip). */
+int vx_sim_upload(const float *s, int64_t v, int32_t t, vx_sim **out);
+
+/* Contextual: only the normalised query vectors are kept; S_doc tiles are formed inside the DP kernel. */
+int vx_sim_contextual(const float *q_vec, int32_t t, int32_t d, vx_sim **out);
+
+int vx_sim_download(const vx_sim *s, float *out, int64_t v, int32_t t); /* debug hook "static_similarity_matrix" */
+int vx_sim_destroy(vx_sim *s);
+
+/* ---- search: replaces Document.find / Query::match / ResultSet::extend / best_n ---- */
+
+/*
+ * Align the query against every window of the corpus, keep the best max_matches with
+ * score > min_score, order them (score desc, doc desc, slice desc), and trace back the winners.
+ *   hits[max_matches], target[max_matches x T] (InjectiveFlow target, -1 = unmatched),
+ *   dist[max_matches x T] (ScoreComputer: 1 - unmodified sim, or 1)   cpp/metric/alignment.h:307-347
+ * *n_hits receives the number of valid rows.
+ */
+int vx_search(
+	vx_corpus *c, const vx_sim *s,
+	const vx_align_params *ap, const vx_query_params *qp,
+	vx_hit *hits, int16_t *target, float *dist, int32_t *n_hits);
+
+/* Score every window (debug hook "alignment" / tests): score[n_windows] in window order, 0-filled where len<1. */
+int vx_score_all(
+	vx_corpus *c, const vx_sim *s,
+	const vx_align_params *ap, const vx_query_params *qp,
+	float *score_out, int64_t n);
+
+/* Query::abort (cpp/query.h:183-189): the next kernel launch of any running search is skipped. */
+int vx_abort(vx_corpus *c);
+
+/* Device time of the phases of the last vx_search on this corpus, in ms: [0]=DP, [1]=top-k, [2]=traceback. */
+int vx_last_timing(const vx_corpus *c, float *ms3);
+/* Number of kernels the last vx_search / vx_score_all launched. */
+int vx_last_launches(const vx_corpus *c);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* VECTORIAN_B200_H */
