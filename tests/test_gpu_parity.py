@@ -1,0 +1,236 @@
+"""Parity of the CUDA path (through the C ABI) against the oracle on the same seeded inputs.
+
+Bar (BASELINE.json north_star): token/index work bit-exact; with the SAME similarity matrix the
+DP scores are bit-exact too (fp32 add/compare only); the similarity GEMM agrees within 1e-5.
+"""
+
+import numpy as np
+import pytest
+
+from vectorian_b200 import _cabi, gaps
+from tests import helpers
+from tests.helpers import GAPS, LOCALITIES, align_params
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def engine():
+	from vectorian_b200 import engine as e
+	_cabi.lib()
+	return e
+
+
+def make_both(engine, oracle, corpus, window_size=1, window_step=1, with_pos=False, boost=None):
+	pos = corpus.get("token_pos") if with_pos else None
+	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"],
+		corpus["doc_span_off"], window_size, window_step, token_pos=pos)
+	oc = oracle.OracleCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"],
+		corpus["doc_span_off"], window_size, window_step, token_pos=pos, boost=boost)
+	if boost is not None:
+		dc.set_boost(boost)
+	return dc, oc
+
+
+def run_case(engine, oracle, dc, oc, s, locality, gap, t, k=50, min_score=0.0, contextual=False, sim=None, **qkw):
+	ap, keep = align_params(locality, gap, dc.max_len, t)
+	qp, keep2 = _cabi.make_query_params(max_matches=k, min_score=min_score, **qkw)
+	if sim is None:
+		sim = engine.DeviceSim.upload(s)
+	g_all = dc.score_all(sim, ap, qp)
+	o_all = oc.score_all(s, ap, qp, n_threads=4, contextual=contextual)
+	np.testing.assert_array_equal(g_all, o_all)
+	gpu = dc.search(sim, ap, qp)
+	ref = oc.search(s, ap, qp, n_threads=4, contextual=contextual)
+	wd, wsl, _, _ = oc.windows()
+	helpers.assert_hits_match(gpu, ref, o_all, wd, wsl)
+	return gpu
+
+
+def test_kat_through_cabi(engine, oracle):
+	"""The pyalign known answers (tests/test_oracle_kat.py) through vx_search: a one-sentence corpus
+	whose token ids 0..L-1 index the rows of an uploaded similarity matrix."""
+	from tests.test_oracle_kat import equality
+	cases = [
+		(equality("AATCG", "AACG", 1, -1), _cabi.VX_GLOBAL, gaps.LinearGapCost(2), 2.0, [[0, 0], [1, 1], [3, 2], [4, 3]]),
+		(equality("AATCG", "AACG", 1, -1), _cabi.VX_LOCAL, gaps.LinearGapCost(2), 2.0, [[3, 2], [4, 3]]),
+		(equality("CG", "CCGA", 1, -1), _cabi.VX_GLOBAL, gaps.LogarithmicGapCost(3, 1), -3.6931472, [[0, 0], [1, 3]]),
+		(equality("AGAT", "CTCT", 10, -30), _cabi.VX_GLOBAL, gaps.AffineGapCost(25, 1), -44.0, [[3, 3]]),
+		(equality("GGTGTGA"[:6], "TCGCGT", 0, -1), _cabi.VX_SEMIGLOBAL, gaps.AffineGapCost(5, 1), None, None),
+	]
+	for sim, locality, gap, score, edges in cases:
+		len_s, len_t = sim.shape
+		dc = engine.DeviceCorpus(np.arange(len_s, dtype=np.int32), [0, len_s], [0], [len_s], [0, 1])
+		ap, keep = align_params(locality, gap, len_s, len_t)
+		qp, _ = _cabi.make_query_params(max_matches=1, min_score=-1e30)
+		hits, target, dist = dc.search(engine.DeviceSim.upload(sim), ap, qp)
+		o_score, o_target = oracle.align(sim, ap)
+		assert len(hits) == 1
+		assert np.float32(hits["score"][0]) == np.float32(o_score) / np.float32(len_t)
+		np.testing.assert_array_equal(target[0], o_target)
+		if score is not None:
+			assert np.float32(hits["score"][0]) == np.float32(score) / np.float32(len_t)
+			assert oracle.edges_from_target(target[0]) == edges
+
+
+@pytest.mark.parametrize("gap_name", list(GAPS.keys()))
+@pytest.mark.parametrize("locality", LOCALITIES)
+def test_all_solvers_bit_exact(engine, oracle, gap_name, locality):
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=2500, t=8, seed=11)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	dc, oc = make_both(engine, oracle, corpus)
+	run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], 8)
+
+
+@pytest.mark.parametrize("t", [1, 2, 3, 5, 7, 12, 13, 16])
+def test_query_lengths(engine, oracle, t):
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=1500, t=t, seed=23 + t)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	dc, oc = make_both(engine, oracle, corpus)
+	for locality in LOCALITIES:
+		for gap_name in ("linear0.2", "affine", "smooth5"):
+			run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], t)
+
+
+def test_long_query_uses_exact_path(engine, oracle):
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=400, t=21, seed=5)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	dc, oc = make_both(engine, oracle, corpus)
+	for locality in LOCALITIES:
+		run_case(engine, oracle, dc, oc, s, locality, GAPS["smooth5"], 21, k=10)
+		run_case(engine, oracle, dc, oc, s, locality, GAPS["affine"], 21, k=10)
+
+
+def test_similarity_gemm(engine, oracle):
+	"""vx_sim_static vs the oracle: 1e-5 (summation order differs, as between BLAS builds)."""
+	for t, dim in ((5, 300), (8, 300), (12, 128), (16, 50)):
+		corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=10, vocab=5000, dim=dim, t=t, seed=t)
+		emb[17, :] = 0  # a vanishing vector: 0/0 -> nan -> 0
+		q_vec = emb[q_id].copy()
+		q_id[-1] = -1  # a query token outside the vocabulary gets no identity fix-up
+		de = engine.DeviceEmbedding(emb)
+		sim = engine.DeviceSim.static(de, q_id, q_vec)
+		got = sim.download()
+		want = oracle.sim_static(emb, q_id, q_vec)
+		np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6)
+		assert np.all(got >= 0) and np.all(got <= 1)
+		for j, i in enumerate(q_id):
+			if i >= 0:
+				assert got[i, j] == 1.0
+		assert np.all(got[17] == 0)
+
+
+def test_end_to_end_with_device_gemm(engine, oracle):
+	"""Whole path on the device (GEMM -> DP -> top-k -> traceback) vs. the oracle, 1e-5 relative."""
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=3000, vocab=3000, dim=300, t=12, seed=3)
+	dc, oc = make_both(engine, oracle, corpus)
+	sim = engine.DeviceSim.static(engine.DeviceEmbedding(emb), q_id, q_vec)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	ap, keep = align_params(_cabi.VX_LOCAL, gaps.smooth_gap_cost(5), dc.max_len, 12)
+	qp, _ = _cabi.make_query_params(max_matches=100, min_score=0.0)
+	g_all = dc.score_all(sim, ap, qp)
+	o_all = oc.score_all(s, ap, qp, n_threads=4)
+	np.testing.assert_allclose(g_all, o_all, rtol=1e-5, atol=1e-7)
+	gpu = dc.search(sim, ap, qp)
+	ref = oc.search(s, ap, qp, n_threads=4)
+	wd, wsl, _, _ = oc.windows()
+	helpers.assert_hits_match(gpu, ref, o_all, wd, wsl, rel_tol=1e-5)
+
+
+def test_windows_and_boost(engine, oracle):
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=1200, t=6, seed=41)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	rng = np.random.default_rng(0)
+	boost = rng.uniform(0.5, 1.5, size=len(corpus["span_start"])).astype(np.float32)
+	for ws, st in ((1, 1), (3, 1), (3, 2), (2, 5), (8, 8)):
+		dc, oc = make_both(engine, oracle, corpus, ws, st, boost=boost)
+		wd, wsl, wtok, wlen = oc.windows()
+		assert dc.n_windows == len(wd)
+		assert dc.n_cells == int(wlen.sum())
+		assert dc.max_len == int(wlen.max())
+		run_case(engine, oracle, dc, oc, s, _cabi.VX_LOCAL, GAPS["linear0.2"], 6)
+		run_case(engine, oracle, dc, oc, s, _cabi.VX_GLOBAL, GAPS["smooth5"], 6)
+
+
+def test_tag_weighted_and_submatch(engine, oracle):
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=800, t=7, seed=77, with_pos=True)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	dc, oc = make_both(engine, oracle, corpus, with_pos=True)
+	rng = np.random.default_rng(1)
+	t_weights = rng.uniform(0.2, 2.0, size=7).astype(np.float32)
+	t_pos = rng.integers(0, 17, size=7).astype(np.int8)
+	for locality in LOCALITIES:
+		for gap_name in ("linear0.2", "affine", "smooth5"):
+			run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], 7,
+				t_weights=t_weights, t_pos=t_pos, pos_mismatch_penalty=0.4, similarity_threshold=0.15)
+			run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], 7, submatch_weight=0.5)
+
+
+def test_edge_cases(engine, oracle):
+	# ragged: empty document, empty spans, single-token sentences, a sentence longer than 64 tokens
+	token_id = np.arange(200, dtype=np.int32) % 50
+	doc_tok_off = [0, 0, 120, 200]
+	span_start = [0, 1, 1, 2, 100, 0, 80]
+	span_end = [1, 1, 2, 100, 120, 80, 80]
+	doc_span_off = [0, 0, 5, 7]
+	corpus = dict(token_id=token_id, doc_tok_off=doc_tok_off, span_start=span_start, span_end=span_end, doc_span_off=doc_span_off)
+	rng = np.random.default_rng(5)
+	s = rng.uniform(0, 1, size=(50, 5)).astype(np.float32)
+	dc, oc = make_both(engine, oracle, corpus)
+	assert dc.n_windows == 5
+	for locality in LOCALITIES:
+		for gap_name in ("none", "linear0.2", "affine", "smooth5"):
+			run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], 5, k=3)
+			run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], 5, k=100, min_score=0.3)
+	# empty query -> no matches (matcher_impl.h:80-83); empty corpus -> no matches
+	ap, _ = align_params(_cabi.VX_LOCAL, None, dc.max_len, 0)
+	qp, _ = _cabi.make_query_params(max_matches=10, min_score=0.0)
+	hits, _, _ = dc.search(engine.DeviceSim.upload(np.zeros((50, 0), dtype=np.float32)), ap, qp)
+	assert len(hits) == 0
+	empty = engine.DeviceCorpus(np.zeros(0, np.int32), [0], [], [], [0])
+	assert empty.n_windows == 0
+	hits, _, _ = empty.search(engine.DeviceSim.upload(s), ap, qp)
+	assert len(hits) == 0
+
+
+def test_error_behaviour(engine):
+	"""Same failures as the reference, as VxError (the reference raises RuntimeError/ValueError)."""
+	tok = np.zeros(10, np.int32)
+	with pytest.raises(_cabi.VxError, match="window size"):
+		engine.DeviceCorpus(tok, [0, 10], [0], [10], [0, 1], window_size=0)
+	with pytest.raises(_cabi.VxError, match="window step"):
+		engine.DeviceCorpus(tok, [0, 10], [0], [10], [0, 1], window_step=0)
+	dc = engine.DeviceCorpus(tok, [0, 10], [0], [10], [0, 1])
+	sim = engine.DeviceSim.upload(np.ones((1, 3), np.float32))
+	ap, keep = _cabi.make_align_params(_cabi.VX_LOCAL, _cabi.VX_GAP_GENERAL, w_s=np.zeros(4), w_t=np.zeros(4))
+	qp, _ = _cabi.make_query_params(max_matches=5, min_score=0.0)
+	with pytest.raises(_cabi.VxError, match="expected gap cost tensor length of 11, got 4"):
+		dc.search(sim, ap, qp)
+	ap2, _ = _cabi.make_align_params(7, _cabi.VX_GAP_LINEAR)
+	with pytest.raises(_cabi.VxError, match="invalid locality"):
+		dc.search(sim, ap2, qp)
+	qp0, _ = _cabi.make_query_params(max_matches=0, min_score=0.0)
+	ap3, _ = _cabi.make_align_params(_cabi.VX_LOCAL, _cabi.VX_GAP_LINEAR)
+	with pytest.raises(_cabi.VxError, match="max_matches"):
+		dc.search(sim, ap3, qp0)
+	with pytest.raises(_cabi.VxError, match="fewer rows"):
+		engine.DeviceCorpus(np.full(10, 5, np.int32), [0, 10], [0], [10], [0, 1]).search(sim, ap3, qp)
+
+
+def test_many_ties_topk(engine, oracle):
+	"""All windows identical -> every score ties; the order must be (doc desc, slice desc)."""
+	n = 5000
+	token_id = np.zeros(n * 4, np.int32)
+	starts = (np.arange(n) % 100) * 4
+	doc_span_off = np.arange(0, n + 1, 100)
+	doc_tok_off = doc_span_off * 4
+	corpus = dict(token_id=token_id, doc_tok_off=doc_tok_off, span_start=starts, span_end=starts + 4, doc_span_off=doc_span_off)
+	s = np.full((1, 3), 0.5, np.float32)
+	dc, oc = make_both(engine, oracle, corpus)
+	ap, _ = align_params(_cabi.VX_LOCAL, None, 4, 3)
+	qp, _ = _cabi.make_query_params(max_matches=130, min_score=0.0)
+	hits, target, dist = dc.search(engine.DeviceSim.upload(s), ap, qp)
+	assert len(hits) == 130
+	assert np.all(hits["score"] == hits["score"][0])
+	want = [(49 - i // 100, 99 - i % 100) for i in range(130)]
+	assert [(int(h["doc"]), int(h["slice"])) for h in hits] == want

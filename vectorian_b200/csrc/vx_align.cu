@@ -1,0 +1,451 @@
+// Score-only alignment kernels (the hot loop).
+//
+// Replaces MatcherImpl::run_matches -> InjectiveAlignment::make_match -> {Linear,Affine,General}
+// GapCostSolver::solve for every window of the corpus
+// (vectorian/core/cpp/match/matcher_impl.h:71-109, cpp/metric/alignment.h:247-294,
+//  pyalign/algorithm/solver.h:2817-2847, 2962-3028, 3130-3175).
+//
+// The reference fills a value + traceback matrix per window.  The maximum of a set of fp32
+// candidates does not depend on the order they are compared in, so the SCORE needs no traceback and
+// no tie-breaking: these kernels keep one DP row in registers and emit only the normalised score.
+// Tracebacks are recomputed for the k winners by vx_trace.cu, which does reproduce the reference's
+// candidate order.  fp32 add / compare only, compiled with -fmad=false: bit-identical to the oracle.
+//
+// Mapping: one warp per tile of 32 equal-length windows, one window per lane; the warp walks the
+// token positions in lock step (no divergence) and every token-id load is one coalesced 128 B line.
+#include "vx_internal.cuh"
+
+#include <math_constants.h>
+
+template<int TP>
+__device__ __forceinline__ void load_row(const float *__restrict__ s, int32_t id, float (&row)[TP]) {
+	const float4 *p = reinterpret_cast<const float4*>(s + (size_t)id * TP);
+	#pragma unroll
+	for (int i = 0; i < TP / 4; i++) {
+		const float4 x = __ldg(p + i);
+		row[4 * i + 0] = x.x;
+		row[4 * i + 1] = x.y;
+		row[4 * i + 2] = x.z;
+		row[4 * i + 3] = x.w;
+	}
+}
+
+__device__ __forceinline__ float finish_score(float raw, float total, float boost) {
+	// Score::Score (cpp/match/match.h:302-307) with reference_score == total for submatch_weight == 0.
+	return (raw / total) * boost;
+}
+
+struct ScoreArgs {
+	const VxTile *tiles;
+	int64_t n_tiles;
+	const int32_t *tok;
+	const float *s;        // [V x TP]
+	const float *boost;    // by slot or nullptr
+	float *score;          // by slot
+	int32_t t;
+	float total;
+};
+
+// ---------------------------------------------------------------------------
+// linear gap cost: Needleman-Wunsch / Smith-Waterman / semiglobal
+// ---------------------------------------------------------------------------
+
+template<int TP, int LOC>
+__global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs, float gt) {
+	const int64_t tile = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (tile >= a.n_tiles) {
+		return;
+	}
+	const int lane = threadIdx.x & 31;
+	const VxTile tl = a.tiles[tile];
+	const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
+	const int len = tl.len;
+	const int t = a.t;
+
+	float h[TP];   // h[v] = V[u-1, v]
+	#pragma unroll
+	for (int v = 0; v < TP; v++) {
+		h[v] = LOC == VX_GLOBAL ? -((float)(v + 1) * gt) : 0.0f;   // solver.h:2804-2806
+	}
+	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+	float last_col = 0.0f;
+
+	float row[TP];
+	int32_t id = tok[0];
+	load_row<TP>(a.s, id, row);
+
+	for (int u = 0; u < len; u++) {
+		float cur[TP];
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			cur[v] = row[v];
+		}
+		if (u + 1 < len) {
+			id = tok[(size_t)(u + 1) * 32];
+			load_row<TP>(a.s, id, row);
+		}
+
+		float diag = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
+		float left = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;  // V[u, -1]
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			const float up = h[v];
+			float x = fmaxf(fmaxf(diag + cur[v], up - gs), left - gt);
+			if (LOC == VX_LOCAL) {
+				x = fmaxf(x, 0.0f);
+				if (v < t) {
+					best = fmaxf(best, x);
+				}
+			}
+			diag = up;
+			h[v] = x;
+			left = x;
+			if (v == t - 1) {
+				last_col = x;
+			}
+		}
+		if (LOC == VX_SEMIGLOBAL) {
+			best = fmaxf(best, last_col);
+		}
+	}
+
+	float raw;
+	if (LOC == VX_LOCAL) {
+		raw = best;
+	} else if (LOC == VX_GLOBAL) {
+		raw = last_col;
+	} else {
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			if (v < t) {
+				best = fmaxf(best, h[v]);
+			}
+		}
+		raw = best;
+	}
+
+	const int64_t slot = tile * 32 + lane;
+	const float boost = a.boost ? a.boost[slot] : 1.0f;
+	a.score[slot] = lane < tl.n_valid ? finish_score(raw, a.total, boost) : -CUDART_INF_F;
+}
+
+// ---------------------------------------------------------------------------
+// affine gap cost: Gotoh
+// ---------------------------------------------------------------------------
+
+struct AffineArgs {
+	float open_s, ext_s, open_t, ext_t;
+};
+
+__device__ __forceinline__ float affine_w(float ext, float open0, int k) {
+	return k == 0 ? 0.0f : ext * (float)k + open0;   // AffineCost, solver.h:2850-2873
+}
+
+template<int TP, int LOC>
+__global__ void __launch_bounds__(128) score_affine_kernel(ScoreArgs a, AffineArgs g) {
+	const int64_t tile = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (tile >= a.n_tiles) {
+		return;
+	}
+	const int lane = threadIdx.x & 31;
+	const VxTile tl = a.tiles[tile];
+	const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
+	const int len = tl.len;
+	const int t = a.t;
+
+	const float w1s = g.ext_s + g.open_s;
+	const float w1t = g.ext_t + g.open_t;
+
+	float d[TP], p[TP];   // D[u-1, v], P[u-1, v]
+	#pragma unroll
+	for (int v = 0; v < TP; v++) {
+		d[v] = LOC == VX_GLOBAL ? -affine_w(g.ext_t, g.open_t, v + 1) : 0.0f;
+		p[v] = -CUDART_INF_F;
+	}
+	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+	float last_col = 0.0f;
+
+	float row[TP];
+	int32_t id = tok[0];
+	load_row<TP>(a.s, id, row);
+
+	for (int u = 0; u < len; u++) {
+		float cur[TP];
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			cur[v] = row[v];
+		}
+		if (u + 1 < len) {
+			id = tok[(size_t)(u + 1) * 32];
+			load_row<TP>(a.s, id, row);
+		}
+
+		float diag = LOC == VX_GLOBAL ? -affine_w(g.ext_s, g.open_s, u) : 0.0f;       // D[u-1, -1]
+		float left = LOC == VX_GLOBAL ? -affine_w(g.ext_s, g.open_s, u + 1) : 0.0f;   // D[u, -1]
+		float q = -CUDART_INF_F;                                                       // Q[u, -1]
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			const float up = d[v];
+			const float pv = fmaxf(up - w1s, p[v] - g.ext_s);      // Gotoh (4)
+			q = fmaxf(left - w1t, q - g.ext_t);                    // Gotoh (5)
+			float x = fmaxf(fmaxf(diag + cur[v], pv), q);          // Gotoh (1)
+			if (LOC == VX_LOCAL) {
+				x = fmaxf(x, 0.0f);
+				if (v < t) {
+					best = fmaxf(best, x);
+				}
+			}
+			p[v] = pv;
+			diag = up;
+			d[v] = x;
+			left = x;
+			if (v == t - 1) {
+				last_col = x;
+			}
+		}
+		if (LOC == VX_SEMIGLOBAL) {
+			best = fmaxf(best, last_col);
+		}
+	}
+
+	float raw;
+	if (LOC == VX_LOCAL) {
+		raw = best;
+	} else if (LOC == VX_GLOBAL) {
+		raw = last_col;
+	} else {
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			if (v < t) {
+				best = fmaxf(best, d[v]);
+			}
+		}
+		raw = best;
+	}
+
+	const int64_t slot = tile * 32 + lane;
+	const float boost = a.boost ? a.boost[slot] : 1.0f;
+	a.score[slot] = lane < tl.n_valid ? finish_score(raw, a.total, boost) : -CUDART_INF_F;
+}
+
+// ---------------------------------------------------------------------------
+// general gap cost: Waterman-Smith-Beyer, any window length (column history in global scratch)
+// ---------------------------------------------------------------------------
+//
+// V[u,v] = max( [0], V[u-1,v-1] + sim, max_{k<u} V[k,v] - w_s[u-k], max_{k<v} V[u,k] - w_t[v-k] )
+// (solver.h:3145-3173).  Persistent warps stride over the tiles; each warp owns a scratch region
+// hist[u][v][lane] holding the finished rows of its current tile.
+
+template<int TP, int LOC>
+__global__ void __launch_bounds__(128) score_general_scratch_kernel(
+	ScoreArgs a, const float *__restrict__ w_s, const float *__restrict__ w_t,
+	float *__restrict__ scratch, int32_t max_len) {
+
+	const int lane = threadIdx.x & 31;
+	const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int64_t n_warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+	float *hist = scratch + (size_t)warp * max_len * TP * 32 + lane;
+	const int t = a.t;
+
+	float wt[TP + 1];
+	#pragma unroll
+	for (int k = 0; k <= TP; k++) {
+		wt[k] = k <= t ? __ldg(w_t + k) : 0.0f;
+	}
+
+	for (int64_t tile = warp; tile < a.n_tiles; tile += n_warps) {
+		const VxTile tl = a.tiles[tile];
+		const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
+		const int len = tl.len;
+
+		float top[TP];   // V[-1, v]
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			top[v] = LOC == VX_GLOBAL ? -wt[v + 1] : 0.0f;
+		}
+		float prev[TP];  // V[u-1, v]
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			prev[v] = top[v];
+		}
+		float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+		float last_col = 0.0f;
+
+		for (int u = 0; u < len; u++) {
+			float sim[TP];
+			load_row<TP>(a.s, tok[(size_t)u * 32], sim);
+
+			// vertical candidates, k = -1 .. u-1
+			float vert[TP];
+			const float w_top = __ldg(w_s + u + 1);
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				vert[v] = top[v] - w_top;
+			}
+			for (int k = 0; k < u; k++) {
+				const float wk = __ldg(w_s + (u - k));
+				const float *hk = hist + (size_t)k * TP * 32;
+				#pragma unroll
+				for (int v = 0; v < TP; v++) {
+					vert[v] = fmaxf(vert[v], hk[v * 32] - wk);
+				}
+			}
+
+			const float left_border = LOC == VX_GLOBAL ? -__ldg(w_s + u + 1) : 0.0f;   // V[u, -1]
+			float diag = LOC == VX_GLOBAL ? (u == 0 ? -wt[0] : -__ldg(w_s + u)) : 0.0f;  // V[u-1, -1]
+			float cur[TP];
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				float x = fmaxf(diag + sim[v], vert[v]);
+				x = fmaxf(x, left_border - wt[v + 1]);
+				#pragma unroll
+				for (int k = 0; k < v; k++) {
+					x = fmaxf(x, cur[k] - wt[v - k]);
+				}
+				if (LOC == VX_LOCAL) {
+					x = fmaxf(x, 0.0f);
+					if (v < t) {
+						best = fmaxf(best, x);
+					}
+				}
+				diag = prev[v];
+				cur[v] = x;
+				if (v == t - 1) {
+					last_col = x;
+				}
+			}
+			float *hu = hist + (size_t)u * TP * 32;
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				prev[v] = cur[v];
+				hu[v * 32] = cur[v];
+			}
+			if (LOC == VX_SEMIGLOBAL) {
+				best = fmaxf(best, last_col);
+			}
+		}
+
+		float raw;
+		if (LOC == VX_LOCAL) {
+			raw = best;
+		} else if (LOC == VX_GLOBAL) {
+			raw = last_col;
+		} else {
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				if (v < t) {
+					best = fmaxf(best, prev[v]);
+				}
+			}
+			raw = best;
+		}
+		const int64_t slot = tile * 32 + lane;
+		const float boost = a.boost ? a.boost[slot] : 1.0f;
+		a.score[slot] = lane < tl.n_valid ? finish_score(raw, a.total, boost) : -CUDART_INF_F;
+		__syncwarp();
+	}
+}
+
+// ---------------------------------------------------------------------------
+// dispatch
+// ---------------------------------------------------------------------------
+
+static int g_sm_count = 0;
+
+static int sm_count() {
+	if (g_sm_count == 0) {
+		int dev = 0;
+		cudaGetDevice(&dev);
+		cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+	}
+	return g_sm_count;
+}
+
+template<int TP, int LOC>
+static int launch_score_tl(vx_corpus *c, const ScoreArgs &a, const VxAlignDev &ap) {
+	const int warps = 4;
+	const unsigned grid = (unsigned)((a.n_tiles + warps - 1) / warps);
+	switch (ap.gap_kind) {
+		case VX_GAP_LINEAR:
+			score_linear_kernel<TP, LOC><<<grid, warps * 32, 0, c->stream>>>(a, ap.lin_s, ap.lin_t);
+			return 1;
+		case VX_GAP_AFFINE: {
+			AffineArgs g{ap.aff_open_s, ap.aff_ext_s, ap.aff_open_t, ap.aff_ext_t};
+			score_affine_kernel<TP, LOC><<<grid, warps * 32, 0, c->stream>>>(a, g);
+			return 1;
+		}
+		default: {
+			// persistent: 16 warps per SM
+			const int blocks = sm_count() * 4;
+			const size_t need = sizeof(float) * (size_t)blocks * warps * c->max_len * TP * 32;
+			if (c->scratch_bytes < need) {
+				if (c->d_scratch) {
+					cudaFree(c->d_scratch);
+					c->d_scratch = nullptr;
+					c->scratch_bytes = 0;
+				}
+				if (cudaMalloc(&c->d_scratch, need) != cudaSuccess) {
+					vx_set_error("cudaMalloc of the general-gap scratch failed");
+					return -1;
+				}
+				c->scratch_bytes = need;
+			}
+			score_general_scratch_kernel<TP, LOC><<<blocks, warps * 32, 0, c->stream>>>(
+				a, ap.w_s, ap.w_t, (float*)c->d_scratch, c->max_len);
+			return 1;
+		}
+	}
+}
+
+template<int TP>
+static int launch_score_t(vx_corpus *c, const ScoreArgs &a, const VxAlignDev &ap) {
+	switch (ap.locality) {
+		case VX_LOCAL:
+			return launch_score_tl<TP, VX_LOCAL>(c, a, ap);
+		case VX_GLOBAL:
+			return launch_score_tl<TP, VX_GLOBAL>(c, a, ap);
+		default:
+			return launch_score_tl<TP, VX_SEMIGLOBAL>(c, a, ap);
+	}
+}
+
+// Fast path preconditions: static similarity, T <= 16, plain (isolated) scoring with
+// submatch_weight == 0, so that reference_score == T exactly.  Everything else is scored by the
+// exact kernel in vx_trace.cu (the caller decides).
+int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp) {
+	if (c->n_tiles == 0) {
+		return 0;
+	}
+	ScoreArgs a;
+	a.tiles = c->d_tiles;
+	a.n_tiles = c->n_tiles;
+	a.tok = c->d_tok;
+	a.s = s->d_s;
+	a.boost = c->d_boost;
+	a.score = c->d_score;
+	a.t = qp.t;
+	a.total = qp.total;
+	int n;
+	switch (s->tp) {
+		case 4:
+			n = launch_score_t<4>(c, a, ap);
+			break;
+		case 8:
+			n = launch_score_t<8>(c, a, ap);
+			break;
+		case 12:
+			n = launch_score_t<12>(c, a, ap);
+			break;
+		case 16:
+			n = launch_score_t<16>(c, a, ap);
+			break;
+		default:
+			vx_set_error("vx_launch_score: query longer than the fast path supports");
+			return -1;
+	}
+	if (n >= 0 && cudaGetLastError() != cudaSuccess) {
+		vx_set_error("score kernel launch failed");
+		return -1;
+	}
+	return n;
+}

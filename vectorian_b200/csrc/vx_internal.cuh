@@ -1,0 +1,166 @@
+// Internal declarations shared by the .cu files of libvectorian_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/vectorian_b200.h"
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+
+void vx_set_error(const std::string &msg);
+
+#define VX_FAIL(code, msg) do { vx_set_error(msg); return (code); } while (0)
+
+#define VX_CUDA(expr) do { \
+		cudaError_t _e = (expr); \
+		if (_e != cudaSuccess) { \
+			vx_set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+			return VX_ERR_CUDA; \
+		} \
+	} while (0)
+
+// ---------------------------------------------------------------------------
+// device layout
+// ---------------------------------------------------------------------------
+
+// A tile = 32 windows of identical length, one per lane of a warp.  Token u of lane l lives at
+// tok[(base32 * 32) + u * 32 + l]  ->  a warp reads one 128-byte line per token position.
+struct VxTile {
+	uint32_t base32;   // token offset of the tile / 32
+	uint16_t len;      // window length (tokens)
+	uint16_t n_valid;  // lanes [0, n_valid) hold real windows
+};
+
+constexpr int VX_TILE = 32;
+constexpr uint32_t VX_NO_WINDOW = 0xffffffffu;
+
+struct vx_corpus {
+	int device = 0;
+	int64_t n_tok_raw = 0;        // tokens handed in
+	int64_t n_win = 0;            // windows with len >= 1 (window order = document-major, slice ascending)
+	int64_t n_cells = 0;          // sum of window lengths
+	int32_t n_doc = 0;
+	int32_t max_len = 0;
+	int64_t n_tiles = 0;
+	int64_t n_slots = 0;          // n_tiles * 32
+	int64_t n_tok_tiled = 0;
+
+	// host-side window tables (only read for the k winners)
+	std::vector<int32_t> win_doc, win_slice;
+	std::vector<int64_t> win_tok;         // absolute token offset of each window (for set_contextual)
+	std::vector<int64_t> doc_span_off;    // boost index = doc_span_off[doc] + slice
+
+	// device arrays
+	int32_t *d_tok = nullptr;        // tiled token ids
+	int8_t *d_pos = nullptr;         // tiled POS ids (optional)
+	VxTile *d_tiles = nullptr;       // sorted by descending length
+	uint32_t *d_orig = nullptr;      // slot -> window index (VX_NO_WINDOW for padding lanes)
+	uint32_t *d_slot_of = nullptr;   // window index -> slot
+	float *d_boost = nullptr;        // by slot (optional)
+	float *d_ctx = nullptr;          // contextual vectors, tiled like d_tok: [(base + u*32 + l) * d] (optional)
+	int32_t ctx_dim = 0;
+	float *d_score = nullptr;        // by slot, scratch of the last search
+	void *d_work = nullptr;          // top-k / traceback workspace
+	size_t work_bytes = 0;
+	void *d_scratch = nullptr;       // DP scratch of the exact kernel
+	size_t scratch_bytes = 0;
+	void *h_res = nullptr;           // pinned host mirror of the result block
+	size_t h_res_bytes = 0;
+	int32_t max_token_id = -1;       // -1 = unknown (corpus created from device memory)
+
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+	float last_ms[3] = {0, 0, 0};
+	int last_launches = 0;
+	volatile int aborted = 0;
+};
+
+struct vx_embedding {
+	int64_t v = 0;
+	int32_t d = 0;
+	float *d_ehat = nullptr;         // [v x d] L2-normalised rows
+};
+
+struct vx_sim {
+	int64_t rows = 0;                // V (static) or 0 (contextual)
+	int32_t t = 0;
+	int32_t tp = 0;                  // row stride in floats = round_up(t, 4)
+	float *d_s = nullptr;            // [rows x tp], columns >= t are zero
+	int32_t contextual = 0;
+	int32_t d = 0;
+	float *d_qhat = nullptr;         // contextual: [t x d] normalised query vectors
+};
+
+// Per-query constants handed to the kernels by value.
+constexpr int VX_MAX_T_FAST = 16;    // query lengths with a register-resident fast path
+constexpr int VX_MAX_T_MASK = 32;    // matched-set bitmask width of the exact kernel
+
+struct VxAlignDev {
+	int32_t locality;
+	int32_t gap_kind;
+	float lin_s, lin_t;
+	float aff_open_s, aff_ext_s, aff_open_t, aff_ext_t;
+	const float *w_s;    // device, general gap tables
+	const float *w_t;
+	int32_t n_w_s, n_w_t;
+};
+
+struct VxQueryDev {
+	int32_t t;
+	int32_t tag_weighted;
+	float submatch_weight;
+	float min_score;
+	float pos_mismatch_penalty;
+	float similarity_threshold;
+	float total;                         // max_sum_of_similarities
+	float t_weights[VX_MAX_T_MASK];      // valid when t <= 32
+	int8_t t_pos[VX_MAX_T_MASK];
+	const float *t_weights_dev;          // device copies for t > 32
+	const int8_t *t_pos_dev;
+};
+
+// ---------------------------------------------------------------------------
+// kernels (launchers); each returns the number of kernels it launched or < 0 on error
+// ---------------------------------------------------------------------------
+
+// vx_align.cu -- score-only DP over every tile; writes c->d_score[slot].
+int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp);
+
+// vx_trace.cu -- exact DP with traceback for a list of slots (device array), one thread per item.
+struct VxTraceOut {
+	float *score;       // [n] normalised score
+	float *score_max;   // [n]
+	int16_t *target;    // [n x t]
+	float *dist;        // [n x t]
+	uint32_t *win;      // [n] window index of each item
+};
+int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp,
+	const uint32_t *d_slots, int64_t slot_base, const int32_t *d_n_items, int32_t max_items, VxTraceOut out);
+size_t vx_trace_scratch_bytes(int32_t max_len, int32_t t, int32_t max_items, int32_t gap_kind);
+
+// vx_topk.cu -- exact top-k of d_score under (score desc, window index desc).
+struct VxTopkOut {
+	uint32_t *slots;    // [k] device: winning slots, best first
+	int32_t *n;         // device: number of winners
+	float *scores;      // [k] device
+};
+size_t vx_topk_work_bytes(int32_t k);
+int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out);
+
+// vx_sim.cu
+int vx_launch_normalize(const float *d_in, float *d_out, int64_t rows, int32_t d, cudaStream_t st);
+int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float *d_qhat,
+	const int32_t *d_qid, int32_t t, int32_t tp, float *d_s, cudaStream_t st);
+
+// vx_pack.cu
+int vx_launch_pack(const int32_t *d_tok_raw, const int8_t *d_pos_raw, const int64_t *d_win_tok,
+	const VxTile *d_tiles, const uint32_t *d_orig, int64_t n_tiles,
+	int32_t *d_tok, int8_t *d_pos, cudaStream_t st);
+int vx_launch_pack_ctx(const float *d_x_raw, const int64_t *d_win_tok, const VxTile *d_tiles,
+	const uint32_t *d_orig, int64_t n_tiles, int32_t d, float *d_ctx, cudaStream_t st);
+int vx_launch_unpermute(const float *d_score, const uint32_t *d_slot_of, int64_t n_win, float *d_out, cudaStream_t st);

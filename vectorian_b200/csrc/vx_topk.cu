@@ -1,0 +1,292 @@
+// Exact top-k over the per-window scores.
+//
+// Replaces ResultSet (vectorian/core/cpp/result_set.h:17-153): the bounded heap with strict
+// `score > worst_score()` admission, ResultSet::extend across documents and best_n's partial_sort
+// (cpp/result_set.cpp:3-21).  Order: score desc, then document id desc, then slice id desc
+// (Match::compare_by_score, cpp/match/match_impl.h:8-42, made total -- SURVEY.md A9).  Because
+// window indices are document-major / slice-ascending, that order is the descending order of the
+// 64-bit key  (orderable(score) << 32 | window_index), all keys distinct.
+//
+// Method: MSD radix select on that key (11/11/10 bits over the score, then 11/11/10 over the index)
+// entirely on the device -- each level is a histogram pass restricted to the surviving prefix plus
+// a one-block scan; as soon as the survivors fit the candidate buffer they are collected and
+// sorted by one block (bitonic, shared memory).  No host round trip until the final copy.
+#include "vx_internal.cuh"
+
+constexpr int TOPK_LEVELS = 6;
+constexpr int TOPK_BINS = 2048;
+constexpr int TOPK_CAP = 8192;
+
+__constant__ int c_shift[TOPK_LEVELS] = {53, 42, 32, 21, 10, 0};
+__constant__ int c_bits[TOPK_LEVELS] = {11, 11, 10, 11, 11, 10};
+
+struct TopkState {
+	unsigned long long prefix;   // digits fixed so far (right aligned)
+	unsigned int greater;        // # keys strictly above the prefix group
+	unsigned int done;
+	int shift_done;              // keys >= (prefix << shift_done) are collected
+	unsigned int n_cand;
+	int n_out;
+	int pad;
+};
+
+struct TopkWork {
+	TopkState st;
+	unsigned int hist[TOPK_LEVELS][TOPK_BINS];
+	unsigned long long cand[TOPK_CAP];
+};
+
+__device__ __forceinline__ unsigned int score_key(float f) {
+	if (f == 0.0f) {
+		f = 0.0f;   // -0 -> +0
+	}
+	const unsigned int b = __float_as_uint(f);
+	return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+__device__ __forceinline__ float key_score(unsigned int k) {
+	return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+__global__ void topk_hist_kernel(TopkWork *w, int level, const float *__restrict__ score,
+	const uint32_t *__restrict__ orig, int64_t n_slots, float min_score) {
+
+	if (w->st.done) {
+		return;
+	}
+	__shared__ unsigned int h[TOPK_BINS];
+	for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
+		h[i] = 0;
+	}
+	__syncthreads();
+
+	const unsigned long long prefix = w->st.prefix;
+	const int shift = c_shift[level];
+	const int bits = c_bits[level];
+	const unsigned int mask = (1u << bits) - 1;
+	const int hi_shift = shift + bits;
+
+	for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_slots;
+		p += (int64_t)gridDim.x * blockDim.x) {
+
+		const float sc = score[p];
+		if (!(sc > min_score)) {
+			continue;   // strict admission (cpp/metric/alignment.h:284); also drops NaN and padding lanes
+		}
+		const unsigned int sk = score_key(sc);
+		unsigned long long key;
+		if (level < 3) {
+			key = (unsigned long long)sk << 32;   // the index digits are not needed yet
+		} else {
+			if ((unsigned long long)sk != (prefix >> (32 - hi_shift))) {
+				// score differs from the fixed 32-bit score prefix -> not in the group
+				continue;
+			}
+			key = ((unsigned long long)sk << 32) | orig[p];
+		}
+		if (level > 0 && hi_shift < 64 && (key >> hi_shift) != prefix) {
+			continue;
+		}
+		atomicAdd(&h[(unsigned int)(key >> shift) & mask], 1u);
+	}
+	__syncthreads();
+	for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
+		if (h[i]) {
+			atomicAdd(&w->hist[level][i], h[i]);
+		}
+	}
+}
+
+// One block: pick the bin holding the k-th key.
+__global__ void topk_scan_kernel(TopkWork *w, int level, int k) {
+	if (w->st.done) {
+		return;
+	}
+	__shared__ unsigned int part[32];
+	__shared__ int sel_bin;
+	__shared__ unsigned int sel_above;
+	const int nb = 1 << c_bits[level];
+	const unsigned int *h = w->hist[level];
+	const unsigned int greater = w->st.greater;
+
+	// thread i owns bins [nb-1 - 2i, nb-2 - 2i] (descending); suffix sums by a block scan
+	const int tid = threadIdx.x;   // blockDim.x == 1024
+	const int b0 = nb - 1 - 2 * tid, b1 = b0 - 1;
+	const unsigned int c0 = b0 >= 0 ? h[b0] : 0, c1 = b1 >= 0 ? h[b1] : 0;
+	unsigned int x = c0 + c1;
+	// inclusive scan across the block
+	const int lane = tid & 31, wid = tid >> 5;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const unsigned int y = __shfl_up_sync(0xffffffffu, x, o);
+		if (lane >= o) {
+			x += y;
+		}
+	}
+	if (lane == 31) {
+		part[wid] = x;
+	}
+	if (tid == 0) {
+		sel_bin = -1;
+		sel_above = 0;
+	}
+	__syncthreads();
+	if (wid == 0) {
+		unsigned int p = part[lane];
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const unsigned int y = __shfl_up_sync(0xffffffffu, p, o);
+			if (lane >= o) {
+				p += y;
+			}
+		}
+		part[lane] = p;
+	}
+	__syncthreads();
+	const unsigned int incl = x + (wid > 0 ? part[wid - 1] : 0);   // keys in bins >= b1
+	const unsigned int excl = incl - c0 - c1;                      // keys in bins > b0
+	// the k-th key is in the first bin (from the top) where greater + cumulative >= k
+	if (b0 >= 0 && greater + excl < (unsigned int)k && greater + excl + c0 >= (unsigned int)k) {
+		sel_bin = b0;
+		sel_above = excl;
+	} else if (b1 >= 0 && greater + excl + c0 < (unsigned int)k && greater + incl >= (unsigned int)k) {
+		sel_bin = b1;
+		sel_above = excl + c0;
+	}
+	__syncthreads();
+	if (tid == 0) {
+		const unsigned int total = part[31];
+		int bin = sel_bin;
+		unsigned int above = sel_above;
+		if (bin < 0) {
+			// fewer than k keys in total: take everything
+			bin = 0;
+			above = total - h[0];
+		}
+		const unsigned int g = greater + above;
+		const unsigned int cnt = h[bin];
+		w->st.prefix = (w->st.prefix << c_bits[level]) | (unsigned long long)bin;
+		w->st.greater = g;
+		if (g + cnt <= TOPK_CAP || level == TOPK_LEVELS - 1) {
+			w->st.done = 1;
+			w->st.shift_done = c_shift[level];
+		}
+	}
+}
+
+__global__ void topk_collect_kernel(TopkWork *w, const float *__restrict__ score,
+	const uint32_t *__restrict__ orig, int64_t n_slots, float min_score) {
+
+	const int shift = w->st.shift_done;
+	const unsigned long long thr = w->st.prefix << shift;
+	for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_slots;
+		p += (int64_t)gridDim.x * blockDim.x) {
+
+		const float sc = score[p];
+		if (!(sc > min_score)) {
+			continue;
+		}
+		const unsigned long long hi = (unsigned long long)score_key(sc) << 32;
+		if ((hi | 0xffffffffull) < thr) {
+			continue;
+		}
+		const unsigned long long key = hi | orig[p];
+		if (key >= thr) {
+			const unsigned int i = atomicAdd(&w->st.n_cand, 1u);
+			if (i < TOPK_CAP) {
+				w->cand[i] = key;
+			}
+		}
+	}
+}
+
+// One block: bitonic sort (descending) of the candidates in shared memory, emit the best k.
+__global__ void topk_sort_kernel(TopkWork *w, int k, const uint32_t *__restrict__ slot_of,
+	uint32_t *__restrict__ out_slots, float *__restrict__ out_scores, int32_t *__restrict__ out_n) {
+
+	extern __shared__ unsigned long long keys[];   // TOPK_CAP
+	unsigned int n = w->st.n_cand;
+	if (n > TOPK_CAP) {
+		n = TOPK_CAP;
+	}
+	unsigned int m = 1;
+	while (m < n) {
+		m <<= 1;
+	}
+	for (unsigned int i = threadIdx.x; i < m; i += blockDim.x) {
+		keys[i] = i < n ? w->cand[i] : 0ull;
+	}
+	__syncthreads();
+	for (unsigned int size = 2; size <= m; size <<= 1) {
+		for (unsigned int stride = size >> 1; stride > 0; stride >>= 1) {
+			for (unsigned int i = threadIdx.x; i < m; i += blockDim.x) {
+				const unsigned int j = i ^ stride;
+				if (j > i) {
+					const bool desc = (i & size) == 0;
+					const unsigned long long a = keys[i], b = keys[j];
+					if (desc ? a < b : a > b) {
+						keys[i] = b;
+						keys[j] = a;
+					}
+				}
+			}
+			__syncthreads();
+		}
+	}
+	const unsigned int n_out = n < (unsigned int)k ? n : (unsigned int)k;
+	for (unsigned int i = threadIdx.x; i < n_out; i += blockDim.x) {
+		const unsigned long long key = keys[i];
+		out_slots[i] = slot_of[(uint32_t)(key & 0xffffffffull)];
+		out_scores[i] = key_score((unsigned int)(key >> 32));
+	}
+	if (threadIdx.x == 0) {
+		*out_n = (int32_t)n_out;
+		w->st.n_out = (int)n_out;
+	}
+}
+
+size_t vx_topk_work_bytes(int32_t k) {
+	return sizeof(TopkWork) + (size_t)k * (sizeof(uint32_t) + sizeof(float)) + 64;
+}
+
+int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out) {
+	if (k > TOPK_CAP) {
+		vx_set_error("max_matches larger than 8192 is not supported");
+		return -1;
+	}
+	TopkWork *w = (TopkWork*)work;
+	uint8_t *tail = (uint8_t*)work + sizeof(TopkWork);
+	out->slots = (uint32_t*)tail;
+	out->scores = (float*)(tail + (size_t)k * sizeof(uint32_t));
+	out->n = (int32_t*)(tail + (size_t)k * (sizeof(uint32_t) + sizeof(float)));
+
+	cudaStream_t st = c->stream;
+	int launches = 0;
+	cudaMemsetAsync(w, 0, sizeof(TopkState) + sizeof(unsigned int) * TOPK_LEVELS * TOPK_BINS, st);
+	cudaMemsetAsync(out->n, 0, sizeof(int32_t), st);
+
+	int sms = 148;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+	int64_t blocks = (c->n_slots + 255) / 256;
+	if (blocks > sms * 8) {
+		blocks = sms * 8;
+	}
+	if (blocks < 1) {
+		blocks = 1;
+	}
+	for (int level = 0; level < TOPK_LEVELS; level++) {
+		topk_hist_kernel<<<(unsigned)blocks, 256, 0, st>>>(w, level, c->d_score, c->d_orig, c->n_slots, min_score);
+		topk_scan_kernel<<<1, 1024, 0, st>>>(w, level, k);
+		launches += 2;
+	}
+	topk_collect_kernel<<<(unsigned)blocks, 256, 0, st>>>(w, c->d_score, c->d_orig, c->n_slots, min_score);
+	const size_t smem = sizeof(unsigned long long) * TOPK_CAP;
+	cudaFuncSetAttribute(topk_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+	topk_sort_kernel<<<1, 1024, smem, st>>>(w, k, c->d_slot_of, out->slots, out->scores, out->n);
+	launches += 2;
+	if (cudaGetLastError() != cudaSuccess) {
+		vx_set_error("top-k kernel launch failed");
+		return -1;
+	}
+	return launches;
+}

@@ -1,0 +1,406 @@
+// Exact alignment with traceback for a list of windows (one thread per window).
+//
+// Used (a) for the k winners of a search, to produce the InjectiveFlow the reference attaches to
+// every Match, and (b) as the exact scorer for the option combinations whose normaliser depends on
+// the traceback (tag-weighted similarity, submatch_weight != 0).
+//
+// This kernel reproduces the reference's candidate ORDER, not just its maxima:
+//   TracingAccumulator: first push assigns, later pushes replace only if strictly greater
+//     (pyalign/algorithm/solver.h:1320-1340, 1393-1401)
+//   candidate lists of the three solvers (solver.h:2829-2846, 2981-3026, 3145-3173)
+//   seeds per locality (solver.h:2027-2050, 2166-2180, 2258-2286), Optima (1954-1959)
+//   traceback walk + path_compressor (solver.h:1489-1528, 822-838)
+//   flow / score (vectorian/core/cpp/metric/alignment.h:84-106, 175-205, 247-294, 307-347;
+//                 cpp/match/match.h:95-132, 302-307)
+#include "vx_internal.cuh"
+
+#include <math_constants.h>
+
+#define NO_TB ((int16_t)-32768)
+
+struct Layer {
+	float *val;
+	int16_t *tbu, *tbv;
+	int ld;
+	__device__ __forceinline__ size_t at(int u, int v) const {
+		return (size_t)(u + 1) * ld + (v + 1);
+	}
+};
+
+struct Acc {
+	float val;
+	int16_t u, v;
+	bool started;
+	__device__ __forceinline__ void begin(bool local) {
+		started = local;
+		val = 0.0f;
+		u = v = NO_TB;
+	}
+	__device__ __forceinline__ void push(float x, int pu, int pv) {
+		if (!started || x > val) {
+			val = x;
+			u = (int16_t)pu;
+			v = (int16_t)pv;
+			started = true;
+		}
+	}
+	__device__ __forceinline__ void store(Layer &m, int cu, int cv) const {
+		const size_t i = m.at(cu, cv);
+		m.val[i] = val;
+		m.tbu[i] = u;
+		m.tbv[i] = v;
+	}
+};
+
+__device__ __forceinline__ void clear_tb_border(Layer &m, int len_s, int len_t) {
+	for (int u = -1; u < len_s; u++) {
+		m.tbu[m.at(u, -1)] = NO_TB;
+		m.tbv[m.at(u, -1)] = NO_TB;
+	}
+	for (int v = -1; v < len_t; v++) {
+		m.tbu[m.at(-1, v)] = NO_TB;
+		m.tbv[m.at(-1, v)] = NO_TB;
+	}
+}
+
+__device__ __forceinline__ float affine_at(float ext, float open0, int k) {
+	return k == 0 ? 0.0f : ext * (float)k + open0;
+}
+
+struct TraceArgs {
+	const VxTile *tiles;
+	const int32_t *tok;
+	const int8_t *pos;
+	const float *boost;
+	const float *s;          // static: [V x tp]
+	int32_t tp;
+	const float *ctx;        // contextual: tiled normalised vectors
+	const float *qhat;       // contextual: [t x d]
+	int32_t ctx_dim;
+	int32_t contextual;
+	uint8_t *scratch;
+	size_t scratch_per_item;
+	int32_t max_len;
+	const uint32_t *slots;    // nullptr -> slot = slot_base + item (score-everything mode)
+	int64_t slot_base;
+	const uint32_t *orig;
+	const int32_t *n_items;   // device count (may be nullptr -> max_items)
+	int32_t max_items;
+	VxTraceOut out;
+};
+
+__device__ __forceinline__ float raw_sim(const TraceArgs &a, size_t tok_index, int32_t id, int j) {
+	if (a.contextual) {
+		const float *x = a.ctx + tok_index * a.ctx_dim;
+		const float *q = a.qhat + (size_t)j * a.ctx_dim;
+		float acc = 0.0f;
+		for (int k = 0; k < a.ctx_dim; k++) {
+			acc = fmaf(x[k], q[k], acc);
+		}
+		return fminf(fmaxf(acc, 0.0f), 1.0f);
+	}
+	return a.s[(size_t)id * a.tp + j];
+}
+
+__global__ void trace_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
+	const int item = blockIdx.x * blockDim.x + threadIdx.x;
+	const int n_items = a.n_items ? *a.n_items : a.max_items;
+	if (item >= n_items || item >= a.max_items) {
+		return;
+	}
+	const int64_t slot = a.slots ? (int64_t)a.slots[item] : a.slot_base + item;
+	const VxTile tl = a.tiles[slot >> 5];
+	const int lane = (int)(slot & 31);
+	if (lane >= tl.n_valid) {
+		a.out.score[item] = -CUDART_INF_F;   // padding lane
+		return;
+	}
+	const size_t tok0 = (size_t)tl.base32 * 32 + lane;
+	const int len_s = tl.len;
+	const int len_t = qp.t;
+	const bool local = ap.locality == VX_LOCAL;
+	const bool global = ap.locality == VX_GLOBAL;
+
+	// carve the scratch: sim[len_s x len_t], then layers
+	uint8_t *base = a.scratch + (size_t)item * a.scratch_per_item;
+	float *sim = reinterpret_cast<float*>(base);
+	const size_t n_cell = (size_t)(a.max_len + 1) * (len_t + 1);
+	float *vals = sim + (size_t)a.max_len * len_t;
+	int16_t *tbs = reinterpret_cast<int16_t*>(vals + n_cell * 3);
+	Layer D{vals, tbs, tbs + n_cell, len_t + 1};
+	Layer P{vals + n_cell, tbs + 2 * n_cell, tbs + 3 * n_cell, len_t + 1};
+	Layer Q{vals + 2 * n_cell, tbs + 4 * n_cell, tbs + 5 * n_cell, len_t + 1};
+
+	// similarity of the slice (StaticEmbeddingSlice / ContextualEmbeddingSlice / TagWeightedSlice)
+	for (int u = 0; u < len_s; u++) {
+		const size_t ti = tok0 + (size_t)u * 32;
+		const int32_t id = a.tok[ti];
+		for (int j = 0; j < len_t; j++) {
+			float x = raw_sim(a, ti, id, j);
+			if (qp.tag_weighted) {
+				const float tw = len_t <= VX_MAX_T_MASK ? qp.t_weights[j] : qp.t_weights_dev[j];
+				const int8_t tpos = len_t <= VX_MAX_T_MASK ? qp.t_pos[j] : qp.t_pos_dev[j];
+				float weight = tw;
+				if (a.pos[ti] != tpos) {
+					weight *= 1.0f - qp.pos_mismatch_penalty;
+				}
+				const float sc = x * weight;
+				x = sc <= qp.similarity_threshold ? 0.0f : sc;
+			}
+			sim[(size_t)u * len_t + j] = x;
+		}
+	}
+
+	// ---- solve ----
+	if (ap.gap_kind == VX_GAP_LINEAR) {
+		const float gs = ap.lin_s, gt = ap.lin_t;
+		for (int u = -1; u < len_s; u++) {
+			D.val[D.at(u, -1)] = global ? ((float)(u + 1) * gs) * -1.0f : 0.0f;
+		}
+		for (int v = -1; v < len_t; v++) {
+			D.val[D.at(-1, v)] = global ? ((float)(v + 1) * gt) * -1.0f : 0.0f;
+		}
+		clear_tb_border(D, len_s, len_t);
+		for (int u = 0; u < len_s; u++) {
+			for (int v = 0; v < len_t; v++) {
+				Acc acc;
+				acc.begin(local);
+				acc.push(D.val[D.at(u - 1, v - 1)] + sim[(size_t)u * len_t + v], u - 1, v - 1);
+				acc.push(D.val[D.at(u - 1, v)] - gs, u - 1, v);
+				acc.push(D.val[D.at(u, v - 1)] - gt, u, v - 1);
+				acc.store(D, u, v);
+			}
+		}
+	} else if (ap.gap_kind == VX_GAP_GENERAL) {
+		const float *ws = ap.w_s, *wt = ap.w_t;
+		for (int u = -1; u < len_s; u++) {
+			D.val[D.at(u, -1)] = global ? ws[u + 1] * -1.0f : 0.0f;
+		}
+		for (int v = -1; v < len_t; v++) {
+			D.val[D.at(-1, v)] = global ? wt[v + 1] * -1.0f : 0.0f;
+		}
+		clear_tb_border(D, len_s, len_t);
+		for (int u = 0; u < len_s; u++) {
+			for (int v = 0; v < len_t; v++) {
+				Acc acc;
+				acc.begin(local);
+				acc.push(D.val[D.at(u - 1, v - 1)] + sim[(size_t)u * len_t + v], u - 1, v - 1);
+				for (int k = -1; k < u; k++) {
+					acc.push(D.val[D.at(k, v)] - ws[u - k], k, v);
+				}
+				for (int k = -1; k < v; k++) {
+					acc.push(D.val[D.at(u, k)] - wt[v - k], u, k);
+				}
+				acc.store(D, u, v);
+			}
+		}
+	} else {
+		const float ninf = -CUDART_INF_F;
+		for (int u = -1; u < len_s; u++) {
+			Q.val[Q.at(u, -1)] = ninf;
+		}
+		for (int v = -1; v < len_t; v++) {
+			P.val[P.at(-1, v)] = ninf;
+		}
+		for (int u = -1; u < len_s; u++) {
+			const float b = global ? affine_at(ap.aff_ext_s, ap.aff_open_s, u + 1) * -1.0f : 0.0f;
+			D.val[D.at(u, -1)] = b;
+			P.val[P.at(u, -1)] = b;
+		}
+		for (int v = -1; v < len_t; v++) {
+			const float b = global ? affine_at(ap.aff_ext_t, ap.aff_open_t, v + 1) * -1.0f : 0.0f;
+			D.val[D.at(-1, v)] = b;
+			Q.val[Q.at(-1, v)] = b;
+		}
+		clear_tb_border(D, len_s, len_t);
+		clear_tb_border(P, len_s, len_t);
+		clear_tb_border(Q, len_s, len_t);
+		const float w1s = ap.aff_ext_s + ap.aff_open_s;
+		const float w1t = ap.aff_ext_t + ap.aff_open_t;
+		for (int i = 0; i < len_s; i++) {
+			for (int j = 0; j < len_t; j++) {
+				{
+					Acc acc;
+					acc.begin(false);
+					acc.push(D.val[D.at(i - 1, j)] - w1s, i - 1, j);
+					const size_t k = P.at(i - 1, j);
+					acc.push(P.val[k] - ap.aff_ext_s, P.tbu[k], P.tbv[k]);
+					acc.store(P, i, j);
+				}
+				{
+					Acc acc;
+					acc.begin(false);
+					acc.push(D.val[D.at(i, j - 1)] - w1t, i, j - 1);
+					const size_t k = Q.at(i, j - 1);
+					acc.push(Q.val[k] - ap.aff_ext_t, Q.tbu[k], Q.tbv[k]);
+					acc.store(Q, i, j);
+				}
+				{
+					Acc acc;
+					acc.begin(local);
+					acc.push(D.val[D.at(i - 1, j - 1)] + sim[(size_t)i * len_t + j], i - 1, j - 1);
+					const size_t kp = P.at(i, j);
+					acc.push(P.val[kp], P.tbu[kp], P.tbv[kp]);
+					const size_t kq = Q.at(i, j);
+					acc.push(Q.val[kq], Q.tbu[kq], Q.tbv[kq]);
+					acc.store(D, i, j);
+				}
+			}
+		}
+	}
+
+	// ---- seeds ----
+	int16_t *target = a.out.target ? a.out.target + (size_t)item * len_t :
+		reinterpret_cast<int16_t*>(tbs + n_cell * 6);
+	for (int v = 0; v < len_t; v++) {
+		target[v] = -1;
+	}
+	int su = -1, sv = -1;
+	bool have_seed = false;
+	if (local) {
+		float best = -CUDART_INF_F;
+		for (int i = len_s - 1; i >= 0; i--) {
+			for (int j = len_t - 1; j >= 0; j--) {
+				const float x = D.val[D.at(i, j)];
+				if (x > best) {
+					best = x;
+					su = i;
+					sv = j;
+				}
+			}
+		}
+		have_seed = best > -CUDART_INF_F;
+	} else if (global) {
+		su = len_s - 1;
+		sv = len_t - 1;
+		have_seed = true;
+	} else {
+		float best = -CUDART_INF_F;
+		for (int j = 0; j < len_t; j++) {
+			const float x = D.val[D.at(len_s - 1, j)];
+			if (x > best) {
+				best = x;
+				su = len_s - 1;
+				sv = j;
+			}
+		}
+		for (int i = 0; i < len_s; i++) {
+			const float x = D.val[D.at(i, len_t - 1)];
+			if (x > best) {
+				best = x;
+				su = i;
+				sv = len_t - 1;
+			}
+		}
+		have_seed = best > -CUDART_INF_F;
+	}
+
+	// ---- traceback ----
+	float raw = -CUDART_INF_F;
+	if (have_seed) {
+		int u = su, v = sv;
+		raw = D.val[D.at(u, v)];
+		int last_u = u, last_v = v;   // first step only arms the compressor
+		while (u >= 0 && v >= 0 && (!local || D.val[D.at(u, v)] > 0.0f)) {
+			const size_t i = D.at(u, v);
+			const int nu = D.tbu[i], nv = D.tbv[i];
+			u = nu;
+			v = nv;
+			if (u != last_u && v != last_v && last_u >= 0 && last_v >= 0) {
+				target[last_v] = (int16_t)last_u;
+			}
+			last_u = u;
+			last_v = v;
+		}
+	}
+
+	// ---- score ----
+	float matched = 0.0f;
+	for (int j = 0; j < len_t; j++) {
+		if (target[j] >= 0) {
+			matched += qp.tag_weighted ?
+				(len_t <= VX_MAX_T_MASK ? qp.t_weights[j] : qp.t_weights_dev[j]) : 1.0f;
+		}
+	}
+	const float total = qp.total;
+	const float unmatched_weight = powf((total - matched) / total, qp.submatch_weight);
+	const float ref = matched + unmatched_weight * (total - matched);
+	const float boost = a.boost ? a.boost[slot] : 1.0f;
+	a.out.score[item] = (raw / ref) * boost;
+	if (a.out.score_max) {
+		a.out.score_max[item] = ref;
+	}
+	if (a.out.win) {
+		a.out.win[item] = a.orig[slot];
+	}
+
+	// ---- ScoreComputer: dist = 1 - unmodified_similarity(target, j) ----
+	if (a.out.dist) {
+		for (int j = 0; j < len_t; j++) {
+			const int u = target[j];
+			float dv = 1.0f;
+			if (u >= 0) {
+				const size_t ti = tok0 + (size_t)u * 32;
+				dv = 1.0f - raw_sim(a, ti, a.tok[ti], j);
+			}
+			a.out.dist[(size_t)item * len_t + j] = dv;
+		}
+	}
+}
+
+size_t vx_trace_scratch_bytes(int32_t max_len, int32_t t, int32_t max_items, int32_t gap_kind) {
+	(void)gap_kind;
+	const size_t n_cell = (size_t)(max_len + 1) * (t + 1);
+	size_t per_item = sizeof(float) * (size_t)max_len * t + n_cell * 3 * sizeof(float) + n_cell * 6 * sizeof(int16_t)
+		+ sizeof(int16_t) * (size_t)t;
+	per_item = (per_item + 15) & ~(size_t)15;
+	return per_item * (size_t)max_items;
+}
+
+int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp,
+	const uint32_t *d_slots, int64_t slot_base, const int32_t *d_n_items, int32_t max_items, VxTraceOut out) {
+
+	if (max_items <= 0) {
+		return 0;
+	}
+	const size_t need = vx_trace_scratch_bytes(c->max_len, qp.t, max_items, ap.gap_kind);
+	if (c->scratch_bytes < need) {
+		if (c->d_scratch) {
+			cudaFree(c->d_scratch);
+			c->d_scratch = nullptr;
+			c->scratch_bytes = 0;
+		}
+		if (cudaMalloc(&c->d_scratch, need) != cudaSuccess) {
+			vx_set_error("cudaMalloc of the traceback scratch failed");
+			return -1;
+		}
+		c->scratch_bytes = need;
+	}
+	TraceArgs a;
+	a.tiles = c->d_tiles;
+	a.tok = c->d_tok;
+	a.pos = c->d_pos;
+	a.boost = c->d_boost;
+	a.s = s->d_s;
+	a.tp = s->tp;
+	a.ctx = c->d_ctx;
+	a.qhat = s->d_qhat;
+	a.ctx_dim = s->d;
+	a.contextual = s->contextual;
+	a.scratch = (uint8_t*)c->d_scratch;
+	a.scratch_per_item = need / (size_t)max_items;
+	a.max_len = c->max_len;
+	a.slots = d_slots;
+	a.slot_base = slot_base;
+	a.orig = c->d_orig;
+	a.n_items = d_n_items;
+	a.max_items = max_items;
+	a.out = out;
+	const int threads = 32;
+	trace_kernel<<<(max_items + threads - 1) / threads, threads, 0, c->stream>>>(a, ap, qp);
+	if (cudaGetLastError() != cudaSuccess) {
+		vx_set_error("trace kernel launch failed");
+		return -1;
+	}
+	return 1;
+}

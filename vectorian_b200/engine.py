@@ -1,0 +1,207 @@
+"""Thin object layer over the C ABI: device corpus, embedding, similarity matrix, search.
+
+These are the objects the reference keeps behind pybind11 (``core.Document`` /
+``core.Vocabulary`` / ``core.Query`` / ``core.ResultSet``, reference:
+vectorian/core/cpp/module.cpp:30-152); everything here forwards to
+libvectorian_b200.so and raises if the CUDA library or device is missing.
+"""
+
+import ctypes as C
+
+import numpy as np
+
+from . import _cabi
+from ._cabi import ptr, check, HIT_DTYPE, Hit
+
+
+class DeviceCorpus:
+	"""Documents packed once into device-resident token tiles for one partition.
+
+	Replaces the list of ``core.Document`` + ``Spans::iterate``
+	(reference: vectorian/core/cpp/document.h:147-169, cpp/document.cpp:30-58).
+	"""
+
+	def __init__(self, token_id, doc_tok_off, span_start, span_end, doc_span_off,
+			window_size=1, window_step=1, token_pos=None, on_device=False):
+		lib = _cabi.lib()
+		self._lib = lib
+		self._h = C.c_void_p()
+		doc_tok_off = np.ascontiguousarray(doc_tok_off, dtype=np.int64)
+		span_start = np.ascontiguousarray(span_start, dtype=np.int32)
+		span_end = np.ascontiguousarray(span_end, dtype=np.int32)
+		doc_span_off = np.ascontiguousarray(doc_span_off, dtype=np.int64)
+		n_doc = len(doc_tok_off) - 1
+		if on_device:
+			# token_id / token_pos are torch CUDA tensors (int32 / int8)
+			n_tok = int(token_id.numel())
+			check(lib.vx_corpus_create_dev(
+				C.c_void_p(token_id.data_ptr()),
+				C.c_void_p(token_pos.data_ptr() if token_pos is not None else None),
+				n_tok, ptr(doc_tok_off, C.c_int64), n_doc,
+				ptr(span_start, C.c_int32), ptr(span_end, C.c_int32), ptr(doc_span_off, C.c_int64),
+				int(window_size), int(window_step), C.byref(self._h)), lib)
+		else:
+			token_id = np.ascontiguousarray(token_id, dtype=np.int32)
+			if token_pos is not None:
+				token_pos = np.ascontiguousarray(token_pos, dtype=np.int8)
+			check(lib.vx_corpus_create(
+				ptr(token_id, C.c_int32), ptr(token_pos, C.c_int8), len(token_id),
+				ptr(doc_tok_off, C.c_int64), n_doc,
+				ptr(span_start, C.c_int32), ptr(span_end, C.c_int32), ptr(doc_span_off, C.c_int64),
+				int(window_size), int(window_step), C.byref(self._h)), lib)
+		self.n_doc = n_doc
+		self.n_spans = int(doc_span_off[-1])
+
+	def close(self):
+		if self._h:
+			self._lib.vx_corpus_destroy(self._h)
+			self._h = C.c_void_p()
+
+	def __del__(self):
+		try:
+			self.close()
+		except Exception:
+			pass
+
+	@property
+	def handle(self):
+		return self._h
+
+	@property
+	def n_windows(self):
+		return int(self._lib.vx_corpus_n_windows(self._h))
+
+	@property
+	def n_tokens(self):
+		return int(self._lib.vx_corpus_n_tokens(self._h))
+
+	@property
+	def n_cells(self):
+		return int(self._lib.vx_corpus_n_cells(self._h))
+
+	@property
+	def max_len(self):
+		return int(self._lib.vx_corpus_max_len(self._h))
+
+	def set_boost(self, boost):
+		if boost is None:
+			check(self._lib.vx_corpus_set_boost(self._h, ptr(None, C.c_float), 0), self._lib)
+			return
+		boost = np.ascontiguousarray(boost, dtype=np.float32)
+		check(self._lib.vx_corpus_set_boost(self._h, ptr(boost, C.c_float), len(boost)), self._lib)
+
+	def set_contextual(self, x):
+		x = np.ascontiguousarray(x, dtype=np.float32)
+		check(self._lib.vx_corpus_set_contextual(self._h, ptr(x, C.c_float), x.shape[0], x.shape[1]), self._lib)
+
+	def abort(self):
+		self._lib.vx_abort(self._h)
+
+	def search(self, sim, ap, qp):
+		"""Returns (hits structured array, target[n x T] int16, dist[n x T] float32)."""
+		k = max(int(qp.max_matches), 1)
+		t = max(sim.t, 1)
+		hits = np.zeros((k,), dtype=HIT_DTYPE)
+		target = np.full((k, t), -1, dtype=np.int16)
+		dist = np.ones((k, t), dtype=np.float32)
+		n = C.c_int32(0)
+		check(self._lib.vx_search(self._h, sim.handle, C.byref(ap), C.byref(qp),
+			hits.ctypes.data_as(C.POINTER(Hit)), ptr(target, C.c_int16), ptr(dist, C.c_float), C.byref(n)), self._lib)
+		return hits[:n.value], target[:n.value, :sim.t], dist[:n.value, :sim.t]
+
+	def score_all(self, sim, ap, qp):
+		n = self.n_windows
+		out = np.zeros((n,), dtype=np.float32)
+		check(self._lib.vx_score_all(self._h, sim.handle, C.byref(ap), C.byref(qp), ptr(out, C.c_float), n), self._lib)
+		return out
+
+	def last_timing(self):
+		ms = np.zeros((3,), dtype=np.float32)
+		check(self._lib.vx_last_timing(self._h, ptr(ms, C.c_float)), self._lib)
+		return dict(dp_ms=float(ms[0]), topk_ms=float(ms[1]), traceback_ms=float(ms[2]))
+
+	def last_launches(self):
+		return int(self._lib.vx_last_launches(self._h))
+
+
+class DeviceEmbedding:
+	"""A static embedding table, L2-normalised on the device (reference: embedding/vectors.py:71-86)."""
+
+	def __init__(self, vectors):
+		lib = _cabi.lib()
+		self._lib = lib
+		self._h = C.c_void_p()
+		vectors = np.ascontiguousarray(vectors, dtype=np.float32)
+		self.shape = vectors.shape
+		check(lib.vx_embedding_create(ptr(vectors, C.c_float), vectors.shape[0], vectors.shape[1], C.byref(self._h)), lib)
+
+	def close(self):
+		if self._h:
+			self._lib.vx_embedding_destroy(self._h)
+			self._h = C.c_void_p()
+
+	def __del__(self):
+		try:
+			self.close()
+		except Exception:
+			pass
+
+	@property
+	def handle(self):
+		return self._h
+
+
+class DeviceSim:
+	"""The query's similarity matrix on the device (reference: cpp/metric/metric.h:9-52)."""
+
+	def __init__(self, handle, rows, t, lib):
+		self._h = handle
+		self._lib = lib
+		self.rows = rows
+		self.t = t
+
+	@classmethod
+	def static(cls, embedding, q_id, q_vec):
+		"""S = clip01(cos(E, Q)) with the identity fix-up (reference: cpp/metric/static.cpp:9-78)."""
+		lib = _cabi.lib()
+		q_id = np.ascontiguousarray(q_id, dtype=np.int32)
+		q_vec = np.ascontiguousarray(q_vec, dtype=np.float32).reshape(len(q_id), -1)
+		h = C.c_void_p()
+		check(lib.vx_sim_static(embedding.handle, ptr(q_id, C.c_int32), ptr(q_vec, C.c_float), len(q_id), C.byref(h)), lib)
+		return cls(h, embedding.shape[0], len(q_id), lib)
+
+	@classmethod
+	def upload(cls, s):
+		lib = _cabi.lib()
+		s = np.ascontiguousarray(s, dtype=np.float32)
+		h = C.c_void_p()
+		check(lib.vx_sim_upload(ptr(s, C.c_float), s.shape[0], s.shape[1], C.byref(h)), lib)
+		return cls(h, s.shape[0], s.shape[1], lib)
+
+	@classmethod
+	def contextual(cls, q_vec):
+		lib = _cabi.lib()
+		q_vec = np.ascontiguousarray(q_vec, dtype=np.float32)
+		h = C.c_void_p()
+		check(lib.vx_sim_contextual(ptr(q_vec, C.c_float), q_vec.shape[0], q_vec.shape[1], C.byref(h)), lib)
+		return cls(h, 0, q_vec.shape[0], lib)
+
+	def download(self):
+		out = np.zeros((self.rows, self.t), dtype=np.float32)
+		check(self._lib.vx_sim_download(self._h, ptr(out, C.c_float), self.rows, self.t), self._lib)
+		return out
+
+	def close(self):
+		if self._h:
+			self._lib.vx_sim_destroy(self._h)
+			self._h = C.c_void_p()
+
+	def __del__(self):
+		try:
+			self.close()
+		except Exception:
+			pass
+
+	@property
+	def handle(self):
+		return self._h
