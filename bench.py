@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""Headline benchmark: Waterman-Smith-Beyer brute-force search (BASELINE.json configs[2]).
+
+One step = one query through the whole hot path over the resident corpus shard:
+similarity GEMM (query x vocabulary) -> per-sentence WSB alignment -> device top-k ->
+traceback of the winners -> (N > 1) all-gather + merge of the per-rank top-k.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--sentences S]
+
+N > 1 is launched by torchrun (one rank per GPU, NCCL).  Weak scaling: every rank holds
+`--sentences` sentences (default 50M = the named corpus on one GPU).
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+	sys.path.insert(0, ROOT)
+
+T_QUERY = 12
+VOCAB = 50_000
+DIM = 300
+TOPK = 100
+N_QUERIES = 8
+
+
+def wsb_params(max_len, t):
+	from vectorian_b200 import _cabi, gaps
+	r = gaps.resolve_gap_costs(gaps.smooth_gap_cost(5), max_len, t)
+	kind = r.pop("gap_kind")
+	return _cabi.make_align_params(_cabi.VX_LOCAL, kind, **r)
+
+
+def ops_per_sentence(lens, t):
+	"""Algorithmic FP32 lane-ops of Local WSB: 2 per candidate + 1 zero-compare per cell."""
+	l = lens.astype(np.float64)
+	cand = l * t + t * l * (l + 1) / 2 + l * t * (t + 1) / 2
+	return 2 * cand + l * t
+
+
+class ClockSampler:
+	"""nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+	def __init__(self, index):
+		self.rows = []
+		q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+			"clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+			"clocks_event_reasons.sw_power_cap")
+		try:
+			self.p = subprocess.Popen(
+				["nvidia-smi", f"--id={index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+				stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+			self.t = threading.Thread(target=self._read, daemon=True)
+			self.t.start()
+		except Exception:
+			self.p = None
+
+	def _read(self):
+		for line in self.p.stdout:
+			self.rows.append((time.perf_counter(), line.strip()))
+
+	def stop(self, t0, t1):
+		if self.p is None:
+			return None
+		time.sleep(0.15)
+		self.p.terminate()
+		sm, mx, reasons = [], [], set()
+		for ts, line in self.rows:
+			f = [x.strip() for x in line.split(",")]
+			if len(f) < 7 or not (t0 <= ts <= t1 + 0.2):
+				continue
+			try:
+				sm.append(float(f[0]))
+				mx.append(float(f[1]))
+			except ValueError:
+				continue
+			for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+				if val.lower().startswith("active"):
+					reasons.add(name)
+		if not sm:
+			return None
+		return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_port_rate(sample_sentences, threads, seed=1234):
+	"""Times the oracle (CPU port of the reference path) on a bounded sample of the same workload."""
+	from vectorian_b200 import _cabi, synthetic
+	from oracle import oracle
+	corpus = synthetic.make_corpus(sample_sentences, VOCAB, seed=seed)
+	emb = synthetic.make_embedding(VOCAB, DIM)
+	q_id = synthetic.make_query(T_QUERY, VOCAB)
+	oc = oracle.OracleCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"],
+		corpus["span_end"], corpus["doc_span_off"])
+	ap, keep = wsb_params(int(corpus["lens"].max()), T_QUERY)
+	qp, _ = _cabi.make_query_params(max_matches=TOPK, min_score=0.0)
+	t0 = time.perf_counter()
+	s = oracle.sim_static(emb, q_id, emb[q_id])
+	hits, _, _ = oc.search(s, ap, qp, n_threads=threads)
+	dt = time.perf_counter() - t0
+	return sample_sentences / dt, dt, len(hits)
+
+
+def run_reference(args):
+	"""--impl reference: the reference's CPU implementation of the path on the host cores.
+
+	The unmodified reference needs xtensor/xsimd/xtensor-python (absent, no network), so this arm
+	times the oracle port (kind "port") with all host threads; each step is a bounded sample."""
+	rank = int(os.environ.get("RANK", "0"))
+	if rank != 0:
+		return
+	threads = os.cpu_count() or 1
+	sample = args.cpu_sample
+	rates = []
+	for i in range(args.warmup + args.steps):
+		r, dt, n = cpu_port_rate(sample, threads, seed=1234 + i)
+		if i >= args.warmup:
+			rates.append((r, dt))
+	value = float(np.mean([r for r, _ in rates]))
+	line = {
+		"impl": "reference", "metric": "sentences/sec (WSB alignment, 12-token query, top-100)",
+		"value": value, "unit": "sentences/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+		"ms_per_step": float(np.mean([dt for _, dt in rates]) * 1e3), "higher_is_better": True, "scaling": "weak",
+		"vs_baseline": None, "dtype": "f32", "data": "synthetic",
+		"config": {"workload": workload_name(args), "sample_sentences_per_step": sample},
+		"cpu_baseline": {"value": value, "unit": "sentences/s", "cores": threads, "kind": "port",
+			"sample": f"{sample} sentences per step of the same synthetic workload"},
+		"e2e": {"value": value, "unit": "sentences/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+		"gcups": value * 25 * T_QUERY / 1e9,
+	}
+	print(json.dumps(line), flush=True)
+
+
+def workload_name(args):
+	return (f"C3: Waterman-Smith-Beyer Local, smooth_gap_cost(5), T={T_QUERY}, V={VOCAB}x{DIM} static embedding, "
+		f"top-{TOPK}, {args.sentences} sentences per GPU (~25 tokens each, Zipf ids)")
+
+
+def main():
+	ap_ = argparse.ArgumentParser()
+	ap_.add_argument("--gpus", type=int, default=1)
+	ap_.add_argument("--steps", type=int, default=20)
+	ap_.add_argument("--warmup", type=int, default=3)
+	ap_.add_argument("--impl", default="ours")
+	ap_.add_argument("--sentences", type=int, default=50_000_000)
+	ap_.add_argument("--cpu-sample", type=int, default=200_000)
+	ap_.add_argument("--no-cpu-baseline", action="store_true")
+	args = ap_.parse_args()
+	args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
+
+	if args.impl == "reference":
+		run_reference(args)
+		return
+
+	import torch
+	import torch.distributed as dist
+	from vectorian_b200 import _cabi, engine, synthetic
+	from vectorian_b200.distributed import gather_topk
+
+	rank = int(os.environ.get("RANK", "0"))
+	world = int(os.environ.get("WORLD_SIZE", "1"))
+	local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+	torch.cuda.set_device(local_rank)
+	if world > 1:
+		dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+	# ---- resident state: corpus shard + embedding (setup, untimed) ----
+	t_setup = time.perf_counter()
+	tok, tables = synthetic.make_corpus_device(args.sentences, VOCAB, seed=synthetic.CORPUS_SEED + rank,
+		device=f"cuda:{local_rank}")
+	torch.cuda.synchronize()
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"],
+		tables["doc_span_off"], on_device=True)
+	lens = tables["lens"]
+	n_doc_local = tables["n_doc"]
+	del tok
+	torch.cuda.empty_cache()
+	emb = synthetic.make_embedding(VOCAB, DIM)
+	de = engine.DeviceEmbedding(emb)
+	rng = np.random.default_rng(synthetic.QUERY_SEED)
+	queries = [synthetic.make_query(T_QUERY, VOCAB, seed=synthetic.QUERY_SEED + i) for i in range(N_QUERIES)]
+	# per-step inputs live in pinned host memory: query token ids + their (unnormalised) vectors
+	q_ids = [torch.from_numpy(q).pin_memory() for q in queries]
+	q_vecs = [torch.from_numpy(emb[q].copy()).pin_memory() for q in queries]
+	ap, keep = wsb_params(dc.max_len, T_QUERY)
+	qp, _ = _cabi.make_query_params(max_matches=TOPK, min_score=0.0)
+	setup_s = time.perf_counter() - t_setup
+
+	def step(i):
+		"""The public-API call a user makes; inputs from pinned host memory, results back on the host."""
+		j = i % N_QUERIES
+		sim = engine.DeviceSim.static(de, q_ids[j].numpy(), q_vecs[j].numpy())
+		hits, target, distance = dc.search(sim, ap, qp)
+		dev_ms = sim.build_ms + sum(dc.last_timing().values())
+		launches = sim.launches + dc.last_launches()
+		sim.close()
+		if world > 1:
+			hits, target, distance = gather_topk(hits, target, distance, TOPK, doc_offset=rank * n_doc_local)
+		return hits, dev_ms, launches
+
+	def barrier():
+		if world > 1:
+			dist.barrier()
+		torch.cuda.synchronize()
+
+	for i in range(args.warmup):
+		step(i)
+
+	sampler = ClockSampler(local_rank) if rank == 0 else None
+	barrier()
+	t0 = time.perf_counter()
+	dev_ms_total, dp_ms_total, launches_total = 0.0, 0.0, 0
+	last_hits = None
+	for i in range(args.steps):
+		last_hits, dev_ms, launches = step(args.warmup + i)
+		dev_ms_total += dev_ms
+		dp_ms_total += dc.last_timing()["dp_ms"]
+		launches_total += launches
+	barrier()
+	t1 = time.perf_counter()
+	clocks = sampler.stop(t0, t1) if sampler else None
+
+	wall_s = t1 - t0
+	times = torch.tensor([wall_s, dev_ms_total / 1e3, dp_ms_total / 1e3], dtype=torch.float64, device="cuda")
+	counts = torch.tensor([float(dc.n_windows), float(dc.n_cells), float(launches_total)], dtype=torch.float64, device="cuda")
+	if world > 1:
+		dist.all_reduce(times, op=dist.ReduceOp.MAX)
+		dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+	wall_s, dev_s, dp_s = [float(x) for x in times.cpu()]
+	n_sent, n_cells, launches_all = [float(x) for x in counts.cpu()]
+
+	if rank == 0:
+		peaks = {}
+		try:
+			peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+		except Exception:
+			pass
+		hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+		peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+		sm_max = float(peaks.get("sm_max_mhz", 1965.0))
+		sms = _cabi.lib().vx_device_sm_count()
+
+		value = n_sent * args.steps / dev_s            # device-timed (CUDA events), inputs resident
+		e2e = n_sent * args.steps / wall_s             # public API, host buffers, H2D/D2H inside
+		# dominant kernel = the WSB DP: algorithmic bytes = 4 B per token id + 4 B per sentence
+		alg_bytes = 4.0 * dc.n_cells + 4.0 * dc.n_windows
+		dp_ms = dp_s * 1e3 / args.steps
+		achieved = alg_bytes / (dp_ms * 1e-3) / 1e9
+		lane_ops = float(ops_per_sentence(lens, T_QUERY).sum())
+		issue_peak = sms * 128 * sm_max * 1e6
+		issue_ach = lane_ops / (dp_ms * 1e-3)
+
+		line = {
+			"metric": "sentences/sec (WSB alignment, 12-token query, top-100)",
+			"value": value, "unit": "sentences/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+			"ms_per_step": dev_s * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak",
+			"vs_baseline": None, "dtype": "f32", "data": "synthetic",
+			"config": {"workload": workload_name(args), "l2": "inputs larger than L2 (token tiles %.1f GB per GPU)" % (4.0 * dc.n_cells / 1e9),
+				"queries": f"{N_QUERIES} distinct queries in rotation", "parallelism": f"sentence shards x{world}, top-k all-gather"},
+			"gcups": n_cells * T_QUERY * args.steps / dev_s / 1e9,
+			"e2e": {"value": e2e, "unit": "sentences/s",
+				"h2d_bytes_per_step": int(T_QUERY * 4 + T_QUERY * DIM * 4 + (dc.max_len + 1 + T_QUERY + 1) * 4),
+				"d2h_bytes_per_step": int(TOPK * (16 + 6 * T_QUERY) + 16), "ms_per_step": wall_s * 1e3 / args.steps},
+			"gpu_launches": int(launches_all),
+			"roofline": {"bound": "hbm", "kernel": "WSB score kernel (vx_align.cu)", "achieved": achieved, "peak": hbm_peak,
+				"unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+				"algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": dp_ms,
+				"note": "the static-embedding DP is FP32-issue-bound, not HBM-bound (SURVEY.md 8d): see issue_roofline"},
+			"issue_roofline": {"bound": "fp32 issue (FADD + FMNMX per candidate)", "achieved": issue_ach / 1e12,
+				"peak": issue_peak / 1e12, "unit": "T lane-op/s", "frac": issue_ach / issue_peak,
+				"lane_ops_per_launch": lane_ops, "sms": sms, "clock_mhz": sm_max},
+			"phases_ms": {k: v for k, v in dc.last_timing().items()},
+			"setup_s": setup_s,
+			"top_score": float(last_hits["score"][0]) if len(last_hits) else None,
+		}
+		if clocks:
+			line["clocks"] = clocks
+		if world == 1 and not args.no_cpu_baseline:
+			threads = os.cpu_count() or 1
+			r, dt, _ = cpu_port_rate(args.cpu_sample, threads)
+			line["cpu_baseline"] = {"value": r, "unit": "sentences/s", "cores": threads, "kind": "port",
+				"sample": f"{args.cpu_sample} sentences of the same synthetic workload, {dt:.1f} s"}
+		print(json.dumps(line), flush=True)
+
+	if world > 1:
+		dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+	main()

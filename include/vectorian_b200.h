@@ -166,6 +166,9 @@ int vx_sim_upload(const float *s, int64_t v, int32_t t, vx_sim **out);
 int vx_sim_contextual(const float *q_vec, int32_t t, int32_t d, vx_sim **out);
 
 int vx_sim_download(const vx_sim *s, float *out, int64_t v, int32_t t); /* debug hook "static_similarity_matrix" */
+/* Device time (CUDA events) of the kernels that built this matrix, in ms, and how many were launched. */
+float vx_sim_build_ms(const vx_sim *s);
+int vx_sim_launches(const vx_sim *s);
 int vx_sim_destroy(vx_sim *s);
 
 /* ---- search: replaces Document.find / Query::match / ResultSet::extend / best_n ---- */

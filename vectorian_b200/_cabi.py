@@ -146,6 +146,8 @@ _SIGNATURES = {
 	"vx_sim_upload": (C.c_int, [c_float_p, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),
 	"vx_sim_contextual": (C.c_int, [c_float_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
 	"vx_sim_download": (C.c_int, [C.c_void_p, c_float_p, C.c_int64, C.c_int32]),
+	"vx_sim_build_ms": (C.c_float, [C.c_void_p]),
+	"vx_sim_launches": (C.c_int, [C.c_void_p]),
 	"vx_sim_destroy": (C.c_int, [C.c_void_p]),
 	"vx_search": (C.c_int, [
 		C.c_void_p, C.c_void_p, C.POINTER(AlignParams), C.POINTER(QueryParams),

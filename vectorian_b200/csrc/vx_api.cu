@@ -351,6 +351,7 @@ extern "C" int vx_corpus_set_boost(vx_corpus *c, const float *boost, int64_t n) 
 		VX_TRY(dev_alloc(&c->d_boost, (size_t)c->n_slots));
 	}
 	VX_CUDA(cudaMemcpy(c->d_boost, by_slot.data(), sizeof(float) * (size_t)c->n_slots, cudaMemcpyHostToDevice));
+	VX_CUDA(cudaDeviceSynchronize());
 	return VX_OK;
 }
 
@@ -468,17 +469,28 @@ extern "C" int vx_sim_static(const vx_embedding *e, const int32_t *q_id, const f
 		if ((rc = dev_alloc(&d_qid, (size_t)t)) != VX_OK) break;
 		cudaMemcpyAsync(d_q, q_vec, sizeof(float) * (size_t)t * e->d, cudaMemcpyHostToDevice, 0);
 		cudaMemcpyAsync(d_qid, q_id, sizeof(int32_t) * (size_t)t, cudaMemcpyHostToDevice, 0);
-		vx_launch_normalize(d_q, d_qhat, t, e->d, 0);
-		if (vx_launch_sim_static(e->d_ehat, e->v, e->d, d_qhat, d_qid, t, s->tp, s->d_s, 0) < 0) {
+		cudaEvent_t e0, e1;
+		cudaEventCreate(&e0);
+		cudaEventCreate(&e1);
+		cudaEventRecord(e0, 0);
+		s->launches += vx_launch_normalize(d_q, d_qhat, t, e->d, 0);
+		const int n_launched = vx_launch_sim_static(e->d_ehat, e->v, e->d, d_qhat, d_qid, t, s->tp, s->d_s, 0);
+		cudaEventRecord(e1, 0);
+		if (n_launched < 0) {
 			vx_set_error("similarity kernel: unsupported query length");
 			rc = VX_ERR_INVALID;
-			break;
+		} else {
+			s->launches += n_launched;
 		}
 		cudaError_t err = cudaStreamSynchronize(0);
 		if (err != cudaSuccess) {
 			vx_set_error(std::string("similarity kernel failed: ") + cudaGetErrorString(err));
 			rc = VX_ERR_CUDA;
+		} else {
+			cudaEventElapsedTime(&s->build_ms, e0, e1);
 		}
+		cudaEventDestroy(e0);
+		cudaEventDestroy(e1);
 	} while (0);
 	cudaFree(d_q);
 	cudaFree(d_qhat);
@@ -509,6 +521,11 @@ extern "C" int vx_sim_upload(const float *sm, int64_t v, int32_t t, vx_sim **out
 	if (v * t > 0) {
 		cudaError_t err = cudaMemcpy2D(s->d_s, sizeof(float) * s->tp, sm, sizeof(float) * t,
 			sizeof(float) * t, (size_t)v, cudaMemcpyHostToDevice);
+		if (err == cudaSuccess) {
+			// a pageable-memory copy may return before its DMA has landed; searches run on their own
+			// non-blocking stream, so finish it here
+			err = cudaDeviceSynchronize();
+		}
 		if (err != cudaSuccess) {
 			vx_set_error(std::string("similarity upload failed: ") + cudaGetErrorString(err));
 			sim_free(s);
@@ -561,6 +578,14 @@ extern "C" int vx_sim_download(const vx_sim *s, float *out, int64_t v, int32_t t
 			sizeof(float) * t, (size_t)v, cudaMemcpyDeviceToHost));
 	}
 	return VX_OK;
+}
+
+extern "C" float vx_sim_build_ms(const vx_sim *s) {
+	return s ? s->build_ms : 0.0f;
+}
+
+extern "C" int vx_sim_launches(const vx_sim *s) {
+	return s ? s->launches : 0;
 }
 
 extern "C" int vx_sim_destroy(vx_sim *s) {

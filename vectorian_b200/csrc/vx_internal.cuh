@@ -94,6 +94,8 @@ struct vx_sim {
 	int32_t contextual = 0;
 	int32_t d = 0;
 	float *d_qhat = nullptr;         // contextual: [t x d] normalised query vectors
+	float build_ms = 0.0f;           // device time of the kernels that built d_s
+	int launches = 0;
 };
 
 // Per-query constants handed to the kernels by value.

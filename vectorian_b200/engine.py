@@ -186,6 +186,14 @@ class DeviceSim:
 		check(lib.vx_sim_contextual(ptr(q_vec, C.c_float), q_vec.shape[0], q_vec.shape[1], C.byref(h)), lib)
 		return cls(h, 0, q_vec.shape[0], lib)
 
+	@property
+	def build_ms(self):
+		return float(self._lib.vx_sim_build_ms(self._h))
+
+	@property
+	def launches(self):
+		return int(self._lib.vx_sim_launches(self._h))
+
 	def download(self):
 		out = np.zeros((self.rows, self.t), dtype=np.float32)
 		check(self._lib.vx_sim_download(self._h, ptr(out, C.c_float), self.rows, self.t), self._lib)
