@@ -362,7 +362,7 @@ static int sm_count() {
 }
 
 template<int TP, int LOC>
-static int launch_score_tl(vx_corpus *c, const ScoreArgs &a, const VxAlignDev &ap) {
+static int launch_score_tl(vx_corpus *c, const vx_sim *s, const ScoreArgs &a, const VxAlignDev &ap, const VxQueryDev &qp) {
 	const int warps = 4;
 	const unsigned grid = (unsigned)((a.n_tiles + warps - 1) / warps);
 	switch (ap.gap_kind) {
@@ -375,6 +375,17 @@ static int launch_score_tl(vx_corpus *c, const ScoreArgs &a, const VxAlignDev &a
 			return 1;
 		}
 		default: {
+			// windows up to 64 tokens: shared-memory kernel (vx_wsb.cu); the rest: global scratch
+			int64_t first = 0;
+			const int n_fast = vx_launch_wsb(c, s, ap, qp, &first);
+			if (n_fast < 0) {
+				return -1;
+			}
+			if (first == 0) {
+				return n_fast;
+			}
+			ScoreArgs a_long = a;
+			a_long.n_tiles = first;
 			// persistent: 16 warps per SM
 			const int blocks = sm_count() * 4;
 			const size_t need = sizeof(float) * (size_t)blocks * warps * c->max_len * TP * 32;
@@ -391,21 +402,21 @@ static int launch_score_tl(vx_corpus *c, const ScoreArgs &a, const VxAlignDev &a
 				c->scratch_bytes = need;
 			}
 			score_general_scratch_kernel<TP, LOC><<<blocks, warps * 32, 0, c->stream>>>(
-				a, ap.w_s, ap.w_t, (float*)c->d_scratch, c->max_len);
-			return 1;
+				a_long, ap.w_s, ap.w_t, (float*)c->d_scratch, c->max_len);
+			return n_fast + 1;
 		}
 	}
 }
 
 template<int TP>
-static int launch_score_t(vx_corpus *c, const ScoreArgs &a, const VxAlignDev &ap) {
+static int launch_score_t(vx_corpus *c, const vx_sim *s, const ScoreArgs &a, const VxAlignDev &ap, const VxQueryDev &qp) {
 	switch (ap.locality) {
 		case VX_LOCAL:
-			return launch_score_tl<TP, VX_LOCAL>(c, a, ap);
+			return launch_score_tl<TP, VX_LOCAL>(c, s, a, ap, qp);
 		case VX_GLOBAL:
-			return launch_score_tl<TP, VX_GLOBAL>(c, a, ap);
+			return launch_score_tl<TP, VX_GLOBAL>(c, s, a, ap, qp);
 		default:
-			return launch_score_tl<TP, VX_SEMIGLOBAL>(c, a, ap);
+			return launch_score_tl<TP, VX_SEMIGLOBAL>(c, s, a, ap, qp);
 	}
 }
 
@@ -428,16 +439,16 @@ int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 	int n;
 	switch (s->tp) {
 		case 4:
-			n = launch_score_t<4>(c, a, ap);
+			n = launch_score_t<4>(c, s, a, ap, qp);
 			break;
 		case 8:
-			n = launch_score_t<8>(c, a, ap);
+			n = launch_score_t<8>(c, s, a, ap, qp);
 			break;
 		case 12:
-			n = launch_score_t<12>(c, a, ap);
+			n = launch_score_t<12>(c, s, a, ap, qp);
 			break;
 		case 16:
-			n = launch_score_t<16>(c, a, ap);
+			n = launch_score_t<16>(c, s, a, ap, qp);
 			break;
 		default:
 			vx_set_error("vx_launch_score: query longer than the fast path supports");

@@ -94,6 +94,7 @@ static void corpus_free(vx_corpus *c) {
 	cudaFree(c->d_score);
 	cudaFree(c->d_work);
 	cudaFree(c->d_scratch);
+	cudaFree(c->d_counters);
 	if (c->h_res) {
 		cudaFreeHost(c->h_res);
 	}
@@ -217,6 +218,11 @@ static int corpus_create_impl(
 			n_tiles += nt;
 		}
 		c->n_tiles = n_tiles;
+		for (int i = 0; i <= VX_N_CLASS; i++) {
+			// first tile with len <= 8*i  ==  first_tile of the longest such length
+			const int32_t lmax = std::min<int32_t>(8 * i, c->max_len);
+			c->class_first[i] = i == 0 || lmax < 1 ? n_tiles : first_tile[lmax];
+		}
 		c->n_slots = n_tiles * VX_TILE;
 		c->n_tok_tiled = base32 * 32;
 	}
@@ -269,6 +275,11 @@ static int corpus_create_impl(
 			if ((rc = dev_alloc(&c->d_pos, (size_t)c->n_tok_tiled)) != VX_OK) break;
 		}
 		if ((rc = dev_alloc(&c->d_score, (size_t)c->n_slots)) != VX_OK) break;
+		{
+			unsigned int *ctr = nullptr;
+			if ((rc = dev_alloc(&ctr, 16)) != VX_OK) break;
+			c->d_counters = ctr;
+		}
 		cudaMemcpyAsync(d_win_tok, hw.tok.data(), sizeof(int64_t) * (size_t)c->n_win, cudaMemcpyHostToDevice, c->stream);
 		cudaMemcpyAsync(c->d_tiles, tiles.data(), sizeof(VxTile) * (size_t)c->n_tiles, cudaMemcpyHostToDevice, c->stream);
 		cudaMemcpyAsync(c->d_orig, orig.data(), sizeof(uint32_t) * (size_t)c->n_slots, cudaMemcpyHostToDevice, c->stream);

@@ -37,6 +37,7 @@ struct VxTile {
 };
 
 constexpr int VX_TILE = 32;
+constexpr int VX_N_CLASS = 8;        // length classes of 8 tokens: windows up to 64 tokens take the fast WSB kernel
 constexpr uint32_t VX_NO_WINDOW = 0xffffffffu;
 
 struct vx_corpus {
@@ -72,6 +73,10 @@ struct vx_corpus {
 	void *h_res = nullptr;           // pinned host mirror of the result block
 	size_t h_res_bytes = 0;
 	int32_t max_token_id = -1;       // -1 = unknown (corpus created from device memory)
+	// tiles are sorted by descending length: class_first[i] = first tile whose windows are <= 8*i long
+	// (class_first[0] = n_tiles); the shared-memory WSB kernel is launched once per class of 8
+	int64_t class_first[VX_N_CLASS + 1] = {0};
+	void *d_counters = nullptr;      // 16 x uint32 tile counters of the persistent kernels
 
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -110,6 +115,8 @@ struct VxAlignDev {
 	const float *w_s;    // device, general gap tables
 	const float *w_t;
 	int32_t n_w_s, n_w_t;
+	const float *h_w_s;  // the same tables on the host (kernel-parameter copies)
+	const float *h_w_t;
 };
 
 struct VxQueryDev {
@@ -132,6 +139,10 @@ struct VxQueryDev {
 
 // vx_align.cu -- score-only DP over every tile; writes c->d_score[slot].
 int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp);
+
+// vx_wsb.cu -- general gap cost, windows up to 64 tokens, history in shared memory.  Handles the
+// tiles [*first_tile, n_tiles); the longer ones are left to the scratch kernel of vx_align.cu.
+int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, int64_t *first_tile);
 
 // vx_trace.cu -- exact DP with traceback for a list of slots (device array), one thread per item.
 struct VxTraceOut {

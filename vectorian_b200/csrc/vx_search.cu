@@ -172,6 +172,8 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 	a.w_t = p->gap_t;
 	a.n_w_s = (int32_t)n_ws;
 	a.n_w_t = (int32_t)n_wt;
+	a.h_w_s = ap->w_s;
+	a.h_w_t = ap->w_t;
 	if (n_ws) {
 		VX_CUDA(cudaMemcpyAsync(p->gap_s, ap->w_s, sizeof(float) * n_ws, cudaMemcpyHostToDevice, c->stream));
 		VX_CUDA(cudaMemcpyAsync(p->gap_t, ap->w_t, sizeof(float) * n_wt, cudaMemcpyHostToDevice, c->stream));

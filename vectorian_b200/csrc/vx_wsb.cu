@@ -1,0 +1,390 @@
+// Waterman-Smith-Beyer (general gap cost) score kernel: the roofline-critical kernel of the path.
+//
+// Replaces GeneralGapCostSolver::solve (pyalign/algorithm/solver.h:3130-3175) + the per-sentence
+// loop of MatcherImpl::run_matches (vectorian/core/cpp/match/matcher_impl.h:71-109) for every window
+// of at most VX_WSB_MAX_LEN tokens; longer windows take score_general_scratch_kernel (vx_align.cu).
+//
+//   V[u,v] = max( [0], V[u-1,v-1] + sim(u,v), max_{k<u} V[k,v] - w_s[u-k], max_{k<v} V[u,k] - w_t[v-k] )
+//
+// Work per window of L tokens against T query tokens: L*T*(L+T)/2 candidates, each one fp32 add and
+// one fp32 max -- the kernel is bound by the fma/alu issue pipes, not by HBM (100 B of token ids per
+// window).  Design (measured on B200 with scripts/ubench/pipes.cu: FADD r,c = 1 cyc/warp/SMSP,
+// FMNMX3 = 2 cyc, so 2 candidates cost 3 issue slots when both adds read one register + one
+// constant/uniform operand and the two maxima fold into one 3-input FMNMX3):
+//   * one window per lane, 32 equal-length windows per warp (a tile): no divergence, token ids are
+//     read as one 128-byte line per token position;
+//   * rows are processed in blocks of U: the U x T accumulators of the block live in registers; a
+//     finished row is read back from shared memory once per BLOCK (not once per row), so every
+//     LDS.128 feeds 4*U candidates;
+//   * finished rows (the column history the vertical gap scan needs) are kept in shared memory as
+//     [u][v/4][lane] float4 -- conflict-free LDS.128/STS.128, L*T*128 bytes per warp;
+//   * gap tables come from the kernel parameter bank (constant operands / uniform loads), the
+//     similarity rows S[id, 0..T) from L2/L1 with float4 loads issued one block ahead of their use;
+//   * persistent warps pull tiles from an atomic counter; one launch per length class so that the
+//     shared-memory slice of a warp (and therefore warps per SM) matches the class.
+// fp32 add / max only, compiled with -fmad=false: scores are bit-identical to the oracle.
+#include "vx_internal.cuh"
+
+#include <math_constants.h>
+#include <cstring>
+
+constexpr int VX_WSB_MAX_LEN = 64;
+constexpr int VX_WSB_U = 4;
+
+struct WsbArgs {
+	const VxTile *tiles;
+	const int32_t *tok;
+	const float *s;          // [V x TP]
+	const float *boost;      // by slot or nullptr
+	float *score;            // by slot
+	unsigned int *counter;   // tile counter of this launch (zeroed by the host)
+	int64_t tile_begin, tile_end;
+	int32_t t;
+	int32_t cap;             // rows of history per warp in shared memory
+	float total;
+	float ws[VX_WSB_MAX_LEN + 4];   // w_s[0..64], gap cost along the sentence
+	float wt[VX_MAX_T_FAST + 4];    // w_t[0..16], gap cost along the query
+};
+
+__device__ __forceinline__ float max3(float a, float b, float c) {
+	float r;
+	asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+	return r;
+}
+
+// One block of NR rows u0 .. u0+NR-1 of one tile.
+//   prev[v]  in: V[u0-1, v]  out: V[u0+NR-1, v]
+template<int TP, int LOC, bool BORD, int NR>
+__device__ __forceinline__ void wsb_block(
+	const WsbArgs &a, const int32_t *__restrict__ tok, float4 *__restrict__ hist,
+	const int u0, const int t, float (&prev)[TP], float &best, float &last_col) {
+
+	constexpr int Q = TP / 4;
+	const float4 *__restrict__ s4 = reinterpret_cast<const float4*>(a.s);
+
+	// similarity rows of the block
+	float sim[NR][TP];
+	#pragma unroll
+	for (int i = 0; i < NR; i++) {
+		const int32_t id = tok[(size_t)(u0 + i) * 32];
+		#pragma unroll
+		for (int q = 0; q < Q; q++) {
+			const float4 x = __ldg(s4 + (size_t)id * Q + q);
+			sim[i][4 * q + 0] = x.x;
+			sim[i][4 * q + 1] = x.y;
+			sim[i][4 * q + 2] = x.z;
+			sim[i][4 * q + 3] = x.w;
+		}
+	}
+
+	// accumulators: vertical candidates from the border row k = -1 (or the Local zero)
+	float acc[NR][TP];
+	#pragma unroll
+	for (int i = 0; i < NR; i++) {
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			if (BORD) {
+				const float top = LOC == VX_GLOBAL ? -a.wt[v + 1] : 0.0f;   // V[-1, v]  (solver.h:3108-3117)
+				acc[i][v] = top - a.ws[u0 + i + 1];
+			} else {
+				acc[i][v] = 0.0f;
+			}
+		}
+	}
+
+	// vertical candidates from the finished rows k = 0 .. u0-1 (u0 is a multiple of U, U even)
+	#pragma unroll 1
+	for (int k = 0; k < u0; k += 2) {
+		float h0[TP], h1[TP];
+		#pragma unroll
+		for (int q = 0; q < Q; q++) {
+			const float4 x = hist[((size_t)k * Q + q) * 32];
+			const float4 y = hist[((size_t)(k + 1) * Q + q) * 32];
+			h0[4 * q + 0] = x.x; h0[4 * q + 1] = x.y; h0[4 * q + 2] = x.z; h0[4 * q + 3] = x.w;
+			h1[4 * q + 0] = y.x; h1[4 * q + 1] = y.y; h1[4 * q + 2] = y.z; h1[4 * q + 3] = y.w;
+		}
+		#pragma unroll
+		for (int i = 0; i < NR; i++) {
+			const float w0 = a.ws[u0 + i - k];
+			const float w1 = a.ws[u0 + i - k - 1];
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				acc[i][v] = max3(acc[i][v], h0[v] - w0, h1[v] - w1);
+			}
+		}
+	}
+
+	// the rows of the block, in order
+	#pragma unroll
+	for (int i = 0; i < NR; i++) {
+		const int u = u0 + i;
+		// vertical candidates from the rows of this block
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			float x = acc[i][v];
+			int j = 0;
+			#pragma unroll
+			for (; j + 1 < i; j += 2) {
+				x = max3(x, acc[j][v] - a.ws[i - j], acc[j + 1][v] - a.ws[i - j - 1]);
+			}
+			if (j < i) {
+				x = fmaxf(x, acc[j][v] - a.ws[i - j]);
+			}
+			acc[i][v] = x;
+		}
+		// V[u, -1] and V[u-1, -1]
+		const float left = BORD ? (LOC == VX_GLOBAL ? -a.ws[u + 1] : 0.0f) : 0.0f;
+		float diag = BORD ? (LOC == VX_GLOBAL ? (u == 0 ? -a.wt[0] : -a.ws[u]) : 0.0f) : 0.0f;
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			float x = fmaxf(acc[i][v], diag + sim[i][v]);
+			diag = i == 0 ? prev[v] : acc[i - 1][v];
+			int k = 0;
+			if (BORD) {
+				x = fmaxf(x, left - a.wt[v + 1]);
+			}
+			#pragma unroll
+			for (; k + 1 < v; k += 2) {
+				x = max3(x, acc[i][k] - a.wt[v - k], acc[i][k + 1] - a.wt[v - k - 1]);
+			}
+			if (k < v) {
+				x = fmaxf(x, acc[i][k] - a.wt[v - k]);
+			}
+			acc[i][v] = x;
+		}
+		if (LOC == VX_LOCAL) {
+			constexpr int NF = TP - 3;   // columns [0, NF) always belong to the query (TP - 4 < t <= TP)
+			constexpr int NP = NF / 2 * 2;
+			#pragma unroll
+			for (int v = 0; v < NP; v += 2) {
+				best = max3(best, acc[i][v], acc[i][v + 1]);
+			}
+			#pragma unroll
+			for (int v = NP; v < TP; v++) {
+				if (v < NF || v < t) {
+					best = fmaxf(best, acc[i][v]);
+				}
+			}
+		} else {
+			#pragma unroll
+			for (int v = TP - 4; v < TP; v++) {
+				if (v == t - 1) {
+					last_col = acc[i][v];
+				}
+			}
+			if (LOC == VX_SEMIGLOBAL) {
+				best = fmaxf(best, last_col);
+			}
+		}
+	}
+
+	// publish the rows
+	#pragma unroll
+	for (int i = 0; i < NR; i++) {
+		#pragma unroll
+		for (int q = 0; q < Q; q++) {
+			hist[((size_t)(u0 + i) * Q + q) * 32] =
+				make_float4(acc[i][4 * q + 0], acc[i][4 * q + 1], acc[i][4 * q + 2], acc[i][4 * q + 3]);
+		}
+	}
+	#pragma unroll
+	for (int v = 0; v < TP; v++) {
+		prev[v] = acc[NR - 1][v];
+	}
+}
+
+template<int TP, int LOC, bool BORD>
+__global__ void __launch_bounds__(512, 1) wsb_score_kernel(const __grid_constant__ WsbArgs a) {
+	extern __shared__ float4 wsb_smem[];
+	constexpr int Q = TP / 4;
+	constexpr int U = VX_WSB_U;
+	const int lane = threadIdx.x & 31;
+	const int warp = threadIdx.x >> 5;
+	float4 *hist = wsb_smem + (size_t)warp * a.cap * Q * 32 + lane;
+	const int t = a.t;
+
+	for (;;) {
+		unsigned int got = 0;
+		if (lane == 0) {
+			got = atomicAdd(a.counter, 1u);
+		}
+		got = __shfl_sync(0xffffffffu, got, 0);
+		const int64_t tile = a.tile_begin + got;
+		if (tile >= a.tile_end) {
+			break;
+		}
+		const VxTile tl = a.tiles[tile];
+		const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
+		const int len = tl.len;
+
+		float prev[TP];
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			prev[v] = BORD && LOC == VX_GLOBAL ? -a.wt[v + 1] : 0.0f;   // V[-1, v]
+		}
+		float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+		float last_col = 0.0f;
+
+		int u0 = 0;
+		#pragma unroll 1
+		for (; u0 + U <= len; u0 += U) {
+			wsb_block<TP, LOC, BORD, U>(a, tok, hist, u0, t, prev, best, last_col);
+		}
+		switch (len - u0) {
+			case 1:
+				wsb_block<TP, LOC, BORD, 1>(a, tok, hist, u0, t, prev, best, last_col);
+				break;
+			case 2:
+				wsb_block<TP, LOC, BORD, 2>(a, tok, hist, u0, t, prev, best, last_col);
+				break;
+			case 3:
+				wsb_block<TP, LOC, BORD, 3>(a, tok, hist, u0, t, prev, best, last_col);
+				break;
+			default:
+				break;
+		}
+
+		float raw;
+		if (LOC == VX_LOCAL) {
+			raw = best;
+		} else if (LOC == VX_GLOBAL) {
+			raw = last_col;
+		} else {
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				if (v < t) {
+					best = fmaxf(best, prev[v]);
+				}
+			}
+			raw = best;
+		}
+		const int64_t slot = tile * 32 + lane;
+		const float boost = a.boost ? a.boost[slot] : 1.0f;
+		a.score[slot] = lane < tl.n_valid ? (raw / a.total) * boost : -CUDART_INF_F;
+		__syncwarp();
+	}
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+
+template<int TP, int LOC, bool BORD>
+static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms) {
+	const size_t per_warp = (size_t)cap * TP * 32 * sizeof(float);
+	const size_t smem_max = 227 * 1024;
+	int warps = (int)(smem_max / per_warp);
+	if (warps > 16) {
+		warps = 16;
+	}
+	if (warps < 1) {
+		return -1;
+	}
+	const int64_t n_tiles = a.tile_end - a.tile_begin;
+	const int64_t want_blocks = (n_tiles + warps - 1) / warps;
+	const int blocks = (int)(want_blocks < sms ? want_blocks : sms);
+	const size_t smem = per_warp * warps;
+	a.cap = cap;
+	static bool attr_set = false;
+	if (!attr_set) {
+		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max);
+		attr_set = true;
+	}
+	wsb_score_kernel<TP, LOC, BORD><<<blocks, warps * 32, smem, c->stream>>>(a);
+	return 1;
+}
+
+template<int TP>
+static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord) {
+	if (loc == VX_LOCAL) {
+		return bord ? launch_class<TP, VX_LOCAL, true>(c, a, cap, sms) : launch_class<TP, VX_LOCAL, false>(c, a, cap, sms);
+	}
+	if (loc == VX_GLOBAL) {
+		return launch_class<TP, VX_GLOBAL, true>(c, a, cap, sms);
+	}
+	return launch_class<TP, VX_SEMIGLOBAL, true>(c, a, cap, sms);
+}
+
+// Scores every tile whose windows are at most VX_WSB_MAX_LEN long; *first_tile receives the index of
+// the first tile handled (tiles are sorted by descending length, so [0, *first_tile) are the long ones
+// left to the scratch kernel).  Returns launches or < 0.
+int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, int64_t *first_tile) {
+	const float *h_ws = ap.h_w_s, *h_wt = ap.h_w_t;
+
+	*first_tile = c->n_tiles;
+	if (c->n_tiles == 0) {
+		return 0;
+	}
+	int sms = 148;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+
+	WsbArgs a;
+	memset(&a, 0, sizeof(a));
+	a.tiles = c->d_tiles;
+	a.tok = c->d_tok;
+	a.s = s->d_s;
+	a.boost = c->d_boost;
+	a.score = c->d_score;
+	a.t = qp.t;
+	a.total = qp.total;
+	const int n_ws = ap.n_w_s < VX_WSB_MAX_LEN + 1 ? ap.n_w_s : VX_WSB_MAX_LEN + 1;
+	bool nonneg = true;
+	for (int i = 0; i < n_ws; i++) {
+		a.ws[i] = h_ws[i];
+		nonneg = nonneg && h_ws[i] >= 0.0f;
+	}
+	for (int i = 0; i <= qp.t && i < ap.n_w_t; i++) {
+		a.wt[i] = h_wt[i];
+		nonneg = nonneg && h_wt[i] >= 0.0f;
+	}
+	// With non-negative gap costs the border candidates of a Local alignment (0 - w) never beat the
+	// Local zero, so the kernel variant without them gives the same maxima.
+	const bool bord = !(ap.locality == VX_LOCAL && nonneg);
+
+	// length classes of 8 rows; c->class_first[i] = first tile whose length is <= 8 * i
+	int launches = 0;
+	unsigned int *counters = (unsigned int*)c->d_counters;
+	cudaMemsetAsync(counters, 0, sizeof(unsigned int) * 16, c->stream);
+	for (int cls = VX_WSB_MAX_LEN / 8; cls >= 1; cls--) {
+		const int64_t begin = c->class_first[cls];
+		const int64_t end = c->class_first[cls - 1];
+		if (begin >= end) {
+			continue;
+		}
+		if (begin < *first_tile) {
+			*first_tile = begin;
+		}
+		a.tile_begin = begin;
+		a.tile_end = end;
+		a.counter = counters + cls;
+		const int cap = cls * 8;
+		int rc;
+		switch (s->tp) {
+			case 4:
+				rc = launch_class_t<4>(c, a, cap, sms, ap.locality, bord);
+				break;
+			case 8:
+				rc = launch_class_t<8>(c, a, cap, sms, ap.locality, bord);
+				break;
+			case 12:
+				rc = launch_class_t<12>(c, a, cap, sms, ap.locality, bord);
+				break;
+			case 16:
+				rc = launch_class_t<16>(c, a, cap, sms, ap.locality, bord);
+				break;
+			default:
+				vx_set_error("vx_launch_wsb: query longer than the fast path supports");
+				return -1;
+		}
+		if (rc < 0) {
+			vx_set_error("vx_launch_wsb: shared-memory slice does not fit");
+			return -1;
+		}
+		launches += rc;
+	}
+	if (cudaGetLastError() != cudaSuccess) {
+		vx_set_error("WSB score kernel launch failed");
+		return -1;
+	}
+	return launches;
+}
