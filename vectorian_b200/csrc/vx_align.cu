@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 	}
 	const int lane = threadIdx.x & 31;
 	const VxTile tl = a.tiles[tile];
-	const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
+	const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + lane) * 4;
 	const int len = tl.len;
 	const int t = a.t;
 
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 			cur[v] = row[v];
 		}
 		if (u + 1 < len) {
-			id = tok[(size_t)(u + 1) * 32];
+			id = tok[vx_elem(0, u + 1, 0)];
 			load_row<TP>(a.s, id, row);
 		}
 
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(128) score_affine_kernel(ScoreArgs a, AffineAr
 	}
 	const int lane = threadIdx.x & 31;
 	const VxTile tl = a.tiles[tile];
-	const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
+	const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + lane) * 4;
 	const int len = tl.len;
 	const int t = a.t;
 
@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(128) score_affine_kernel(ScoreArgs a, AffineAr
 			cur[v] = row[v];
 		}
 		if (u + 1 < len) {
-			id = tok[(size_t)(u + 1) * 32];
+			id = tok[vx_elem(0, u + 1, 0)];
 			load_row<TP>(a.s, id, row);
 		}
 
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(128) score_general_scratch_kernel(
 
 	for (int64_t tile = warp; tile < a.n_tiles; tile += n_warps) {
 		const VxTile tl = a.tiles[tile];
-		const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
+		const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + lane) * 4;
 		const int len = tl.len;
 
 		float top[TP];   // V[-1, v]
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(128) score_general_scratch_kernel(
 
 		for (int u = 0; u < len; u++) {
 			float sim[TP];
-			load_row<TP>(a.s, tok[(size_t)u * 32], sim);
+			load_row<TP>(a.s, tok[vx_elem(0, u, 0)], sim);
 
 			// vertical candidates, k = -1 .. u-1
 			float vert[TP];

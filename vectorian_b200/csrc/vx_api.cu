@@ -199,21 +199,21 @@ static int corpus_create_impl(
 	std::vector<int64_t> first_tile((size_t)c->max_len + 2, 0);
 	std::vector<VxTile> tiles;
 	{
-		int64_t n_tiles = 0, base32 = 0;
+		int64_t n_tiles = 0, base128 = 0;
 		for (int32_t l = c->max_len; l >= 1; l--) {
 			first_tile[l] = n_tiles;
 			const int64_t nt = (count[l] + VX_TILE - 1) / VX_TILE;
 			for (int64_t i = 0; i < nt; i++) {
 				VxTile t;
-				if (base32 > 0xffffffffll) {
+				if (base128 > 0xffffffffll) {
 					corpus_free(c);
-					VX_FAIL(VX_ERR_INVALID, "tiled corpus exceeds 2^37 tokens per GPU: shard the corpus");
+					VX_FAIL(VX_ERR_INVALID, "tiled corpus exceeds 2^39 tokens per GPU: shard the corpus");
 				}
-				t.base32 = (uint32_t)base32;
+				t.base128 = (uint32_t)base128;
 				t.len = (uint16_t)l;
 				t.n_valid = (uint16_t)std::min<int64_t>(VX_TILE, count[l] - i * VX_TILE);
 				tiles.push_back(t);
-				base32 += l;
+				base128 += (l + 3) / 4;
 			}
 			n_tiles += nt;
 		}
@@ -224,7 +224,7 @@ static int corpus_create_impl(
 			c->class_first[i] = i == 0 || lmax < 1 ? n_tiles : first_tile[lmax];
 		}
 		c->n_slots = n_tiles * VX_TILE;
-		c->n_tok_tiled = base32 * 32;
+		c->n_tok_tiled = base128 * 128 + VX_TOK_SLACK;
 	}
 	std::vector<uint32_t> orig((size_t)c->n_slots, VX_NO_WINDOW);
 	std::vector<uint32_t> slot_of((size_t)c->n_win);
@@ -267,10 +267,12 @@ static int corpus_create_impl(
 			}
 		}
 		if ((rc = dev_alloc(&d_win_tok, (size_t)c->n_win)) != VX_OK) break;
-		if ((rc = dev_alloc(&c->d_tiles, (size_t)c->n_tiles)) != VX_OK) break;
+		if ((rc = dev_alloc(&c->d_tiles, (size_t)c->n_tiles + 1)) != VX_OK) break;
+		cudaMemsetAsync(c->d_tiles + c->n_tiles, 0, sizeof(VxTile), c->stream);
 		if ((rc = dev_alloc(&c->d_orig, (size_t)c->n_slots)) != VX_OK) break;
 		if ((rc = dev_alloc(&c->d_slot_of, (size_t)c->n_win)) != VX_OK) break;
 		if ((rc = dev_alloc(&c->d_tok, (size_t)c->n_tok_tiled)) != VX_OK) break;
+		cudaMemsetAsync(c->d_tok + (c->n_tok_tiled - VX_TOK_SLACK), 0, sizeof(int32_t) * VX_TOK_SLACK, c->stream);
 		if (d_pos_raw) {
 			if ((rc = dev_alloc(&c->d_pos, (size_t)c->n_tok_tiled)) != VX_OK) break;
 		}

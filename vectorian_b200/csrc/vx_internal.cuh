@@ -28,13 +28,23 @@ void vx_set_error(const std::string &msg);
 // device layout
 // ---------------------------------------------------------------------------
 
-// A tile = 32 windows of identical length, one per lane of a warp.  Token u of lane l lives at
-// tok[(base32 * 32) + u * 32 + l]  ->  a warp reads one 128-byte line per token position.
+// A tile = 32 windows of identical length, one per lane of a warp.  Tokens are stored in quads:
+// tokens 4q .. 4q+3 of lane l are the 16 bytes at tok[((base128 + q) * 32 + l) * 4 ...], so a warp
+// reads four token positions with one coalesced 512-byte LDG.128.  A tile occupies ceil(len / 4)
+// quads; the unused positions of the last quad and the lanes >= n_valid hold id 0.  Tiles are sorted
+// by descending length and stored back to back, so the token stream of consecutive tiles is contiguous.
 struct VxTile {
-	uint32_t base32;   // token offset of the tile / 32
+	uint32_t base128;  // element offset of the tile / 128
 	uint16_t len;      // window length (tokens)
 	uint16_t n_valid;  // lanes [0, n_valid) hold real windows
 };
+
+// element index of token u of lane l in a tile
+__host__ __device__ __forceinline__ size_t vx_elem(uint32_t base128, int u, int lane) {
+	return (((size_t)base128 + (size_t)(u >> 2)) * 32 + (size_t)lane) * 4 + (size_t)(u & 3);
+}
+
+constexpr int VX_TOK_SLACK = 4 * 128;   // elements readable past the last tile (prefetch runs ahead)
 
 constexpr int VX_TILE = 32;
 constexpr int VX_N_CLASS = 8;        // length classes of 8 tokens: windows up to 64 tokens take the fast WSB kernel
@@ -63,7 +73,7 @@ struct vx_corpus {
 	uint32_t *d_orig = nullptr;      // slot -> window index (VX_NO_WINDOW for padding lanes)
 	uint32_t *d_slot_of = nullptr;   // window index -> slot
 	float *d_boost = nullptr;        // by slot (optional)
-	float *d_ctx = nullptr;          // contextual vectors, tiled like d_tok: [(base + u*32 + l) * d] (optional)
+	float *d_ctx = nullptr;          // contextual vectors, tiled like d_tok: [vx_elem(base128, u, l) * d] (optional)
 	int32_t ctx_dim = 0;
 	float *d_score = nullptr;        // by slot, scratch of the last search
 	void *d_work = nullptr;          // top-k / traceback workspace

@@ -5,8 +5,8 @@
 // tag-weighted similarity) reach the DP, so those are all that is kept on the device.
 #include "vx_internal.cuh"
 
-// One warp per tile.  Lane l owns window orig[tile*32+l]; the warp walks u = 0..len-1 and writes
-// one coalesced 128-byte line per u.
+// One warp per tile.  Lane l owns window orig[tile*32+l]; the warp walks the quads of the tile and
+// writes 32 x (4 elements) contiguously per quad (512 bytes of ids, 128 bytes of POS tags).
 template<typename T>
 __global__ void pack_tiles_kernel(
 	const T *__restrict__ raw, const int64_t *__restrict__ win_tok,
@@ -21,9 +21,9 @@ __global__ void pack_tiles_kernel(
 	const VxTile t = tiles[tile];
 	const uint32_t w = orig[tile * VX_TILE + lane];
 	const T *src = w == VX_NO_WINDOW ? nullptr : raw + win_tok[w];
-	T *dst = out + (size_t)t.base32 * 32 + lane;
-	for (int u = 0; u < t.len; u++) {
-		dst[(size_t)u * 32] = src ? src[u] : pad_value;
+	const int n_pad = (t.len + 3) & ~3;
+	for (int u = 0; u < n_pad; u++) {
+		out[vx_elem(t.base128, u, lane)] = src && u < t.len ? src[u] : pad_value;
 	}
 }
 
@@ -48,7 +48,7 @@ int vx_launch_pack(const int32_t *d_tok_raw, const int8_t *d_pos_raw, const int6
 	return launches;
 }
 
-// Contextual vectors: vector of token u of lane l at ctx[((base + u*32 + l) * d) ...].
+// Contextual vectors: vector of token u of lane l at ctx[vx_elem(base128, u, l) * d ...].
 __global__ void pack_ctx_kernel(
 	const float *__restrict__ raw, const int64_t *__restrict__ win_tok,
 	const VxTile *__restrict__ tiles, const uint32_t *__restrict__ orig,
@@ -60,7 +60,6 @@ __global__ void pack_ctx_kernel(
 		return;
 	}
 	const VxTile t = tiles[tile];
-	const size_t base = (size_t)t.base32 * 32;
 	const int64_t total = (int64_t)t.len * 32 * d;
 	for (int64_t i = threadIdx.x; i < total; i += blockDim.x) {
 		const int k = (int)(i % d);
@@ -68,7 +67,7 @@ __global__ void pack_ctx_kernel(
 		const int lane = (int)(ul & 31);
 		const int u = (int)(ul >> 5);
 		const uint32_t w = orig[tile * VX_TILE + lane];
-		out[(base + (size_t)u * 32 + lane) * d + k] =
+		out[vx_elem(t.base128, u, lane) * d + k] =
 			w == VX_NO_WINDOW ? 0.0f : raw[(win_tok[w] + u) * d + k];
 	}
 }

@@ -115,7 +115,6 @@ __global__ void trace_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
 		a.out.score[item] = -CUDART_INF_F;   // padding lane
 		return;
 	}
-	const size_t tok0 = (size_t)tl.base32 * 32 + lane;
 	const int len_s = tl.len;
 	const int len_t = qp.t;
 	const bool local = ap.locality == VX_LOCAL;
@@ -133,7 +132,7 @@ __global__ void trace_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
 
 	// similarity of the slice (StaticEmbeddingSlice / ContextualEmbeddingSlice / TagWeightedSlice)
 	for (int u = 0; u < len_s; u++) {
-		const size_t ti = tok0 + (size_t)u * 32;
+		const size_t ti = vx_elem(tl.base128, u, lane);
 		const int32_t id = a.tok[ti];
 		for (int j = 0; j < len_t; j++) {
 			float x = raw_sim(a, ti, id, j);
@@ -340,7 +339,7 @@ __global__ void trace_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
 			const int u = target[j];
 			float dv = 1.0f;
 			if (u >= 0) {
-				const size_t ti = tok0 + (size_t)u * 32;
+				const size_t ti = vx_elem(tl.base128, u, lane);
 				dv = 1.0f - raw_sim(a, ti, a.tok[ti], j);
 			}
 			a.out.dist[(size_t)item * len_t + j] = dv;

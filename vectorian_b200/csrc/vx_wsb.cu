@@ -37,8 +37,9 @@ struct WsbArgs {
 	const float *s;          // [V x TP]
 	const float *boost;      // by slot or nullptr
 	float *score;            // by slot
-	unsigned int *counter;   // tile counter of this launch (zeroed by the host)
+	unsigned int *counter;   // chunk counter of this launch (zeroed by the host)
 	int64_t tile_begin, tile_end;
+	int32_t chunk;           // tiles per reservation
 	int32_t t;
 	int32_t cap;             // rows of history per warp in shared memory
 	float total;
@@ -52,30 +53,55 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
 	return r;
 }
 
-// One block of NR rows u0 .. u0+NR-1 of one tile.
-//   prev[v]  in: V[u0-1, v]  out: V[u0+NR-1, v]
-template<int TP, int LOC, bool BORD, int NR>
-__device__ __forceinline__ void wsb_block(
-	const WsbArgs &a, const int32_t *__restrict__ tok, float4 *__restrict__ hist,
-	const int u0, const int t, float (&prev)[TP], float &best, float &last_col) {
-
-	constexpr int Q = TP / 4;
-	const float4 *__restrict__ s4 = reinterpret_cast<const float4*>(a.s);
-
-	// similarity rows of the block
-	float sim[NR][TP];
-	#pragma unroll
-	for (int i = 0; i < NR; i++) {
-		const int32_t id = tok[(size_t)(u0 + i) * 32];
-		#pragma unroll
-		for (int q = 0; q < Q; q++) {
-			const float4 x = __ldg(s4 + (size_t)id * Q + q);
-			sim[i][4 * q + 0] = x.x;
-			sim[i][4 * q + 1] = x.y;
-			sim[i][4 * q + 2] = x.z;
-			sim[i][4 * q + 3] = x.w;
+// Running maximum that folds two candidates per FMNMX3.  After full unrolling `has` is a
+// compile-time constant, so this costs ceil(n / 2) max instructions for n candidates.
+struct Fold {
+	float x, p;
+	bool has;
+	__device__ __forceinline__ explicit Fold(float x0) : x(x0), p(0.0f), has(false) {}
+	__device__ __forceinline__ void push(float c) {
+		if (has) {
+			x = max3(x, p, c);
+			has = false;
+		} else {
+			p = c;
+			has = true;
 		}
 	}
+	__device__ __forceinline__ float done() const {
+		return has ? fmaxf(x, p) : x;
+	}
+};
+
+template<int TP>
+__device__ __forceinline__ void load_sim_row(const float4 *__restrict__ s4, int32_t id, float (&row)[TP]) {
+	#pragma unroll
+	for (int q = 0; q < TP / 4; q++) {
+		const float4 x = __ldg(s4 + (size_t)id * (TP / 4) + q);
+		row[4 * q + 0] = x.x;
+		row[4 * q + 1] = x.y;
+		row[4 * q + 2] = x.z;
+		row[4 * q + 3] = x.w;
+	}
+}
+
+__device__ __forceinline__ int32_t quad_get(const int4 &q, int i) {
+	return i == 0 ? q.x : i == 1 ? q.y : i == 2 ? q.z : q.w;
+}
+
+// One block of NR rows u0 .. u0+NR-1 of one tile.
+//   prev[v]  in: V[u0-1, v]  out: V[u0+NR-1, v]
+//   sim      in: S rows of this block; out: S rows of the NEXT block of the warp's token stream
+//            (each row is re-loaded as soon as it has been consumed, ids from idq_next)
+template<int TP, int LOC, bool BORD, int NR>
+__device__ __forceinline__ void wsb_block(
+	const WsbArgs &a, float4 *__restrict__ hist, const int u0, const int t,
+	float (&prev)[TP], float &best, float &last_col,
+	float (&sim)[VX_WSB_U][TP], const int4 &idq_next) {
+
+	constexpr int Q = TP / 4;
+	constexpr int U = VX_WSB_U;
+	const float4 *__restrict__ s4 = reinterpret_cast<const float4*>(a.s);
 
 	// accumulators: vertical candidates from the border row k = -1 (or the Local zero)
 	float acc[NR][TP];
@@ -118,40 +144,30 @@ __device__ __forceinline__ void wsb_block(
 	#pragma unroll
 	for (int i = 0; i < NR; i++) {
 		const int u = u0 + i;
-		// vertical candidates from the rows of this block
-		#pragma unroll
-		for (int v = 0; v < TP; v++) {
-			float x = acc[i][v];
-			int j = 0;
-			#pragma unroll
-			for (; j + 1 < i; j += 2) {
-				x = max3(x, acc[j][v] - a.ws[i - j], acc[j + 1][v] - a.ws[i - j - 1]);
-			}
-			if (j < i) {
-				x = fmaxf(x, acc[j][v] - a.ws[i - j]);
-			}
-			acc[i][v] = x;
-		}
 		// V[u, -1] and V[u-1, -1]
 		const float left = BORD ? (LOC == VX_GLOBAL ? -a.ws[u + 1] : 0.0f) : 0.0f;
 		float diag = BORD ? (LOC == VX_GLOBAL ? (u == 0 ? -a.wt[0] : -a.ws[u]) : 0.0f) : 0.0f;
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
-			float x = fmaxf(acc[i][v], diag + sim[i][v]);
+			Fold f(acc[i][v]);
+			#pragma unroll
+			for (int j = 0; j < i; j++) {
+				f.push(acc[j][v] - a.ws[i - j]);          // rows of this block
+			}
+			f.push(diag + sim[i][v]);
 			diag = i == 0 ? prev[v] : acc[i - 1][v];
-			int k = 0;
 			if (BORD) {
-				x = fmaxf(x, left - a.wt[v + 1]);
+				f.push(left - a.wt[v + 1]);
 			}
 			#pragma unroll
-			for (; k + 1 < v; k += 2) {
-				x = max3(x, acc[i][k] - a.wt[v - k], acc[i][k + 1] - a.wt[v - k - 1]);
+			for (int k = 0; k < v; k++) {
+				f.push(acc[i][k] - a.wt[v - k]);          // cells to the left
 			}
-			if (k < v) {
-				x = fmaxf(x, acc[i][k] - a.wt[v - k]);
-			}
-			acc[i][v] = x;
+			acc[i][v] = f.done();
 		}
+		// this row of S has been consumed: fetch the same row of the next block
+		load_sim_row<TP>(s4, quad_get(idq_next, i), sim[i]);
+
 		if (LOC == VX_LOCAL) {
 			constexpr int NF = TP - 3;   // columns [0, NF) always belong to the query (TP - 4 < t <= TP)
 			constexpr int NP = NF / 2 * 2;
@@ -166,16 +182,21 @@ __device__ __forceinline__ void wsb_block(
 				}
 			}
 		} else {
+			// V[u, t-1]; written as a masked maximum so that the register array is never indexed dynamically
+			float lc = -CUDART_INF_F;
 			#pragma unroll
 			for (int v = TP - 4; v < TP; v++) {
-				if (v == t - 1) {
-					last_col = acc[i][v];
-				}
+				lc = fmaxf(lc, v == t - 1 ? acc[i][v] : -CUDART_INF_F);
 			}
+			last_col = lc;
 			if (LOC == VX_SEMIGLOBAL) {
 				best = fmaxf(best, last_col);
 			}
 		}
+	}
+	#pragma unroll
+	for (int i = NR; i < U; i++) {
+		load_sim_row<TP>(s4, quad_get(idq_next, i), sim[i]);
 	}
 
 	// publish the rows
@@ -194,7 +215,7 @@ __device__ __forceinline__ void wsb_block(
 }
 
 template<int TP, int LOC, bool BORD>
-__global__ void __launch_bounds__(512, 1) wsb_score_kernel(const __grid_constant__ WsbArgs a) {
+__global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant__ WsbArgs a) {
 	extern __shared__ float4 wsb_smem[];
 	constexpr int Q = TP / 4;
 	constexpr int U = VX_WSB_U;
@@ -202,66 +223,93 @@ __global__ void __launch_bounds__(512, 1) wsb_score_kernel(const __grid_constant
 	const int warp = threadIdx.x >> 5;
 	float4 *hist = wsb_smem + (size_t)warp * a.cap * Q * 32 + lane;
 	const int t = a.t;
+	const float4 *__restrict__ s4 = reinterpret_cast<const float4*>(a.s);
 
 	for (;;) {
+		// reserve a chunk of consecutive tiles; their token quads form one contiguous stream
 		unsigned int got = 0;
 		if (lane == 0) {
 			got = atomicAdd(a.counter, 1u);
 		}
 		got = __shfl_sync(0xffffffffu, got, 0);
-		const int64_t tile = a.tile_begin + got;
+		int64_t tile = a.tile_begin + (int64_t)got * a.chunk;
 		if (tile >= a.tile_end) {
 			break;
 		}
-		const VxTile tl = a.tiles[tile];
-		const int32_t *tok = a.tok + (size_t)tl.base32 * 32 + lane;
-		const int len = tl.len;
+		const int64_t tile_stop = tile + a.chunk < a.tile_end ? tile + a.chunk : a.tile_end;
+		VxTile tl = a.tiles[tile];
+		const int4 *__restrict__ quads = reinterpret_cast<const int4*>(a.tok) + (size_t)tl.base128 * 32 + lane;
 
-		float prev[TP];
-		#pragma unroll
-		for (int v = 0; v < TP; v++) {
-			prev[v] = BORD && LOC == VX_GLOBAL ? -a.wt[v + 1] : 0.0f;   // V[-1, v]
+		// software pipeline over the stream: ids two blocks ahead, S rows one block ahead
+		float sim[U][TP];
+		int4 idq_next;
+		{
+			const int4 idq = __ldg(quads);
+			idq_next = __ldg(quads + 32);
+			#pragma unroll
+			for (int i = 0; i < U; i++) {
+				load_sim_row<TP>(s4, quad_get(idq, i), sim[i]);
+			}
 		}
-		float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
-		float last_col = 0.0f;
+		quads += 64;
 
-		int u0 = 0;
-		#pragma unroll 1
-		for (; u0 + U <= len; u0 += U) {
-			wsb_block<TP, LOC, BORD, U>(a, tok, hist, u0, t, prev, best, last_col);
-		}
-		switch (len - u0) {
-			case 1:
-				wsb_block<TP, LOC, BORD, 1>(a, tok, hist, u0, t, prev, best, last_col);
-				break;
-			case 2:
-				wsb_block<TP, LOC, BORD, 2>(a, tok, hist, u0, t, prev, best, last_col);
-				break;
-			case 3:
-				wsb_block<TP, LOC, BORD, 3>(a, tok, hist, u0, t, prev, best, last_col);
-				break;
-			default:
-				break;
-		}
+		for (; tile < tile_stop; tile++) {
+			const VxTile tl_next = a.tiles[tile + 1];   // d_tiles has one padding entry
+			const int len = tl.len;
 
-		float raw;
-		if (LOC == VX_LOCAL) {
-			raw = best;
-		} else if (LOC == VX_GLOBAL) {
-			raw = last_col;
-		} else {
+			float prev[TP];
 			#pragma unroll
 			for (int v = 0; v < TP; v++) {
-				if (v < t) {
-					best = fmaxf(best, prev[v]);
-				}
+				prev[v] = BORD && LOC == VX_GLOBAL ? -a.wt[v + 1] : 0.0f;   // V[-1, v]
 			}
-			raw = best;
+			float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+			float last_col = 0.0f;
+
+			int u0 = 0;
+			#pragma unroll 1
+			for (; u0 + U <= len; u0 += U) {
+				const int4 idq_far = __ldg(quads);
+				quads += 32;
+				wsb_block<TP, LOC, BORD, U>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
+				idq_next = idq_far;
+			}
+			if (u0 < len) {
+				const int4 idq_far = __ldg(quads);
+				quads += 32;
+				switch (len - u0) {
+					case 1:
+						wsb_block<TP, LOC, BORD, 1>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
+						break;
+					case 2:
+						wsb_block<TP, LOC, BORD, 2>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
+						break;
+					default:
+						wsb_block<TP, LOC, BORD, 3>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
+						break;
+				}
+				idq_next = idq_far;
+			}
+
+			float raw;
+			if (LOC == VX_LOCAL) {
+				raw = best;
+			} else if (LOC == VX_GLOBAL) {
+				raw = last_col;
+			} else {
+				#pragma unroll
+				for (int v = 0; v < TP; v++) {
+					if (v < t) {
+						best = fmaxf(best, prev[v]);
+					}
+				}
+				raw = best;
+			}
+			const int64_t slot = tile * 32 + lane;
+			const float boost = a.boost ? a.boost[slot] : 1.0f;
+			a.score[slot] = lane < tl.n_valid ? (raw / a.total) * boost : -CUDART_INF_F;
+			tl = tl_next;
+			__syncwarp();
 		}
-		const int64_t slot = tile * 32 + lane;
-		const float boost = a.boost ? a.boost[slot] : 1.0f;
-		a.score[slot] = lane < tl.n_valid ? (raw / a.total) * boost : -CUDART_INF_F;
-		__syncwarp();
 	}
 }
 
@@ -274,14 +322,20 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms) {
 	const size_t per_warp = (size_t)cap * TP * 32 * sizeof(float);
 	const size_t smem_max = 227 * 1024;
 	int warps = (int)(smem_max / per_warp);
-	if (warps > 16) {
-		warps = 16;
+	if (warps > 8) {
+		warps = 8;
 	}
 	if (warps < 1) {
 		return -1;
 	}
 	const int64_t n_tiles = a.tile_end - a.tile_begin;
-	const int64_t want_blocks = (n_tiles + warps - 1) / warps;
+	// tiles per reservation: large enough to amortise the pipeline prologue, small enough that the
+	// last chunks balance (>= 32 chunks per warp when the class is big)
+	int64_t chunk = n_tiles / ((int64_t)sms * warps * 32);
+	chunk = chunk < 1 ? 1 : chunk > 8 ? 8 : chunk;
+	a.chunk = (int32_t)chunk;
+	const int64_t n_chunks = (n_tiles + chunk - 1) / chunk;
+	const int64_t want_blocks = (n_chunks + warps - 1) / warps;
 	const int blocks = (int)(want_blocks < sms ? want_blocks : sms);
 	const size_t smem = per_warp * warps;
 	a.cap = cap;
