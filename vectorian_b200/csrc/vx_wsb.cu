@@ -16,8 +16,12 @@
 //   * rows are processed in blocks of U: the U x T accumulators of the block live in registers; a
 //     finished row is read back from shared memory once per BLOCK (not once per row), so every
 //     LDS.128 feeds 4*U candidates;
-//   * finished rows (the column history the vertical gap scan needs) are kept in shared memory as
-//     [u][v/4][lane] float4 -- conflict-free LDS.128/STS.128, L*T*128 bytes per warp;
+//   * finished rows (the column history the vertical gap scan needs) live in TENSOR MEMORY first:
+//     the kernel allocates the SM's 512 TMEM columns and uses them as a per-thread scratchpad
+//     (tcgen05.st / tcgen05.ld .32x32b: thread = TMEM lane, row u = T consecutive columns), 20 rows
+//     per window at 8 warps per SM; rows beyond that go to shared memory as [u][v/4][lane] float4
+//     (conflict-free LDS.128/STS.128).  TMEM + smem together hold 8 warps x 32 windows x 36 rows, which
+//     is what lets two warps share each scheduler (one warp alone issues every other cycle at best);
 //   * gap tables come from the kernel parameter bank (constant operands / uniform loads), the
 //     similarity rows S[id, 0..T) from L2/L1 with float4 loads issued one block ahead of their use;
 //   * persistent warps pull tiles from an atomic counter; one launch per length class so that the
@@ -41,7 +45,9 @@ struct WsbArgs {
 	int64_t tile_begin, tile_end;
 	int32_t chunk;           // tiles per reservation
 	int32_t t;
-	int32_t cap;             // rows of history per warp in shared memory
+	int32_t cap;             // rows of history per warp in shared memory (rows rt .. rt+cap-1)
+	int32_t rt;              // rows [0, rt) of the history live in tensor memory (multiple of U)
+	int32_t tmem_cols;       // TMEM columns owned by one warp (256: two warps per lane quarter, 512: one)
 	float total;
 	float ws[VX_WSB_MAX_LEN + 4];   // w_s[0..64], gap cost along the sentence
 	float wt[VX_MAX_T_FAST + 4];    // w_t[0..16], gap cost along the query
@@ -51,6 +57,31 @@ __device__ __forceinline__ float max3(float a, float b, float c) {
 	float r;
 	asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
 	return r;
+}
+
+// ---- tensor memory as a per-thread scratchpad (SASS: LDTM / STTM) ----
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float *r) {
+	uint32_t a, b, c, d;
+	asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+		: "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(taddr));
+	r[0] = __uint_as_float(a);
+	r[1] = __uint_as_float(b);
+	r[2] = __uint_as_float(c);
+	r[3] = __uint_as_float(d);
+}
+
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, const float *r) {
+	asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+		:: "r"(taddr), "r"(__float_as_uint(r[0])), "r"(__float_as_uint(r[1])),
+		"r"(__float_as_uint(r[2])), "r"(__float_as_uint(r[3])) : "memory");
+}
+
+__device__ __forceinline__ void tmem_wait_ld() {
+	asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tmem_wait_st() {
+	asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
 // Running maximum that folds two candidates per FMNMX3.  After full unrolling `has` is a
@@ -95,9 +126,9 @@ __device__ __forceinline__ int32_t quad_get(const int4 &q, int i) {
 //            (each row is re-loaded as soon as it has been consumed, ids from idq_next)
 template<int TP, int LOC, bool BORD, int NR>
 __device__ __forceinline__ void wsb_block(
-	const WsbArgs &a, float4 *__restrict__ hist, const int u0, const int t,
+	const WsbArgs &a, const uint32_t tmem, float4 *__restrict__ hist, const int u0, const int t,
 	float (&prev)[TP], float &best, float &last_col,
-	float (&sim)[VX_WSB_U][TP], const int4 &idq_next) {
+	float (&sim)[VX_WSB_U][TP], int4 &idq_next, const int4 *__restrict__ &quads) {
 
 	constexpr int Q = TP / 4;
 	constexpr int U = VX_WSB_U;
@@ -118,14 +149,36 @@ __device__ __forceinline__ void wsb_block(
 		}
 	}
 
-	// vertical candidates from the finished rows k = 0 .. u0-1 (u0 is a multiple of U, U even)
+	// vertical candidates from the finished rows k = 0 .. u0-1 (u0 and rt are multiples of U, U even):
+	// rows [0, rt) from tensor memory, rows [rt, u0) from shared memory
+	const int rt = a.rt;
+	const int k_tmem = u0 < rt ? u0 : rt;
 	#pragma unroll 1
-	for (int k = 0; k < u0; k += 2) {
+	for (int k = 0; k < k_tmem; k += 2) {
 		float h0[TP], h1[TP];
 		#pragma unroll
 		for (int q = 0; q < Q; q++) {
-			const float4 x = hist[((size_t)k * Q + q) * 32];
-			const float4 y = hist[((size_t)(k + 1) * Q + q) * 32];
+			tmem_ld4(tmem + (uint32_t)(k * TP + 4 * q), h0 + 4 * q);
+			tmem_ld4(tmem + (uint32_t)((k + 1) * TP + 4 * q), h1 + 4 * q);
+		}
+		tmem_wait_ld();
+		#pragma unroll
+		for (int i = 0; i < NR; i++) {
+			const float w0 = a.ws[u0 + i - k];
+			const float w1 = a.ws[u0 + i - k - 1];
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				acc[i][v] = max3(acc[i][v], h0[v] - w0, h1[v] - w1);
+			}
+		}
+	}
+	#pragma unroll 1
+	for (int k = rt; k < u0; k += 2) {
+		float h0[TP], h1[TP];
+		#pragma unroll
+		for (int q = 0; q < Q; q++) {
+			const float4 x = hist[((size_t)(k - rt) * Q + q) * 32];
+			const float4 y = hist[((size_t)(k - rt + 1) * Q + q) * 32];
 			h0[4 * q + 0] = x.x; h0[4 * q + 1] = x.y; h0[4 * q + 2] = x.z; h0[4 * q + 3] = x.w;
 			h1[4 * q + 0] = y.x; h1[4 * q + 1] = y.y; h1[4 * q + 2] = y.z; h1[4 * q + 3] = y.w;
 		}
@@ -139,6 +192,12 @@ __device__ __forceinline__ void wsb_block(
 			}
 		}
 	}
+
+	// token ids: idq_next (ids of the next block, loaded one block ago) is consumed by the row-wise
+	// S refills below; the ids of the block after that are requested now
+	const int4 idq_use = idq_next;
+	idq_next = __ldg(quads);
+	quads += 32;
 
 	// the rows of the block, in order
 	#pragma unroll
@@ -166,7 +225,7 @@ __device__ __forceinline__ void wsb_block(
 			acc[i][v] = f.done();
 		}
 		// this row of S has been consumed: fetch the same row of the next block
-		load_sim_row<TP>(s4, quad_get(idq_next, i), sim[i]);
+		load_sim_row<TP>(s4, quad_get(idq_use, i), sim[i]);
 
 		if (LOC == VX_LOCAL) {
 			constexpr int NF = TP - 3;   // columns [0, NF) always belong to the query (TP - 4 < t <= TP)
@@ -196,16 +255,27 @@ __device__ __forceinline__ void wsb_block(
 	}
 	#pragma unroll
 	for (int i = NR; i < U; i++) {
-		load_sim_row<TP>(s4, quad_get(idq_next, i), sim[i]);
+		load_sim_row<TP>(s4, quad_get(idq_use, i), sim[i]);
 	}
 
 	// publish the rows
-	#pragma unroll
-	for (int i = 0; i < NR; i++) {
+	if (u0 < rt) {
 		#pragma unroll
-		for (int q = 0; q < Q; q++) {
-			hist[((size_t)(u0 + i) * Q + q) * 32] =
-				make_float4(acc[i][4 * q + 0], acc[i][4 * q + 1], acc[i][4 * q + 2], acc[i][4 * q + 3]);
+		for (int i = 0; i < NR; i++) {
+			#pragma unroll
+			for (int q = 0; q < Q; q++) {
+				tmem_st4(tmem + (uint32_t)((u0 + i) * TP + 4 * q), &acc[i][4 * q]);
+			}
+		}
+		tmem_wait_st();
+	} else {
+		#pragma unroll
+		for (int i = 0; i < NR; i++) {
+			#pragma unroll
+			for (int q = 0; q < Q; q++) {
+				hist[((size_t)(u0 - rt + i) * Q + q) * 32] =
+					make_float4(acc[i][4 * q + 0], acc[i][4 * q + 1], acc[i][4 * q + 2], acc[i][4 * q + 3]);
+			}
 		}
 	}
 	#pragma unroll
@@ -217,11 +287,26 @@ __device__ __forceinline__ void wsb_block(
 template<int TP, int LOC, bool BORD>
 __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant__ WsbArgs a) {
 	extern __shared__ float4 wsb_smem[];
+	__shared__ uint32_t tmem_base_sh;
 	constexpr int Q = TP / 4;
 	constexpr int U = VX_WSB_U;
 	const int lane = threadIdx.x & 31;
 	const int warp = threadIdx.x >> 5;
 	float4 *hist = wsb_smem + (size_t)warp * a.cap * Q * 32 + lane;
+
+	// all 512 TMEM columns of the SM (one CTA per SM); warp w owns lanes 32*(w%4).. and a column range
+	if (warp == 0) {
+		const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&tmem_base_sh);
+		const uint32_t ncols = 512;
+		asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(dst), "r"(ncols) : "memory");
+		asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+	}
+	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+	__syncthreads();
+	asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+	const uint32_t tmem_base = tmem_base_sh;
+	const uint32_t tmem = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(a.tmem_cols * (warp >> 2));
+
 	const int t = a.t;
 	const float4 *__restrict__ s4 = reinterpret_cast<const float4*>(a.s);
 
@@ -268,26 +353,20 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 			int u0 = 0;
 			#pragma unroll 1
 			for (; u0 + U <= len; u0 += U) {
-				const int4 idq_far = __ldg(quads);
-				quads += 32;
-				wsb_block<TP, LOC, BORD, U>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
-				idq_next = idq_far;
+				wsb_block<TP, LOC, BORD, U>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 			}
 			if (u0 < len) {
-				const int4 idq_far = __ldg(quads);
-				quads += 32;
 				switch (len - u0) {
 					case 1:
-						wsb_block<TP, LOC, BORD, 1>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
+						wsb_block<TP, LOC, BORD, 1>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 					case 2:
-						wsb_block<TP, LOC, BORD, 2>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
+						wsb_block<TP, LOC, BORD, 2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 					default:
-						wsb_block<TP, LOC, BORD, 3>(a, hist, u0, t, prev, best, last_col, sim, idq_next);
+						wsb_block<TP, LOC, BORD, 3>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 				}
-				idq_next = idq_far;
 			}
 
 			float raw;
@@ -311,6 +390,13 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 			__syncwarp();
 		}
 	}
+
+	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+	__syncthreads();
+	if (warp == 0) {
+		const uint32_t ncols = 512;
+		asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(ncols) : "memory");
+	}
 }
 
 // ---------------------------------------------------------------------------
@@ -319,15 +405,27 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 
 template<int TP, int LOC, bool BORD>
 static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms) {
-	const size_t per_warp = (size_t)cap * TP * 32 * sizeof(float);
-	const size_t smem_max = 227 * 1024;
-	int warps = (int)(smem_max / per_warp);
-	if (warps > 8) {
-		warps = 8;
+	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
+	// SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a TMEM lane quarter
+	// and gets 256 columns.  Long classes fall back to <= 4 warps with 512 columns each.
+	const size_t row_bytes = (size_t)TP * 32 * sizeof(float);
+	const size_t smem_max = 227 * 1024 - 1024;
+	int warps = 0, rt = 0, tmem_cols = 256, rows_smem = 0;
+	for (int w = 8; w >= 1; w--) {
+		tmem_cols = w > 4 ? 256 : 512;
+		rt = tmem_cols / TP / VX_WSB_U * VX_WSB_U;
+		rows_smem = cap > rt ? cap - rt : 0;
+		if ((size_t)rows_smem * row_bytes * w <= smem_max) {
+			warps = w;
+			break;
+		}
 	}
 	if (warps < 1) {
 		return -1;
 	}
+	a.rt = rt;
+	a.tmem_cols = tmem_cols;
+	a.cap = rows_smem;
 	const int64_t n_tiles = a.tile_end - a.tile_begin;
 	// tiles per reservation: large enough to amortise the pipeline prologue, small enough that the
 	// last chunks balance (>= 32 chunks per warp when the class is big)
@@ -337,11 +435,10 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms) {
 	const int64_t n_chunks = (n_tiles + chunk - 1) / chunk;
 	const int64_t want_blocks = (n_chunks + warps - 1) / warps;
 	const int blocks = (int)(want_blocks < sms ? want_blocks : sms);
-	const size_t smem = per_warp * warps;
-	a.cap = cap;
+	const size_t smem = (size_t)rows_smem * row_bytes * warps;
 	static bool attr_set = false;
 	if (!attr_set) {
-		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_max);
+		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
 		attr_set = true;
 	}
 	wsb_score_kernel<TP, LOC, BORD><<<blocks, warps * 32, smem, c->stream>>>(a);
