@@ -152,6 +152,7 @@ def main():
 	ap_.add_argument("--sentences", type=int, default=50_000_000)
 	ap_.add_argument("--cpu-sample", type=int, default=200_000)
 	ap_.add_argument("--no-cpu-baseline", action="store_true")
+	ap_.add_argument("--no-clocks", action="store_true")
 	args = ap_.parse_args()
 	args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -213,7 +214,7 @@ def main():
 	for i in range(args.warmup):
 		step(i)
 
-	sampler = ClockSampler(local_rank) if rank == 0 else None
+	sampler = ClockSampler(local_rank) if rank == 0 and not args.no_clocks else None
 	barrier()
 	t0 = time.perf_counter()
 	dev_ms_total, dp_ms_total, launches_total = 0.0, 0.0, 0
