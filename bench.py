@@ -258,6 +258,16 @@ def main():
 		issue_peak = sms * 128 * sm_max * 1e6
 		issue_ach = lane_ops / (dp_ms * 1e-3)
 
+		traffic, traffic_note = None, None
+		try:
+			tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+			ratio = (tr["dram_bytes_read"] + tr["dram_bytes_write"]) / tr["algorithmic_bytes"]
+			traffic = ratio * alg_bytes
+			traffic_note = "ncu dram bytes / algorithmic bytes = %.3f on the %d-sentence capture (%s), scaled to this launch" % (
+				ratio, tr["workload_sentences"], tr["source"])
+		except Exception:
+			pass
+
 		line = {
 			"metric": "sentences/sec (WSB alignment, 12-token query, top-100)",
 			"value": value, "unit": "sentences/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -270,8 +280,8 @@ def main():
 				"h2d_bytes_per_step": int(T_QUERY * 4 + T_QUERY * DIM * 4 + (dc.max_len + 1 + T_QUERY + 1) * 4),
 				"d2h_bytes_per_step": int(TOPK * (16 + 6 * T_QUERY) + 16), "ms_per_step": wall_s * 1e3 / args.steps},
 			"gpu_launches": int(launches_all),
-			"roofline": {"bound": "hbm", "kernel": "WSB score kernel (vx_align.cu)", "achieved": achieved, "peak": hbm_peak,
-				"unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+			"roofline": {"bound": "hbm", "kernel": "wsb_score_kernel (vx_wsb.cu), all length-class launches of one query", "achieved": achieved, "peak": hbm_peak,
+				"unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "traffic_note": traffic_note, "peak_source": peak_src, "binding": "issue_roofline",
 				"algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": dp_ms,
 				"note": "the static-embedding DP is FP32-issue-bound, not HBM-bound (SURVEY.md 8d): see issue_roofline"},
 			"issue_roofline": {"bound": "fp32 issue (FADD + FMNMX per candidate)", "achieved": issue_ach / 1e12,
