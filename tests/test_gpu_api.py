@@ -1,0 +1,186 @@
+"""The drop-in Python API (Session / Partition / Index.find / match objects) on the GPU against the
+oracle driven with the same token tables, the same similarity matrix and the same options."""
+
+import numpy as np
+import pytest
+
+from vectorian_b200 import _cabi, gaps
+from vectorian_b200.alignment import GlobalAlignment, SemiGlobalAlignment, LocalAlignment
+from vectorian_b200.corpus import Corpus, Document, whitespace_nlp
+from vectorian_b200.embedding import KeyedVectors, ContextualEmbedding
+from vectorian_b200.session import Session
+from vectorian_b200.sim.span import OptimizedSpanSim
+from vectorian_b200.sim.token import EmbeddingTokenSim
+from vectorian_b200.sim.vector import CosineSim, PNormSim
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+POS = ["NOUN", "VERB", "ADJ", "ADP", "DET"]
+TAG = ["NN", "VB", "JJ", "IN", "DT"]
+
+
+def make_session(n_docs=7, sent_per_doc=60, vocab=400, dim=16, seed=3, contextual_dim=0):
+	rng = np.random.default_rng(seed)
+	words = [f"w{i}" for i in range(vocab)]
+	cdf = np.cumsum(1.0 / np.arange(1, vocab + 1))
+	cdf /= cdf[-1]
+	docs = []
+	for d in range(n_docs):
+		sents, pos, tag = [], [], []
+		for _ in range(sent_per_doc):
+			n = int(np.clip(np.rint(rng.normal(12, 5)), 1, 40))
+			ids = np.minimum(np.searchsorted(cdf, rng.random(n)), vocab - 1)
+			sents.append([words[i] for i in ids])
+			k = rng.integers(0, len(POS), size=n)
+			pos.append([POS[i] for i in k])
+			tag.append([TAG[i] for i in k])
+		ctx = {}
+		if contextual_dim:
+			n_tok = sum(len(s) for s in sents)
+			ctx = {"ctx": rng.standard_normal((n_tok, contextual_dim)).astype(np.float32)}
+		docs.append(Document.from_sentences(sents, pos=pos, tag=tag, contextual_embeddings=ctx))
+	centroids = rng.standard_normal((30, dim)).astype(np.float32)
+	matrix = centroids[rng.integers(0, 30, size=vocab)] + 0.3 * rng.standard_normal((vocab, dim)).astype(np.float32)
+	emb = KeyedVectors("toy", (words, matrix))
+	embeddings = [emb]
+	if contextual_dim:
+		crng = np.random.default_rng(seed + 100)
+		table = {}
+		def encode(tokens):
+			return np.array([table.setdefault(t, crng.standard_normal(contextual_dim).astype(np.float32)) for t in tokens])
+		embeddings.append(ContextualEmbedding("ctx", encode, contextual_dim))
+	return Session(Corpus(docs), embeddings), embeddings
+
+
+def oracle_corpus(oracle, session, partition, boost=None):
+	docs = session.documents
+	tok = np.concatenate([d.token_id for d in docs])
+	pos = np.concatenate([d.token_pos for d in docs])
+	starts, ends, span_off, tok_off = [], [], [0], [0]
+	for d in docs:
+		s, e = d.span_table(partition.level)
+		starts.append(s)
+		ends.append(e)
+		span_off.append(span_off[-1] + len(s))
+		tok_off.append(tok_off[-1] + d.n_tokens)
+	return oracle.OracleCorpus(tok, np.array(tok_off), np.concatenate(starts), np.concatenate(ends), np.array(span_off),
+		partition.window_size, partition.window_step, token_pos=pos, boost=boost)
+
+
+def check_find(oracle, session, emb, index, text, n, min_score, s=None, qkw=None, contextual=False):
+	from vectorian_b200 import engine
+	result = index.find(text, n=n, min_score=min_score)
+	query = index.make_query(text, n=n, min_score=min_score)
+	p = query.prepare(whitespace_nlp)
+	t = p.n_tokens
+	partition = index.partition
+	oc = oracle_corpus(oracle, session, partition)
+	if s is None:
+		de, vv = session.device_embedding(emb)
+		q_vec = session.to_encoder(emb).encode_tokens(p.token_str).unmodified
+		q_id = np.where(p.token_id < session.vocab.size, p.token_id, -1).astype(np.int32)
+		s = engine.DeviceSim.static(de, q_id, q_vec).download()     # the same bits vx_search consumed
+	a = query.options["metric"]["alignment"]["options"]
+	ap, keep = helpers.align_params(a["locality"], a["gap_cost"], session.device_corpus(partition).max_len, t)
+	qp, keep2 = _cabi.make_query_params(max_matches=n, min_score=min_score, **(qkw or {}))
+	o_all = oc.score_all(s, ap, qp, n_threads=2, contextual=contextual)
+	ref = oc.search(s, ap, qp, n_threads=2, contextual=contextual)
+	wd, wsl, _, _ = oc.windows()
+	hits = np.zeros((len(result),), dtype=_cabi.HIT_DTYPE)
+	for i, m in enumerate(result):
+		hits[i] = (m.score, m.score_max, m.prepared_doc.id, m.slice_id)
+	target = np.array([m.flow["target"] for m in result], dtype=np.int16).reshape(len(result), t)
+	dist = np.array([m.flow["dist"] for m in result], dtype=np.float32).reshape(len(result), t)
+	helpers.assert_hits_match((hits, target, dist), ref, o_all, wd, wsl)
+	return result, p
+
+
+QUERY = "w3 w17 w5 w120 w1 w9 unknownword w2"
+
+
+@pytest.mark.parametrize("alignment", [
+	LocalAlignment(gap=gaps.smooth_gap_cost(5)), GlobalAlignment(gap=gaps.LinearGapCost(0.2)),
+	SemiGlobalAlignment(gap=gaps.AffineGapCost(u=0.3, v=0.1)), LocalAlignment()])
+def test_find_matches_oracle(oracle, alignment):
+	session, (emb,) = make_session()
+	metric = OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), alignment)
+	index = session.partition("sentence").index(metric, nlp=whitespace_nlp)
+	result, p = check_find(oracle, session, emb, index, QUERY, n=25, min_score=0.05)
+	assert len(result) > 0 and result.duration > 0
+	m = result[0]
+	assert m.metric == "toy-cosine" and m.level == "word"
+	assert m.flow["type"] == "injective" and m.flow["target"].dtype == np.int16
+	# match objects: regions / omitted / to_json are consistent with the flow
+	matched = [j for j, u in enumerate(m.flow["target"]) if u >= 0]
+	regions = m.regions(5)
+	assert sum(1 for r in regions if r.match) == len(matched)
+	assert len(m.omitted) == p.n_tokens - len(matched)
+	span = m.doc_span
+	for r in regions:
+		if r.match:
+			e = r.match.edges[0]
+			assert span[int(m.flow["target"][e.t.index])].text == r.s
+	js = m.to_json()
+	assert js["slice"] == m.slice_id and js["score"] == m.score and len(js["regions"]) == len(regions)
+
+
+def test_windows_and_token_level(oracle):
+	session, (emb,) = make_session(n_docs=3, sent_per_doc=40)
+	metric = OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), LocalAlignment(gap=gaps.LinearGapCost(0.1)))
+	for partition in (session.partition("sentence", 3, 2), session.partition("token", 9, 4)):
+		index = partition.index(metric, nlp=whitespace_nlp)
+		check_find(oracle, session, emb, index, QUERY, n=10, min_score=0.0)
+
+
+def test_tag_weighted_and_host_vector_sim(oracle):
+	session, (emb,) = make_session()
+	ts = EmbeddingTokenSim(emb, CosineSim())
+	tag_weights = {"NN": 2.0, "VB": 0.5}
+	metric = OptimizedSpanSim(ts, LocalAlignment(gap=gaps.LinearGapCost(0.2)), tag_weights=tag_weights,
+		pos_mismatch_penalty=0.3, similarity_threshold=0.2)
+	index = session.partition("sentence").index(metric, nlp=whitespace_nlp)
+	p = index.make_query(QUERY).prepare(whitespace_nlp)
+	qkw = dict(t_weights=np.array([tag_weights.get(x, 1.0) for x in p.token_tag], dtype=np.float32),
+		t_pos=p.token_pos, pos_mismatch_penalty=0.3, similarity_threshold=0.2)
+	check_find(oracle, session, emb, index, QUERY, n=15, min_score=0.01, qkw=qkw)
+
+	# a VectorSim the device does not evaluate itself: computed on the host, uploaded
+	pn = PNormSim(p=2, scale=0.25)
+	metric = OptimizedSpanSim(EmbeddingTokenSim(emb, pn), LocalAlignment(gap=gaps.smooth_gap_cost(3)))
+	index = session.partition("sentence").index(metric, nlp=whitespace_nlp)
+	de, vv = session.device_embedding(emb)
+	qv = session.to_encoder(emb).encode_tokens(p.token_str)
+	s = np.zeros((session.vocab.size, p.n_tokens), dtype=np.float32)
+	pn(vv, qv, s)
+	for j, i in enumerate(p.token_id):
+		if i < session.vocab.size:
+			s[i, j] = 1.0
+	np.clip(s, 0, 1, out=s)
+	check_find(oracle, session, emb, index, QUERY, n=15, min_score=0.01, s=s)
+
+
+def test_contextual_embedding(oracle):
+	session, (emb, ctx) = make_session(n_docs=3, sent_per_doc=30, contextual_dim=24)
+	metric = OptimizedSpanSim(EmbeddingTokenSim(ctx, CosineSim()), GlobalAlignment(gap=gaps.LinearGapCost(0.1)))
+	index = session.partition("sentence").index(metric, nlp=whitespace_nlp)
+	text = "w3 w17 w5 w120 w1"
+	p = index.make_query(text).prepare(whitespace_nlp)
+	x = np.concatenate([d.doc.contextual_embeddings["ctx"] for d in session.documents])
+	q_vec = ctx.create_encoder(session).encode([[text[t['start']:t['end']] for t in p.tokens]])[0]
+	s = oracle.sim_contextual(x, q_vec)
+	result = index.find(text, n=10, min_score=-10.0)
+	oc = oracle_corpus(oracle, session, index.partition)
+	ap, keep = helpers.align_params(_cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), session.device_corpus(index.partition).max_len, p.n_tokens)
+	qp, _ = _cabi.make_query_params(max_matches=10, min_score=-10.0)
+	ref = oc.search(s, ap, qp, n_threads=2, contextual=True)
+	got = np.array([m.score for m in result], dtype=np.float32)
+	np.testing.assert_allclose(got, ref[0]["score"], rtol=1e-5, atol=1e-6)
+
+
+def test_empty_query_and_errors():
+	session, (emb,) = make_session(n_docs=2, sent_per_doc=5)
+	index = session.partition("sentence").index(session.default_metric(), nlp=whitespace_nlp)
+	assert len(index.find("   ")) == 0                       # vectorian/index.py:533-534
+	with pytest.raises(ValueError):
+		index.find("w1 w2", options={"bogus_option": 1})     # cpp/query.cpp:59-68

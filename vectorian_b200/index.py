@@ -1,0 +1,480 @@
+"""Query / Match / Index / BruteForceIndex with the reference's signatures (vectorian/index.py).
+
+``BruteForceIndex._find`` is where the reference fans out ``core.Document.find`` over a thread pool
+(index.py:530-560); here it is one ``vx_sim_*`` + one ``vx_search`` on the device corpus of the
+partition and, with several ranks, one gather of the per-rank top-k.
+"""
+
+import collections
+import functools
+import logging
+import time
+
+import numpy as np
+
+from . import _cabi, engine, gaps
+from .corpus import whitespace_nlp, Span
+from .distributed import gather_topk
+from .embedding import Vectors
+
+
+class Query:
+	"""vectorian/index.py:26-54"""
+
+	def __init__(self, index, vocab, text, options):
+		self._index = index
+		self._vocab = vocab
+		self._text = text
+		self._options = options
+
+	@property
+	def index(self):
+		return self._index
+
+	@property
+	def text(self):
+		return self._text
+
+	@property
+	def options(self):
+		return self._options
+
+	def prepare(self, nlp):
+		return PreparedQuery(self, self._vocab, nlp)
+
+
+class _QueryDoc:
+	"""The query seen as a one-span document (what Token / Span objects need)."""
+
+	def __init__(self, text, tokens, strs):
+		self.text_str = text
+		self.token_idx = np.array([t['start'] for t in tokens], dtype=np.int32)
+		self.token_len = np.array([t['end'] - t['start'] for t in tokens], dtype=np.int32)
+		self.token_str = strs
+
+
+class PreparedQuery:
+	"""vectorian/index.py:56-169: tokenise, filter, normalise, map to vocabulary ids.
+
+	``nlp`` is any callable text -> list of token dicts with 'start', 'end', 'pos', 'tag' (the
+	``doc.to_json()["tokens"]`` of a spaCy pipeline); objects with ``to_json`` are accepted too."""
+
+	def __init__(self, query, vocab, nlp):
+		self._query = query
+		self._vocab = vocab
+		text = query.text
+		doc = (nlp or whitespace_nlp)(text)
+		tokens = doc.to_json()["tokens"] if hasattr(doc, "to_json") else list(doc)
+		for attr in ('pos', 'tag'):
+			f = query.options.get(f'{attr}_filter')
+			if f:
+				s = set(f)
+				tokens = [t for t in tokens if t.get(attr) not in s]
+		session = query.index.session
+		norm = session.normalization
+		kept, strs = [], []
+		for t in tokens:
+			s = norm.token_to_str(text[t['start']:t['end']])
+			if s:                                  # TokenTable.add drops empty tokens (corpus/document.py:63-100)
+				kept.append(t)
+				strs.append(s)
+		self._tokens = kept
+		self._token_str = strs
+		# ids: corpus vocabulary first, then per-query ids |V|, |V|+1, ... (IncrementalLexicon,
+		# vectorian/core/cpp/vocabulary.h:152-157)
+		extra = {}
+		ids = []
+		for s in strs:
+			i = vocab.tokens.get(s)
+			if i < 0:
+				i = extra.setdefault(s, vocab.size + len(extra))
+			ids.append(i)
+		self._token_id = np.array(ids, dtype=np.int32)
+		self._token_pos = np.array([vocab.pos.get(t.get('pos', 'X')) for t in kept], dtype=np.int8)
+		self._token_tag = [t.get('tag', 'X') for t in kept]
+		self._doc = _QueryDoc(text, kept, strs)
+
+	@property
+	def index(self):
+		return self._query.index
+
+	@property
+	def text_str(self):
+		return self._query.text
+
+	@property
+	def options(self):
+		return self._query.options
+
+	@property
+	def n_tokens(self):
+		return len(self._tokens)
+
+	@property
+	def token_str(self):
+		return self._token_str
+
+	@property
+	def token_id(self):
+		return self._token_id
+
+	@property
+	def token_pos(self):
+		return self._token_pos
+
+	@property
+	def token_tag(self):
+		return self._token_tag
+
+	@property
+	def tokens(self):
+		return self._tokens
+
+	@property
+	def span(self):
+		return Span(self._doc, 0, self.n_tokens)
+
+	def __getitem__(self, i):
+		return self.span[i]
+
+	def __len__(self):
+		return self.n_tokens
+
+
+Region = collections.namedtuple('Region', ['s', 'match', 'gap_penalty'])
+TokenMatch = collections.namedtuple('TokenMatch', ['pos_s', 'edges'])
+TokenMatchEdge = collections.namedtuple('TokenMatchEdge', ['t', 'flow', 'distance', 'metric'])
+TokenMatchT = collections.namedtuple('TokenMatchT', ['text', 'index', 'pos'])
+PartitionData = collections.namedtuple('PartitionData', ['level', 'window_size', 'window_step'])
+
+
+def _gap_cost_fn(resolved, side):
+	"""gap_cost_s / gap_cost_t of the solver in use (cpp/metric/alignment.h:296-304)."""
+	kind = resolved['gap_kind']
+	k = 0 if side == 's' else 1
+	if kind == _cabi.VX_GAP_LINEAR:
+		u = resolved['lin'][k]
+		return lambda n: float(np.float32(u) * np.float32(n))
+	if kind == _cabi.VX_GAP_AFFINE:
+		open0, ext = resolved['affine_s' if side == 's' else 'affine_t']
+		return lambda n: 0.0 if n == 0 else float(np.float32(ext) * np.float32(n) + np.float32(open0))
+	w = resolved['w_s' if side == 's' else 'w_t']
+	return lambda n: float(w[min(int(n), len(w) - 1)])
+
+
+class Match:
+	"""vectorian/index.py:192-292"""
+
+	@property
+	def partition(self):
+		return self.index.partition
+
+	@property
+	def doc_span(self):
+		return self.prepared_doc.span(self.query.index.partition, self.slice_id)
+
+	@property
+	def doc(self):
+		return self.prepared_doc.doc
+
+	@property
+	def slice(self):
+		return self.partition.slice_id_to_slice(self.slice_id)
+
+	@property
+	def flow(self):
+		return None
+
+	def to_json(self, context_size=10):
+		regions = []
+		partition = self.query.options["partition"]
+		span_info = self.prepared_doc.span_info(PartitionData(**partition), self.slice_id)
+		for region in self.regions(context_size):
+			if region.match:
+				edges = [{
+					't': {'text': e.t.text, 'index': e.t.index, 'pos': e.t.pos},
+					'flow': e.flow, 'distance': e.distance, 'metric': e.metric} for e in region.match.edges]
+				regions.append(dict(s=region.s, pos_s=region.match.pos_s, edges=edges))
+			else:
+				regions.append(dict(s=region.s, gap_penalty=region.gap_penalty))
+		return dict(
+			slice=self.slice_id, location=span_info, score=self.score, metric=self.metric,
+			regions=regions, omitted=self.omitted, level=self.level)
+
+
+class CoreMatch(Match):
+	"""A match produced by the device search; same getters as vectorian/index.py:295-379 over
+	Match / InjectiveFlow (vectorian/core/cpp/match/match.h:275-425, cpp/match/flow.cpp:190-216)."""
+
+	def __init__(self, index, query, hit, target, dist, metric_name, gap_fns):
+		self._index = index
+		self._session = index.session
+		self._query = query
+		self._score = float(hit["score"])
+		self._score_max = float(hit["score_max"])
+		self._doc_id = int(hit["doc"])
+		self._slice_id = int(hit["slice"])
+		self._target = np.array(target, dtype=np.int16)
+		self._dist = np.array(dist, dtype=np.float32)
+		self._metric = metric_name
+		self._gap_fns = gap_fns
+		self._level = "word"
+
+	@property
+	def index(self):
+		return self._index
+
+	@property
+	def query(self):
+		return self._query
+
+	@property
+	def prepared_doc(self):
+		return self._session.documents[self._doc_id]
+
+	@property
+	def slice_id(self):
+		return self._slice_id
+
+	@property
+	def score(self):
+		return self._score
+
+	@property
+	def score_max(self):
+		return self._score_max
+
+	@property
+	def metric(self):
+		return self._metric
+
+	@property
+	def level(self):
+		return self._level
+
+	@property
+	def flow(self):
+		"""InjectiveFlow::to_py (cpp/match/flow.cpp:190-216)."""
+		matched = self._target >= 0
+		return {
+			'type': 'injective',
+			'target': self._target,
+			'flow': matched.astype(np.float32),
+			'dist': self._dist,
+		}
+
+	@property
+	def omitted(self):
+		"""Query tokens without a partner (Flow::py_omitted, cpp/match/flow.cpp:169-188)."""
+		text = self._query.text_str
+		return [text[t['start']:t['end']] for t, u in zip(self._query.tokens, self._target) if u < 0]
+
+	def regions(self, context_size=10):
+		"""Matched / unmatched character regions of the window (Flow::py_regions, cpp/match/flow.cpp:8-167)."""
+		pdoc = self.prepared_doc
+		doc = pdoc.doc
+		s_text = doc.text_str
+		t_text = self._query.text_str
+		part = self._index.partition
+		span = pdoc.span(part, self._slice_id)
+		token_at, n_tok = span.start, doc.n_tokens
+		idx, ln = doc.token_idx, doc.token_len
+		edges = sorted((int(u), j) for j, u in enumerate(self._target) if u >= 0)
+		regions = []
+		if not edges:
+			s0 = int(idx[token_at])
+			s1 = int(idx[min(token_at + len(span), n_tok - 1)])
+			return [Region(s=s_text[s0:s1], match=None, gap_penalty=0.0)]
+		gap_s, gap_t = self._gap_fns
+		last_anchor = max(0, token_at + edges[0][0] - context_size)
+		last_matched = False
+		last_source = -1
+		for target, source in edges:
+			s_i = token_at + target
+			idx0 = int(idx[last_anchor])
+			if int(idx[s_i]) > idx0:
+				p = gap_s(s_i - last_anchor) if last_matched else 0.0
+				regions.append(Region(s=s_text[idx0:int(idx[s_i])], match=None, gap_penalty=p))
+			if last_source >= 0:
+				p = gap_t(source - last_source - 1)
+				if p > 0.0:
+					regions.append(Region(s="", match=None, gap_penalty=p))
+			last_source = source
+			t = self._query.tokens[source]
+			edge = TokenMatchEdge(
+				t=TokenMatchT(text=t_text[t['start']:t['end']], index=source, pos=t.get('pos', 'X')),
+				flow=1.0, distance=float(self._dist[source]), metric=self._metric)
+			regions.append(Region(
+				s=s_text[int(idx[s_i]):int(idx[s_i]) + int(ln[s_i])],
+				match=TokenMatch(pos_s=doc.token_pos[s_i], edges=[edge]), gap_penalty=0.0))
+			last_anchor = s_i + 1
+			last_matched = True
+		up_to = min(last_anchor + context_size, n_tok - 1)
+		if up_to > last_anchor:
+			idx0 = int(idx[last_anchor])
+			regions.append(Region(s=s_text[idx0:int(idx[up_to])], match=None, gap_penalty=0.0))
+		return regions
+
+
+class Index:
+	"""vectorian/index.py:430-501"""
+
+	def __init__(self, partition, sim):
+		self._partition = partition
+		self._sim = sim
+		if not partition.contiguous:
+			logging.warning("the used partition is non-contiguous, you will miss parts of the content.")
+
+	@property
+	def partition(self):
+		return self._partition
+
+	@property
+	def session(self):
+		return self._partition.session
+
+	@property
+	def sim(self):
+		return self._sim
+
+	def describe(self):
+		data = {'partition': self._partition.to_args(), 'metric': self._sim.to_args(self)}
+		try:
+			import yaml
+			print(yaml.dump(data))
+		except ImportError:
+			print(data)
+
+	def make_query(self, text, n=10, min_score=0.0, debug=None, options: dict = dict()):
+		options = options.copy()
+		options["max_matches"] = n
+		options["min_score"] = min_score
+		if debug is not None:
+			options["debug"] = debug
+		options["partition"] = self._partition.to_args()
+		if self._sim is not None:
+			sim_args = self._sim.to_args(self)
+			if sim_args:
+				options["metric"] = sim_args
+		return Query(self, self._partition.session.vocab, text, options)
+
+	def find(self, text, n=10, min_score=0.0, debug=None, disable_progress=False,
+			run_task=None, make_result=None, options: dict = dict()):
+		start_time = time.time()
+		query = self.make_query(text, n=n, min_score=min_score, debug=debug, options=options)
+		session = self._partition.session
+		if make_result is None:
+			make_result = session.make_result
+		if run_task is None:
+			run_task = functools.partial(session.on_progress, disable_progress=disable_progress)
+		matches = run_task(lambda progress: self._find(query, progress=progress))
+		return make_result(self, matches, duration=time.time() - start_time)
+
+
+# options core.Query.initialize accepts (vectorian/core/cpp/query.cpp:40-57)
+_KNOWN_OPTIONS = frozenset([
+	"metric", "pos_filter", "tag_filter", "submatch_weight", "bidirectional", "max_matches",
+	"min_score", "partition", "debug", "slice_strategy"])
+
+
+class BruteForceIndex(Index):
+	"""vectorian/index.py:508-560"""
+
+	def __init__(self, *args, nlp=None, saliency=None, **kwargs):
+		super().__init__(*args, **kwargs)
+		self._nlp = nlp
+		self._saliency = saliency   # callable(prepared_doc, partition) -> float32[n_spans], the Booster values
+		self._boost_set = False
+		self.last_timing = None
+
+	def _similarity(self, p_query, metric_args):
+		"""The query's similarity matrix on the device (cpp/metric/static.cpp:9-78, contextual.cpp:26-63)."""
+		session = self.session
+		token_sim = metric_args['token_metric']
+		if token_sim.is_modifier:
+			raise NotImplementedError("modified token similarities are not on the device path yet (SURVEY.md 8f-3)")
+		embedding = token_sim.embedding
+		vector_sim = token_sim.similarity
+		encoder = session.to_encoder(embedding)
+		if encoder.is_contextual:
+			if not vector_sim.on_device:
+				raise NotImplementedError("contextual embeddings support CosineSim only")
+			q_vec = encoder.encode([[p_query.text_str[t['start']:t['end']] for t in p_query.tokens]])[0]
+			if q_vec.shape[0] != p_query.n_tokens:
+				raise ValueError("contextual encoder returned a wrong number of query vectors")
+			dc = session.load_contextual(self.partition, embedding)
+			return dc, engine.DeviceSim.contextual(q_vec)
+		dc = session.device_corpus(self.partition)
+		de, vocab_vectors = session.device_embedding(embedding)
+		q_vectors = encoder.encode_tokens(p_query.token_str)
+		q_id = np.where(p_query.token_id < session.vocab.size, p_query.token_id, -1).astype(np.int32)
+		if vector_sim.on_device:
+			return dc, engine.DeviceSim.static(de, q_id, q_vectors.unmodified)
+		# any other VectorSim: evaluated on the host exactly as the reference's callback does, then
+		# identity fix-up + clip (cpp/metric/static.cpp:58-75) and upload
+		s = np.zeros((session.vocab.size, p_query.n_tokens), dtype=np.float32)
+		vector_sim(vocab_vectors, q_vectors, s)
+		for j, i in enumerate(q_id):
+			if i >= 0:
+				s[i, j] = 1.0
+		np.clip(s, 0.0, 1.0, out=s)
+		return dc, engine.DeviceSim.upload(s)
+
+	def _find(self, query, n_threads=None, progress=None):
+		p_query = query.prepare(self._nlp)
+		if len(p_query) == 0:
+			return []
+		options = query.options
+		for k in options.keys():
+			if k not in _KNOWN_OPTIONS:
+				raise ValueError(f"illegal option {k}")          # cpp/query.cpp:59-68
+		metric_args = options.get("metric")
+		if not metric_args:
+			raise ValueError("no metric specified")
+		session = self.session
+		t = p_query.n_tokens
+
+		dc, sim = self._similarity(p_query, metric_args)
+		if self._saliency is not None and not self._boost_set:
+			lo, hi = session.shard[2:]
+			boost = [np.asarray(self._saliency(d, self.partition), dtype=np.float32) for d in session.documents[lo:hi]]
+			dc.set_boost(np.concatenate(boost) if boost else np.zeros((0,), np.float32))
+			self._boost_set = True
+
+		alignment = metric_args['alignment']
+		if alignment.get('algorithm') != 'pyalign':
+			raise NotImplementedError(f"algorithm {alignment.get('algorithm')} is outside the B200 hot path")
+		a_opt = alignment['options']
+		resolved = gaps.resolve_gap_costs(a_opt.get('gap_cost'), max(dc.max_len, 1), t)
+		gap_fns = (_gap_cost_fn(resolved, 's'), _gap_cost_fn(resolved, 't'))
+		r = dict(resolved)
+		kind = r.pop('gap_kind')
+		ap, keep_a = _cabi.make_align_params(a_opt['locality'], kind, **r)
+
+		qkw = {}
+		if metric_args['metric'] == 'alignment-tag-weighted':
+			tw = metric_args['tag_weights']
+			qkw = dict(
+				t_weights=np.array([tw.get(tag, 1.0) for tag in p_query.token_tag], dtype=np.float32),
+				t_pos=p_query.token_pos,
+				pos_mismatch_penalty=metric_args.get('pos_mismatch_penalty', 0),
+				similarity_threshold=metric_args.get('similarity_threshold', 0))
+		# Match::metric is the name of the token metric (vectorian/sim/token.py:39-44)
+		metric_name = metric_args['token_metric'].to_args(self)['name']
+		k = int(options.get("max_matches", 100))
+		qp, keep_q = _cabi.make_query_params(
+			max_matches=k, min_score=options.get("min_score", 0.2),
+			submatch_weight=options.get("submatch_weight", 0.0), **qkw)
+
+		hits, target, dist = dc.search(sim, ap, qp)
+		self.last_timing = dict(dc.last_timing(), sim_ms=sim.build_ms)
+		sim.close()
+		rank, world, doc_lo, _ = session.shard
+		if world > 1:
+			hits, target, dist = gather_topk(hits, target, dist, k, doc_offset=doc_lo)
+		elif doc_lo:
+			hits = hits.copy()
+			hits["doc"] += doc_lo
+		if progress:
+			progress(1.0)
+		return [CoreMatch(self, p_query, h, tg, ds, metric_name, gap_fns) for h, tg, ds in zip(hits, target, dist)]
