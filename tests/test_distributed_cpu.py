@@ -1,0 +1,80 @@
+"""Sentence-sharded search, host logic on CPU: world_size-2 gloo all-gather + merge of per-rank top-k."""
+
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from vectorian_b200._cabi import HIT_DTYPE
+from vectorian_b200.distributed import gather_topk, merge_hits, shard_documents
+
+
+def _free_port():
+	with socket.socket() as s:
+		s.bind(("127.0.0.1", 0))
+		return s.getsockname()[1]
+
+
+def _rank_rows(rank, n, t, k_seed=0):
+	rng = np.random.default_rng(100 + rank + k_seed)
+	hits = np.zeros((n,), dtype=HIT_DTYPE)
+	# scores on a coarse grid so that ties across ranks occur
+	hits["score"] = np.sort(rng.integers(0, 12, size=n).astype(np.float32) / 16)[::-1]
+	hits["score_max"] = t
+	hits["doc"] = rng.integers(0, 5, size=n)          # local document ids
+	hits["slice"] = rng.permutation(1000)[:n]
+	target = rng.integers(-1, 40000, size=(n, t)).astype(np.int16)
+	distance = rng.random((n, t)).astype(np.float32)
+	return hits, target, distance
+
+
+def _worker(rank, world, port, k, t, out_dir):
+	os.environ["MASTER_ADDR"] = "127.0.0.1"
+	os.environ["MASTER_PORT"] = str(port)
+	dist.init_process_group("gloo", rank=rank, world_size=world)
+	n_local = [7, 3][rank]
+	hits, target, distance = _rank_rows(rank, n_local, t)
+	g = gather_topk(hits, target, distance, k, doc_offset=rank * 5)
+	np.savez(os.path.join(out_dir, f"r{rank}.npz"), hits=g[0], target=g[1], distance=g[2])
+	dist.destroy_process_group()
+
+
+def test_gather_topk_world2(tmp_path):
+	world, k, t = 2, 6, 5
+	mp.spawn(_worker, args=(world, _free_port(), k, t, str(tmp_path)), nprocs=world, join=True)
+	parts = []
+	for rank, n_local in enumerate([7, 3]):
+		h, tg, ds = _rank_rows(rank, n_local, t)
+		h = h.copy()
+		h["doc"] += rank * 5
+		parts.append((h, tg, ds))
+	want = merge_hits(parts, k)
+	for rank in range(world):
+		got = np.load(os.path.join(str(tmp_path), f"r{rank}.npz"))
+		np.testing.assert_array_equal(got["hits"], want[0])
+		np.testing.assert_array_equal(got["target"], want[1])      # int16 targets survive the float32 transport bit-exactly
+		np.testing.assert_array_equal(got["distance"], want[2])
+	# total order: score desc, doc desc, slice desc
+	h = want[0]
+	for a, b in zip(h[:-1], h[1:]):
+		assert (a["score"], a["doc"], a["slice"]) > (b["score"], b["doc"], b["slice"])
+
+
+def test_merge_empty_and_shards():
+	e = merge_hits([], 5)
+	assert len(e[0]) == 0
+	h, tg, ds = _rank_rows(0, 4, 3)
+	m = merge_hits([(h[:0], tg[:0], ds[:0]), (h, tg, ds)], 10)
+	assert len(m[0]) == 4
+	# contiguous, covering, balanced by weight
+	w = np.array([10, 1, 1, 1, 1, 10, 1, 1, 1, 1], dtype=np.float64)
+	bounds = [shard_documents(len(w), 2, r, w) for r in range(2)]
+	assert bounds[0][0] == 0 and bounds[0][1] == bounds[1][0] and bounds[1][1] == len(w)
+	assert abs(w[:bounds[0][1]].sum() - w.sum() / 2) <= 10
+	for world in (1, 3, 8, 16):
+		b = [shard_documents(5, world, r) for r in range(world)]
+		assert b[0][0] == 0 and b[-1][1] == 5
+		assert all(x[1] == y[0] for x, y in zip(b[:-1], b[1:]))
