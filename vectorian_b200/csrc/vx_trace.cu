@@ -347,6 +347,334 @@ __global__ void trace_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
 	}
 }
 
+
+// ---------------------------------------------------------------------------
+// One WARP per item, matrices in shared memory, anti-diagonal wavefront: used for the k winners of a
+// search.  Every cell is still evaluated by ONE lane with the reference's candidate order, so the
+// traceback pointers are identical to trace_kernel's; only independent cells run concurrently.
+// ---------------------------------------------------------------------------
+
+struct SLayer {
+	float *val;
+	int16_t *tbu, *tbv;
+	int ld;
+	__device__ __forceinline__ int at(int u, int v) const {
+		return (u + 1) * ld + (v + 1);
+	}
+};
+
+struct SAcc {
+	float val;
+	int16_t u, v;
+	bool started;
+	__device__ __forceinline__ void begin(bool local) {
+		started = local;
+		val = 0.0f;
+		u = v = NO_TB;
+	}
+	__device__ __forceinline__ void push(float x, int pu, int pv) {
+		if (!started || x > val) {
+			val = x;
+			u = (int16_t)pu;
+			v = (int16_t)pv;
+			started = true;
+		}
+	}
+	__device__ __forceinline__ void store(SLayer &m, int cu, int cv) const {
+		const int i = m.at(cu, cv);
+		m.val[i] = val;
+		m.tbu[i] = u;
+		m.tbv[i] = v;
+	}
+};
+
+__global__ void __launch_bounds__(32) trace_warp_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
+	extern __shared__ float tw_smem[];
+	const int item = blockIdx.x;
+	const int lane = threadIdx.x;
+	const int n_items = a.n_items ? *a.n_items : a.max_items;
+	if (item >= n_items || item >= a.max_items) {
+		return;
+	}
+	const int64_t slot = a.slots ? (int64_t)a.slots[item] : a.slot_base + item;
+	const VxTile tl = a.tiles[slot >> 5];
+	const int wlane = (int)(slot & 31);
+	if (wlane >= tl.n_valid) {
+		if (lane == 0) {
+			a.out.score[item] = -CUDART_INF_F;
+		}
+		return;
+	}
+	const int len_s = tl.len;
+	const int len_t = qp.t;
+	const bool local = ap.locality == VX_LOCAL;
+	const bool global = ap.locality == VX_GLOBAL;
+	const int n_layers = ap.gap_kind == VX_GAP_AFFINE ? 3 : 1;
+	const int ld = len_t + 1;
+	const int n_cell = (len_s + 1) * ld;
+
+	// shared layout: sim[len_s * len_t] | val[n_layers * n_cell] | tb[n_layers * 2 * n_cell] (int16) | target[len_t] (int16)
+	float *sim = tw_smem;
+	float *vals = sim + len_s * len_t;
+	int16_t *tbs = reinterpret_cast<int16_t*>(vals + n_layers * n_cell);
+	int16_t *target_sh = tbs + n_layers * 2 * n_cell;
+	SLayer D{vals, tbs, tbs + n_cell, ld};
+	SLayer P{vals + n_cell, tbs + 2 * n_cell, tbs + 3 * n_cell, ld};
+	SLayer Q{vals + 2 * n_cell, tbs + 4 * n_cell, tbs + 5 * n_cell, ld};
+
+	// similarity of the slice (same arithmetic as trace_kernel)
+	for (int c = lane; c < len_s * len_t; c += 32) {
+		const int u = c / len_t, j = c - u * len_t;
+		const size_t ti = vx_elem(tl.base128, u, wlane);
+		float x = raw_sim(a, ti, a.tok[ti], j);
+		if (qp.tag_weighted) {
+			const float tw = len_t <= VX_MAX_T_MASK ? qp.t_weights[j] : qp.t_weights_dev[j];
+			const int8_t tpos = len_t <= VX_MAX_T_MASK ? qp.t_pos[j] : qp.t_pos_dev[j];
+			float weight = tw;
+			if (a.pos[ti] != tpos) {
+				weight *= 1.0f - qp.pos_mismatch_penalty;
+			}
+			const float sc = x * weight;
+			x = sc <= qp.similarity_threshold ? 0.0f : sc;
+		}
+		sim[c] = x;
+	}
+
+	// borders
+	const float ninf = -CUDART_INF_F;
+	for (int u = -1 + lane; u < len_s; u += 32) {
+		float b;
+		if (ap.gap_kind == VX_GAP_LINEAR) {
+			b = global ? ((float)(u + 1) * ap.lin_s) * -1.0f : 0.0f;
+		} else if (ap.gap_kind == VX_GAP_GENERAL) {
+			b = global ? ap.w_s[u + 1] * -1.0f : 0.0f;
+		} else {
+			b = global ? affine_at(ap.aff_ext_s, ap.aff_open_s, u + 1) * -1.0f : 0.0f;
+		}
+		for (int l = 0; l < n_layers; l++) {
+			const int i = D.at(u, -1) + l * n_cell;
+			vals[i] = l == 2 ? ninf : b;             // Q[u,-1] = -inf, D and P get the border
+			tbs[2 * l * n_cell + D.at(u, -1)] = NO_TB;
+			tbs[(2 * l + 1) * n_cell + D.at(u, -1)] = NO_TB;
+		}
+	}
+	__syncwarp();
+	for (int v = -1 + lane; v < len_t; v += 32) {
+		float b;
+		if (ap.gap_kind == VX_GAP_LINEAR) {
+			b = global ? ((float)(v + 1) * ap.lin_t) * -1.0f : 0.0f;
+		} else if (ap.gap_kind == VX_GAP_GENERAL) {
+			b = global ? ap.w_t[v + 1] * -1.0f : 0.0f;
+		} else {
+			b = global ? affine_at(ap.aff_ext_t, ap.aff_open_t, v + 1) * -1.0f : 0.0f;
+		}
+		for (int l = 0; l < n_layers; l++) {
+			// P[-1,v] = -inf except the corner, which the column pass above set (trace_kernel order:
+			// -inf first, then borders: D, P first column; D, Q first row)
+			const int i = D.at(-1, v);
+			if (l == 1) {
+				if (v >= 0) {
+					vals[n_cell + i] = ninf;
+				}
+			} else {
+				vals[l * n_cell + i] = b;
+			}
+			tbs[2 * l * n_cell + i] = NO_TB;
+			tbs[(2 * l + 1) * n_cell + i] = NO_TB;
+		}
+	}
+	__syncwarp();
+	if (n_layers == 3 && lane == 0) {
+		// corner values as trace_kernel leaves them: D = P = Q = border(0) = 0 (or -0)
+		const float b0 = global ? affine_at(ap.aff_ext_s, ap.aff_open_s, 0) * -1.0f : 0.0f;
+		const float b1 = global ? affine_at(ap.aff_ext_t, ap.aff_open_t, 0) * -1.0f : 0.0f;
+		vals[D.at(-1, -1)] = b1;
+		vals[n_cell + D.at(-1, -1)] = b0;
+		vals[2 * n_cell + D.at(-1, -1)] = b1;
+	}
+	__syncwarp();
+
+	// ---- solve: anti-diagonals ----
+	const float w1s = ap.aff_ext_s + ap.aff_open_s;
+	const float w1t = ap.aff_ext_t + ap.aff_open_t;
+	for (int d = 0; d <= len_s + len_t - 2; d++) {
+		const int u_lo = d - (len_t - 1) > 0 ? d - (len_t - 1) : 0;
+		const int u_hi = d < len_s - 1 ? d : len_s - 1;
+		for (int u = u_lo + lane; u <= u_hi; u += 32) {
+			const int v = d - u;
+			const float sv = sim[u * len_t + v];
+			if (ap.gap_kind == VX_GAP_LINEAR) {
+				SAcc acc;
+				acc.begin(local);
+				acc.push(D.val[D.at(u - 1, v - 1)] + sv, u - 1, v - 1);
+				acc.push(D.val[D.at(u - 1, v)] - ap.lin_s, u - 1, v);
+				acc.push(D.val[D.at(u, v - 1)] - ap.lin_t, u, v - 1);
+				acc.store(D, u, v);
+			} else if (ap.gap_kind == VX_GAP_GENERAL) {
+				SAcc acc;
+				acc.begin(local);
+				acc.push(D.val[D.at(u - 1, v - 1)] + sv, u - 1, v - 1);
+				for (int k = -1; k < u; k++) {
+					acc.push(D.val[D.at(k, v)] - ap.w_s[u - k], k, v);
+				}
+				for (int k = -1; k < v; k++) {
+					acc.push(D.val[D.at(u, k)] - ap.w_t[v - k], u, k);
+				}
+				acc.store(D, u, v);
+			} else {
+				{
+					SAcc acc;
+					acc.begin(false);
+					acc.push(D.val[D.at(u - 1, v)] - w1s, u - 1, v);
+					const int k = P.at(u - 1, v);
+					acc.push(P.val[k] - ap.aff_ext_s, P.tbu[k], P.tbv[k]);
+					acc.store(P, u, v);
+				}
+				{
+					SAcc acc;
+					acc.begin(false);
+					acc.push(D.val[D.at(u, v - 1)] - w1t, u, v - 1);
+					const int k = Q.at(u, v - 1);
+					acc.push(Q.val[k] - ap.aff_ext_t, Q.tbu[k], Q.tbv[k]);
+					acc.store(Q, u, v);
+				}
+				{
+					SAcc acc;
+					acc.begin(local);
+					acc.push(D.val[D.at(u - 1, v - 1)] + sv, u - 1, v - 1);
+					const int kp = P.at(u, v);
+					acc.push(P.val[kp], P.tbu[kp], P.tbv[kp]);
+					const int kq = Q.at(u, v);
+					acc.push(Q.val[kq], Q.tbu[kq], Q.tbv[kq]);
+					acc.store(D, u, v);
+				}
+			}
+		}
+		__syncwarp();
+	}
+
+
+	// ---- seed (solver.h:2027-2050, 2166-2180, 2258-2286): best cell, FIRST in scan order on ties ----
+	int su = -1, sv = -1;
+	bool have_seed = false;
+	if (global) {
+		su = len_s - 1;
+		sv = len_t - 1;
+		have_seed = true;
+	} else {
+		// scan order index: Local: (len_s-1-u) * len_t + (len_t-1-v); Semiglobal: last row v = 0.., then last column u = 0..
+		const int n_scan = local ? len_s * len_t : len_t + len_s;
+		float best = -CUDART_INF_F;
+		int best_i = 0x7fffffff;
+		for (int i = lane; i < n_scan; i += 32) {
+			int u, v;
+			if (local) {
+				u = len_s - 1 - i / len_t;
+				v = len_t - 1 - i % len_t;
+			} else if (i < len_t) {
+				u = len_s - 1;
+				v = i;
+			} else {
+				u = i - len_t;
+				v = len_t - 1;
+			}
+			const float x = D.val[D.at(u, v)];
+			if (x > best) {
+				best = x;
+				best_i = i;
+			}
+		}
+		#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) {
+			const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+			const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+			if (ob > best || (ob == best && oi < best_i)) {
+				best = ob;
+				best_i = oi;
+			}
+		}
+		have_seed = best > -CUDART_INF_F;
+		if (have_seed) {
+			if (local) {
+				su = len_s - 1 - best_i / len_t;
+				sv = len_t - 1 - best_i % len_t;
+			} else if (best_i < len_t) {
+				su = len_s - 1;
+				sv = best_i;
+			} else {
+				su = best_i - len_t;
+				sv = len_t - 1;
+			}
+		}
+	}
+
+	for (int v = lane; v < len_t; v += 32) {
+		target_sh[v] = -1;
+	}
+	__syncwarp();
+
+	// ---- traceback (lane 0), score, flow ----
+	if (lane == 0) {
+		float raw = -CUDART_INF_F;
+		if (have_seed) {
+			int u = su, v = sv;
+			raw = D.val[D.at(u, v)];
+			int last_u = u, last_v = v;
+			while (u >= 0 && v >= 0 && (!local || D.val[D.at(u, v)] > 0.0f)) {
+				const int i = D.at(u, v);
+				const int nu = D.tbu[i], nv = D.tbv[i];
+				u = nu;
+				v = nv;
+				if (u != last_u && v != last_v && last_u >= 0 && last_v >= 0) {
+					target_sh[last_v] = (int16_t)last_u;
+				}
+				last_u = u;
+				last_v = v;
+			}
+		}
+		float matched = 0.0f;
+		for (int j = 0; j < len_t; j++) {
+			if (target_sh[j] >= 0) {
+				matched += qp.tag_weighted ?
+					(len_t <= VX_MAX_T_MASK ? qp.t_weights[j] : qp.t_weights_dev[j]) : 1.0f;
+			}
+		}
+		const float total = qp.total;
+		const float unmatched_weight = powf((total - matched) / total, qp.submatch_weight);
+		const float ref = matched + unmatched_weight * (total - matched);
+		const float boost = a.boost ? a.boost[slot] : 1.0f;
+		a.out.score[item] = (raw / ref) * boost;
+		if (a.out.score_max) {
+			a.out.score_max[item] = ref;
+		}
+		if (a.out.win) {
+			a.out.win[item] = a.orig[slot];
+		}
+	}
+	__syncwarp();
+	for (int j = lane; j < len_t; j += 32) {
+		const int u = target_sh[j];
+		if (a.out.target) {
+			a.out.target[(size_t)item * len_t + j] = (int16_t)u;
+		}
+		if (a.out.dist) {
+			float dv = 1.0f;
+			if (u >= 0) {
+				const size_t ti = vx_elem(tl.base128, u, wlane);
+				dv = 1.0f - raw_sim(a, ti, a.tok[ti], j);
+			}
+			a.out.dist[(size_t)item * len_t + j] = dv;
+		}
+	}
+}
+
+static size_t trace_warp_smem(int32_t max_len, int32_t t, int32_t gap_kind) {
+	const size_t n_layers = gap_kind == VX_GAP_AFFINE ? 3 : 1;
+	const size_t n_cell = (size_t)(max_len + 1) * (t + 1);
+	size_t b = sizeof(float) * (size_t)max_len * t + n_layers * n_cell * (sizeof(float) + 2 * sizeof(int16_t))
+		+ sizeof(int16_t) * (size_t)t;
+	return (b + 15) & ~(size_t)15;
+}
 size_t vx_trace_scratch_bytes(int32_t max_len, int32_t t, int32_t max_items, int32_t gap_kind) {
 	(void)gap_kind;
 	const size_t n_cell = (size_t)(max_len + 1) * (t + 1);
@@ -361,6 +689,39 @@ int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 
 	if (max_items <= 0) {
 		return 0;
+	}
+	const size_t warp_smem = trace_warp_smem(c->max_len, qp.t, ap.gap_kind);
+	if (d_slots && warp_smem <= 200 * 1024) {
+		// the k winners: one warp each, matrices in shared memory
+		TraceArgs a;
+		a.tiles = c->d_tiles;
+		a.tok = c->d_tok;
+		a.pos = c->d_pos;
+		a.boost = c->d_boost;
+		a.s = s->d_s;
+		a.tp = s->tp;
+		a.ctx = c->d_ctx;
+		a.qhat = s->d_qhat;
+		a.ctx_dim = s->d;
+		a.contextual = s->contextual;
+		a.scratch = nullptr;
+		a.scratch_per_item = 0;
+		a.max_len = c->max_len;
+		a.slots = d_slots;
+		a.slot_base = slot_base;
+		a.orig = c->d_orig;
+		a.n_items = d_n_items;
+		a.max_items = max_items;
+		a.out = out;
+		if (warp_smem > 48 * 1024) {
+			cudaFuncSetAttribute(trace_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)warp_smem);
+		}
+		trace_warp_kernel<<<max_items, 32, warp_smem, c->stream>>>(a, ap, qp);
+		if (cudaGetLastError() != cudaSuccess) {
+			vx_set_error("trace (warp) kernel launch failed");
+			return -1;
+		}
+		return 1;
 	}
 	const size_t need = vx_trace_scratch_bytes(c->max_len, qp.t, max_items, ap.gap_kind);
 	if (c->scratch_bytes < need) {
