@@ -448,12 +448,94 @@ extern "C" int vx_embedding_destroy(vx_embedding *e) {
 	return VX_OK;
 }
 
+// ---- buffer pool + similarity stream ----
+
+#include <mutex>
+
+struct PoolEntry {
+	size_t bytes;
+	void *p;
+};
+static std::mutex g_pool_mutex;
+static std::vector<PoolEntry> g_pool;
+static cudaStream_t g_sim_stream = nullptr;
+
+void *vx_pool_alloc(size_t bytes) {
+	if (bytes == 0) {
+		bytes = 16;
+	}
+	{
+		std::lock_guard<std::mutex> lock(g_pool_mutex);
+		for (size_t i = 0; i < g_pool.size(); i++) {
+			if (g_pool[i].bytes == bytes) {
+				void *p = g_pool[i].p;
+				g_pool.erase(g_pool.begin() + i);
+				return p;
+			}
+		}
+	}
+	void *p = nullptr;
+	if (cudaMalloc(&p, bytes) != cudaSuccess) {
+		cudaGetLastError();
+		return nullptr;
+	}
+	return p;
+}
+
+void vx_pool_free(void *p, size_t bytes) {
+	if (!p) {
+		return;
+	}
+	if (bytes == 0) {
+		bytes = 16;
+	}
+	void *evict = nullptr;
+	{
+		std::lock_guard<std::mutex> lock(g_pool_mutex);
+		g_pool.push_back(PoolEntry{bytes, p});
+		if (g_pool.size() > 16) {
+			evict = g_pool.front().p;
+			g_pool.erase(g_pool.begin());
+		}
+	}
+	if (evict) {
+		cudaFree(evict);
+	}
+}
+
+cudaStream_t vx_sim_stream() {
+	if (!g_sim_stream) {
+		cudaStreamCreateWithFlags(&g_sim_stream, cudaStreamNonBlocking);
+	}
+	return g_sim_stream;
+}
+
 static void sim_free(vx_sim *s) {
 	if (s) {
-		cudaFree(s->d_s);
+		// all users of the buffers (searches) have synchronised before they returned; later builds that
+		// recycle them are ordered behind this sim's own kernels on the similarity stream
+		vx_pool_free(s->d_s, s->s_bytes);
+		vx_pool_free(s->d_tmp, s->tmp_bytes);
 		cudaFree(s->d_qhat);
+		if (s->ev0) {
+			cudaEventDestroy(s->ev0);
+		}
+		if (s->ev1) {
+			cudaEventDestroy(s->ev1);
+		}
 		delete s;
 	}
+}
+
+static int sim_alloc_s(vx_sim *s) {
+	s->s_bytes = sizeof(float) * (size_t)s->rows * s->tp;
+	s->d_s = (float*)vx_pool_alloc(s->s_bytes);
+	if (!s->d_s) {
+		VX_FAIL(VX_ERR_CUDA, "cudaMalloc of the similarity matrix failed");
+	}
+	cudaEventCreate(&s->ev0);
+	cudaEventCreate(&s->ev1);
+	return VX_OK;
 }
 
 extern "C" int vx_sim_static(const vx_embedding *e, const int32_t *q_id, const float *q_vec, int32_t t, vx_sim **out) {
@@ -468,51 +550,49 @@ extern "C" int vx_sim_static(const vx_embedding *e, const int32_t *q_id, const f
 	s->rows = e->v;
 	s->t = t;
 	s->tp = std::max(4, (t + 3) / 4 * 4);
-	float *d_q = nullptr, *d_qhat = nullptr;
-	int32_t *d_qid = nullptr;
-	int rc = VX_OK;
-	do {
-		if ((rc = dev_alloc(&s->d_s, (size_t)s->rows * s->tp)) != VX_OK) break;
+	cudaStream_t st = vx_sim_stream();
+	int rc = sim_alloc_s(s);
+	if (rc == VX_OK) {
+		cudaEventRecord(s->ev0, st);
 		if (t == 0) {
-			cudaMemset(s->d_s, 0, sizeof(float) * (size_t)s->rows * s->tp);
-			break;
-		}
-		if ((rc = dev_alloc(&d_q, (size_t)t * e->d)) != VX_OK) break;
-		if ((rc = dev_alloc(&d_qhat, (size_t)t * e->d)) != VX_OK) break;
-		if ((rc = dev_alloc(&d_qid, (size_t)t)) != VX_OK) break;
-		cudaMemcpyAsync(d_q, q_vec, sizeof(float) * (size_t)t * e->d, cudaMemcpyHostToDevice, 0);
-		cudaMemcpyAsync(d_qid, q_id, sizeof(int32_t) * (size_t)t, cudaMemcpyHostToDevice, 0);
-		cudaEvent_t e0, e1;
-		cudaEventCreate(&e0);
-		cudaEventCreate(&e1);
-		cudaEventRecord(e0, 0);
-		s->launches += vx_launch_normalize(d_q, d_qhat, t, e->d, 0);
-		const int n_launched = vx_launch_sim_static(e->d_ehat, e->v, e->d, d_qhat, d_qid, t, s->tp, s->d_s, 0);
-		cudaEventRecord(e1, 0);
-		if (n_launched < 0) {
-			vx_set_error("similarity kernel: unsupported query length");
-			rc = VX_ERR_INVALID;
+			cudaMemsetAsync(s->d_s, 0, s->s_bytes, st);
 		} else {
-			s->launches += n_launched;
+			// staging: q[t x d] | qhat[t x d] | qid[t]
+			const size_t n_q = (size_t)t * e->d;
+			s->tmp_bytes = (sizeof(float) * 2 * n_q + sizeof(int32_t) * (size_t)t + 255) & ~(size_t)255;
+			s->d_tmp = vx_pool_alloc(s->tmp_bytes);
+			if (!s->d_tmp) {
+				vx_set_error("cudaMalloc of the query staging buffer failed");
+				rc = VX_ERR_CUDA;
+			} else {
+				float *d_q = (float*)s->d_tmp;
+				float *d_qhat = d_q + n_q;
+				int32_t *d_qid = (int32_t*)(d_qhat + n_q);
+				cudaMemcpyAsync(d_q, q_vec, sizeof(float) * n_q, cudaMemcpyHostToDevice, st);
+				cudaMemcpyAsync(d_qid, q_id, sizeof(int32_t) * (size_t)t, cudaMemcpyHostToDevice, st);
+				s->launches += vx_launch_normalize(d_q, d_qhat, t, e->d, st);
+				const int n_launched = vx_launch_sim_static(e->d_ehat, e->v, e->d, d_qhat, d_qid, t, s->tp, s->d_s, st);
+				if (n_launched < 0) {
+					vx_set_error("similarity kernel: unsupported query length");
+					rc = VX_ERR_INVALID;
+				} else {
+					s->launches += n_launched;
+				}
+			}
 		}
-		cudaError_t err = cudaStreamSynchronize(0);
-		if (err != cudaSuccess) {
-			vx_set_error(std::string("similarity kernel failed: ") + cudaGetErrorString(err));
+		cudaEventRecord(s->ev1, st);
+		s->timed = true;
+		if (rc == VX_OK && cudaGetLastError() != cudaSuccess) {
+			vx_set_error("similarity kernel launch failed");
 			rc = VX_ERR_CUDA;
-		} else {
-			cudaEventElapsedTime(&s->build_ms, e0, e1);
 		}
-		cudaEventDestroy(e0);
-		cudaEventDestroy(e1);
-	} while (0);
-	cudaFree(d_q);
-	cudaFree(d_qhat);
-	cudaFree(d_qid);
+	}
 	if (rc != VX_OK) {
+		cudaStreamSynchronize(st);
 		sim_free(s);
 		return rc;
 	}
-	*out = s;
+	*out = s;   // asynchronous: searches wait on ev1 (vx_search), downloads synchronise
 	return VX_OK;
 }
 
@@ -525,7 +605,7 @@ extern "C" int vx_sim_upload(const float *sm, int64_t v, int32_t t, vx_sim **out
 	s->rows = v;
 	s->t = t;
 	s->tp = std::max(4, (t + 3) / 4 * 4);
-	int rc = dev_alloc(&s->d_s, (size_t)v * s->tp);
+	int rc = sim_alloc_s(s);
 	if (rc != VX_OK) {
 		sim_free(s);
 		return rc;
@@ -586,6 +666,9 @@ extern "C" int vx_sim_download(const vx_sim *s, float *out, int64_t v, int32_t t
 	if (!s || !out || s->contextual || v != s->rows || t != s->t) {
 		VX_FAIL(VX_ERR_INVALID, "similarity matrix shape mismatch");
 	}
+	if (s->ev1) {
+		VX_CUDA(cudaEventSynchronize(s->ev1));
+	}
 	if (v * t > 0) {
 		VX_CUDA(cudaMemcpy2D(out, sizeof(float) * t, s->d_s, sizeof(float) * s->tp,
 			sizeof(float) * t, (size_t)v, cudaMemcpyDeviceToHost));
@@ -594,7 +677,17 @@ extern "C" int vx_sim_download(const vx_sim *s, float *out, int64_t v, int32_t t
 }
 
 extern "C" float vx_sim_build_ms(const vx_sim *s) {
-	return s ? s->build_ms : 0.0f;
+	if (!s) {
+		return 0.0f;
+	}
+	if (s->timed && s->ev0 && s->ev1 && cudaEventSynchronize(s->ev1) == cudaSuccess) {
+		float ms = 0.0f;
+		if (cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) {
+			return ms;
+		}
+		cudaGetLastError();
+	}
+	return s->build_ms;
 }
 
 extern "C" int vx_sim_launches(const vx_sim *s) {

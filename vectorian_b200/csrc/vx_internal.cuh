@@ -109,9 +109,20 @@ struct vx_sim {
 	int32_t contextual = 0;
 	int32_t d = 0;
 	float *d_qhat = nullptr;         // contextual: [t x d] normalised query vectors
-	float build_ms = 0.0f;           // device time of the kernels that built d_s
+	float build_ms = 0.0f;           // device time of the kernels that built d_s (resolved lazily from ev0/ev1)
 	int launches = 0;
+	size_t s_bytes = 0;              // size of the d_s allocation (returned to the pool on destroy)
+	void *d_tmp = nullptr;           // pooled staging of the query vectors / ids
+	size_t tmp_bytes = 0;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // ev1 doubles as the "S is ready" event searches wait on
+	bool timed = false;
 };
+
+// Small cache of device buffers keyed by size: per-query allocations (S, staging) are recycled instead
+// of going through cudaMalloc / cudaFree (which synchronise the device) on every query.
+void *vx_pool_alloc(size_t bytes);
+void vx_pool_free(void *p, size_t bytes);
+cudaStream_t vx_sim_stream();
 
 // Per-query constants handed to the kernels by value.
 constexpr int VX_MAX_T_FAST = 16;    // query lengths with a register-resident fast path

@@ -261,6 +261,9 @@ extern "C" int vx_search(
 	}
 
 	cudaStream_t st = c->stream;
+	if (s->ev1) {
+		cudaStreamWaitEvent(st, s->ev1, 0);   // S may still be under construction on the similarity stream
+	}
 	cudaEventRecord(c->ev[0], st);
 	int n = score_everything(c, s, p);
 	if (n < 0) {
@@ -341,6 +344,9 @@ extern "C" int vx_score_all(
 	if (p.t < 1) {
 		memset(score_out, 0, sizeof(float) * (size_t)n);
 		return VX_OK;
+	}
+	if (s->ev1) {
+		cudaStreamWaitEvent(c->stream, s->ev1, 0);
 	}
 	int k = score_everything(c, s, p);
 	if (k < 0) {
