@@ -219,8 +219,8 @@ static int corpus_create_impl(
 		}
 		c->n_tiles = n_tiles;
 		for (int i = 0; i <= VX_N_CLASS; i++) {
-			// first tile with len <= 8*i  ==  first_tile of the longest such length
-			const int32_t lmax = std::min<int32_t>(8 * i, c->max_len);
+			// first tile with len <= 4*i  ==  first_tile of the longest such length
+			const int32_t lmax = std::min<int32_t>(4 * i, c->max_len);
 			c->class_first[i] = i == 0 || lmax < 1 ? n_tiles : first_tile[lmax];
 		}
 		c->n_slots = n_tiles * VX_TILE;

@@ -47,7 +47,7 @@ __host__ __device__ __forceinline__ size_t vx_elem(uint32_t base128, int u, int 
 constexpr int VX_TOK_SLACK = 4 * 128;   // elements readable past the last tile (prefetch runs ahead)
 
 constexpr int VX_TILE = 32;
-constexpr int VX_N_CLASS = 8;        // length classes of 8 tokens: windows up to 64 tokens take the fast WSB kernel
+constexpr int VX_N_CLASS = 16;       // length classes of 4 tokens: windows up to 64 tokens take the fast WSB kernel
 constexpr uint32_t VX_NO_WINDOW = 0xffffffffu;
 
 struct vx_corpus {
@@ -83,8 +83,8 @@ struct vx_corpus {
 	void *h_res = nullptr;           // pinned host mirror of the result block
 	size_t h_res_bytes = 0;
 	int32_t max_token_id = -1;       // -1 = unknown (corpus created from device memory)
-	// tiles are sorted by descending length: class_first[i] = first tile whose windows are <= 8*i long
-	// (class_first[0] = n_tiles); the shared-memory WSB kernel is launched once per class of 8
+	// tiles are sorted by descending length: class_first[i] = first tile whose windows are <= 4*i long
+	// (class_first[0] = n_tiles); the WSB kernel is launched once per run of classes with equal occupancy
 	int64_t class_first[VX_N_CLASS + 1] = {0};
 	void *d_counters = nullptr;      // 16 x uint32 tile counters of the persistent kernels
 

@@ -403,23 +403,32 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 // host side
 // ---------------------------------------------------------------------------
 
+// History placement for windows of up to `cap` rows: rows [0, rt) in tensor memory, the rest in shared
+// memory.  Eight warps per SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a
+// TMEM lane quarter and gets 256 columns.  Long classes fall back to <= 4 warps with 512 columns each.
+static void wsb_plan(int tp, int cap, int *warps, int *rt, int *tmem_cols, int *rows_smem) {
+	const size_t row_bytes = (size_t)tp * 32 * sizeof(float);
+	const size_t smem_max = 227 * 1024 - 1024;
+	*warps = 0;
+	for (int w = 8; w >= 1; w--) {
+		*tmem_cols = w > 4 ? 256 : 512;
+		*rt = *tmem_cols / tp / VX_WSB_U * VX_WSB_U;
+		*rows_smem = cap > *rt ? cap - *rt : 0;
+		if ((size_t)*rows_smem * row_bytes * w <= smem_max) {
+			*warps = w;
+			return;
+		}
+	}
+}
+
 template<int TP, int LOC, bool BORD>
 static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms) {
 	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
 	// SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a TMEM lane quarter
 	// and gets 256 columns.  Long classes fall back to <= 4 warps with 512 columns each.
-	const size_t row_bytes = (size_t)TP * 32 * sizeof(float);
-	const size_t smem_max = 227 * 1024 - 1024;
 	int warps = 0, rt = 0, tmem_cols = 256, rows_smem = 0;
-	for (int w = 8; w >= 1; w--) {
-		tmem_cols = w > 4 ? 256 : 512;
-		rt = tmem_cols / TP / VX_WSB_U * VX_WSB_U;
-		rows_smem = cap > rt ? cap - rt : 0;
-		if ((size_t)rows_smem * row_bytes * w <= smem_max) {
-			warps = w;
-			break;
-		}
-	}
+	wsb_plan(TP, cap, &warps, &rt, &tmem_cols, &rows_smem);
+	const size_t row_bytes = (size_t)TP * 32 * sizeof(float);
 	if (warps < 1) {
 		return -1;
 	}
@@ -492,23 +501,42 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	// Local zero, so the kernel variant without them gives the same maxima.
 	const bool bord = !(ap.locality == VX_LOCAL && nonneg);
 
-	// length classes of 8 rows; c->class_first[i] = first tile whose length is <= 8 * i
+	// length classes of 4 rows (c->class_first[i] = first tile whose length is <= 4 * i), longest first;
+	// consecutive classes that run at the same number of warps per SM share one launch sized for the
+	// longest of them (everything up to 36 rows at T <= 12 is ONE launch at 8 warps per SM)
 	int launches = 0;
 	unsigned int *counters = (unsigned int*)c->d_counters;
 	cudaMemsetAsync(counters, 0, sizeof(unsigned int) * 16, c->stream);
-	for (int cls = VX_WSB_MAX_LEN / 8; cls >= 1; cls--) {
+	int n_groups = 0;
+	for (int cls = VX_WSB_MAX_LEN / 4; cls >= 1; ) {
+		if (c->class_first[cls] >= c->class_first[cls - 1]) {
+			cls--;   // no tiles of this length: the next group is sized for the longest length present
+			continue;
+		}
+		int w_top, rt_, tc_, rs_;
+		wsb_plan(s->tp, cls * 4, &w_top, &rt_, &tc_, &rs_);
+		int lo = cls;
+		while (lo > 1) {
+			int w_lo;
+			wsb_plan(s->tp, (lo - 1) * 4, &w_lo, &rt_, &tc_, &rs_);
+			if (w_lo != w_top && w_top < 8) {
+				break;
+			}
+			lo--;
+		}
 		const int64_t begin = c->class_first[cls];
-		const int64_t end = c->class_first[cls - 1];
+		const int64_t end = c->class_first[lo - 1];
+		const int cap = cls * 4;
+		cls = lo - 1;
 		if (begin >= end) {
 			continue;
 		}
 		if (begin < *first_tile) {
 			*first_tile = begin;
 		}
+		a.counter = counters + (n_groups++ & 15);
 		a.tile_begin = begin;
 		a.tile_end = end;
-		a.counter = counters + cls;
-		const int cap = cls * 8;
 		int rc;
 		switch (s->tp) {
 			case 4:
