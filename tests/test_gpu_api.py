@@ -11,7 +11,8 @@ from vectorian_b200.embedding import KeyedVectors, ContextualEmbedding
 from vectorian_b200.session import Session
 from vectorian_b200.sim.span import OptimizedSpanSim
 from vectorian_b200.sim.token import EmbeddingTokenSim
-from vectorian_b200.sim.vector import CosineSim, PNormSim
+from vectorian_b200.sim.vector import CosineSim, PNormDistance, ModifiedVectorSim
+from vectorian_b200.sim.kernel import Scale, DistanceToSimilarity
 from tests import helpers
 
 pytestmark = pytest.mark.gpu
@@ -146,7 +147,7 @@ def test_tag_weighted_and_host_vector_sim(oracle):
 	check_find(oracle, session, emb, index, QUERY, n=15, min_score=0.01, qkw=qkw)
 
 	# a VectorSim the device does not evaluate itself: computed on the host, uploaded
-	pn = PNormSim(p=2, scale=0.25)
+	pn = ModifiedVectorSim(PNormDistance(p=2), Scale(0.25), DistanceToSimilarity())
 	metric = OptimizedSpanSim(EmbeddingTokenSim(emb, pn), LocalAlignment(gap=gaps.smooth_gap_cost(3)))
 	index = session.partition("sentence").index(metric, nlp=whitespace_nlp)
 	de, vv = session.device_embedding(emb)

@@ -12,7 +12,8 @@ from vectorian_b200.index import BruteForceIndex, Index, PreparedQuery, Query
 from vectorian_b200.session import Session, Partition
 from vectorian_b200.sim.span import OptimizedSpanSim
 from vectorian_b200.sim.token import EmbeddingTokenSim
-from vectorian_b200.sim.vector import CosineSim, PNormSim
+from vectorian_b200.sim.vector import CosineSim, PNormDistance, ModifiedVectorSim
+from vectorian_b200.sim.kernel import Scale, DistanceToSimilarity
 
 
 def tiny_session():
@@ -62,7 +63,7 @@ def test_vectors_normalized():
 	out = np.zeros((3, 3), dtype=np.float32)
 	CosineSim()(v, v, out)
 	np.testing.assert_allclose(np.diag(out), [1, 0, 1], rtol=1e-6)
-	assert CosineSim().on_device and not PNormSim().on_device
+	assert CosineSim().on_device and not PNormDistance().on_device
 
 
 def test_session_vocabulary_and_query_ids():

@@ -57,19 +57,65 @@ class FuzzyJaccardSim(VectorSim):
 		return "fuzzy-jaccard"
 
 
-class PNormSim(VectorSim):
-	"""sim/vector.py:141-163: max(0, 1 - |a - b|_p * scale)"""
+class ImprovedSqrtCosineSim(VectorSim):
+	"""sim/vector.py:98-131 (Sohangir & Wang 2017), vectors made non-negative first."""
 
-	def __init__(self, p=2, scale=1):
+	@staticmethod
+	def _to_non_negative(x):
+		t = np.repeat(x, 2, axis=-1)
+		t[:, 1::2] = -t[:, 1::2]
+		return np.maximum(0, t)
+
+	def compute(self, a, b, out):
+		a_pos = self._to_non_negative(a.unmodified)
+		b_pos = self._to_non_negative(b.unmodified)
+		num = np.sum(np.sqrt(a_pos[:, np.newaxis] * b_pos[np.newaxis, :]), axis=-1)
+		x = np.sqrt(np.sum(a_pos, axis=-1))
+		y = np.sqrt(np.sum(b_pos, axis=-1))
+		denom = x[:, np.newaxis] * y[np.newaxis, :]
+		with np.errstate(divide='ignore', invalid='ignore'):
+			out[:, :] = num / denom
+		np.nan_to_num(out, copy=False, nan=0)
+
+	@property
+	def name(self):
+		return "improved-sqrt-cosine"
+
+
+class PNormDistance(VectorSim):
+	"""A p-norm DISTANCE (sim/vector.py:134-160); combine with kernel.DistanceToSimilarity."""
+
+	def __init__(self, p=2):
 		self._p = p
-		self._scale = scale
 
 	def compute(self, a, b, out):
 		d = a.unmodified[:, np.newaxis] - b.unmodified[np.newaxis, :]
 		d = np.sum(np.power(np.abs(d), self._p), axis=-1)
 		d = np.power(d, 1 / self._p)
-		out[:, :] = np.maximum(0, 1 - d * self._scale)
+		out[:, :] = d
 
 	@property
 	def name(self):
 		return f"p-norm({self._p})"
+
+
+class EuclideanDistance(PNormDistance):
+	def __init__(self):
+		super().__init__(p=2)
+
+
+class ModifiedVectorSim(VectorSim):
+	"""A VectorSim whose output is modified by unary operators (sim/vector.py:176-200)."""
+
+	def __init__(self, source, *operators):
+		from .kernel import Kernel
+		self._source = source
+		self._kernel = Kernel(operators)
+
+	def compute(self, a, b, out):
+		self._source(a, b, out)
+		self._kernel(out)
+
+	@property
+	def name(self):
+		return self._kernel.name(self._source.name)
