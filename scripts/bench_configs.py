@@ -1,0 +1,87 @@
+#!/usr/bin/env python
+"""Secondary measurements: the other BASELINE.json configs on ONE GPU, per-phase device times and
+roofline fractions (bench.py stays the C3 headline).  Usage: python scripts/bench_configs.py [c2] [c1] [c4] ...
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from vectorian_b200 import _cabi, engine, gaps, synthetic  # noqa: E402
+
+
+def peaks():
+	try:
+		return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+	except Exception:
+		return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}
+
+
+def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand_per_cell=None):
+	import torch
+	tok, tables = synthetic.make_corpus_device(n_sent, vocab, device="cuda:0")
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	del tok
+	emb = synthetic.make_embedding(vocab, dim)
+	de = engine.DeviceEmbedding(emb)
+	r = gaps.resolve_gap_costs(gap, dc.max_len, t)
+	kind = r.pop("gap_kind")
+	ap, keep = _cabi.make_align_params(locality, kind, **r)
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
+	queries = [synthetic.make_query(t, vocab, seed=99 + i) for i in range(8)]
+	tm = {"sim_ms": [], "dp_ms": [], "topk_ms": [], "traceback_ms": [], "wall_ms": []}
+	for i in range(3 + steps):
+		q = queries[i % 8]
+		t0 = time.perf_counter()
+		sim = engine.DeviceSim.static(de, q, emb[q])
+		hits, target, dist = dc.search(sim, ap, qp)
+		t1 = time.perf_counter()
+		if i >= 3:
+			lt = dc.last_timing()
+			for kk in ("dp_ms", "topk_ms", "traceback_ms"):
+				tm[kk].append(lt[kk])
+			tm["sim_ms"].append(sim.build_ms)
+			tm["wall_ms"].append((t1 - t0) * 1e3)
+		sim.close()
+	p = peaks()
+	med = {kk: float(np.median(v)) for kk, v in tm.items()}
+	dev_ms = med["sim_ms"] + med["dp_ms"] + med["topk_ms"] + med["traceback_ms"]
+	lens = tables["lens"].astype(np.float64)
+	cells = float((lens * t).sum())
+	sms = _cabi.lib().vx_device_sm_count()
+	issue_peak = sms * 128 * p.get("sm_max_mhz", 1965.0) * 1e6
+	out = {
+		"config": name, "sentences": n_sent, "T": t, "V": vocab, "d": dim, "n_hits": int(len(hits)),
+		"ms": med, "device_ms": dev_ms, "sentences_per_s_device": n_sent / dev_ms * 1e3, "sentences_per_s_e2e": n_sent / med["wall_ms"] * 1e3,
+		"gcups": cells / dev_ms / 1e6,
+		"dp_hbm_frac": (4 * lens.sum() + 4 * n_sent) / (med["dp_ms"] * 1e-3) / 1e9 / p["hbm_gbs"],
+		"dp_l2_gather_gbs": cells * 4 / (med["dp_ms"] * 1e-3) / 1e9,
+		"sim_hbm_frac": (4.0 * vocab * dim + 4.0 * vocab * ((t + 3) // 4 * 4)) / (med["sim_ms"] * 1e-3) / 1e9 / p["hbm_gbs"],
+	}
+	if cand_per_cell:
+		ops = 2 * cand_per_cell * cells
+		out["dp_issue_frac"] = ops / (med["dp_ms"] * 1e-3) / issue_peak
+	print(json.dumps(out), flush=True)
+	dc.close()
+	return out
+
+
+def main():
+	which = sys.argv[1:] or ["c1", "c2"]
+	if "c1" in which:   # the reference's own CPU-runnable case, on the GPU for comparison
+		run_static("C1 NW Global linear(0.2) T=5 10k V=50k", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.2), 5, 10_000, 50_000, 300, cand_per_cell=3)
+	if "c2" in which:
+		run_static("C2 SW Local linear(0.2) T=8 1M V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 1_000_000, 200_000, 300, cand_per_cell=3.5)
+	if "c2big" in which:
+		run_static("C2x SW Local linear(0.2) T=8 20M V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 20_000_000, 200_000, 300, cand_per_cell=3.5)
+	if "gotoh" in which:
+		run_static("Gotoh Local affine(0.3,0.1) T=8 20M V=50k", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1), 8, 20_000_000, 50_000, 300, cand_per_cell=7.5)
+
+
+if __name__ == "__main__":
+	main()

@@ -109,6 +109,95 @@ __global__ void sim_static_kernel(const float *__restrict__ ehat, int64_t v, int
 	}
 }
 
+
+// 8 lanes per row, 2 rows per lane group: lane `sub` of a group takes the dimensions k = 8m + sub, so
+// the group reads 32 contiguous bytes of each row per step and -- with Qhat staged k-major in shared
+// memory ([d][TPS], TPS padded so that the 8 lanes hit 8 different bank quads) -- one LDS.128 feeds
+// 4 FFMA of each of the 2 rows.  3 shuffle steps reduce a row.  E is read exactly once: HBM-bound.
+template<int TP>
+__global__ void __launch_bounds__(256) sim_static_g8_kernel(const float *__restrict__ ehat, int64_t v, int32_t d,
+	const float *__restrict__ qhat, const int32_t *__restrict__ qid, int32_t t,
+	float *__restrict__ s) {
+
+	constexpr int TPS = TP % 8 == 0 ? TP + 4 : TP;
+	extern __shared__ float q_sh[];   // [d][TPS], columns >= t are zero
+	for (int i = threadIdx.x; i < d * TP; i += blockDim.x) {
+		const int k = i / TP, j = i - k * TP;
+		q_sh[k * TPS + j] = j < t ? qhat[(size_t)j * d + k] : 0.0f;
+	}
+	__syncthreads();
+
+	const int lane = threadIdx.x & 31;
+	const int sub = lane & 7;
+	const int grp = lane >> 3;
+	const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+	const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+
+	for (int64_t row0 = warp * 8; row0 < v; row0 += warps_total * 8) {
+		const int64_t ra = row0 + grp * 2, rb = ra + 1;
+		const float *__restrict__ pa = ehat + (ra < v ? ra : v - 1) * d;
+		const float *__restrict__ pb = ehat + (rb < v ? rb : v - 1) * d;
+		float acc_a[TP], acc_b[TP];
+		#pragma unroll
+		for (int j = 0; j < TP; j++) {
+			acc_a[j] = 0.0f;
+			acc_b[j] = 0.0f;
+		}
+		#pragma unroll 4
+		for (int k = sub; k < d; k += 8) {
+			const float xa = __ldg(pa + k);
+			const float xb = __ldg(pb + k);
+			const float4 *__restrict__ q4 = reinterpret_cast<const float4*>(q_sh + k * TPS);
+			#pragma unroll
+			for (int jq = 0; jq < TP / 4; jq++) {
+				const float4 qv = q4[jq];
+				acc_a[4 * jq + 0] = fmaf(xa, qv.x, acc_a[4 * jq + 0]);
+				acc_a[4 * jq + 1] = fmaf(xa, qv.y, acc_a[4 * jq + 1]);
+				acc_a[4 * jq + 2] = fmaf(xa, qv.z, acc_a[4 * jq + 2]);
+				acc_a[4 * jq + 3] = fmaf(xa, qv.w, acc_a[4 * jq + 3]);
+				acc_b[4 * jq + 0] = fmaf(xb, qv.x, acc_b[4 * jq + 0]);
+				acc_b[4 * jq + 1] = fmaf(xb, qv.y, acc_b[4 * jq + 1]);
+				acc_b[4 * jq + 2] = fmaf(xb, qv.z, acc_b[4 * jq + 2]);
+				acc_b[4 * jq + 3] = fmaf(xb, qv.w, acc_b[4 * jq + 3]);
+			}
+		}
+		#pragma unroll
+		for (int j = 0; j < TP; j++) {
+			#pragma unroll
+			for (int o = 4; o > 0; o >>= 1) {
+				acc_a[j] += __shfl_xor_sync(0xffffffffu, acc_a[j], o);
+				acc_b[j] += __shfl_xor_sync(0xffffffffu, acc_b[j], o);
+			}
+		}
+		if (sub == 0) {
+			#pragma unroll
+			for (int r = 0; r < 2; r++) {
+				const int64_t row = ra + r;
+				if (row < v) {
+					float out[TP];
+					#pragma unroll
+					for (int j = 0; j < TP; j++) {
+						float x = 0.0f;
+						if (j < t) {
+							x = r == 0 ? acc_a[j] : acc_b[j];
+							if (qid[j] == row) {
+								x = 1.0f;                     // identity fix-up, cpp/metric/static.cpp:58-67
+							}
+							x = fminf(fmaxf(x, 0.0f), 1.0f);  // clip, cpp/metric/metric.h:28-30
+						}
+						out[j] = x;
+					}
+					float4 *dst = reinterpret_cast<float4*>(s + row * TP);
+					#pragma unroll
+					for (int jq = 0; jq < TP / 4; jq++) {
+						dst[jq] = make_float4(out[4 * jq], out[4 * jq + 1], out[4 * jq + 2], out[4 * jq + 3]);
+					}
+				}
+			}
+		}
+	}
+}
+
 int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float *d_qhat,
 	const int32_t *d_qid, int32_t t, int32_t tp, float *d_s, cudaStream_t st) {
 
@@ -116,6 +205,27 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 		return 0;
 	}
 	const int warps = 8;
+	{
+		const size_t smem4 = sizeof(float) * (size_t)d * (tp % 8 == 0 ? tp + 4 : tp);
+		int64_t blocks4 = (v + warps * 8 - 1) / (warps * 8);
+		const int64_t cap4 = 148 * (smem4 > 48 * 1024 ? 2 : 6);
+		if (blocks4 > cap4) {
+			blocks4 = cap4;
+		}
+		#define VX_SIM4_CASE(TP) case TP: \
+			cudaFuncSetAttribute(sim_static_g8_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4); \
+			sim_static_g8_kernel<TP><<<(unsigned)blocks4, warps * 32, smem4, st>>>(d_ehat, v, d, d_qhat, d_qid, t, d_s); \
+			return 1;
+		switch (tp) {
+			VX_SIM4_CASE(4)
+			VX_SIM4_CASE(8)
+			VX_SIM4_CASE(12)
+			VX_SIM4_CASE(16)
+			default:
+				return -1;
+		}
+		#undef VX_SIM4_CASE
+	}
 	const size_t smem = sizeof(float) * (size_t)t * d;
 	int64_t blocks = (v + warps - 1) / warps;
 	if (blocks > 148 * 16) {

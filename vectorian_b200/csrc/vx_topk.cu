@@ -245,6 +245,218 @@ __global__ void topk_sort_kernel(TopkWork *w, int k, const uint32_t *__restrict_
 	}
 }
 
+
+// ---------------------------------------------------------------------------
+// All of the above in ONE cooperative launch (grid-wide barriers between the phases): the six
+// histogram / scan levels, the collect pass and the final sort.  At a few million scores the
+// separate launches cost more than the passes themselves.
+// ---------------------------------------------------------------------------
+
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+__device__ __forceinline__ void topk_scan_block0(TopkWork *w, int level, int k, unsigned int *part, int *sel) {
+	// same selection rule as topk_scan_kernel, executed by block 0 (256 threads, 8 bins per thread)
+	const int nb = 1 << c_bits[level];
+	const unsigned int *h = w->hist[level];
+	const unsigned int greater = w->st.greater;
+	const int tid = threadIdx.x;
+	const int per = TOPK_BINS / 256;
+	// thread tid owns bins nb-1-per*tid .. nb-per*(tid+1) (descending)
+	unsigned int cnt[TOPK_BINS / 256];
+	unsigned int sum = 0;
+	#pragma unroll
+	for (int i = 0; i < per; i++) {
+		const int b = nb - 1 - (per * tid + i);
+		cnt[i] = b >= 0 ? h[b] : 0;
+		sum += cnt[i];
+	}
+	// exclusive prefix of `sum` over threads (descending bins): warp scan + cross-warp
+	const int lane = tid & 31, wid = tid >> 5;
+	unsigned int x = sum;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const unsigned int y = __shfl_up_sync(0xffffffffu, x, o);
+		if (lane >= o) {
+			x += y;
+		}
+	}
+	if (lane == 31) {
+		part[wid] = x;
+	}
+	if (tid == 0) {
+		sel[0] = -1;
+		sel[1] = 0;
+	}
+	__syncthreads();
+	unsigned int base = 0;
+	for (int i = 0; i < wid; i++) {
+		base += part[i];
+	}
+	unsigned int above = base + x - sum;   // keys in bins above this thread's first bin
+	#pragma unroll
+	for (int i = 0; i < per; i++) {
+		const int b = nb - 1 - (per * tid + i);
+		if (b >= 0 && greater + above < (unsigned int)k && greater + above + cnt[i] >= (unsigned int)k) {
+			sel[0] = b;
+			sel[1] = (int)above;
+		}
+		above += cnt[i];
+	}
+	__syncthreads();
+	if (tid == 0) {
+		unsigned int total = 0;
+		for (int i = 0; i < 8; i++) {
+			total += part[i];
+		}
+		int bin = sel[0];
+		unsigned int ab = (unsigned int)sel[1];
+		if (bin < 0) {
+			bin = 0;                  // fewer than k keys in total: take everything
+			ab = total - h[0];
+		}
+		const unsigned int g = greater + ab;
+		const unsigned int c = h[bin];
+		w->st.prefix = (w->st.prefix << c_bits[level]) | (unsigned long long)bin;
+		w->st.greater = g;
+		if (g + c <= TOPK_CAP || level == TOPK_LEVELS - 1) {
+			w->st.done = 1;
+			w->st.shift_done = c_shift[level];
+		}
+	}
+	__syncthreads();
+}
+
+__global__ void __launch_bounds__(256) topk_fused_kernel(TopkWork *w, int k, const float *__restrict__ score,
+	const uint32_t *__restrict__ orig, const uint32_t *__restrict__ slot_of, int64_t n_slots, float min_score,
+	uint32_t *__restrict__ out_slots, float *__restrict__ out_scores, int32_t *__restrict__ out_n) {
+
+	cg::grid_group grid = cg::this_grid();
+	extern __shared__ unsigned long long fused_smem[];   // TOPK_CAP keys (block 0's sort); histogram aliases it
+	unsigned int *h = reinterpret_cast<unsigned int*>(fused_smem);
+	__shared__ unsigned int part[8];
+	__shared__ int sel[2];
+
+	for (int level = 0; level < TOPK_LEVELS; level++) {
+		// ---- histogram of the digit of this level among the keys that share the fixed prefix ----
+		for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
+			h[i] = 0;
+		}
+		__syncthreads();
+		const unsigned long long prefix = w->st.prefix;
+		const int shift = c_shift[level];
+		const int bits = c_bits[level];
+		const unsigned int mask = (1u << bits) - 1;
+		const int hi_shift = shift + bits;
+		for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_slots; p += (int64_t)gridDim.x * blockDim.x) {
+			const float sc = score[p];
+			if (!(sc > min_score)) {
+				continue;
+			}
+			const unsigned int sk = score_key(sc);
+			unsigned long long key;
+			if (level < 3) {
+				key = (unsigned long long)sk << 32;
+			} else {
+				if ((unsigned long long)sk != (prefix >> (32 - hi_shift))) {
+					continue;
+				}
+				key = ((unsigned long long)sk << 32) | orig[p];
+			}
+			if (level > 0 && hi_shift < 64 && (key >> hi_shift) != prefix) {
+				continue;
+			}
+			atomicAdd(&h[(unsigned int)(key >> shift) & mask], 1u);
+		}
+		__syncthreads();
+		for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
+			if (h[i]) {
+				atomicAdd(&w->hist[level][i], h[i]);
+			}
+		}
+		__threadfence();
+		grid.sync();
+		if (blockIdx.x == 0) {
+			topk_scan_block0(w, level, k, part, sel);
+			__threadfence();
+		}
+		grid.sync();
+		if (w->st.done) {
+			break;
+		}
+	}
+
+	// ---- collect the survivors ----
+	{
+		const int shift = w->st.shift_done;
+		const unsigned long long thr = w->st.prefix << shift;
+		for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_slots; p += (int64_t)gridDim.x * blockDim.x) {
+			const float sc = score[p];
+			if (!(sc > min_score)) {
+				continue;
+			}
+			const unsigned long long hi = (unsigned long long)score_key(sc) << 32;
+			if ((hi | 0xffffffffull) < thr) {
+				continue;
+			}
+			const unsigned long long key = hi | orig[p];
+			if (key >= thr) {
+				const unsigned int i = atomicAdd(&w->st.n_cand, 1u);
+				if (i < TOPK_CAP) {
+					w->cand[i] = key;
+				}
+			}
+		}
+	}
+	__threadfence();
+	grid.sync();
+	if (blockIdx.x != 0) {
+		return;
+	}
+
+	// ---- block 0: bitonic sort (descending), emit the best k ----
+	unsigned long long *keys = fused_smem;
+	unsigned int n = w->st.n_cand;
+	if (n > TOPK_CAP) {
+		n = TOPK_CAP;
+	}
+	unsigned int m = 1;
+	while (m < n) {
+		m <<= 1;
+	}
+	__syncthreads();
+	for (unsigned int i = threadIdx.x; i < m; i += blockDim.x) {
+		keys[i] = i < n ? w->cand[i] : 0ull;
+	}
+	__syncthreads();
+	for (unsigned int size = 2; size <= m; size <<= 1) {
+		for (unsigned int stride = size >> 1; stride > 0; stride >>= 1) {
+			for (unsigned int i = threadIdx.x; i < m; i += blockDim.x) {
+				const unsigned int j = i ^ stride;
+				if (j > i) {
+					const bool desc = (i & size) == 0;
+					const unsigned long long a = keys[i], b = keys[j];
+					if (desc ? a < b : a > b) {
+						keys[i] = b;
+						keys[j] = a;
+					}
+				}
+			}
+			__syncthreads();
+		}
+	}
+	const unsigned int n_out = n < (unsigned int)k ? n : (unsigned int)k;
+	for (unsigned int i = threadIdx.x; i < n_out; i += blockDim.x) {
+		const unsigned long long key = keys[i];
+		out_slots[i] = slot_of[(uint32_t)(key & 0xffffffffull)];
+		out_scores[i] = key_score((unsigned int)(key >> 32));
+	}
+	if (threadIdx.x == 0) {
+		*out_n = (int32_t)n_out;
+		w->st.n_out = (int)n_out;
+	}
+}
+
 size_t vx_topk_work_bytes(int32_t k) {
 	return sizeof(TopkWork) + (size_t)k * (sizeof(uint32_t) + sizeof(float)) + 64;
 }
@@ -273,6 +485,46 @@ int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkO
 	}
 	if (blocks < 1) {
 		blocks = 1;
+	}
+	{
+		// one cooperative launch when the device supports it (B200 does)
+		static int coop = -1, max_blocks_per_sm = 0;
+		const size_t smem_f = sizeof(unsigned long long) * TOPK_CAP;
+		if (coop < 0) {
+			cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
+			cudaFuncSetAttribute(topk_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f);
+			cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_blocks_per_sm, topk_fused_kernel, 256, smem_f);
+			if (max_blocks_per_sm < 1) {
+				coop = 0;
+			}
+		}
+		// (its 3 blocks per SM cannot keep enough loads in flight for very large inputs: those keep the
+		// multi-launch path, where the passes are HBM-bound and the launch gaps do not matter)
+		if (coop > 0 && c->n_slots <= ((int64_t)4 << 20)) {
+			int per_sm = max_blocks_per_sm > 3 ? 3 : max_blocks_per_sm;
+			int64_t g = (c->n_slots + 255) / 256;
+			if (g > (int64_t)sms * per_sm) {
+				g = (int64_t)sms * per_sm;
+			}
+			if (g < 1) {
+				g = 1;
+			}
+			TopkWork *w_ = w;
+			int k_ = k;
+			const float *score_ = c->d_score;
+			const uint32_t *orig_ = c->d_orig, *slot_of_ = c->d_slot_of;
+			int64_t n_ = c->n_slots;
+			float ms_ = min_score;
+			uint32_t *os_ = out->slots;
+			float *osc_ = out->scores;
+			int32_t *on_ = out->n;
+			void *args[] = {&w_, &k_, &score_, &orig_, &slot_of_, &n_, &ms_, &os_, &osc_, &on_};
+			if (cudaLaunchCooperativeKernel((void*)topk_fused_kernel, dim3((unsigned)g), dim3(256), args, smem_f, st) == cudaSuccess) {
+				return 1;
+			}
+			cudaGetLastError();
+			coop = 0;
+		}
 	}
 	for (int level = 0; level < TOPK_LEVELS; level++) {
 		topk_hist_kernel<<<(unsigned)blocks, 256, 0, st>>>(w, level, c->d_score, c->d_orig, c->n_slots, min_score);
