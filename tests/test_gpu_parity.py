@@ -234,3 +234,31 @@ def test_many_ties_topk(engine, oracle):
 	assert np.all(hits["score"] == hits["score"][0])
 	want = [(49 - i // 100, 99 - i % 100) for i in range(130)]
 	assert [(int(h["doc"]), int(h["slice"])) for h in hits] == want
+
+
+@pytest.mark.parametrize("gap_name", ["linear0.2", "affine", "smooth5"])
+def test_contextual_fast_path(engine, oracle, gap_name):
+	"""Per-token contextual vectors: S_doc formed on the device (ctx_sim_kernel), then the same DP kernels.
+	fp32 scores within 1e-5 of the oracle (the dot products sum in a different order)."""
+	rng = np.random.default_rng(77)
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=1200, t=7, seed=31)
+	n_tok = len(corpus["token_id"])
+	for dim in (32, 30):   # 16-byte vector path and the scalar path
+		centroids = rng.standard_normal((40, dim)).astype(np.float32)
+		x = centroids[corpus["token_id"] % 40] + 0.4 * rng.standard_normal((n_tok, dim)).astype(np.float32)
+		q = centroids[rng.integers(0, 40, size=7)] + 0.4 * rng.standard_normal((7, dim)).astype(np.float32)
+		dc, oc = make_both(engine, oracle, corpus)
+		dc.set_contextual(x)
+		sim = engine.DeviceSim.contextual(q)
+		s = oracle.sim_contextual(x, q)
+		for locality in LOCALITIES:
+			ap, keep = align_params(locality, GAPS[gap_name], dc.max_len, 7)
+			qp, _ = _cabi.make_query_params(max_matches=30, min_score=0.0)
+			g_all = dc.score_all(sim, ap, qp)
+			o_all = oc.score_all(s, ap, qp, n_threads=4, contextual=True)
+			np.testing.assert_allclose(g_all, o_all, rtol=1e-5, atol=2e-6)
+			gpu = dc.search(sim, ap, qp)
+			ref = oc.search(s, ap, qp, n_threads=4, contextual=True)
+			wd, wsl, _, _ = oc.windows()
+			helpers.assert_hits_match(gpu, ref, o_all, wd, wsl, rel_tol=1e-5)
+			assert dc.last_launches() <= 8   # the fast kernels, not the exact per-window scorer

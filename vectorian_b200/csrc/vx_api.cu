@@ -91,6 +91,8 @@ static void corpus_free(vx_corpus *c) {
 	cudaFree(c->d_slot_of);
 	cudaFree(c->d_boost);
 	cudaFree(c->d_ctx);
+	cudaFree(c->d_iota);
+	cudaFree(c->d_sdoc);
 	cudaFree(c->d_score);
 	cudaFree(c->d_work);
 	cudaFree(c->d_scratch);
@@ -386,6 +388,12 @@ extern "C" int vx_corpus_set_contextual(vx_corpus *c, const float *x, int64_t n_
 		cudaFree(c->d_ctx);
 		c->d_ctx = nullptr;
 		if ((rc = dev_alloc(&c->d_ctx, (size_t)c->n_tok_tiled * d)) != VX_OK) break;
+		cudaMemsetAsync(c->d_ctx, 0, sizeof(float) * (size_t)c->n_tok_tiled * d, c->stream);   // padding positions = zero vectors
+		if (!c->d_iota) {
+			if ((rc = dev_alloc(&c->d_iota, (size_t)c->n_tok_tiled)) != VX_OK) break;
+			vx_launch_iota(c->d_iota, c->n_tok_tiled, c->stream);
+		}
+		c->sdoc_of = nullptr;
 		cudaMemcpyAsync(d_raw, x, sizeof(float) * (size_t)n_tok * d, cudaMemcpyHostToDevice, c->stream);
 		cudaMemcpyAsync(d_win_tok, c->win_tok.data(), sizeof(int64_t) * (size_t)c->n_win, cudaMemcpyHostToDevice, c->stream);
 		vx_launch_normalize(d_raw, d_norm, n_tok, d, c->stream);

@@ -75,6 +75,11 @@ struct vx_corpus {
 	float *d_boost = nullptr;        // by slot (optional)
 	float *d_ctx = nullptr;          // contextual vectors, tiled like d_tok: [vx_elem(base128, u, l) * d] (optional)
 	int32_t ctx_dim = 0;
+	int32_t *d_iota = nullptr;       // element index of every tiled token position: the "token ids" of a contextual
+	                                 // query, so that the static DP kernels gather rows of S_doc unchanged
+	float *d_sdoc = nullptr;         // S_doc[n_tok_tiled x tp] of the last contextual query
+	size_t sdoc_bytes = 0;
+	const vx_sim *sdoc_of = nullptr; // the query d_sdoc currently holds (nullptr: none); reset at the start of every search
 	float *d_score = nullptr;        // by slot, scratch of the last search
 	void *d_work = nullptr;          // top-k / traceback workspace
 	size_t work_bytes = 0;
@@ -190,6 +195,10 @@ int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkO
 int vx_launch_normalize(const float *d_in, float *d_out, int64_t rows, int32_t d, cudaStream_t st);
 int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float *d_qhat,
 	const int32_t *d_qid, int32_t t, int32_t tp, float *d_s, cudaStream_t st);
+
+int vx_launch_ctx_sim(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
+	float *d_sdoc, cudaStream_t st);
+int vx_launch_iota(int32_t *d_out, int64_t n, cudaStream_t st);
 
 // vx_pack.cu
 int vx_launch_pack(const int32_t *d_tok_raw, const int8_t *d_pos_raw, const int64_t *d_win_tok,

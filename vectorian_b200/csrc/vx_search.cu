@@ -115,7 +115,8 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 
 	p->t = t;
 	p->k = std::max(qp->max_matches, 1);
-	p->fast = !s->contextual && s->tp <= VX_MAX_T_FAST && !qp->tag_weighted && qp->submatch_weight == 0.0f;
+	// contextual queries take the same fast kernels: S_doc is formed first, d_iota stands in for the ids
+	p->fast = (!s->contextual || c->d_iota) && s->tp <= VX_MAX_T_FAST && !qp->tag_weighted && qp->submatch_weight == 0.0f;
 
 	// ---- workspace layout ----
 	size_t off = 0;
@@ -210,7 +211,47 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 }
 
 // Fill c->d_score for every slot; returns kernels launched or < 0.
+// S_doc = clip01(X . Qhat^T) for every token element (once per query); returns launches or < 0
+static int ensure_sdoc(vx_corpus *c, const vx_sim *s) {
+	if (c->sdoc_of == s) {
+		return 0;
+	}
+	const size_t need = sizeof(float) * (size_t)c->n_tok_tiled * s->tp;
+	if (c->sdoc_bytes < need) {
+		cudaFree(c->d_sdoc);
+		c->d_sdoc = nullptr;
+		c->sdoc_bytes = 0;
+		if (cudaMalloc((void**)&c->d_sdoc, need) != cudaSuccess) {
+			vx_set_error("cudaMalloc of the contextual similarity scratch failed");
+			return -1;
+		}
+		c->sdoc_bytes = need;
+	}
+	const int n = vx_launch_ctx_sim(c->d_ctx, c->n_tok_tiled, c->ctx_dim, s->d_qhat, s->t, s->tp, c->d_sdoc, c->stream);
+	if (n < 0 || cudaGetLastError() != cudaSuccess) {
+		vx_set_error("contextual similarity kernel launch failed");
+		return -1;
+	}
+	c->sdoc_of = s;
+	return n;
+}
+
 static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
+	if (p.fast && s->contextual) {
+		const int n0 = ensure_sdoc(c, s);
+		if (n0 < 0) {
+			return n0;
+		}
+		vx_sim shadow = *s;
+		shadow.contextual = 0;
+		shadow.d_s = c->d_sdoc;
+		shadow.rows = c->n_tok_tiled;
+		int32_t *tok = c->d_tok;
+		c->d_tok = c->d_iota;               // "token id" = element index -> row of S_doc
+		const int n1 = vx_launch_score(c, &shadow, p.ap, p.qp);
+		c->d_tok = tok;
+		return n1 < 0 ? n1 : n0 + n1;
+	}
 	if (p.fast) {
 		return vx_launch_score(c, s, p.ap, p.qp);
 	}
@@ -247,6 +288,7 @@ extern "C" int vx_search(
 	*n_hits = 0;
 	QueryPlan p;
 	VX_TRY(make_plan(c, s, ap, qp, true, &p));
+	c->sdoc_of = nullptr;   // a new vx_sim may reuse the address of a destroyed one: never trust a stale S_doc
 	c->last_launches = 0;
 	c->last_ms[0] = c->last_ms[1] = c->last_ms[2] = 0.0f;
 	if (p.t < 1 || c->n_win == 0) {
@@ -334,6 +376,7 @@ extern "C" int vx_score_all(
 	VX_TRY(vx_require_init());
 	QueryPlan p;
 	VX_TRY(make_plan(c, s, ap, qp, false, &p));
+	c->sdoc_of = nullptr;
 	if (!score_out || n != c->n_win) {
 		VX_FAIL(VX_ERR_INVALID, "score_out must hold one float per window");
 	}

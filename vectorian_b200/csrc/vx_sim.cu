@@ -246,3 +246,148 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 	#undef VX_SIM_CASE
 	return 1;
 }
+
+
+// ---------------------------------------------------------------------------
+// Contextual similarity: S_doc[e, 0..TP) = clip01(X[e, :] . Qhat[j, :]) for every token element e of the
+// tiled corpus (replaces the per-document GEMM of ContextualEmbeddingSimilarityMatrixFactory,
+// vectorian/core/cpp/metric/contextual.cpp:26-63, and ContextualEmbeddingSlice::similarity,
+// cpp/slice/contextual.h:65-67).  FP32 SIMT version: every thread owns two elements, streams their
+// d floats with 16-byte loads (the rows are contiguous, each fetched line is consumed by the same
+// thread over the next 8 loads) and takes Qhat k-major from shared memory as broadcast LDS.128.
+// X is read exactly once: 4*d bytes in, 4*TP bytes out per token.
+// ---------------------------------------------------------------------------
+
+template<int TP>
+__global__ void __launch_bounds__(128) ctx_sim_kernel(const float *__restrict__ x, int64_t n_elem, int32_t d,
+	const float *__restrict__ qhat, int32_t t, float *__restrict__ sdoc) {
+
+	extern __shared__ float q_sh[];   // [d][TP], columns >= t are zero
+	for (int i = threadIdx.x; i < d * TP; i += blockDim.x) {
+		const int k = i / TP, j = i - k * TP;
+		q_sh[i] = j < t ? qhat[(size_t)j * d + k] : 0.0f;
+	}
+	__syncthreads();
+	const float4 *__restrict__ q4 = reinterpret_cast<const float4*>(q_sh);
+	const int d4 = d >> 2;
+
+	for (int64_t base = (int64_t)blockIdx.x * 256; base < n_elem; base += (int64_t)gridDim.x * 256) {
+		const int64_t ea = base + threadIdx.x, eb = ea + 128;
+		const float4 *__restrict__ pa = reinterpret_cast<const float4*>(x + (ea < n_elem ? ea : n_elem - 1) * d);
+		const float4 *__restrict__ pb = reinterpret_cast<const float4*>(x + (eb < n_elem ? eb : n_elem - 1) * d);
+		float acc_a[TP], acc_b[TP];
+		#pragma unroll
+		for (int j = 0; j < TP; j++) {
+			acc_a[j] = 0.0f;
+			acc_b[j] = 0.0f;
+		}
+		#pragma unroll 4
+		for (int i = 0; i < d4; i++) {
+			const float4 xa = __ldg(pa + i);
+			const float4 xb = __ldg(pb + i);
+			const float xa_[4] = {xa.x, xa.y, xa.z, xa.w};
+			const float xb_[4] = {xb.x, xb.y, xb.z, xb.w};
+			#pragma unroll
+			for (int kk = 0; kk < 4; kk++) {
+				#pragma unroll
+				for (int jq = 0; jq < TP / 4; jq++) {
+					const float4 qv = q4[(4 * i + kk) * (TP / 4) + jq];
+					acc_a[4 * jq + 0] = fmaf(xa_[kk], qv.x, acc_a[4 * jq + 0]);
+					acc_a[4 * jq + 1] = fmaf(xa_[kk], qv.y, acc_a[4 * jq + 1]);
+					acc_a[4 * jq + 2] = fmaf(xa_[kk], qv.z, acc_a[4 * jq + 2]);
+					acc_a[4 * jq + 3] = fmaf(xa_[kk], qv.w, acc_a[4 * jq + 3]);
+					acc_b[4 * jq + 0] = fmaf(xb_[kk], qv.x, acc_b[4 * jq + 0]);
+					acc_b[4 * jq + 1] = fmaf(xb_[kk], qv.y, acc_b[4 * jq + 1]);
+					acc_b[4 * jq + 2] = fmaf(xb_[kk], qv.z, acc_b[4 * jq + 2]);
+					acc_b[4 * jq + 3] = fmaf(xb_[kk], qv.w, acc_b[4 * jq + 3]);
+				}
+			}
+		}
+		#pragma unroll
+		for (int r = 0; r < 2; r++) {
+			const int64_t e = r == 0 ? ea : eb;
+			if (e < n_elem) {
+				float4 *dst = reinterpret_cast<float4*>(sdoc + e * TP);
+				#pragma unroll
+				for (int jq = 0; jq < TP / 4; jq++) {
+					float o[4];
+					#pragma unroll
+					for (int c = 0; c < 4; c++) {
+						const float v = r == 0 ? acc_a[4 * jq + c] : acc_b[4 * jq + c];
+						o[c] = 4 * jq + c < t ? fminf(fmaxf(v, 0.0f), 1.0f) : 0.0f;   // clip, contextual.cpp:52-56
+					}
+					dst[jq] = make_float4(o[0], o[1], o[2], o[3]);
+				}
+			}
+		}
+	}
+}
+
+// generic d (not a multiple of 4): one thread per element, scalar loads
+template<int TP>
+__global__ void __launch_bounds__(128) ctx_sim_scalar_kernel(const float *__restrict__ x, int64_t n_elem, int32_t d,
+	const float *__restrict__ qhat, int32_t t, float *__restrict__ sdoc) {
+
+	const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (e >= n_elem) {
+		return;
+	}
+	const float *px = x + e * d;
+	#pragma unroll
+	for (int j = 0; j < TP; j++) {
+		float acc = 0.0f;
+		if (j < t) {
+			for (int k = 0; k < d; k++) {
+				acc = fmaf(px[k], qhat[(size_t)j * d + k], acc);
+			}
+			acc = fminf(fmaxf(acc, 0.0f), 1.0f);
+		}
+		sdoc[e * TP + j] = acc;
+	}
+}
+
+int vx_launch_ctx_sim(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
+	float *d_sdoc, cudaStream_t st) {
+
+	if (n_elem == 0) {
+		return 0;
+	}
+	const bool vec = d % 4 == 0 && (size_t)d * tp * sizeof(float) <= 200 * 1024;
+	const size_t smem = sizeof(float) * (size_t)d * tp;
+	int64_t blocks = (n_elem + 255) / 256;
+	if (blocks > 148 * 8) {
+		blocks = 148 * 8;
+	}
+	#define VX_CTX_CASE(TP) case TP: \
+		if (vec) { \
+			cudaFuncSetAttribute(ctx_sim_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+			ctx_sim_kernel<TP><<<(unsigned)blocks, 128, smem, st>>>(d_x, n_elem, d, d_qhat, t, d_sdoc); \
+		} else { \
+			ctx_sim_scalar_kernel<TP><<<(unsigned)((n_elem + 127) / 128), 128, 0, st>>>(d_x, n_elem, d, d_qhat, t, d_sdoc); \
+		} \
+		break;
+	switch (tp) {
+		VX_CTX_CASE(4)
+		VX_CTX_CASE(8)
+		VX_CTX_CASE(12)
+		VX_CTX_CASE(16)
+		default:
+			return -1;
+	}
+	#undef VX_CTX_CASE
+	return 1;
+}
+
+__global__ void iota_kernel(int32_t *out, int64_t n) {
+	for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+		out[i] = (int32_t)i;
+	}
+}
+
+int vx_launch_iota(int32_t *d_out, int64_t n, cudaStream_t st) {
+	if (n == 0) {
+		return 0;
+	}
+	iota_kernel<<<148 * 8, 256, 0, st>>>(d_out, n);
+	return 1;
+}

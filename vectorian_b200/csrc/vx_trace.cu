@@ -90,6 +90,9 @@ struct TraceArgs {
 };
 
 __device__ __forceinline__ float raw_sim(const TraceArgs &a, size_t tok_index, int32_t id, int j) {
+	if (a.contextual == 2) {
+		return a.s[tok_index * a.tp + j];   // S_doc of this query is resident (formed by ctx_sim_kernel)
+	}
 	if (a.contextual) {
 		const float *x = a.ctx + tok_index * a.ctx_dim;
 		const float *q = a.qhat + (size_t)j * a.ctx_dim;
@@ -704,6 +707,10 @@ int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 		a.qhat = s->d_qhat;
 		a.ctx_dim = s->d;
 		a.contextual = s->contextual;
+		if (s->contextual && c->sdoc_of == s) {
+			a.s = c->d_sdoc;
+			a.contextual = 2;
+		}
 		a.scratch = nullptr;
 		a.scratch_per_item = 0;
 		a.max_len = c->max_len;
@@ -747,6 +754,10 @@ int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 	a.qhat = s->d_qhat;
 	a.ctx_dim = s->d;
 	a.contextual = s->contextual;
+	if (s->contextual && c->sdoc_of == s) {
+		a.s = c->d_sdoc;
+		a.contextual = 2;
+	}
 	a.scratch = (uint8_t*)c->d_scratch;
 	a.scratch_per_item = need / (size_t)max_items;
 	a.max_len = c->max_len;
