@@ -71,6 +71,45 @@ def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand
 	return out
 
 
+def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
+	rng = np.random.default_rng(5)
+	corpus = synthetic.make_corpus(n_sent, 50_000)
+	n_tok = len(corpus["token_id"])
+	x = rng.standard_normal((n_tok, dim), dtype=np.float32)
+	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"], corpus["doc_span_off"])
+	dc.set_contextual(x)
+	r = gaps.resolve_gap_costs(gap, dc.max_len, t)
+	kind = r.pop("gap_kind")
+	ap, keep = _cabi.make_align_params(locality, kind, **r)
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=-1e30)
+	tm = {"dp_ms": [], "topk_ms": [], "traceback_ms": [], "wall_ms": []}
+	for i in range(3 + steps):
+		q = x[rng.integers(0, n_tok, size=t)] + 0.1 * rng.standard_normal((t, dim), dtype=np.float32)
+		t0 = time.perf_counter()
+		sim = engine.DeviceSim.contextual(q)
+		hits, target, dist = dc.search(sim, ap, qp)
+		t1 = time.perf_counter()
+		if i >= 3:
+			lt = dc.last_timing()
+			for kk in ("dp_ms", "topk_ms", "traceback_ms"):
+				tm[kk].append(lt[kk])
+			tm["wall_ms"].append((t1 - t0) * 1e3)
+		sim.close()
+	p = peaks()
+	med = {kk: float(np.median(v)) for kk, v in tm.items()}
+	tp = (t + 3) // 4 * 4
+	lens = corpus["lens"].astype(np.float64)
+	n_pad = float((np.ceil(lens / 4) * 4).sum())   # token positions incl. quad padding (approx.: 32-lane tiles)
+	gemm_bytes = n_pad * (4.0 * dim + 4.0 * tp)
+	out = {"config": name, "sentences": n_sent, "tokens": n_tok, "T": t, "d": dim, "ms": med,
+		"sentences_per_s_device": n_sent / (med["dp_ms"] + med["topk_ms"] + med["traceback_ms"]) * 1e3,
+		"sentences_per_s_e2e": n_sent / med["wall_ms"] * 1e3,
+		"note": "dp_ms = contextual similarity GEMM + DP kernels",
+		"gemm_dp_hbm_frac_lower_bound": gemm_bytes / (med["dp_ms"] * 1e-3) / 1e9 / p["hbm_gbs"], "top_score": float(hits["score"][0])}
+	print(json.dumps(out), flush=True)
+	dc.close()
+
+
 def main():
 	which = sys.argv[1:] or ["c1", "c2"]
 	if "c1" in which:   # the reference's own CPU-runnable case, on the GPU for comparison
@@ -79,6 +118,9 @@ def main():
 		run_static("C2 SW Local linear(0.2) T=8 1M V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 1_000_000, 200_000, 300, cand_per_cell=3.5)
 	if "c2big" in which:
 		run_static("C2x SW Local linear(0.2) T=8 20M V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 20_000_000, 200_000, 300, cand_per_cell=3.5)
+	if "c4" in which:
+		run_contextual("C4 NW Global linear(0.1) contextual d=128 T=8, 200k sentences (1/3 of one GPU's C4 shard)", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 8, 200_000, 128)
+		run_contextual("C4b same, T=16", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 16, 200_000, 128)
 	if "gotoh" in which:
 		run_static("Gotoh Local affine(0.3,0.1) T=8 20M V=50k", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1), 8, 20_000_000, 50_000, 300, cand_per_cell=7.5)
 
