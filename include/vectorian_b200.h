@@ -199,6 +199,12 @@ int vx_last_timing(const vx_corpus *c, float *ms3);
 /* Number of kernels the last vx_search / vx_score_all launched. */
 int vx_last_launches(const vx_corpus *c);
 
+/* Test hook: S_doc[n_elem][tp] = clip01(X . Qhat^T) for host X[n_elem][d] and host Qhat[t][d] (already
+ * normalised), through kernel 0 = FP32 SIMT (ctx_sim_kernel) or 1 = tcgen05 3xTF32 (ctx_mma_kernel);
+ * VX_ERR_INVALID when the tensor-core kernel does not handle the shape.  ms (may be NULL) = kernel time. */
+int vx_debug_ctx_sim(const float *x, int64_t n_elem, int32_t d, const float *qhat, int32_t t, int32_t tp,
+	int32_t kernel, float *sdoc_out, float *ms);
+
 #ifdef __cplusplus
 }
 #endif

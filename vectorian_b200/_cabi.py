@@ -158,6 +158,8 @@ _SIGNATURES = {
 	"vx_abort": (C.c_int, [C.c_void_p]),
 	"vx_last_timing": (C.c_int, [C.c_void_p, c_float_p]),
 	"vx_last_launches": (C.c_int, [C.c_void_p]),
+	"vx_debug_ctx_sim": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
+		C.c_int32, C.c_void_p, C.c_void_p]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES.keys())

@@ -346,11 +346,20 @@ __global__ void __launch_bounds__(128) ctx_sim_scalar_kernel(const float *__rest
 	}
 }
 
+int vx_ctx_force_simt = 0;   // set by the vx_debug_ctx_sim test hook
+
 int vx_launch_ctx_sim(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
 	float *d_sdoc, cudaStream_t st) {
 
 	if (n_elem == 0) {
 		return 0;
+	}
+	static const bool simt_env = getenv("VX_CTX_SIMT") != nullptr;   // A/B switch for measurements
+	if (!simt_env && !vx_ctx_force_simt) {
+		const int rc = vx_launch_ctx_mma(d_x, n_elem, d, d_qhat, t, tp, d_sdoc, st);
+		if (rc != 0) {
+			return rc;
+		}
 	}
 	const bool vec = d % 4 == 0 && (size_t)d * tp * sizeof(float) <= 200 * 1024;
 	const size_t smem = sizeof(float) * (size_t)d * tp;
