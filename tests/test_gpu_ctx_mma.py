@@ -34,7 +34,7 @@ def unit(rng, n, d):
 
 @pytest.mark.parametrize("n,d,t,tp", [
 	(128, 64, 3, 4), (1000, 128, 8, 8), (4096 + 77, 128, 12, 12), (20000, 128, 13, 16),
-	(3000, 256, 16, 16), (128 * 148 * 3 + 5, 64, 5, 8), (777, 192, 7, 8)])
+	(3000, 256, 16, 16), (128 * 148 * 3 + 5, 64, 5, 8), (777, 192, 7, 8), (50, 96, 2, 4), (2500, 768, 9, 12), (129, 32, 1, 4)])
 def test_mma_matches_simt_and_float64(n, d, t, tp):
 	rng = np.random.default_rng(n + d + t)
 	x, q = unit(rng, n, d), unit(rng, t, d)

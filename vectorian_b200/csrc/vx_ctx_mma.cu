@@ -22,18 +22,18 @@
 // Shared-memory ring: 3 stages x 64 KB (hi + lo), Qhat hi / lo resident (d * 128 B).
 
 #include "vx_internal.cuh"
+#include <cuda.h>
 
 namespace {
 
 constexpr int CM_ROWS = 128;                 // tokens per tile (UMMA M)
-constexpr int CM_KS = 64;                    // floats of K per stage: two SWIZZLE_128B sub-tiles
-constexpr int CM_SUB_BYTES = CM_ROWS * 128;  // one sub-tile: 128 rows x 128 B
-constexpr int CM_STAGE_BYTES = 4 * CM_SUB_BYTES;   // hi sub0, hi sub1, lo sub0, lo sub1
-constexpr int CM_NSTAGE = 3;
-constexpr int CM_PRODUCERS = 256;
-constexpr int CM_THREADS = CM_PRODUCERS + 32 + 128;
-constexpr int CM_MAX_D = 256;
-constexpr int CM_ACC_COLS = 128;              // TMEM columns per accumulator set (5 x 16 used), two sets
+constexpr int CM_SUB_BYTES = CM_ROWS * 128;  // one sub-tile: 128 rows x 32 floats
+constexpr int CM_WARP_EPI = 8;               // warps 0-7 convert, 8-11 epilogue, 12 MMA, 13 TMA
+constexpr int CM_WARP_MMA = 12;
+constexpr int CM_WARP_TMA = 13;
+constexpr int CM_THREADS = 14 * 32;
+constexpr int CM_MAX_D = 768;
+constexpr int CM_MAX_RAW = 12;
 constexpr int CM_BCHUNK_BYTES = 32 * 128;    // Qhat per 32-float chunk of K: rows 0-15 = hi, rows 16-31 = lo, 128 B each
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -73,6 +73,36 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint
 		"}" :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
 }
 
+__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
+	asm volatile(
+		"{\n\t"
+		".reg .pred p;\n\t"
+		"setp.ne.b32 p, %4, 0;\n\t"
+		"tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+		"}" :: "r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
+}
+
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+	asm volatile(
+		"tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+		"%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+		:: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+		   "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+		   "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+		   "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+	asm volatile(
+		"tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+		"%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+		: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+		  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+		  "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+		  "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+		: "r"(taddr));
+}
+
 // K-major SWIZZLE_128B shared-memory descriptor (cute/arch/mma_sm100_desc.hpp: start >> 4 in [0,14),
 // LBO [16,30) = 1 (unused for swizzled K-major), SBO [32,46) = 1024 B >> 4 between 8-row groups,
 // version [46,48) = 1, layout [61,64) = 2 = SWIZZLE_128B)
@@ -92,48 +122,58 @@ __device__ __forceinline__ void split_tf32(float x, float &hi, float &lo) {
 }
 
 struct CtxMmaArgs {
-	const float *x;      // [n_elem][d]
 	const float *qhat;   // [t][d]
 	float *sdoc;         // [n_elem][tp]
 	int64_t n_elem;
 	int32_t d, t, tp, n_tiles;
+	int32_t n_raw;       // stages of the raw-X ring in shared memory
 };
 
+// TMEM map (columns): [0, 128) accumulator set 0, [128, 256) set 1 (each: 4 x {16 hi.hi, 16 cross}),
+// [256, 512) ring of 4 A stages, each 32 columns x_hi + 32 columns x_lo of one 32-float chunk of K
+constexpr int CM_ACC_COLS = 128;
+constexpr int CM_A_COL0 = 256;
+constexpr int CM_NA = 4;
+
 template<int TP>
-__global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const CtxMmaArgs a) {
+__global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_constant__ CUtensorMap tmap, const CtxMmaArgs a) {
 	extern __shared__ uint8_t smem_raw[];
 	const uint32_t raw = smem_u32(smem_raw);
 	const uint32_t base = (raw + 1023u) & ~1023u;          // SWIZZLE_128B tiles want 1024-byte alignment
 	uint8_t *const sm = smem_raw + (base - raw);
 
-	const int n_chunk = a.d / 32;                          // 32-float chunks of K
-	const int n_stage_k = a.d / CM_KS;                     // slabs per tile
-	const uint32_t off_b_hi = CM_NSTAGE * CM_STAGE_BYTES;
-	const uint32_t off_b_lo = off_b_hi + 16 * 128;
-	const uint32_t off_bar = off_b_hi + n_chunk * CM_BCHUNK_BYTES;
-	// barriers: full[3], empty[3], acc_full[2], acc_empty[2], then the TMEM base address
-	const uint32_t bar_full = base + off_bar, bar_empty = bar_full + 8 * CM_NSTAGE;
-	const uint32_t bar_acc_full = bar_empty + 8 * CM_NSTAGE, bar_acc_empty = bar_acc_full + 16;
-	uint32_t *const tmem_slot = reinterpret_cast<uint32_t*>(sm + off_bar + 8 * (2 * CM_NSTAGE + 4));
+	const int n_chunk = a.d / 32;                          // 32-float chunks of K = sub-tiles per tile
+	const uint32_t n_raw = a.n_raw;
+	const uint32_t off_b = n_raw * CM_SUB_BYTES;           // Qhat operand: n_chunk x 4 KB
+	const uint32_t off_bar = off_b + n_chunk * CM_BCHUNK_BYTES;
+	// barriers: raw_full[16], raw_empty[16], a_full[4], a_empty[4], acc_full[2], acc_empty[2], TMEM base
+	const uint32_t bar_raw_full = base + off_bar, bar_raw_empty = bar_raw_full + 8 * 16;
+	const uint32_t bar_a_full = bar_raw_empty + 8 * 16, bar_a_empty = bar_a_full + 8 * CM_NA;
+	const uint32_t bar_acc_full = bar_a_empty + 8 * CM_NA, bar_acc_empty = bar_acc_full + 16;
+	uint32_t *const tmem_slot = reinterpret_cast<uint32_t*>(sm + off_bar + 8 * (32 + 2 * CM_NA + 4));
 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
 	if (threadIdx.x == 0) {
-		for (int s = 0; s < CM_NSTAGE; s++) {
-			mbar_init(bar_full + 8 * s, CM_PRODUCERS);
-			mbar_init(bar_empty + 8 * s, 1);
+		for (uint32_t s = 0; s < n_raw; s++) {
+			mbar_init(bar_raw_full + 8 * s, 1);            // the TMA producer's arrive.expect_tx
+			mbar_init(bar_raw_empty + 8 * s, 4);           // one arrive per converter warp of the sub-tile
+		}
+		for (int s = 0; s < CM_NA; s++) {
+			mbar_init(bar_a_full + 8 * s, 4);
+			mbar_init(bar_a_empty + 8 * s, 1);             // tcgen05.commit
 		}
 		for (int b = 0; b < 2; b++) {
-			mbar_init(bar_acc_full + 8 * b, 1);
-			mbar_init(bar_acc_empty + 8 * b, 128);
+			mbar_init(bar_acc_full + 8 * b, 1);            // tcgen05.commit
+			mbar_init(bar_acc_empty + 8 * b, 4);           // one arrive per epilogue warp
 		}
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
-	if (warp == 8) {
-		asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" :: "r"(smem_u32(tmem_slot)) : "memory");
+	if (warp == CM_WARP_MMA) {
+		asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" :: "r"(smem_u32(tmem_slot)) : "memory");
 		asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 	}
-	// Qhat -> hi / lo tiles in the same swizzled K-major layout (rows >= t are zero)
+	// Qhat -> one K-major SWIZZLE_128B operand of 32 rows per chunk: rows 0-15 hi, rows 16-31 lo (rows >= t zero)
 	for (int i = threadIdx.x; i < 16 * a.d; i += CM_THREADS) {
 		const int n = i / a.d, k = i - n * a.d;
 		float hi = 0.0f, lo = 0.0f;
@@ -141,115 +181,121 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const CtxMmaArgs
 			split_tf32(__ldg(a.qhat + (size_t)n * a.d + k), hi, lo);
 		}
 		const int chunk = k >> 5, kc = (k >> 2) & 7, w = k & 3;
-		const uint32_t o = chunk * CM_BCHUNK_BYTES + n * 128 + ((kc ^ (n & 7)) << 4) + 4 * w;
-		*reinterpret_cast<float*>(sm + off_b_hi + o) = hi;
-		*reinterpret_cast<float*>(sm + off_b_lo + o) = lo;
+		const uint32_t o = off_b + chunk * CM_BCHUNK_BYTES + n * 128 + ((kc ^ (n & 7)) << 4) + 4 * w;
+		*reinterpret_cast<float*>(sm + o) = hi;
+		*reinterpret_cast<float*>(sm + o + 16 * 128) = lo;
 	}
 	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 	__syncthreads();
 	asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 	const uint32_t tmem = *tmem_slot;
-	if (warp < 8) {
-		// ---- producers ----
-		// software pipeline: the loads of slab it + 1 are in flight while slab it is split and stored
-		auto load_slab = [&](int tile, int ks, float4 (&v)[8]) {
-			const int64_t row0 = (int64_t)tile * CM_ROWS;
-			#pragma unroll
-			for (int i = 0; i < 8; i++) {
-				const int f = i * CM_PRODUCERS + threadIdx.x;
-				const int row = f >> 4, c16 = f & 15;
-				int64_t e = row0 + row;
-				e = e < a.n_elem ? e : a.n_elem - 1;
-				v[i] = __ldg(reinterpret_cast<const float4*>(a.x + e * a.d + ks * CM_KS) + c16);
-			}
-		};
-		auto store_slab = [&](uint32_t it, const float4 (&v)[8]) {
-			const uint32_t s = it % CM_NSTAGE, ph = (it / CM_NSTAGE) & 1;
-			mbar_wait(bar_empty + 8 * s, ph ^ 1);
-			uint8_t *const st = sm + s * CM_STAGE_BYTES;
-			#pragma unroll
-			for (int i = 0; i < 8; i++) {
-				const int f = i * CM_PRODUCERS + threadIdx.x;
-				const int row = f >> 4, c16 = f & 15;
-				const uint32_t o = (c16 >> 3) * CM_SUB_BYTES + row * 128 + (((c16 & 7) ^ (row & 7)) << 4);
-				float4 hi, lo;
-				split_tf32(v[i].x, hi.x, lo.x);
-				split_tf32(v[i].y, hi.y, lo.y);
-				split_tf32(v[i].z, hi.z, lo.z);
-				split_tf32(v[i].w, hi.w, lo.w);
-				*reinterpret_cast<float4*>(st + o) = hi;
-				*reinterpret_cast<float4*>(st + 2 * CM_SUB_BYTES + o) = lo;
-			}
-			asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-			mbar_arrive(bar_full + 8 * s);
-		};
-		// slab sequence of this CTA: it -> (tile, ks); two slabs are in flight while a third is stored
-		const int my_tiles = blockIdx.x < a.n_tiles ? (a.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-		const uint32_t n_it = (uint32_t)my_tiles * n_stage_k;
-		auto load_it = [&](uint32_t it, float4 (&v)[8]) {
-			if (it < n_it) {
-				const int lt = it / n_stage_k;
-				load_slab(blockIdx.x + lt * gridDim.x, it - lt * n_stage_k, v);
-			}
-		};
-		float4 v0[8], v1[8], v2[8];
-		load_it(0, v0);
-		load_it(1, v1);
-		for (uint32_t it = 0; it < n_it; it += 3) {
-			load_it(it + 2, v2);
-			store_slab(it, v0);
-			if (it + 1 >= n_it) {
-				break;
-			}
-			load_it(it + 3, v0);
-			store_slab(it + 1, v1);
-			if (it + 2 >= n_it) {
-				break;
-			}
-			load_it(it + 4, v1);
-			store_slab(it + 2, v2);
-		}
-	} else if (warp == 8) {
-		// ---- MMA issuer ----
-		uint32_t it = 0, lt = 0;
-		for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, lt++) {
-			const uint32_t b = lt & 1, u = lt >> 1;
-			mbar_wait(bar_acc_empty + 8 * b, (u & 1) ^ 1);
-			asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-			const uint32_t d_tmem = tmem + CM_ACC_COLS * b;
-			for (int ks = 0; ks < n_stage_k; ks++, it++) {
-				const uint32_t s = it % CM_NSTAGE, ph = (it / CM_NSTAGE) & 1;
-				mbar_wait(bar_full + 8 * s, ph);
-				asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-				if (lane == 0) {
-					const uint32_t a_hi = base + s * CM_STAGE_BYTES, a_lo = a_hi + 2 * CM_SUB_BYTES;
-					#pragma unroll
-					for (int sub = 0; sub < 2; sub++) {
-						const uint32_t b_hi = base + off_b_hi + (2 * ks + sub) * CM_BCHUNK_BYTES;
-						#pragma unroll
-						for (int k8 = 0; k8 < 4; k8++) {
-							const uint32_t ao = sub * CM_SUB_BYTES + 32 * k8;
-							const uint64_t dah = umma_desc(a_hi + ao), dal = umma_desc(a_lo + ao);
-							const uint64_t db = umma_desc(b_hi + 32 * k8);
-							// Qhat hi and lo are one 32-row operand: x_hi . [q_hi; q_lo] leaves hi.hi in columns
-							// [0, 16) and hi.lo in [16, 32) of the accumulator; x_lo . q_hi is added to the latter.
-							// The tensor core truncates on every accumulation, so the large hi.hi sums are kept in
-							// four accumulators (one per k8: partial sums stay small) and added in FP32 afterwards.
-							umma_tf32(d_tmem + 32 * k8, dah, db, CM_IDESC_N32, (ks | sub) != 0);
-							umma_tf32(d_tmem + 32 * k8 + 16, dal, db, CM_IDESC_N16, 1);
-						}
-					}
-					umma_commit(bar_empty + 8 * s);
-					if (ks == n_stage_k - 1) {
-						umma_commit(bar_acc_full + 8 * b);
-					}
+	const int my_tiles = (int)blockIdx.x < a.n_tiles ? (a.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+	const uint32_t n_sub = (uint32_t)my_tiles * n_chunk;   // sub-tiles this CTA processes, in order j = lt * n_chunk + c
+	if (warp == CM_WARP_TMA) {
+		// ---- TMA producer: raw FP32 sub-tiles of X, up to n_raw x 16 KB in flight ----
+		if (lane == 0) {
+			uint32_t s = 0, ph = 0;
+			int c = 0, tile = blockIdx.x;
+			for (uint32_t j = 0; j < n_sub; j++) {
+				mbar_wait(bar_raw_empty + 8 * s, ph ^ 1);
+				asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+					:: "r"(bar_raw_full + 8 * s), "r"((uint32_t)CM_SUB_BYTES) : "memory");
+				asm volatile(
+					"cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+					:: "r"(base + s * CM_SUB_BYTES), "l"(&tmap), "r"(32 * c), "r"(tile * CM_ROWS),
+					   "r"(bar_raw_full + 8 * s) : "memory");
+				if (++s == n_raw) {
+					s = 0;
+					ph ^= 1;
 				}
-				__syncwarp();
+				if (++c == n_chunk) {
+					c = 0;
+					tile += gridDim.x;
+				}
+			}
+		}
+	} else if (warp == CM_WARP_MMA) {
+		// ---- MMA issuer: A (x_hi, x_lo) from TMEM, B (Qhat hi | lo) from shared memory ----
+		int c = 0;
+		uint32_t lt = 0;
+		for (uint32_t j = 0; j < n_sub; j++) {
+			const uint32_t b = lt & 1;
+			if (c == 0) {
+				mbar_wait(bar_acc_empty + 8 * b, ((lt >> 1) & 1) ^ 1);
+			}
+			const uint32_t ts = j % CM_NA, pa = (j / CM_NA) & 1;
+			mbar_wait(bar_a_full + 8 * ts, pa);
+			asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+			if (lane == 0) {
+				const uint32_t d_tmem = tmem + CM_ACC_COLS * b;
+				const uint32_t a_t = tmem + CM_A_COL0 + 64 * ts;
+				const uint32_t b_s = base + off_b + c * CM_BCHUNK_BYTES;
+				#pragma unroll
+				for (int k8 = 0; k8 < 4; k8++) {
+					const uint64_t db = umma_desc(b_s + 32 * k8);
+					// x_hi . [q_hi; q_lo] leaves hi.hi in columns [0, 16) and hi.lo in [16, 32) of accumulator k8;
+					// x_lo . q_hi is added to the latter.  The tensor core truncates on every accumulation, so the
+					// large hi.hi sums are spread over four accumulators (partial sums stay small) and added in
+					// FP32 by the epilogue.
+					umma_tf32_ts(d_tmem + 32 * k8, a_t + 8 * k8, db, CM_IDESC_N32, c != 0);
+					umma_tf32_ts(d_tmem + 32 * k8 + 16, a_t + 32 + 8 * k8, db, CM_IDESC_N16, 1);
+				}
+				umma_commit(bar_a_empty + 8 * ts);
+				if (c == n_chunk - 1) {
+					umma_commit(bar_acc_full + 8 * b);
+				}
+			}
+			__syncwarp();
+			if (++c == n_chunk) {
+				c = 0;
+				lt++;
+			}
+		}
+	} else if (warp < CM_WARP_EPI) {
+		// ---- converters: raw X (smem) -> x_hi, x_lo (TMEM); thread = row, two warps per TMEM lane quarter ----
+		const int q = warp & 3, h = warp >> 2;
+		const int row = 32 * q + lane;
+		for (uint32_t j = h; j < n_sub; j += 2) {
+			const uint32_t s = j % n_raw, ph = (j / n_raw) & 1;
+			mbar_wait(bar_raw_full + 8 * s, ph);
+			const uint8_t *const rp = sm + s * CM_SUB_BYTES + row * 128;
+			float4 v[8];
+			#pragma unroll
+			for (int kc = 0; kc < 8; kc++) {
+				v[kc] = *reinterpret_cast<const float4*>(rp + ((kc ^ (row & 7)) << 4));
+			}
+			uint32_t hi[32], lo[32];
+			#pragma unroll
+			for (int kc = 0; kc < 8; kc++) {
+				const float x[4] = {v[kc].x, v[kc].y, v[kc].z, v[kc].w};
+				#pragma unroll
+				for (int w = 0; w < 4; w++) {
+					float fh, fl;
+					split_tf32(x[w], fh, fl);
+					hi[4 * kc + w] = __float_as_uint(fh);
+					lo[4 * kc + w] = __float_as_uint(fl);
+				}
+			}
+			__syncwarp();
+			if (lane == 0) {
+				mbar_arrive(bar_raw_empty + 8 * s);      // the values are in registers: the stage may be refilled
+			}
+			const uint32_t ts = j % CM_NA, pa = (j / CM_NA) & 1;
+			mbar_wait(bar_a_empty + 8 * ts, pa ^ 1);
+			asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+			const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + CM_A_COL0 + 64 * ts;
+			tmem_st32(taddr, hi);
+			tmem_st32(taddr + 32, lo);
+			asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+			asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+			__syncwarp();
+			if (lane == 0) {
+				mbar_arrive(bar_a_full + 8 * ts);
 			}
 		}
 	} else {
-		// ---- epilogue ----
+		// ---- epilogue: accumulators -> clip01 -> S_doc ----
 		const int q = warp & 3;                 // TMEM lane quarter this warp may read
 		uint32_t lt = 0;
 		for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, lt++) {
@@ -261,14 +307,7 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const CtxMmaArgs
 			#pragma unroll
 			for (int g = 0; g < 4; g++) {
 				uint32_t r[32];
-				asm volatile(
-					"tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-					"%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-					: "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-					  "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-					  "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-					  "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-					: "r"(taddr + 32 * g));
+				tmem_ld32(taddr + 32 * g, r);
 				asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 				#pragma unroll
 				for (int j = 0; j < 16; j++) {
@@ -277,7 +316,10 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const CtxMmaArgs
 				}
 			}
 			asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-			mbar_arrive(bar_acc_empty + 8 * b);
+			__syncwarp();
+			if (lane == 0) {
+				mbar_arrive(bar_acc_empty + 8 * b);
+			}
 			const int64_t e = (int64_t)tile * CM_ROWS + 32 * q + lane;
 			if (e < a.n_elem) {
 				float4 *const dst = reinterpret_cast<float4*>(a.sdoc + e * TP);
@@ -288,37 +330,61 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const CtxMmaArgs
 					for (int w = 0; w < 4; w++) {
 						o_[w] = fminf(fmaxf(hh[4 * jq + w] + cr[4 * jq + w], 0.0f), 1.0f);
 					}
-					const float4 o = make_float4(o_[0], o_[1], o_[2], o_[3]);
-					dst[jq] = o;
+					dst[jq] = make_float4(o_[0], o_[1], o_[2], o_[3]);
 				}
 			}
 		}
 	}
 	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 	__syncthreads();
-	if (warp == 8) {
-		asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" :: "r"(tmem) : "memory");
+	if (warp == CM_WARP_MMA) {
+		asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(tmem) : "memory");
 	}
 }
 
 } // namespace
 
+typedef CUresult (*vx_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+	const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+	CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
 // returns 1 when the tensor-core kernel was launched, 0 when the shape is outside what it handles
-// (the caller then uses the SIMT kernel), -1 on an unsupported tp
+// (the caller then uses the SIMT kernel), -1 on an unsupported tp or a failed tensor-map encode
 int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
 	float *d_sdoc, cudaStream_t st) {
 
-	if (d % CM_KS != 0 || d > CM_MAX_D || n_elem < CM_ROWS) {
+	if (d % 32 != 0 || d > CM_MAX_D || n_elem <= 0 || (reinterpret_cast<uintptr_t>(d_x) & 15) != 0) {
 		return 0;
 	}
 	static int sms = 0;
+	static vx_tmap_encode_fn encode = nullptr;
 	if (sms == 0) {
 		int dev = 0;
 		cudaGetDevice(&dev);
 		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+		void *fn = nullptr;
+		cudaDriverEntryPointQueryResult qres;
+		if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+			qres != cudaDriverEntryPointSuccess) {
+			fn = nullptr;
+		}
+		encode = reinterpret_cast<vx_tmap_encode_fn>(fn);
+	}
+	if (!encode) {
+		return 0;
+	}
+	// X as a 2-d tensor [n_elem][d], box = 32 floats x 128 rows, 128-byte swizzle; rows past n_elem read as zero
+	CUtensorMap tmap;
+	const cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)n_elem};
+	const cuuint64_t gstride[1] = {(cuuint64_t)d * sizeof(float)};
+	const cuuint32_t box[2] = {32, CM_ROWS};
+	const cuuint32_t estr[2] = {1, 1};
+	if (encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(d_x), gdim, gstride, box, estr,
+		CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+		CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+		return -1;
 	}
 	CtxMmaArgs a;
-	a.x = d_x;
 	a.qhat = d_qhat;
 	a.sdoc = d_sdoc;
 	a.n_elem = n_elem;
@@ -326,11 +392,15 @@ int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *
 	a.t = t;
 	a.tp = tp;
 	a.n_tiles = (int32_t)((n_elem + CM_ROWS - 1) / CM_ROWS);
-	const size_t smem = 1024 + (size_t)CM_NSTAGE * CM_STAGE_BYTES + (size_t)(d / 32) * CM_BCHUNK_BYTES + 128;
+	const size_t fixed = 1024 + (size_t)(d / 32) * CM_BCHUNK_BYTES + 512;
+	int n_raw = (int)((227 * 1024 - fixed) / CM_SUB_BYTES);
+	n_raw = n_raw > CM_MAX_RAW ? CM_MAX_RAW : n_raw;
+	a.n_raw = n_raw;
+	const size_t smem = fixed + (size_t)n_raw * CM_SUB_BYTES;
 	const int grid = a.n_tiles < sms ? a.n_tiles : sms;
 	#define VX_CM_CASE(TP) case TP: \
 		cudaFuncSetAttribute(ctx_mma_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-		ctx_mma_kernel<TP><<<grid, CM_THREADS, smem, st>>>(a); \
+		ctx_mma_kernel<TP><<<grid, CM_THREADS, smem, st>>>(tmap, a); \
 		break;
 	switch (tp) {
 		VX_CM_CASE(4)
