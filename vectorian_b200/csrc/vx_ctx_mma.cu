@@ -10,16 +10,21 @@
 //   x = x_hi + x_lo,  q = q_hi + q_lo,  x.q ~= x_hi.q_hi + x_lo.q_hi + x_hi.q_lo      (|dropped| <= 2^-22 |x||q|)
 // with hi = x rounded to TF32 and lo = x - hi (exact in FP32).
 //
-// One persistent CTA per SM, warp-specialised:
-//   warps 0-7   producers: coalesced LDG.128 of a [128 rows x 64 floats] slab of X, split into hi / lo in
-//               registers and stored to shared memory in the K-major SWIZZLE_128B canonical layout
-//               (what a TMA box load with CU_TENSOR_MAP_SWIZZLE_128B would have produced, but the split has
-//               to pass through registers anyway, so the loads do as well)
-//   warp  8     MMA issuer: 24 x tcgen05.mma.kind::tf32 (M=128, N=16, K=8) per slab into TMEM accumulators
-//               (two ping-pong sets of five 16-column accumulators), tcgen05.commit onto mbarriers
-//   warps 9-12  epilogue: tcgen05.ld of the 128 x 16 accumulator (one TMEM lane quarter per warp), clip to
-//               [0, 1], TP floats per row to S_doc
-// Shared-memory ring: 3 stages x 64 KB (hi + lo), Qhat hi / lo resident (d * 128 B).
+// One persistent CTA per SM (17 warps), warp-specialised; a tile is 128 tokens, a sub-tile 32 floats of K:
+//   warp  12    TMA producer: cp.async.bulk.tensor (SWIZZLE_128B box of 128 rows x 32 floats = 16 KB) of raw X
+//               into a ring of up to 12 stages.  ~190 KB in flight per SM is what it takes to stream HBM at
+//               full rate from one CTA per SM (scripts/ubench/readbw.cu: 64 KB in flight = 3.9 TB/s,
+//               128 KB = 6.4, 256 KB = 7.2), far more than registers can hold
+//   warps 0-7   converters: thread = row; LDS.128 of the row's 128 bytes (conflict-free thanks to the swizzle),
+//               split into hi / lo in registers, tcgen05.st (32x32b.x32) into a 4-stage A ring in TMEM.
+//               The stream never goes back to shared memory, which keeps smem traffic at 2 x 4*d bytes per token
+//   warps 13-16 MMA issuers, one per 8-float k-step: tcgen05.mma.kind::tf32 with A from TMEM (M=128, K=8) and
+//               Qhat from shared memory as one stacked operand [q_hi; q_lo] (N=32) resp. q_hi (N=16);
+//               tcgen05.commit onto mbarriers frees the A stage / publishes the accumulators
+//   warps 8-11  epilogue: tcgen05.ld of the accumulators (one TMEM lane quarter per warp, two ping-pong sets),
+//               FP32 sum of the partial accumulators, clip to [0, 1], TP floats per row to S_doc
+// Measured (5M tokens, d=128): 0.42-0.45 ms = 6.4 TB/s = 98% of the measured HBM copy rate; the FP32 SIMT
+// kernel needs 0.73 ms (T<=8) / 1.12 ms (T<=16).  Max error vs float64 1e-7 (SIMT FP32: 2.5e-7).
 
 #include "vx_internal.cuh"
 #include <cuda.h>
@@ -28,10 +33,10 @@ namespace {
 
 constexpr int CM_ROWS = 128;                 // tokens per tile (UMMA M)
 constexpr int CM_SUB_BYTES = CM_ROWS * 128;  // one sub-tile: 128 rows x 32 floats
-constexpr int CM_WARP_EPI = 8;               // warps 0-7 convert, 8-11 epilogue, 12 MMA, 13 TMA
-constexpr int CM_WARP_MMA = 12;
-constexpr int CM_WARP_TMA = 13;
-constexpr int CM_THREADS = 14 * 32;
+constexpr int CM_WARP_EPI = 8;               // warps 0-7 convert, 8-11 epilogue, 12 TMA, 13-16 MMA
+constexpr int CM_WARP_TMA = 12;
+constexpr int CM_WARP_MMA = 13;
+constexpr int CM_THREADS = 17 * 32;
 constexpr int CM_MAX_D = 768;
 constexpr int CM_MAX_RAW = 12;
 constexpr int CM_BCHUNK_BYTES = 32 * 128;    // Qhat per 32-float chunk of K: rows 0-15 = hi, rows 16-31 = lo, 128 B each
@@ -161,10 +166,10 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 		}
 		for (int s = 0; s < CM_NA; s++) {
 			mbar_init(bar_a_full + 8 * s, 4);
-			mbar_init(bar_a_empty + 8 * s, 1);             // tcgen05.commit
+			mbar_init(bar_a_empty + 8 * s, 4);             // tcgen05.commit of each MMA warp
 		}
 		for (int b = 0; b < 2; b++) {
-			mbar_init(bar_acc_full + 8 * b, 1);            // tcgen05.commit
+			mbar_init(bar_acc_full + 8 * b, 4);            // tcgen05.commit of each MMA warp
 			mbar_init(bar_acc_empty + 8 * b, 4);           // one arrive per epilogue warp
 		}
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -215,32 +220,30 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 				}
 			}
 		}
-	} else if (warp == CM_WARP_MMA) {
-		// ---- MMA issuer: A (x_hi, x_lo) from TMEM, B (Qhat hi | lo) from shared memory ----
+	} else if (warp >= CM_WARP_MMA) {
+		// ---- four MMA issuers, one per 8-float step k8 of a sub-tile: A (x_hi, x_lo) from TMEM, B (Qhat hi | lo)
+		// from shared memory.  One warp issuing all eight MMAs of a sub-tile was the bottleneck (~130 mostly
+		// uniform-datapath instructions per sub-tile); the k8 steps use disjoint accumulators, so they split cleanly.
+		const int k8 = warp - CM_WARP_MMA;
+		// x_hi . [q_hi; q_lo] leaves hi.hi in columns [0, 16) and hi.lo in [16, 32) of accumulator k8; x_lo . q_hi is
+		// added to the latter.  The tensor core truncates on every accumulation, so the large hi.hi sums are spread
+		// over four accumulators (partial sums stay small) and added in FP32 by the epilogue.
+		const uint64_t db0 = umma_desc(base + off_b + 32 * k8);
 		int c = 0;
-		uint32_t lt = 0;
+		uint32_t lt = 0, ts = 0, pa = 0;
 		for (uint32_t j = 0; j < n_sub; j++) {
 			const uint32_t b = lt & 1;
 			if (c == 0) {
 				mbar_wait(bar_acc_empty + 8 * b, ((lt >> 1) & 1) ^ 1);
 			}
-			const uint32_t ts = j % CM_NA, pa = (j / CM_NA) & 1;
 			mbar_wait(bar_a_full + 8 * ts, pa);
 			asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 			if (lane == 0) {
-				const uint32_t d_tmem = tmem + CM_ACC_COLS * b;
-				const uint32_t a_t = tmem + CM_A_COL0 + 64 * ts;
-				const uint32_t b_s = base + off_b + c * CM_BCHUNK_BYTES;
-				#pragma unroll
-				for (int k8 = 0; k8 < 4; k8++) {
-					const uint64_t db = umma_desc(b_s + 32 * k8);
-					// x_hi . [q_hi; q_lo] leaves hi.hi in columns [0, 16) and hi.lo in [16, 32) of accumulator k8;
-					// x_lo . q_hi is added to the latter.  The tensor core truncates on every accumulation, so the
-					// large hi.hi sums are spread over four accumulators (partial sums stay small) and added in
-					// FP32 by the epilogue.
-					umma_tf32_ts(d_tmem + 32 * k8, a_t + 8 * k8, db, CM_IDESC_N32, c != 0);
-					umma_tf32_ts(d_tmem + 32 * k8 + 16, a_t + 32 + 8 * k8, db, CM_IDESC_N16, 1);
-				}
+				const uint32_t d_t = tmem + CM_ACC_COLS * b + 32 * k8;
+				const uint32_t a_t = tmem + CM_A_COL0 + 64 * ts + 8 * k8;
+				const uint64_t db = db0 + (uint64_t)(c * (CM_BCHUNK_BYTES >> 4));
+				umma_tf32_ts(d_t, a_t, db, CM_IDESC_N32, c != 0);
+				umma_tf32_ts(d_t + 16, a_t + 32, db, CM_IDESC_N16, 1);
 				umma_commit(bar_a_empty + 8 * ts);
 				if (c == n_chunk - 1) {
 					umma_commit(bar_acc_full + 8 * b);
@@ -250,6 +253,10 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 			if (++c == n_chunk) {
 				c = 0;
 				lt++;
+			}
+			if (++ts == CM_NA) {
+				ts = 0;
+				pa ^= 1;
 			}
 		}
 	} else if (warp < CM_WARP_EPI) {
