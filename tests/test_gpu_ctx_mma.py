@@ -34,7 +34,8 @@ def unit(rng, n, d):
 
 @pytest.mark.parametrize("n,d,t,tp", [
 	(128, 64, 3, 4), (1000, 128, 8, 8), (4096 + 77, 128, 12, 12), (20000, 128, 13, 16),
-	(3000, 256, 16, 16), (128 * 148 * 3 + 5, 64, 5, 8), (777, 192, 7, 8), (50, 96, 2, 4), (2500, 768, 9, 12), (129, 32, 1, 4)])
+	(3000, 256, 16, 16), (128 * 148 * 3 + 5, 64, 5, 8), (777, 192, 7, 8), (50, 96, 2, 4), (2500, 768, 9, 12), (129, 32, 1, 4),
+	(5000, 300, 8, 8), (600, 100, 4, 4), (300, 20, 3, 4)])
 def test_mma_matches_simt_and_float64(n, d, t, tp):
 	rng = np.random.default_rng(n + d + t)
 	x, q = unit(rng, n, d), unit(rng, t, d)
@@ -52,7 +53,7 @@ def test_mma_matches_simt_and_float64(n, d, t, tp):
 
 def test_mma_rejects_other_shapes():
 	rng = np.random.default_rng(0)
-	x, q = unit(rng, 256, 100), unit(rng, 4, 100)
+	x, q = unit(rng, 256, 102), unit(rng, 4, 102)    # rows not 16-byte aligned: no TMA
 	with pytest.raises(RuntimeError):
 		ctx_sim(x, q, 4, 1)
 	simt, _ = ctx_sim(x, q, 4, 0)

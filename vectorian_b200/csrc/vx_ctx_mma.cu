@@ -128,6 +128,7 @@ __device__ __forceinline__ void split_tf32(float x, float &hi, float &lo) {
 
 struct CtxMmaArgs {
 	const float *qhat;   // [t][d]
+	const int32_t *qid;  // static embeddings: vocabulary id of query token j (identity fix-up), else nullptr
 	float *sdoc;         // [n_elem][tp]
 	int64_t n_elem;
 	int32_t d, t, tp, n_tiles;
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 	const uint32_t base = (raw + 1023u) & ~1023u;          // SWIZZLE_128B tiles want 1024-byte alignment
 	uint8_t *const sm = smem_raw + (base - raw);
 
-	const int n_chunk = a.d / 32;                          // 32-float chunks of K = sub-tiles per tile
+	const int n_chunk = (a.d + 31) / 32;                   // 32-float chunks of K = sub-tiles per tile (the last may be partial)
 	const uint32_t n_raw = a.n_raw;
 	const uint32_t off_b = n_raw * CM_SUB_BYTES;           // Qhat operand: n_chunk x 4 KB
 	const uint32_t off_bar = off_b + n_chunk * CM_BCHUNK_BYTES;
@@ -179,16 +180,21 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 		asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 	}
 	// Qhat -> one K-major SWIZZLE_128B operand of 32 rows per chunk: rows 0-15 hi, rows 16-31 lo (rows >= t zero)
-	for (int i = threadIdx.x; i < 16 * a.d; i += CM_THREADS) {
-		const int n = i / a.d, k = i - n * a.d;
+	const int d_pad = 32 * n_chunk;                        // X columns >= d read as zero (TMA out-of-bounds fill)
+	for (int i = threadIdx.x; i < 16 * d_pad; i += CM_THREADS) {
+		const int n = i / d_pad, k = i - n * d_pad;
 		float hi = 0.0f, lo = 0.0f;
-		if (n < a.t) {
+		if (n < a.t && k < a.d) {
 			split_tf32(__ldg(a.qhat + (size_t)n * a.d + k), hi, lo);
 		}
 		const int chunk = k >> 5, kc = (k >> 2) & 7, w = k & 3;
 		const uint32_t o = off_b + chunk * CM_BCHUNK_BYTES + n * 128 + ((kc ^ (n & 7)) << 4) + 4 * w;
 		*reinterpret_cast<float*>(sm + o) = hi;
 		*reinterpret_cast<float*>(sm + o + 16 * 128) = lo;
+	}
+	if (threadIdx.x < 16) {
+		reinterpret_cast<int32_t*>(sm + off_bar + 384)[threadIdx.x] =
+			a.qid && (int)threadIdx.x < a.t ? __ldg(a.qid + threadIdx.x) : -1;
 	}
 	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -304,6 +310,7 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 	} else {
 		// ---- epilogue: accumulators -> clip01 -> S_doc ----
 		const int q = warp & 3;                 // TMEM lane quarter this warp may read
+		const int32_t *const qid = reinterpret_cast<const int32_t*>(sm + off_bar + 384);   // filled before the CTA barrier
 		uint32_t lt = 0;
 		for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, lt++) {
 			const uint32_t b = lt & 1, u = lt >> 1;
@@ -335,7 +342,9 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 					float o_[4];
 					#pragma unroll
 					for (int w = 0; w < 4; w++) {
-						o_[w] = fminf(fmaxf(hh[4 * jq + w] + cr[4 * jq + w], 0.0f), 1.0f);
+						// identity fix-up (cpp/metric/static.cpp:58-67), then clip (cpp/metric/metric.h:28-30)
+						const float x = (int64_t)qid[4 * jq + w] == e ? 1.0f : hh[4 * jq + w] + cr[4 * jq + w];
+						o_[w] = fminf(fmaxf(x, 0.0f), 1.0f);
 					}
 					dst[jq] = make_float4(o_[0], o_[1], o_[2], o_[3]);
 				}
@@ -357,10 +366,10 @@ typedef CUresult (*vx_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint3
 
 // returns 1 when the tensor-core kernel was launched, 0 when the shape is outside what it handles
 // (the caller then uses the SIMT kernel), -1 on an unsupported tp or a failed tensor-map encode
-int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
-	float *d_sdoc, cudaStream_t st) {
+int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,
+	int32_t t, int32_t tp, float *d_sdoc, cudaStream_t st) {
 
-	if (d % 32 != 0 || d > CM_MAX_D || n_elem <= 0 || (reinterpret_cast<uintptr_t>(d_x) & 15) != 0) {
+	if (d % 4 != 0 || d > CM_MAX_D || n_elem <= 0 || (reinterpret_cast<uintptr_t>(d_x) & 15) != 0) {
 		return 0;
 	}
 	static int sms = 0;
@@ -393,13 +402,14 @@ int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *
 	}
 	CtxMmaArgs a;
 	a.qhat = d_qhat;
+	a.qid = d_qid;
 	a.sdoc = d_sdoc;
 	a.n_elem = n_elem;
 	a.d = d;
 	a.t = t;
 	a.tp = tp;
 	a.n_tiles = (int32_t)((n_elem + CM_ROWS - 1) / CM_ROWS);
-	const size_t fixed = 1024 + (size_t)(d / 32) * CM_BCHUNK_BYTES + 512;
+	const size_t fixed = 1024 + (size_t)((d + 31) / 32) * CM_BCHUNK_BYTES + 512;
 	int n_raw = (int)((227 * 1024 - fixed) / CM_SUB_BYTES);
 	n_raw = n_raw > CM_MAX_RAW ? CM_MAX_RAW : n_raw;
 	a.n_raw = n_raw;
@@ -442,7 +452,7 @@ extern "C" int vx_debug_ctx_sim(const float *x, int64_t n_elem, int32_t d, const
 	for (int rep = 0; rep < 2; rep++) {   // the second launch is the timed one
 		VX_CUDA(cudaEventRecord(e0, 0));
 		if (kernel == 1) {
-			rc = vx_launch_ctx_mma(d_x, n_elem, d, d_q, t, tp, d_s, 0);
+			rc = vx_launch_ctx_mma(d_x, n_elem, d, d_q, nullptr, t, tp, d_s, 0);
 		} else {
 			vx_ctx_force_simt = 1;
 			rc = vx_launch_ctx_sim(d_x, n_elem, d, d_q, t, tp, d_s, 0);

@@ -197,8 +197,8 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 	const int32_t *d_qid, int32_t t, int32_t tp, float *d_s, cudaStream_t st);
 
 extern int vx_ctx_force_simt;
-int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
-	float *d_sdoc, cudaStream_t st);
+int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,
+	int32_t t, int32_t tp, float *d_sdoc, cudaStream_t st);
 int vx_launch_ctx_sim(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
 	float *d_sdoc, cudaStream_t st);
 int vx_launch_iota(int32_t *d_out, int64_t n, cudaStream_t st);

@@ -204,6 +204,14 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 	if (v == 0) {
 		return 0;
 	}
+	// tensor-core path (vx_ctx_mma.cu): the same GEMM with the identity fix-up in the epilogue
+	static const bool simt_env = getenv("VX_SIM_SIMT") != nullptr;   // A/B switch for measurements
+	if (!simt_env && !vx_ctx_force_simt) {
+		const int rc = vx_launch_ctx_mma(d_ehat, v, d, d_qhat, d_qid, t, tp, d_s, st);
+		if (rc != 0) {
+			return rc;
+		}
+	}
 	const int warps = 8;
 	{
 		const size_t smem4 = sizeof(float) * (size_t)d * (tp % 8 == 0 ? tp + 4 : tp);
@@ -356,7 +364,7 @@ int vx_launch_ctx_sim(const float *d_x, int64_t n_elem, int32_t d, const float *
 	}
 	static const bool simt_env = getenv("VX_CTX_SIMT") != nullptr;   // A/B switch for measurements
 	if (!simt_env && !vx_ctx_force_simt) {
-		const int rc = vx_launch_ctx_mma(d_x, n_elem, d, d_qhat, t, tp, d_sdoc, st);
+		const int rc = vx_launch_ctx_mma(d_x, n_elem, d, d_qhat, nullptr, t, tp, d_sdoc, st);
 		if (rc != 0) {
 			return rc;
 		}
