@@ -18,5 +18,5 @@ $PCMD > $OUT/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv $PCMD > $OUT/ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
 $PCMD > $OUT/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:$KREGEX -s 3 -c 2 -o $OUT/prof $PCMD > $OUT/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:$KREGEX -s 5 -c 5 -o $OUT/prof $PCMD > $OUT/ncu_full.log 2>&1
 echo "ncu full rc=$?"; tail -3 $OUT/ncu_full.log
