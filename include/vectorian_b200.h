@@ -185,6 +185,16 @@ int vx_search(
 	const vx_align_params *ap, const vx_query_params *qp,
 	vx_hit *hits, int16_t *target, float *dist, int32_t *n_hits);
 
+/* Interactive parameter sweep (BASELINE.json config 5): n_sims queries x n_aps alignment settings over the resident
+ * corpus in ONE call -- the reference runs Session.partition(..).index(..).find(query, options) once per pair
+ * (vectorian/index.py:530-560), re-entering Query::match (cpp/query.cpp:10-30) each time.  All kernels of all pairs
+ * are enqueued back to back; the host waits once.  Pair p = q * n_aps + a writes n_hits[p] rows at
+ * hits[p * max_matches ..], target / dist[(p * max_matches + i) * t_stride ..] (t_stride >= every query's length). */
+int vx_search_batch(
+	vx_corpus *c, const vx_sim *const *sims, int32_t n_sims,
+	const vx_align_params *aps, int32_t n_aps, const vx_query_params *qp, int32_t t_stride,
+	vx_hit *hits, int16_t *target, float *dist, int32_t *n_hits);
+
 /* Score every window (debug hook "alignment" / tests): score[n_windows] in window order, 0-filled where len<1. */
 int vx_score_all(
 	vx_corpus *c, const vx_sim *s,

@@ -262,3 +262,36 @@ def test_contextual_fast_path(engine, oracle, gap_name):
 			wd, wsl, _, _ = oc.windows()
 			helpers.assert_hits_match(gpu, ref, o_all, wd, wsl, rel_tol=1e-5)
 			assert dc.last_launches() <= 8   # the fast kernels, not the exact per-window scorer
+
+
+def test_search_batch_equals_single_searches(engine, oracle):
+	"""vx_search_batch (parameter sweep, BASELINE config 5): queries x settings in one call give exactly the rows of
+	the individual vx_search calls, for queries of different lengths and for every gap kind."""
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=2500, t=8, seed=11)
+	dc, oc = make_both(engine, oracle, corpus)
+	de = engine.DeviceEmbedding(emb)
+	rng = np.random.default_rng(3)
+	sims = []
+	for t in (8, 5, 12, 3):
+		ids = rng.choice(emb.shape[0], size=t, replace=False).astype(np.int32)
+		sims.append(engine.DeviceSim.static(de, ids, emb[ids]))
+	aps, keeps = [], []
+	for gap_name in ("linear0.2", "none", "affine", "smooth5"):
+		for locality in (_cabi.VX_LOCAL, _cabi.VX_GLOBAL):
+			ap, keep = align_params(locality, GAPS[gap_name], dc.max_len, 12)
+			aps.append(ap)
+			keeps.append(keep)
+	qp, _ = _cabi.make_query_params(max_matches=20, min_score=0.0)
+	batch = dc.search_batch(sims, aps, qp)
+	assert len(batch) == len(sims) and len(batch[0]) == len(aps)
+	for q, sim in enumerate(sims):
+		for a, ap in enumerate(aps):
+			hits, target, dist = dc.search(sim, ap, qp)
+			b_hits, b_target, b_dist = batch[q][a]
+			assert len(b_hits) == len(hits)
+			for f in ("score", "score_max", "doc", "slice"):
+				np.testing.assert_array_equal(b_hits[f], hits[f])
+			np.testing.assert_array_equal(b_target, target)
+			np.testing.assert_array_equal(b_dist, dist)
+	# empty batch
+	assert dc.search_batch([], aps, qp) == []

@@ -152,6 +152,9 @@ _SIGNATURES = {
 	"vx_search": (C.c_int, [
 		C.c_void_p, C.c_void_p, C.POINTER(AlignParams), C.POINTER(QueryParams),
 		C.POINTER(Hit), c_int16_p, c_float_p, c_int32_p]),
+	"vx_search_batch": (C.c_int, [
+		C.c_void_p, C.POINTER(C.c_void_p), C.c_int32, C.POINTER(AlignParams), C.c_int32, C.POINTER(QueryParams), C.c_int32,
+		C.POINTER(Hit), c_int16_p, c_float_p, c_int32_p]),
 	"vx_score_all": (C.c_int, [
 		C.c_void_p, C.c_void_p, C.POINTER(AlignParams), C.POINTER(QueryParams),
 		c_float_p, C.c_int64]),

@@ -4,6 +4,7 @@
 // (vectorian/core/cpp/query.cpp:10-30) -> ResultSet::extend -> best_n for the whole corpus at once:
 //   DP scores for every window -> device top-k -> traceback of the winners -> one D2H copy.
 #include "vx_internal.cuh"
+#include <vector>
 
 #include <algorithm>
 #include <cmath>
@@ -30,8 +31,51 @@ struct QueryPlan {
 	int8_t *tpos;
 	// result block (device) and its size
 	uint8_t *res;
+	uint8_t *h_res;      // pinned host copy of the result block
 	size_t res_bytes;
 	size_t off_score, off_score_max, off_win, off_target, off_dist, off_n;
+};
+
+// device block of one plan: gap tables, tag weights, result rows
+struct BlockLayout {
+	size_t off_gs, off_gt, off_tw, off_tpos, off_res, bytes;
+	size_t off_score, off_score_max, off_win, off_target, off_dist, off_n, res_bytes;
+};
+
+static BlockLayout block_layout(int32_t t, int32_t k, size_t n_ws, size_t n_wt) {
+	BlockLayout b;
+	const size_t tt = (size_t)std::max(t, 1);
+	size_t off = 0;
+	b.off_gs = off;
+	off = align_up(off + sizeof(float) * n_ws, 256);
+	b.off_gt = off;
+	off = align_up(off + sizeof(float) * n_wt, 256);
+	b.off_tw = off;
+	off = align_up(off + sizeof(float) * tt, 256);
+	b.off_tpos = off;
+	off = align_up(off + tt, 256);
+	b.off_res = off;
+	size_t r = 0;
+	b.off_score = r;
+	r = align_up(r + sizeof(float) * k, 16);
+	b.off_score_max = r;
+	r = align_up(r + sizeof(float) * k, 16);
+	b.off_win = r;
+	r = align_up(r + sizeof(uint32_t) * k, 16);
+	b.off_target = r;
+	r = align_up(r + sizeof(int16_t) * (size_t)k * tt, 16);
+	b.off_dist = r;
+	r = align_up(r + sizeof(float) * (size_t)k * tt, 16);
+	b.off_n = r;
+	r = align_up(r + sizeof(int32_t), 16);
+	b.res_bytes = r;
+	b.bytes = align_up(off + r, 256);
+	return b;
+}
+
+// position of one (query, setting) pair of vx_search_batch inside the shared work / pinned host buffers
+struct BatchSlot {
+	size_t work_off, host_off;
 };
 
 static int ensure_work(vx_corpus *c, size_t bytes) {
@@ -62,7 +106,7 @@ static int ensure_host(vx_corpus *c, size_t bytes) {
 
 // Validates like the reference does and stages the per-query constants on the device.
 static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, const vx_query_params *qp,
-	bool need_results, QueryPlan *p) {
+	bool need_results, QueryPlan *p, const BatchSlot *batch = nullptr) {
 
 	if (!c || !s || !ap || !qp) {
 		VX_FAIL(VX_ERR_INVALID, "NULL argument");
@@ -118,46 +162,31 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 	// contextual queries take the same fast kernels: S_doc is formed first, d_iota stands in for the ids
 	p->fast = (!s->contextual || c->d_iota) && s->tp <= VX_MAX_T_FAST && !qp->tag_weighted && qp->submatch_weight == 0.0f;
 
-	// ---- workspace layout ----
-	size_t off = 0;
-	const size_t off_topk = off;
-	off = align_up(off + vx_topk_work_bytes(p->k), 256);
+	// ---- workspace layout: [top-k area | block of plan 0 | block of plan 1 | ...] ----
 	const size_t n_ws = ap->gap_kind == VX_GAP_GENERAL ? (size_t)ap->n_w_s : 0;
 	const size_t n_wt = ap->gap_kind == VX_GAP_GENERAL ? (size_t)ap->n_w_t : 0;
-	const size_t off_gs = off;
-	off = align_up(off + sizeof(float) * n_ws, 256);
-	const size_t off_gt = off;
-	off = align_up(off + sizeof(float) * n_wt, 256);
-	const size_t off_tw = off;
-	off = align_up(off + sizeof(float) * (size_t)std::max(t, 1), 256);
-	const size_t off_tpos = off;
-	off = align_up(off + (size_t)std::max(t, 1), 256);
-	const size_t off_res = off;
-	size_t r = 0;
-	p->off_score = r;
-	r = align_up(r + sizeof(float) * p->k, 16);
-	p->off_score_max = r;
-	r = align_up(r + sizeof(float) * p->k, 16);
-	p->off_win = r;
-	r = align_up(r + sizeof(uint32_t) * p->k, 16);
-	p->off_target = r;
-	r = align_up(r + sizeof(int16_t) * (size_t)p->k * std::max(t, 1), 16);
-	p->off_dist = r;
-	r = align_up(r + sizeof(float) * (size_t)p->k * std::max(t, 1), 16);
-	p->off_n = r;
-	r = align_up(r + sizeof(int32_t), 16);
-	p->res_bytes = r;
-	off += r;
-
-	VX_TRY(ensure_work(c, off));
-	VX_TRY(ensure_host(c, p->res_bytes));
+	const BlockLayout bl = block_layout(t, p->k, n_ws, n_wt);
+	p->off_score = bl.off_score;
+	p->off_score_max = bl.off_score_max;
+	p->off_win = bl.off_win;
+	p->off_target = bl.off_target;
+	p->off_dist = bl.off_dist;
+	p->off_n = bl.off_n;
+	p->res_bytes = bl.res_bytes;
+	const size_t topk_bytes = align_up(vx_topk_work_bytes(p->k), 256);
+	if (!batch) {
+		VX_TRY(ensure_work(c, topk_bytes + bl.bytes));
+		VX_TRY(ensure_host(c, bl.res_bytes));
+	}
 	uint8_t *w = (uint8_t*)c->d_work;
-	p->topk = w + off_topk;
-	p->gap_s = (float*)(w + off_gs);
-	p->gap_t = (float*)(w + off_gt);
-	p->tw = (float*)(w + off_tw);
-	p->tpos = (int8_t*)(w + off_tpos);
-	p->res = w + off_res;
+	p->topk = w;
+	w += topk_bytes + (batch ? batch->work_off : 0);
+	p->gap_s = (float*)(w + bl.off_gs);
+	p->gap_t = (float*)(w + bl.off_gt);
+	p->tw = (float*)(w + bl.off_tw);
+	p->tpos = (int8_t*)(w + bl.off_tpos);
+	p->res = w + bl.off_res;
+	p->h_res = (uint8_t*)c->h_res + (batch ? batch->host_off : 0);
 
 	// ---- per-query constants ----
 	VxAlignDev &a = p->ap;
@@ -276,6 +305,79 @@ static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 	return launches;
 }
 
+// Enqueue one query: scores of every slot, top-k, traceback of the winners, result block to pinned host memory.
+// Nothing here waits for the device.
+static int enqueue_search(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events) {
+	cudaStream_t st = c->stream;
+	if (s->ev1) {
+		cudaStreamWaitEvent(st, s->ev1, 0);   // S may still be under construction on the similarity stream
+	}
+	int n = score_everything(c, s, p);
+	if (n < 0) {
+		return VX_ERR_CUDA;
+	}
+	c->last_launches += n;
+	if (phase_events) {
+		cudaEventRecord(c->ev[1], st);
+	}
+	if (c->aborted) {
+		c->aborted = 0;
+		cudaStreamSynchronize(st);
+		VX_FAIL(VX_ERR_ABORTED, "query aborted");
+	}
+
+	VxTopkOut tk;
+	n = vx_launch_topk(c, p.qp.min_score, p.k, p.topk, &tk);
+	if (n < 0) {
+		return VX_ERR_INVALID;
+	}
+	c->last_launches += n;
+	if (phase_events) {
+		cudaEventRecord(c->ev[2], st);
+	}
+
+	VxTraceOut out;
+	out.score = (float*)(p.res + p.off_score);
+	out.score_max = (float*)(p.res + p.off_score_max);
+	out.win = (uint32_t*)(p.res + p.off_win);
+	out.target = (int16_t*)(p.res + p.off_target);
+	out.dist = (float*)(p.res + p.off_dist);
+	n = vx_launch_trace(c, s, p.ap, p.qp, tk.slots, 0, tk.n, p.k, out);
+	if (n < 0) {
+		return VX_ERR_CUDA;
+	}
+	c->last_launches += n;
+	cudaMemcpyAsync(p.res + p.off_n, tk.n, sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+	if (phase_events) {
+		cudaEventRecord(c->ev[3], st);
+	}
+	cudaMemcpyAsync(p.h_res, p.res, p.res_bytes, cudaMemcpyDeviceToHost, st);
+	return VX_OK;
+}
+
+// hits / target / dist rows of one finished query from its pinned result block
+static void unpack_results(const vx_corpus *c, const QueryPlan &p, vx_hit *hits, int16_t *target, float *dist,
+	int32_t *n_hits, int32_t t_stride) {
+
+	const uint8_t *h = p.h_res;
+	const int32_t found = *(const int32_t*)(h + p.off_n);
+	const float *h_score = (const float*)(h + p.off_score);
+	const float *h_score_max = (const float*)(h + p.off_score_max);
+	const uint32_t *h_win = (const uint32_t*)(h + p.off_win);
+	const int16_t *h_target = (const int16_t*)(h + p.off_target);
+	const float *h_dist = (const float*)(h + p.off_dist);
+	for (int32_t i = 0; i < found; i++) {
+		const uint32_t w = h_win[i];
+		hits[i].score = h_score[i];
+		hits[i].score_max = h_score_max[i];
+		hits[i].doc = c->win_doc[w];
+		hits[i].slice = c->win_slice[w];
+		memcpy(target + (size_t)i * t_stride, h_target + (size_t)i * p.t, sizeof(int16_t) * p.t);
+		memcpy(dist + (size_t)i * t_stride, h_dist + (size_t)i * p.t, sizeof(float) * p.t);
+	}
+	*n_hits = found;
+}
+
 extern "C" int vx_search(
 	vx_corpus *c, const vx_sim *s,
 	const vx_align_params *ap, const vx_query_params *qp,
@@ -302,46 +404,9 @@ extern "C" int vx_search(
 		VX_FAIL(VX_ERR_ABORTED, "query aborted");
 	}
 
-	cudaStream_t st = c->stream;
-	if (s->ev1) {
-		cudaStreamWaitEvent(st, s->ev1, 0);   // S may still be under construction on the similarity stream
-	}
-	cudaEventRecord(c->ev[0], st);
-	int n = score_everything(c, s, p);
-	if (n < 0) {
-		return VX_ERR_CUDA;
-	}
-	c->last_launches += n;
-	cudaEventRecord(c->ev[1], st);
-	if (c->aborted) {
-		c->aborted = 0;
-		cudaStreamSynchronize(st);
-		VX_FAIL(VX_ERR_ABORTED, "query aborted");
-	}
-
-	VxTopkOut tk;
-	n = vx_launch_topk(c, p.qp.min_score, p.k, p.topk, &tk);
-	if (n < 0) {
-		return VX_ERR_INVALID;
-	}
-	c->last_launches += n;
-	cudaEventRecord(c->ev[2], st);
-
-	VxTraceOut out;
-	out.score = (float*)(p.res + p.off_score);
-	out.score_max = (float*)(p.res + p.off_score_max);
-	out.win = (uint32_t*)(p.res + p.off_win);
-	out.target = (int16_t*)(p.res + p.off_target);
-	out.dist = (float*)(p.res + p.off_dist);
-	n = vx_launch_trace(c, s, p.ap, p.qp, tk.slots, 0, tk.n, p.k, out);
-	if (n < 0) {
-		return VX_ERR_CUDA;
-	}
-	c->last_launches += n;
-	cudaMemcpyAsync(p.res + p.off_n, tk.n, sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
-	cudaEventRecord(c->ev[3], st);
-	cudaMemcpyAsync(c->h_res, p.res, p.res_bytes, cudaMemcpyDeviceToHost, st);
-	cudaError_t e = cudaStreamSynchronize(st);
+	cudaEventRecord(c->ev[0], c->stream);
+	VX_TRY(enqueue_search(c, s, p, true));
+	cudaError_t e = cudaStreamSynchronize(c->stream);
 	if (e != cudaSuccess) {
 		vx_set_error(std::string("search failed: ") + cudaGetErrorString(e));
 		return VX_ERR_CUDA;
@@ -349,22 +414,95 @@ extern "C" int vx_search(
 	for (int i = 0; i < 3; i++) {
 		cudaEventElapsedTime(&c->last_ms[i], c->ev[i], c->ev[i + 1]);
 	}
+	unpack_results(c, p, hits, target, dist, n_hits, p.t);
+	return VX_OK;
+}
 
-	const uint8_t *h = (const uint8_t*)c->h_res;
-	const int32_t found = *(const int32_t*)(h + p.off_n);
-	const float *h_score = (const float*)(h + p.off_score);
-	const float *h_score_max = (const float*)(h + p.off_score_max);
-	const uint32_t *h_win = (const uint32_t*)(h + p.off_win);
-	for (int32_t i = 0; i < found; i++) {
-		const uint32_t w = h_win[i];
-		hits[i].score = h_score[i];
-		hits[i].score_max = h_score_max[i];
-		hits[i].doc = c->win_doc[w];
-		hits[i].slice = c->win_slice[w];
+// Interactive parameter sweep (BASELINE config 5): n_sims queries x n_aps alignment settings over the resident
+// corpus in one call.  Replaces the reference's loop of Session.partition(..).index(..).find(query, options) calls
+// (vectorian/index.py:530-560 once per query and option set); nothing is re-packed, every kernel of every
+// (query, setting) pair is enqueued back to back and the host waits once.
+extern "C" int vx_search_batch(
+	vx_corpus *c, const vx_sim *const *sims, int32_t n_sims,
+	const vx_align_params *aps, int32_t n_aps, const vx_query_params *qp, int32_t t_stride,
+	vx_hit *hits, int16_t *target, float *dist, int32_t *n_hits) {
+
+	VX_TRY(vx_require_init());
+	if (!c || !sims || !aps || !qp || !n_hits || n_sims < 0 || n_aps < 0) {
+		VX_FAIL(VX_ERR_INVALID, "NULL argument");
 	}
-	memcpy(target, h + p.off_target, sizeof(int16_t) * (size_t)found * p.t);
-	memcpy(dist, h + p.off_dist, sizeof(float) * (size_t)found * p.t);
-	*n_hits = found;
+	const size_t n_pairs = (size_t)n_sims * n_aps;
+	for (size_t i = 0; i < n_pairs; i++) {
+		n_hits[i] = 0;
+	}
+	if (n_pairs == 0) {
+		return VX_OK;
+	}
+	if (!hits || !target || !dist) {
+		VX_FAIL(VX_ERR_INVALID, "output arrays are NULL");
+	}
+	if (qp->max_matches < 1) {
+		VX_FAIL(VX_ERR_INVALID, "max_matches must be > 0");
+	}
+	const int32_t k = qp->max_matches;
+	// buffer positions of every pair, then one allocation
+	std::vector<BatchSlot> slots(n_pairs);
+	size_t work = 0, host = 0;
+	for (int32_t q = 0; q < n_sims; q++) {
+		if (!sims[q]) {
+			VX_FAIL(VX_ERR_INVALID, "NULL similarity handle");
+		}
+		if (sims[q]->t > t_stride) {
+			VX_FAIL(VX_ERR_INVALID, "t_stride is smaller than a query");
+		}
+		for (int32_t ai = 0; ai < n_aps; ai++) {
+			const bool gen = aps[ai].gap_kind == VX_GAP_GENERAL;
+			const BlockLayout bl = block_layout(sims[q]->t, k, gen ? (size_t)std::max(aps[ai].n_w_s, 0) : 0,
+				gen ? (size_t)std::max(aps[ai].n_w_t, 0) : 0);
+			slots[(size_t)q * n_aps + ai] = BatchSlot{work, host};
+			work += bl.bytes;
+			host += align_up(bl.res_bytes, 256);
+		}
+	}
+	VX_TRY(ensure_work(c, align_up(vx_topk_work_bytes(k), 256) + work));
+	VX_TRY(ensure_host(c, host));
+	c->sdoc_of = nullptr;
+	c->last_launches = 0;
+	c->last_ms[0] = c->last_ms[1] = c->last_ms[2] = 0.0f;
+	if (c->aborted) {
+		c->aborted = 0;
+		VX_FAIL(VX_ERR_ABORTED, "query aborted");
+	}
+	std::vector<QueryPlan> plans(n_pairs);
+	cudaEventRecord(c->ev[0], c->stream);
+	int rc = VX_OK;
+	std::vector<char> live(n_pairs, 0);
+	for (int32_t q = 0; q < n_sims && rc == VX_OK; q++) {
+		for (int32_t ai = 0; ai < n_aps && rc == VX_OK; ai++) {
+			const size_t i = (size_t)q * n_aps + ai;
+			rc = make_plan(c, sims[q], &aps[ai], qp, true, &plans[i], &slots[i]);
+			if (rc == VX_OK && plans[i].t >= 1 && c->n_win > 0) {
+				rc = enqueue_search(c, sims[q], plans[i], false);
+				live[i] = 1;
+			}
+		}
+	}
+	cudaEventRecord(c->ev[1], c->stream);
+	cudaError_t e = cudaStreamSynchronize(c->stream);
+	if (rc != VX_OK) {
+		return rc;
+	}
+	if (e != cudaSuccess) {
+		vx_set_error(std::string("batched search failed: ") + cudaGetErrorString(e));
+		return VX_ERR_CUDA;
+	}
+	cudaEventElapsedTime(&c->last_ms[0], c->ev[0], c->ev[1]);   // the whole batch
+	for (size_t i = 0; i < n_pairs; i++) {
+		if (live[i]) {
+			unpack_results(c, plans[i], hits + i * k, target + i * (size_t)k * t_stride,
+				dist + i * (size_t)k * t_stride, &n_hits[i], t_stride);
+		}
+	}
 	return VX_OK;
 }
 

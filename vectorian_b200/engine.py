@@ -109,6 +109,33 @@ class DeviceCorpus:
 			hits.ctypes.data_as(C.POINTER(Hit)), ptr(target, C.c_int16), ptr(dist, C.c_float), C.byref(n)), self._lib)
 		return hits[:n.value], target[:n.value, :sim.t], dist[:n.value, :sim.t]
 
+	def search_batch(self, sims, aps, qp):
+		"""Parameter sweep (vx_search_batch): every query in `sims` against every alignment setting in `aps` in one
+		call.  Returns a list over queries of lists over settings of (hits, target, dist) as `search` returns them."""
+		n_q, n_a = len(sims), len(aps)
+		k = max(int(qp.max_matches), 1)
+		t_stride = max([s.t for s in sims] + [1])
+		n_pairs = n_q * n_a
+		hits = np.zeros((n_pairs, k), dtype=HIT_DTYPE)
+		target = np.full((n_pairs, k, t_stride), -1, dtype=np.int16)
+		dist = np.ones((n_pairs, k, t_stride), dtype=np.float32)
+		n = np.zeros((max(n_pairs, 1),), dtype=np.int32)
+		handles = (C.c_void_p * max(n_q, 1))(*[s.handle for s in sims])
+		ap_arr = (_cabi.AlignParams * max(n_a, 1))()
+		for i, a in enumerate(aps):
+			C.memmove(C.byref(ap_arr[i]), C.byref(a), C.sizeof(_cabi.AlignParams))   # keeps pointers into the caller's tables
+		check(self._lib.vx_search_batch(self._h, handles, n_q, ap_arr, n_a, C.byref(qp), t_stride,
+			hits.ctypes.data_as(C.POINTER(Hit)), ptr(target, C.c_int16), ptr(dist, C.c_float), ptr(n, C.c_int32)), self._lib)
+		out = []
+		for q in range(n_q):
+			row = []
+			for a in range(n_a):
+				p = q * n_a + a
+				m = int(n[p])
+				row.append((hits[p, :m], target[p, :m, :sims[q].t], dist[p, :m, :sims[q].t]))
+			out.append(row)
+		return out
+
 	def score_all(self, sim, ap, qp):
 		n = self.n_windows
 		out = np.zeros((n,), dtype=np.float32)
