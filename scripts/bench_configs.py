@@ -110,8 +110,53 @@ def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
 	dc.close()
 
 
+def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
+	"""C5: n_queries x 8 settings ({LinearGapCost(u), u in 0,.1,.2,.5} x {Local, Global}) without re-preprocessing."""
+	tok, tables = synthetic.make_corpus_device(n_sent, vocab, device="cuda:0")
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	del tok
+	emb = synthetic.make_embedding(vocab, dim)
+	de = engine.DeviceEmbedding(emb)
+	aps, keeps = [], []
+	for loc in (_cabi.VX_LOCAL, _cabi.VX_GLOBAL):
+		for u in (0.0, 0.1, 0.2, 0.5):
+			r = gaps.resolve_gap_costs(gaps.LinearGapCost(u), dc.max_len, t)
+			kind = r.pop("gap_kind")
+			ap, keep = _cabi.make_align_params(loc, kind, **r)
+			aps.append(ap)
+			keeps.append(keep)
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
+	queries = [synthetic.make_query(t, vocab, seed=99 + i) for i in range(n_queries)]
+	res = {}
+	for mode in ("single", "batch"):
+		for rep in range(2):   # first repetition warms up
+			t0 = time.perf_counter()
+			sims = [engine.DeviceSim.static(de, q, emb[q]) for q in queries]
+			if mode == "single":
+				top = [[dc.search(sim, ap, qp)[0]["score"][0] for ap in aps] for sim in sims]
+			else:
+				out = dc.search_batch(sims, aps, qp)
+				top = [[out[q][a][0]["score"][0] for a in range(len(aps))] for q in range(len(sims))]
+				dev_ms = dc.last_timing()["dp_ms"]
+			t1 = time.perf_counter()
+			for sim in sims:
+				sim.close()
+		res[mode] = {"wall_ms": (t1 - t0) * 1e3, "top": top}
+	assert res["single"]["top"] == res["batch"]["top"]
+	pairs = n_queries * len(aps)
+	out = {"config": name, "sentences": n_sent, "T": t, "queries": n_queries, "settings": len(aps),
+		"single_calls_wall_ms": res["single"]["wall_ms"], "batch_wall_ms": res["batch"]["wall_ms"], "batch_device_ms": dev_ms,
+		"ms_per_pair_batch": res["batch"]["wall_ms"] / pairs,
+		"sentence_alignments_per_s_e2e": n_sent * pairs / res["batch"]["wall_ms"] * 1e3,
+		"launches": dc.last_launches()}
+	print(json.dumps(out), flush=True)
+	dc.close()
+
+
 def main():
 	which = sys.argv[1:] or ["c1", "c2"]
+	if "c5" in which:
+		run_sweep("C5 sweep: 64 queries x {linear 0,.1,.2,.5} x {Local,Global}, T=12, 10M sentences (one GPU holds the whole corpus)", 10_000_000)
 	if "c1" in which:   # the reference's own CPU-runnable case, on the GPU for comparison
 		run_static("C1 NW Global linear(0.2) T=5 10k V=50k", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.2), 5, 10_000, 50_000, 300, cand_per_cell=3)
 	if "c2" in which:

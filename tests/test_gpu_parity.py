@@ -275,6 +275,8 @@ def test_search_batch_equals_single_searches(engine, oracle):
 	for t in (8, 5, 12, 3):
 		ids = rng.choice(emb.shape[0], size=t, replace=False).astype(np.int32)
 		sims.append(engine.DeviceSim.static(de, ids, emb[ids]))
+	# an uploaded matrix with negative entries: the fused kernel must keep the explicit Local zero
+	sims.append(engine.DeviceSim.upload((rng.random((emb.shape[0], 6)) * 1.3 - 0.3).astype(np.float32)))
 	aps, keeps = [], []
 	for gap_name in ("linear0.2", "none", "affine", "smooth5"):
 		for locality in (_cabi.VX_LOCAL, _cabi.VX_GLOBAL):

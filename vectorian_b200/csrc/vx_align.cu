@@ -130,6 +130,110 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 }
 
 // ---------------------------------------------------------------------------
+// linear gap cost, several settings of one query at once (vx_search_batch, BASELINE config 5):
+// NL Local settings followed by NG Global settings, each with its own gap costs.  The single-setting kernel is
+// bound by the gather of the S rows (32 different rows per warp and token); here one gathered row feeds NL + NG
+// dynamic-programming columns, so the work per gathered byte is NL + NG times higher and the kernel moves to
+// the FP32 issue limit.  Cell values are the same floats as in score_linear_kernel (max of the same candidates).
+// ---------------------------------------------------------------------------
+
+constexpr int VX_MULTI_MAX = 8;
+
+struct MultiArgs {
+	float gs[VX_MULTI_MAX], gt[VX_MULTI_MAX];
+	float *score[VX_MULTI_MAX];
+};
+
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+	float r;
+	asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+	return r;
+}
+
+template<int TP, int NL, int NG, bool ZC>
+__global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, const __grid_constant__ MultiArgs m) {
+	constexpr int NS = NL + NG;
+	const int64_t tile = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (tile >= a.n_tiles) {
+		return;
+	}
+	const int lane = threadIdx.x & 31;
+	const VxTile tl = a.tiles[tile];
+	const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + lane) * 4;
+	const int len = tl.len;
+
+	float h[NS][TP];              // h[i][v] = V_i[u-1, v]
+	float best[NL > 0 ? NL : 1];  // Local: running maximum (padded columns v >= t only repeat or lower values)
+	#pragma unroll
+	for (int i = 0; i < NS; i++) {
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			h[i][v] = i < NL ? 0.0f : -((float)(v + 1) * m.gt[i]);   // solver.h:2804-2806
+		}
+		if (i < NL) {
+			best[i] = 0.0f;
+		}
+	}
+
+	float row[TP];
+	int32_t id = tok[0];
+	load_row<TP>(a.s, id, row);
+
+	for (int u = 0; u < len; u++) {
+		float cur[TP];
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			cur[v] = row[v];
+		}
+		if (u + 1 < len) {
+			id = tok[vx_elem(0, u + 1, 0)];
+			load_row<TP>(a.s, id, row);
+		}
+		#pragma unroll
+		for (int i = 0; i < NS; i++) {
+			const float gs = m.gs[i], gt = m.gt[i];
+			float diag = i < NL ? 0.0f : -((float)u * gs);        // V[u-1, -1]
+			float left = i < NL ? 0.0f : -((float)(u + 1) * gs);  // V[u, -1]
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				const float up = h[i][v];
+				float x = fmax3(diag + cur[v], up - gs, left - gt);
+				if (i < NL && ZC) {
+					x = fmaxf(x, 0.0f);   // Local zero; with S >= 0 it never wins: diag + S >= 0 already (ZC = false)
+				}
+				diag = up;
+				h[i][v] = x;
+				left = x;
+			}
+			if (i < NL) {
+				#pragma unroll
+				for (int v = 0; v + 1 < TP; v += 2) {
+					best[i] = fmax3(best[i], h[i][v], h[i][v + 1]);
+				}
+			}
+		}
+	}
+
+	const int64_t slot = tile * 32 + lane;
+	const float boost = a.boost ? a.boost[slot] : 1.0f;
+	#pragma unroll
+	for (int i = 0; i < NS; i++) {
+		float raw;
+		if (i < NL) {
+			raw = best[i];
+		} else {
+			raw = h[i][0];                       // V[len-1, t-1]; the selects are opaque to the compiler, which would
+			#pragma unroll                       // otherwise turn the chain into a dynamically indexed local-memory array
+			for (int v = 1; v < TP; v++) {
+				asm("{ .reg .pred p; setp.eq.s32 p, %2, %3; selp.f32 %0, %1, %0, p; }"
+					: "+f"(raw) : "f"(h[i][v]), "r"(v), "r"(a.t - 1));
+			}
+		}
+		m.score[i][slot] = lane < tl.n_valid ? finish_score(raw, a.total, boost) : -CUDART_INF_F;
+	}
+}
+
+// ---------------------------------------------------------------------------
 // affine gap cost: Gotoh
 // ---------------------------------------------------------------------------
 
@@ -417,6 +521,66 @@ static int launch_score_t(vx_corpus *c, const vx_sim *s, const ScoreArgs &a, con
 			return launch_score_tl<TP, VX_GLOBAL>(c, s, a, ap, qp);
 		default:
 			return launch_score_tl<TP, VX_SEMIGLOBAL>(c, s, a, ap, qp);
+	}
+}
+
+template<int TP>
+static int launch_multi_t(const ScoreArgs &a, const MultiArgs &m, int nl, int ng, bool zc, cudaStream_t st) {
+	const int warps = 4;
+	const unsigned grid = (unsigned)((a.n_tiles + warps - 1) / warps);
+	#define VX_MULTI_CASE(NL, NG) if (nl == NL && ng == NG) { \
+		if (zc && NL > 0) { \
+			score_linear_multi_kernel<TP, NL, NG, true><<<grid, warps * 32, 0, st>>>(a, m); \
+		} else { \
+			score_linear_multi_kernel<TP, NL, NG, false><<<grid, warps * 32, 0, st>>>(a, m); \
+		} \
+		return 1; \
+	}
+	VX_MULTI_CASE(4, 4)
+	VX_MULTI_CASE(4, 0)
+	VX_MULTI_CASE(0, 4)
+	VX_MULTI_CASE(2, 2)
+	VX_MULTI_CASE(2, 0)
+	VX_MULTI_CASE(0, 2)
+	#undef VX_MULTI_CASE
+	return 0;
+}
+
+// Several linear-gap settings of one query in one pass over the corpus: nl Local settings then ng Global ones
+// (gs / gt / score in that order).  Returns 1 when launched, 0 when this (nl, ng, tp) shape has no kernel.
+int vx_launch_score_multi(vx_corpus *c, const vx_sim *s, const VxQueryDev &qp, int nl, int ng,
+	const float *gs, const float *gt, float *const *score) {
+
+	if (c->n_tiles == 0 || nl + ng > VX_MULTI_MAX) {
+		return 0;
+	}
+	ScoreArgs a;
+	a.tiles = c->d_tiles;
+	a.n_tiles = c->n_tiles;
+	a.tok = c->d_tok;
+	a.s = s->d_s;
+	a.boost = c->d_boost;
+	a.score = nullptr;
+	a.t = qp.t;
+	a.total = qp.total;
+	MultiArgs m;
+	memset(&m, 0, sizeof(m));
+	for (int i = 0; i < nl + ng; i++) {
+		m.gs[i] = gs[i];
+		m.gt[i] = gt[i];
+		m.score[i] = score[i];
+	}
+	switch (s->tp) {
+		case 4:
+			return launch_multi_t<4>(a, m, nl, ng, !s->nonneg, c->stream);
+		case 8:
+			return launch_multi_t<8>(a, m, nl, ng, !s->nonneg, c->stream);
+		case 12:
+			return launch_multi_t<12>(a, m, nl, ng, !s->nonneg, c->stream);
+		case 16:
+			return launch_multi_t<16>(a, m, nl, ng, !s->nonneg, c->stream);
+		default:
+			return 0;
 	}
 }
 

@@ -94,6 +94,7 @@ static void corpus_free(vx_corpus *c) {
 	cudaFree(c->d_iota);
 	cudaFree(c->d_sdoc);
 	cudaFree(c->d_score);
+	cudaFree(c->d_score_multi);
 	cudaFree(c->d_work);
 	cudaFree(c->d_scratch);
 	cudaFree(c->d_counters);
@@ -556,6 +557,7 @@ extern "C" int vx_sim_static(const vx_embedding *e, const int32_t *q_id, const f
 	}
 	vx_sim *s = new vx_sim();
 	s->rows = e->v;
+	s->nonneg = true;   // clip01 in the kernel epilogue
 	s->t = t;
 	s->tp = std::max(4, (t + 3) / 4 * 4);
 	cudaStream_t st = vx_sim_stream();
@@ -613,6 +615,13 @@ extern "C" int vx_sim_upload(const float *sm, int64_t v, int32_t t, vx_sim **out
 	s->rows = v;
 	s->t = t;
 	s->tp = std::max(4, (t + 3) / 4 * 4);
+	s->nonneg = true;
+	for (int64_t i = 0; i < v * t; i++) {
+		if (!(sm[i] >= 0.0f)) {
+			s->nonneg = false;
+			break;
+		}
+	}
 	int rc = sim_alloc_s(s);
 	if (rc != VX_OK) {
 		sim_free(s);
@@ -644,6 +653,7 @@ extern "C" int vx_sim_contextual(const float *q_vec, int32_t t, int32_t d, vx_si
 	}
 	vx_sim *s = new vx_sim();
 	s->contextual = 1;
+	s->nonneg = true;
 	s->t = t;
 	s->tp = std::max(4, (t + 3) / 4 * 4);
 	s->d = d;

@@ -81,6 +81,7 @@ struct vx_corpus {
 	size_t sdoc_bytes = 0;
 	const vx_sim *sdoc_of = nullptr; // the query d_sdoc currently holds (nullptr: none); reset at the start of every search
 	float *d_score = nullptr;        // by slot, scratch of the last search
+	float *d_score_multi = nullptr;  // 8 x n_slots, vx_search_batch: scores of the fused settings (lazily allocated)
 	void *d_work = nullptr;          // top-k / traceback workspace
 	size_t work_bytes = 0;
 	void *d_scratch = nullptr;       // DP scratch of the exact kernel
@@ -112,6 +113,7 @@ struct vx_sim {
 	int32_t tp = 0;                  // row stride in floats = round_up(t, 4)
 	float *d_s = nullptr;            // [rows x tp], columns >= t are zero
 	int32_t contextual = 0;
+	bool nonneg = false;             // every entry of S is >= 0 (always true for S built on the device: clip01)
 	int32_t d = 0;
 	float *d_qhat = nullptr;         // contextual: [t x d] normalised query vectors
 	float build_ms = 0.0f;           // device time of the kernels that built d_s (resolved lazily from ev0/ev1)
@@ -196,6 +198,8 @@ int vx_launch_normalize(const float *d_in, float *d_out, int64_t rows, int32_t d
 int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float *d_qhat,
 	const int32_t *d_qid, int32_t t, int32_t tp, float *d_s, cudaStream_t st);
 
+int vx_launch_score_multi(vx_corpus *c, const vx_sim *s, const VxQueryDev &qp, int nl, int ng,
+	const float *gs, const float *gt, float *const *score);
 extern int vx_ctx_force_simt;
 int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,
 	int32_t t, int32_t tp, float *d_sdoc, cudaStream_t st);

@@ -307,6 +307,8 @@ static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 
 // Enqueue one query: scores of every slot, top-k, traceback of the winners, result block to pinned host memory.
 // Nothing here waits for the device.
+static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events);
+
 static int enqueue_search(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events) {
 	cudaStream_t st = c->stream;
 	if (s->ev1) {
@@ -317,6 +319,13 @@ static int enqueue_search(vx_corpus *c, const vx_sim *s, const QueryPlan &p, boo
 		return VX_ERR_CUDA;
 	}
 	c->last_launches += n;
+	return enqueue_select(c, s, p, phase_events);
+}
+
+// top-k over c->d_score, traceback of the winners, result block to pinned host memory
+static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events) {
+	cudaStream_t st = c->stream;
+	int n;
 	if (phase_events) {
 		cudaEventRecord(c->ev[1], st);
 	}
@@ -478,12 +487,79 @@ extern "C" int vx_search_batch(
 	int rc = VX_OK;
 	std::vector<char> live(n_pairs, 0);
 	for (int32_t q = 0; q < n_sims && rc == VX_OK; q++) {
+		const vx_sim *s = sims[q];
 		for (int32_t ai = 0; ai < n_aps && rc == VX_OK; ai++) {
-			const size_t i = (size_t)q * n_aps + ai;
-			rc = make_plan(c, sims[q], &aps[ai], qp, true, &plans[i], &slots[i]);
-			if (rc == VX_OK && plans[i].t >= 1 && c->n_win > 0) {
-				rc = enqueue_search(c, sims[q], plans[i], false);
-				live[i] = 1;
+			rc = make_plan(c, s, &aps[ai], qp, true, &plans[(size_t)q * n_aps + ai], &slots[(size_t)q * n_aps + ai]);
+		}
+		if (rc != VX_OK || s->t < 1 || c->n_win == 0) {
+			continue;
+		}
+		if (s->ev1) {
+			cudaStreamWaitEvent(c->stream, s->ev1, 0);
+		}
+		// Linear-gap Local / Global settings of one query share one pass over the corpus (score_linear_multi_kernel)
+		std::vector<int32_t> lo, gl;
+		std::vector<char> done(n_aps, 0);
+		for (int32_t ai = 0; ai < n_aps; ai++) {
+			const QueryPlan &p = plans[(size_t)q * n_aps + ai];
+			if (p.fast && !s->contextual && p.ap.gap_kind == VX_GAP_LINEAR) {
+				if (p.ap.locality == VX_LOCAL) {
+					lo.push_back(ai);
+				} else if (p.ap.locality == VX_GLOBAL) {
+					gl.push_back(ai);
+				}
+			}
+		}
+		while (rc == VX_OK) {
+			int nl = lo.size() >= 4 ? 4 : lo.size() >= 2 ? 2 : 0;
+			int ng = gl.size() >= 4 ? 4 : gl.size() >= 2 ? 2 : 0;
+			if (nl == 4 && ng == 2) {
+				ng = 0;
+			} else if (nl == 2 && ng == 4) {
+				nl = 0;
+			}
+			if (nl + ng == 0) {
+				break;
+			}
+			if (!c->d_score_multi) {
+				if (cudaMalloc(&c->d_score_multi, sizeof(float) * 8 * (size_t)c->n_slots) != cudaSuccess) {
+					cudaGetLastError();
+					break;   // no room for the extra score arrays: the settings run one by one below
+				}
+			}
+			int32_t group[8];
+			float gs[8], gt[8];
+			float *score[8];
+			for (int j = 0; j < nl + ng; j++) {
+				std::vector<int32_t> &from = j < nl ? lo : gl;
+				group[j] = from.back();
+				from.pop_back();
+				const QueryPlan &p = plans[(size_t)q * n_aps + group[j]];
+				gs[j] = p.ap.lin_s;
+				gt[j] = p.ap.lin_t;
+				score[j] = c->d_score_multi + (size_t)j * c->n_slots;
+			}
+			const int launched = vx_launch_score_multi(c, s, plans[(size_t)q * n_aps + group[0]].qp, nl, ng, gs, gt, score);
+			if (launched <= 0) {
+				for (int j = 0; j < nl + ng; j++) {
+					done[group[j]] = 0;   // no kernel for this shape: one by one below
+				}
+				break;
+			}
+			c->last_launches += launched;
+			float *const d_score = c->d_score;
+			for (int j = 0; j < nl + ng && rc == VX_OK; j++) {
+				c->d_score = score[j];
+				rc = enqueue_select(c, s, plans[(size_t)q * n_aps + group[j]], false);
+				done[group[j]] = 1;
+				live[(size_t)q * n_aps + group[j]] = 1;
+			}
+			c->d_score = d_score;
+		}
+		for (int32_t ai = 0; ai < n_aps && rc == VX_OK; ai++) {
+			if (!done[ai]) {
+				rc = enqueue_search(c, s, plans[(size_t)q * n_aps + ai], false);
+				live[(size_t)q * n_aps + ai] = 1;
 			}
 		}
 	}
