@@ -166,6 +166,9 @@ def main():
 	if "c4" in which:
 		run_contextual("C4 NW Global linear(0.1) contextual d=128 T=8, 200k sentences (1/3 of one GPU's C4 shard)", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 8, 200_000, 128)
 		run_contextual("C4b same, T=16", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 16, 200_000, 128)
+	if "wsbloc" in which:
+		for loc, nm in ((_cabi.VX_LOCAL, "Local"), (_cabi.VX_GLOBAL, "Global"), (_cabi.VX_SEMIGLOBAL, "Semiglobal")):
+			run_static("WSB %s smooth_gap_cost(5) T=12 10M V=50k" % nm, loc, gaps.smooth_gap_cost(5), 12, 10_000_000, 50_000, 300)
 	if "gotoh" in which:
 		run_static("Gotoh Local affine(0.3,0.1) T=8 20M V=50k", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1), 8, 20_000_000, 50_000, 300, cand_per_cell=7.5)
 

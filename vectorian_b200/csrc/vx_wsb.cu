@@ -241,11 +241,13 @@ __device__ __forceinline__ void wsb_block(
 				}
 			}
 		} else {
-			// V[u, t-1]; written as a masked maximum so that the register array is never indexed dynamically
-			float lc = -CUDART_INF_F;
+			// V[u, t-1] (TP - 4 < t <= TP); the selects are opaque to the compiler, which would otherwise turn
+			// the chain into a dynamically indexed -- i.e. local-memory -- copy of the accumulators
+			float lc = acc[i][TP - 4];
 			#pragma unroll
-			for (int v = TP - 4; v < TP; v++) {
-				lc = fmaxf(lc, v == t - 1 ? acc[i][v] : -CUDART_INF_F);
+			for (int v = TP - 3; v < TP; v++) {
+				asm("{ .reg .pred p; setp.eq.s32 p, %2, %3; selp.f32 %0, %1, %0, p; }"
+					: "+f"(lc) : "f"(acc[i][v]), "r"(v), "r"(t - 1));
 			}
 			last_col = lc;
 			if (LOC == VX_SEMIGLOBAL) {
