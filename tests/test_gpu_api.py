@@ -185,3 +185,27 @@ def test_empty_query_and_errors():
 	assert len(index.find("   ")) == 0                       # vectorian/index.py:533-534
 	with pytest.raises(ValueError):
 		index.find("w1 w2", options={"bogus_option": 1})     # cpp/query.cpp:59-68
+
+
+def test_sweep_equals_individual_finds():
+	"""index.sweep (parameter sweep over alignment settings, one device call) returns what index.find returns
+	for every (query, index) pair."""
+	from vectorian_b200.index import sweep
+	session, (emb,) = make_session(n_docs=5, sent_per_doc=50)
+	token_sim = EmbeddingTokenSim(emb, CosineSim())
+	partition = session.partition("sentence")
+	alignments = [LocalAlignment(gap=gaps.LinearGapCost(u)) for u in (0.0, 0.1, 0.2, 0.5)]
+	alignments += [GlobalAlignment(gap=gaps.LinearGapCost(u)) for u in (0.0, 0.1, 0.2, 0.5)]
+	alignments += [LocalAlignment(gap=gaps.smooth_gap_cost(5)), SemiGlobalAlignment(gap=gaps.LinearGapCost(0.3))]
+	indexes = [partition.index(OptimizedSpanSim(token_sim, a), nlp=whitespace_nlp) for a in alignments]
+	texts = [QUERY, "w1 w2 w3", "", "w40 w7 w7 w300 w12"]
+	got = sweep(indexes, texts, n=15, min_score=0.01)
+	assert len(got) == len(texts) and all(len(row) == len(indexes) for row in got)
+	for text, row in zip(texts, got):
+		for index, result in zip(indexes, row):
+			ref = index.find(text, n=15, min_score=0.01, disable_progress=True)
+			assert len(result) == len(ref)
+			for m, r in zip(result, ref):
+				assert (m.score, m.prepared_doc is r.prepared_doc, m.slice_id) == (r.score, True, r.slice_id)
+				np.testing.assert_array_equal(m.flow["target"], r.flow["target"])
+				assert m.to_json() == r.to_json()

@@ -420,6 +420,34 @@ class BruteForceIndex(Index):
 		np.clip(s, 0.0, 1.0, out=s)
 		return dc, engine.DeviceSim.upload(s)
 
+	def _align_params(self, metric_args, dc, t):
+		alignment = metric_args['alignment']
+		if alignment.get('algorithm') != 'pyalign':
+			raise NotImplementedError(f"algorithm {alignment.get('algorithm')} is outside the B200 hot path")
+		a_opt = alignment['options']
+		resolved = gaps.resolve_gap_costs(a_opt.get('gap_cost'), max(dc.max_len, 1), t)
+		gap_fns = (_gap_cost_fn(resolved, 's'), _gap_cost_fn(resolved, 't'))
+		r = dict(resolved)
+		kind = r.pop('gap_kind')
+		ap, keep_a = _cabi.make_align_params(a_opt['locality'], kind, **r)
+		return ap, keep_a, gap_fns
+
+	@staticmethod
+	def _query_params(options, metric_args, p_query):
+		qkw = {}
+		if metric_args['metric'] == 'alignment-tag-weighted':
+			tw = metric_args['tag_weights']
+			qkw = dict(
+				t_weights=np.array([tw.get(tag, 1.0) for tag in p_query.token_tag], dtype=np.float32),
+				t_pos=p_query.token_pos,
+				pos_mismatch_penalty=metric_args.get('pos_mismatch_penalty', 0),
+				similarity_threshold=metric_args.get('similarity_threshold', 0))
+		k = int(options.get("max_matches", 100))
+		qp, keep_q = _cabi.make_query_params(
+			max_matches=k, min_score=options.get("min_score", 0.2),
+			submatch_weight=options.get("submatch_weight", 0.0), **qkw)
+		return qp, keep_q, k
+
 	def _find(self, query, n_threads=None, progress=None):
 		p_query = query.prepare(self._nlp)
 		if len(p_query) == 0:
@@ -441,30 +469,10 @@ class BruteForceIndex(Index):
 			dc.set_boost(np.concatenate(boost) if boost else np.zeros((0,), np.float32))
 			self._boost_set = True
 
-		alignment = metric_args['alignment']
-		if alignment.get('algorithm') != 'pyalign':
-			raise NotImplementedError(f"algorithm {alignment.get('algorithm')} is outside the B200 hot path")
-		a_opt = alignment['options']
-		resolved = gaps.resolve_gap_costs(a_opt.get('gap_cost'), max(dc.max_len, 1), t)
-		gap_fns = (_gap_cost_fn(resolved, 's'), _gap_cost_fn(resolved, 't'))
-		r = dict(resolved)
-		kind = r.pop('gap_kind')
-		ap, keep_a = _cabi.make_align_params(a_opt['locality'], kind, **r)
-
-		qkw = {}
-		if metric_args['metric'] == 'alignment-tag-weighted':
-			tw = metric_args['tag_weights']
-			qkw = dict(
-				t_weights=np.array([tw.get(tag, 1.0) for tag in p_query.token_tag], dtype=np.float32),
-				t_pos=p_query.token_pos,
-				pos_mismatch_penalty=metric_args.get('pos_mismatch_penalty', 0),
-				similarity_threshold=metric_args.get('similarity_threshold', 0))
+		ap, keep_a, gap_fns = self._align_params(metric_args, dc, t)
+		qp, keep_q, k = self._query_params(options, metric_args, p_query)
 		# Match::metric is the name of the token metric (vectorian/sim/token.py:39-44)
 		metric_name = metric_args['token_metric'].to_args(self)['name']
-		k = int(options.get("max_matches", 100))
-		qp, keep_q = _cabi.make_query_params(
-			max_matches=k, min_score=options.get("min_score", 0.2),
-			submatch_weight=options.get("submatch_weight", 0.0), **qkw)
 
 		hits, target, dist = dc.search(sim, ap, qp)
 		self.last_timing = dict(dc.last_timing(), sim_ms=sim.build_ms)
@@ -478,3 +486,59 @@ class BruteForceIndex(Index):
 		if progress:
 			progress(1.0)
 		return [CoreMatch(self, p_query, h, tg, ds, metric_name, gap_fns) for h, tg, ds in zip(hits, target, dist)]
+
+
+
+def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
+	"""Interactive parameter sweep (BASELINE.json config 5): every query text against every index of `indexes`
+	-- BruteForceIndex objects over the SAME partition and token similarity that differ in their alignment
+	(locality / gap costs) -- in one device call (vx_search_batch).  The reference runs
+	`index.find(text, ...)` once per pair (vectorian/index.py:481-501); this returns the same Result objects as
+	`[[index.find(text, n, min_score) for index in indexes] for text in texts]`.
+	"""
+	if not indexes or not texts:
+		return [[] for _ in texts]
+	first = indexes[0]
+	session = first.session
+	queries = [[index.make_query(text, n=n, min_score=min_score, options=options) for index in indexes] for text in texts]
+	margs = [q.options.get("metric") for q in queries[0]]
+	same = all(index.partition is first.partition for index in indexes) and all(
+		m and m['metric'] == 'alignment-isolated' and m['token_metric'] is margs[0]['token_metric'] for m in margs)
+	if not same or session.shard[1] > 1:
+		# different partitions / token metrics, tag weights or a sharded session: one find per pair
+		return [[index.find(text, n=n, min_score=min_score, options=options) for index in indexes] for text in texts]
+	start_time = time.time()
+	prepared, sims, live = [], [], []
+	dc = None
+	for qi, row in enumerate(queries):
+		p_query = row[0].prepare(first._nlp)
+		prepared.append(p_query)
+		if len(p_query) > 0:
+			dc, sim = first._similarity(p_query, margs[0])
+			sims.append(sim)
+			live.append(qi)
+	results = [[session.make_result(index, [], duration=0.0) for index in indexes] for _ in texts]
+	if sims:
+		t_max = max(p.n_tokens for p in prepared if len(p) > 0)
+		aps, keeps, gap_fns = [], [], []
+		for index, m in zip(indexes, margs):
+			ap, keep, fns = index._align_params(m, dc, t_max)
+			aps.append(ap)
+			keeps.append(keep)
+			gap_fns.append(fns)
+		qp, keep_q, k = first._query_params(queries[0][0].options, margs[0], prepared[live[0]])
+		out = dc.search_batch(sims, aps, qp)
+		for sim in sims:
+			sim.close()
+		doc_lo = session.shard[2]
+		duration = (time.time() - start_time) / (len(sims) * len(indexes))
+		for row, qi in zip(out, live):
+			for ai, (index, (hits, target, dist)) in enumerate(zip(indexes, row)):
+				if doc_lo:
+					hits = hits.copy()
+					hits["doc"] += doc_lo
+				metric_name = margs[ai]['token_metric'].to_args(index)['name']
+				matches = [CoreMatch(index, prepared[qi], h, tg, ds, metric_name, gap_fns[ai])
+					for h, tg, ds in zip(hits, target, dist)]
+				results[qi][ai] = session.make_result(index, matches, duration=duration)
+	return results
