@@ -209,3 +209,42 @@ def test_sweep_equals_individual_finds():
 				assert (m.score, m.prepared_doc is r.prepared_doc, m.slice_id) == (r.score, True, r.slice_id)
 				np.testing.assert_array_equal(m.flow["target"], r.flow["target"])
 				assert m.to_json() == r.to_json()
+
+
+def test_token_similarity_modifiers(oracle):
+	"""Mixed / maximum / unary token-similarity modifiers (vectorian/sim/modifier.py): operand matrices from the
+	device, combined on the host as the reference does, searched on the device; compared with the oracle fed with the
+	independently combined matrix."""
+	from vectorian_b200 import engine
+	from vectorian_b200.sim.modifier import MixedTokenSimilarity, MaximumTokenSimilarity, UnaryTokenSimilarityModifier
+	from vectorian_b200.sim.kernel import Power, Bias
+	session, (emb,) = make_session()
+	ts_cos = EmbeddingTokenSim(emb, CosineSim())
+	pn = ModifiedVectorSim(PNormDistance(p=2), Scale(0.25), DistanceToSimilarity())
+	ts_pn = EmbeddingTokenSim(emb, pn)
+	partition = session.partition("sentence")
+	p = partition.index(OptimizedSpanSim(ts_cos, LocalAlignment()), nlp=whitespace_nlp).make_query(QUERY).prepare(whitespace_nlp)
+	de, vv = session.device_embedding(emb)
+	qv = session.to_encoder(emb).encode_tokens(p.token_str)
+	q_id = np.where(p.token_id < session.vocab.size, p.token_id, -1).astype(np.int32)
+	s_cos = engine.DeviceSim.static(de, q_id, qv.unmodified).download()
+	s_pn = np.zeros_like(s_cos)
+	pn(vv, qv, s_pn)
+	for j, i in enumerate(q_id):
+		if i >= 0:
+			s_pn[i, j] = 1.0
+	np.clip(s_pn, 0, 1, out=s_pn)
+
+	cases = [
+		(MixedTokenSimilarity([ts_cos, ts_pn], [3, 1]), np.average([s_cos, s_pn], axis=0, weights=[3, 1]).astype(np.float32),
+			"(0.75 * cosine[toy] + 0.25 * "),
+		(MaximumTokenSimilarity([ts_cos, ts_pn]), np.maximum(s_cos, s_pn), "maximum(cosine[toy], "),
+		(UnaryTokenSimilarityModifier(ts_cos, [Power(2.0), Bias(0.05)]), (s_cos ** 2.0 + 0.05).astype(np.float32), None),
+	]
+	for token_sim, s, name_prefix in cases:
+		assert token_sim.is_modifier
+		if name_prefix:
+			assert token_sim.name.startswith(name_prefix)
+		index = partition.index(OptimizedSpanSim(token_sim, LocalAlignment(gap=gaps.LinearGapCost(0.15))), nlp=whitespace_nlp)
+		result, _ = check_find(oracle, session, emb, index, QUERY, n=12, min_score=0.01, s=s)
+		assert len(result) > 0 and result[0].metric == token_sim.name

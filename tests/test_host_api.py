@@ -113,3 +113,43 @@ def test_partition_and_windows():
 	assert d.n_spans(session.partition("sentence")) == 2
 	assert d.span(session.partition("sentence"), 1).text == "on the mat"
 	assert d.span_info(session.partition("sentence"), 1) == {'start': 3, 'end': 6}
+
+
+def test_token_similarity_modifiers_host():
+	"""vectorian/sim/modifier.py: names and the host-side combination of operand matrices."""
+	from vectorian_b200.sim.modifier import (MixedTokenSimilarity, MaximumTokenSimilarity, MinimumTokenSimilarity,
+		UnaryTokenSimilarityModifier)
+	from vectorian_b200.sim.kernel import Scale, Bias
+	from vectorian_b200.sim.token import TokenSim
+
+	class Named(TokenSim):
+		def __init__(self, name):
+			self._n = name
+		name = property(lambda self: self._n)
+		embeddings = property(lambda self: [self._n + "-emb"])
+
+	a, b = Named("a"), Named("b")
+	rng = np.random.default_rng(0)
+	sa, sb = rng.random((6, 3), dtype=np.float32), rng.random((6, 3), dtype=np.float32)
+	ops = [{"similarity": sa}, {"similarity": sb}]
+
+	mixed = MixedTokenSimilarity([a, b], [1, 3])
+	out = {"similarity": np.zeros_like(sa)}
+	mixed(ops, out)
+	np.testing.assert_allclose(out["similarity"], 0.25 * sa + 0.75 * sb, rtol=1e-6)
+	assert mixed.name == "(0.25 * a + 0.75 * b)" and mixed.is_modifier and mixed.embeddings == ["a-emb", "b-emb"]
+
+	for cls, nm in ((MaximumTokenSimilarity, "maximum"), (MinimumTokenSimilarity, "minimum")):
+		m = cls([a, b])
+		out = {"similarity": np.zeros_like(sa)}
+		m(ops, out)
+		np.testing.assert_array_equal(out["similarity"], np.maximum(sa, sb))   # the reference uses argmax for both
+		assert m.name == f"{nm}(a, b)"
+
+	u = UnaryTokenSimilarityModifier(a, [Scale(0.5), Bias(0.1)])
+	out = {"similarity": np.zeros_like(sa)}
+	u(ops[:1], out)
+	np.testing.assert_allclose(out["similarity"], sa * 0.5 + 0.1, rtol=1e-6)
+	assert u.operands == [a] and "a" in u.name
+	with pytest.raises(ValueError):
+		MixedTokenSimilarity([a, b], [1])

@@ -387,12 +387,46 @@ class BruteForceIndex(Index):
 		self._boost_set = False
 		self.last_timing = None
 
+	def _host_matrix(self, p_query, token_sim):
+		"""[V x T] similarity matrix of a static token similarity in host memory: identity fix-up and clip applied
+		(cpp/metric/static.cpp:58-75); modifiers combine their operands' matrices (cpp/metric/modifier.cpp:18-74)."""
+		session = self.session
+		if token_sim.is_modifier:
+			operands = [{"similarity": self._host_matrix(p_query, op)} for op in token_sim.operands]
+			if not operands:
+				raise ValueError("a token similarity modifier needs at least one operand")
+			out = {"similarity": np.zeros_like(operands[0]["similarity"])}
+			token_sim(operands, out)
+			return out["similarity"]
+		embedding = token_sim.embedding
+		vector_sim = token_sim.similarity
+		encoder = session.to_encoder(embedding)
+		if encoder.is_contextual:
+			raise NotImplementedError("contextual embeddings inside a token similarity modifier")
+		de, vocab_vectors = session.device_embedding(embedding)
+		q_vectors = encoder.encode_tokens(p_query.token_str)
+		q_id = np.where(p_query.token_id < session.vocab.size, p_query.token_id, -1).astype(np.int32)
+		if vector_sim.on_device:
+			sim = engine.DeviceSim.static(de, q_id, q_vectors.unmodified)
+			s = sim.download()
+			sim.close()
+			return s
+		# any other VectorSim: evaluated on the host exactly as the reference's callback does
+		s = np.zeros((session.vocab.size, p_query.n_tokens), dtype=np.float32)
+		vector_sim(vocab_vectors, q_vectors, s)
+		for j, i in enumerate(q_id):
+			if i >= 0:
+				s[i, j] = 1.0
+		np.clip(s, 0.0, 1.0, out=s)
+		return s
+
 	def _similarity(self, p_query, metric_args):
 		"""The query's similarity matrix on the device (cpp/metric/static.cpp:9-78, contextual.cpp:26-63)."""
 		session = self.session
 		token_sim = metric_args['token_metric']
 		if token_sim.is_modifier:
-			raise NotImplementedError("modified token similarities are not on the device path yet (SURVEY.md 8f-3)")
+			dc = session.device_corpus(self.partition)
+			return dc, engine.DeviceSim.upload(np.ascontiguousarray(self._host_matrix(p_query, token_sim), dtype=np.float32))
 		embedding = token_sim.embedding
 		vector_sim = token_sim.similarity
 		encoder = session.to_encoder(embedding)
@@ -405,20 +439,17 @@ class BruteForceIndex(Index):
 			dc = session.load_contextual(self.partition, embedding)
 			return dc, engine.DeviceSim.contextual(q_vec)
 		dc = session.device_corpus(self.partition)
-		de, vocab_vectors = session.device_embedding(embedding)
-		q_vectors = encoder.encode_tokens(p_query.token_str)
-		q_id = np.where(p_query.token_id < session.vocab.size, p_query.token_id, -1).astype(np.int32)
 		if vector_sim.on_device:
+			de, _ = session.device_embedding(embedding)
+			q_vectors = encoder.encode_tokens(p_query.token_str)
+			q_id = np.where(p_query.token_id < session.vocab.size, p_query.token_id, -1).astype(np.int32)
 			return dc, engine.DeviceSim.static(de, q_id, q_vectors.unmodified)
-		# any other VectorSim: evaluated on the host exactly as the reference's callback does, then
-		# identity fix-up + clip (cpp/metric/static.cpp:58-75) and upload
-		s = np.zeros((session.vocab.size, p_query.n_tokens), dtype=np.float32)
-		vector_sim(vocab_vectors, q_vectors, s)
-		for j, i in enumerate(q_id):
-			if i >= 0:
-				s[i, j] = 1.0
-		np.clip(s, 0.0, 1.0, out=s)
-		return dc, engine.DeviceSim.upload(s)
+		return dc, engine.DeviceSim.upload(self._host_matrix(p_query, token_sim))
+
+	@staticmethod
+	def _metric_name(index, token_sim):
+		# Match::metric is the name of the token metric (cpp/query.cpp:158-189)
+		return token_sim.name if token_sim.is_modifier else token_sim.to_args(index)['name']
 
 	def _align_params(self, metric_args, dc, t):
 		alignment = metric_args['alignment']
@@ -471,8 +502,7 @@ class BruteForceIndex(Index):
 
 		ap, keep_a, gap_fns = self._align_params(metric_args, dc, t)
 		qp, keep_q, k = self._query_params(options, metric_args, p_query)
-		# Match::metric is the name of the token metric (vectorian/sim/token.py:39-44)
-		metric_name = metric_args['token_metric'].to_args(self)['name']
+		metric_name = self._metric_name(self, metric_args['token_metric'])
 
 		hits, target, dist = dc.search(sim, ap, qp)
 		self.last_timing = dict(dc.last_timing(), sim_ms=sim.build_ms)
@@ -537,7 +567,7 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 				if doc_lo:
 					hits = hits.copy()
 					hits["doc"] += doc_lo
-				metric_name = margs[ai]['token_metric'].to_args(index)['name']
+				metric_name = index._metric_name(index, margs[ai]['token_metric'])
 				matches = [CoreMatch(index, prepared[qi], h, tg, ds, metric_name, gap_fns[ai])
 					for h, tg, ds in zip(hits, target, dist)]
 				results[qi][ai] = session.make_result(index, matches, duration=duration)
