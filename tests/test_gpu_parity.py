@@ -297,3 +297,35 @@ def test_search_batch_equals_single_searches(engine, oracle):
 			np.testing.assert_array_equal(b_dist, dist)
 	# empty batch
 	assert dc.search_batch([], aps, qp) == []
+
+
+@pytest.mark.parametrize("gap_name", ["linear0.2", "affine", "smooth5", "mixed"])
+def test_gpu_scores_equal_reference_solver(engine, gap_name):
+	"""The CUDA path against the REFERENCE'S OWN solver (oracle/_ref: unmodified pyalign solver.h, oracle/ref/):
+	with the similarity matrix the device built, every sentence score is bit-identical to raw / T of the
+	reference solver, for all three localities (Global + affine: border cells go through xt::linspace in the
+	reference, last-bit differences allowed -- see tests/test_oracle_vs_ref.py)."""
+	from oracle import ref
+	if not ref.available():
+		pytest.skip("oracle/_ref/libpyalign_ref.so not built")
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=4000, t=7, seed=23)
+	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"],
+		corpus["doc_span_off"], 1, 1)
+	de = engine.DeviceEmbedding(emb)
+	sim = engine.DeviceSim.static(de, q_id, q_vec)
+	s = sim.download()
+	lens = corpus["lens"]
+	sent_off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+	for locality in LOCALITIES:
+		ap, keep = align_params(locality, GAPS[gap_name], dc.max_len, 7)
+		qp, _ = _cabi.make_query_params(max_matches=10, min_score=0.0)
+		g_all = dc.score_all(sim, ap, qp)
+		resolved = gaps.resolve_gap_costs(GAPS[gap_name], dc.max_len, 7)
+		raw = ref.corpus_scores(locality, resolved, s, corpus["token_id"], sent_off, dc.max_len, n_threads=4, doc_len=97)
+		expect = raw / np.float32(7)
+		if locality == _cabi.VX_GLOBAL and resolved["gap_kind"] == 1:
+			np.testing.assert_allclose(g_all, expect, rtol=1e-6, atol=1e-6)
+		else:
+			np.testing.assert_array_equal(g_all, expect)
+	sim.close()
+	dc.close()
