@@ -19,14 +19,27 @@
 
 template<int TP>
 __device__ __forceinline__ void load_row(const float *__restrict__ s, int32_t id, float (&row)[TP]) {
-	const float4 *p = reinterpret_cast<const float4*>(s + (size_t)id * TP);
-	#pragma unroll
-	for (int i = 0; i < TP / 4; i++) {
-		const float4 x = __ldg(p + i);
-		row[4 * i + 0] = x.x;
-		row[4 * i + 1] = x.y;
-		row[4 * i + 2] = x.z;
-		row[4 * i + 3] = x.w;
+	if constexpr (TP % 8 == 0) {
+		// rows of 32 / 64 bytes: 256-bit loads (LDG.E.256, new on sm_100) halve the requests of this gather,
+		// which is what bounds the linear / affine kernels (32 different rows per warp and token)
+		const float *p = s + (size_t)id * TP;
+		#pragma unroll
+		for (int i = 0; i < TP / 8; i++) {
+			asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+				: "=f"(row[8 * i + 0]), "=f"(row[8 * i + 1]), "=f"(row[8 * i + 2]), "=f"(row[8 * i + 3]),
+				  "=f"(row[8 * i + 4]), "=f"(row[8 * i + 5]), "=f"(row[8 * i + 6]), "=f"(row[8 * i + 7])
+				: "l"(p + 8 * i));
+		}
+	} else {
+		const float4 *p = reinterpret_cast<const float4*>(s + (size_t)id * TP);
+		#pragma unroll
+		for (int i = 0; i < TP / 4; i++) {
+			const float4 x = __ldg(p + i);
+			row[4 * i + 0] = x.x;
+			row[4 * i + 1] = x.y;
+			row[4 * i + 2] = x.z;
+			row[4 * i + 3] = x.w;
+		}
 	}
 }
 
