@@ -296,6 +296,10 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 	const int warp = threadIdx.x >> 5;
 	float4 *hist = wsb_smem + (size_t)warp * a.cap * Q * 32 + lane;
 
+	// let the next length class of this query start filling SMs as soon as CTAs of this launch retire
+	// (programmatic dependent launch; there is no data dependency between the launches of one query)
+	asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
 	// all 512 TMEM columns of the SM (one CTA per SM); warp w owns lanes 32*(w%4).. and a column range
 	if (warp == 0) {
 		const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&tmem_base_sh);
@@ -424,7 +428,7 @@ static void wsb_plan(int tp, int cap, int *warps, int *rt, int *tmem_cols, int *
 }
 
 template<int TP, int LOC, bool BORD>
-static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms) {
+static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap) {
 	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
 	// SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a TMEM lane quarter
 	// and gets 256 columns.  Long classes fall back to <= 4 warps with 512 columns each.
@@ -452,19 +456,35 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms) {
 		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
 		attr_set = true;
 	}
-	wsb_score_kernel<TP, LOC, BORD><<<blocks, warps * 32, smem, c->stream>>>(a);
+	// Every launch after the first of a query is a programmatic dependent launch: the kernels of one query do not
+	// depend on each other (disjoint tiles and score slots, own chunk counter), so the CTAs of the next length
+	// class move onto SMs as the CTAs of this one retire instead of waiting for its slowest CTA.
+	cudaLaunchConfig_t cfg;
+	memset(&cfg, 0, sizeof(cfg));
+	cfg.gridDim = dim3((unsigned)blocks);
+	cfg.blockDim = dim3((unsigned)(warps * 32));
+	cfg.dynamicSmemBytes = smem;
+	cfg.stream = c->stream;
+	cudaLaunchAttribute attr[1];
+	attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+	attr[0].val.programmaticStreamSerializationAllowed = 1;
+	cfg.attrs = attr;
+	cfg.numAttrs = overlap ? 1 : 0;
+	if (cudaLaunchKernelEx(&cfg, wsb_score_kernel<TP, LOC, BORD>, a) != cudaSuccess) {
+		return -1;
+	}
 	return 1;
 }
 
 template<int TP>
-static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord) {
+static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
 	if (loc == VX_LOCAL) {
-		return bord ? launch_class<TP, VX_LOCAL, true>(c, a, cap, sms) : launch_class<TP, VX_LOCAL, false>(c, a, cap, sms);
+		return bord ? launch_class<TP, VX_LOCAL, true>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false>(c, a, cap, sms, overlap);
 	}
 	if (loc == VX_GLOBAL) {
-		return launch_class<TP, VX_GLOBAL, true>(c, a, cap, sms);
+		return launch_class<TP, VX_GLOBAL, true>(c, a, cap, sms, overlap);
 	}
-	return launch_class<TP, VX_SEMIGLOBAL, true>(c, a, cap, sms);
+	return launch_class<TP, VX_SEMIGLOBAL, true>(c, a, cap, sms, overlap);
 }
 
 // Scores every tile whose windows are at most VX_WSB_MAX_LEN long; *first_tile receives the index of
@@ -506,6 +526,11 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	// length classes of 4 rows (c->class_first[i] = first tile whose length is <= 4 * i), longest first;
 	// consecutive classes that run at the same number of warps per SM share one launch sized for the
 	// longest of them (everything up to 36 rows at T <= 12 is ONE launch at 8 warps per SM)
+	static const bool pdl = getenv("VX_NO_PDL") == nullptr;   // A/B switches for measurements
+	// Measured: overlapping the launches of the short classes is neutral to slightly positive at every size; giving the
+	// last (largest) launch the attribute as well saves 12 % at 1 M sentences (tails overlap) but costs 4 % at
+	// 10 M - 50 M, so it is only done for small corpora.
+	const bool pdl_all = getenv("VX_PDL_ALL") != nullptr || c->n_tiles < 65536;
 	int launches = 0;
 	unsigned int *counters = (unsigned int*)c->d_counters;
 	cudaMemsetAsync(counters, 0, sizeof(unsigned int) * 16, c->stream);
@@ -542,16 +567,16 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 		int rc;
 		switch (s->tp) {
 			case 4:
-				rc = launch_class_t<4>(c, a, cap, sms, ap.locality, bord);
+				rc = launch_class_t<4>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
 				break;
 			case 8:
-				rc = launch_class_t<8>(c, a, cap, sms, ap.locality, bord);
+				rc = launch_class_t<8>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
 				break;
 			case 12:
-				rc = launch_class_t<12>(c, a, cap, sms, ap.locality, bord);
+				rc = launch_class_t<12>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
 				break;
 			case 16:
-				rc = launch_class_t<16>(c, a, cap, sms, ap.locality, bord);
+				rc = launch_class_t<16>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
 				break;
 			default:
 				vx_set_error("vx_launch_wsb: query longer than the fast path supports");
