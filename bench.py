@@ -191,7 +191,7 @@ def main():
 	ap_.add_argument("--warmup", type=int, default=3)
 	ap_.add_argument("--impl", default="ours")
 	ap_.add_argument("--sentences", type=int, default=50_000_000)
-	ap_.add_argument("--cpu-sample", type=int, default=400_000)
+	ap_.add_argument("--cpu-sample", type=int, default=1_000_000)
 	ap_.add_argument("--no-cpu-baseline", action="store_true")
 	ap_.add_argument("--no-clocks", action="store_true")
 	args = ap_.parse_args()
