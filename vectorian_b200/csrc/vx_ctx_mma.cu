@@ -28,6 +28,7 @@
 
 #include "vx_internal.cuh"
 #include <cuda.h>
+#include <vector>
 
 namespace {
 
@@ -442,7 +443,12 @@ extern "C" int vx_debug_ctx_sim(const float *x, int64_t n_elem, int32_t d, const
 	cudaEvent_t e0, e1;
 	VX_CUDA(cudaMalloc(&d_x, sizeof(float) * (size_t)n_elem * d));
 	VX_CUDA(cudaMalloc(&d_q, sizeof(float) * (size_t)t * d));
-	VX_CUDA(cudaMalloc(&d_s, sizeof(float) * (size_t)n_elem * tp));
+	// 4 KB guard zones before and after S_doc: an out-of-bounds store of either kernel fails the hook
+	const size_t guard = 1024;
+	float *d_s_alloc = nullptr;
+	VX_CUDA(cudaMalloc(&d_s_alloc, sizeof(float) * ((size_t)n_elem * tp + 2 * guard)));
+	VX_CUDA(cudaMemset(d_s_alloc, 0x5a, sizeof(float) * ((size_t)n_elem * tp + 2 * guard)));
+	d_s = d_s_alloc + guard;
 	VX_CUDA(cudaMemcpy(d_x, x, sizeof(float) * (size_t)n_elem * d, cudaMemcpyHostToDevice));
 	VX_CUDA(cudaMemcpy(d_q, qhat, sizeof(float) * (size_t)t * d, cudaMemcpyHostToDevice));
 	VX_CUDA(cudaMemset(d_s, 0xff, sizeof(float) * (size_t)n_elem * tp));
@@ -470,13 +476,27 @@ extern "C" int vx_debug_ctx_sim(const float *x, int64_t n_elem, int32_t d, const
 		}
 		err = cudaMemcpy(sdoc_out, d_s, sizeof(float) * (size_t)n_elem * tp, cudaMemcpyDeviceToHost);
 	}
+	bool guard_ok = true;
+	if (err == cudaSuccess) {
+		std::vector<uint32_t> g(2 * guard);
+		err = cudaMemcpy(g.data(), d_s_alloc, sizeof(float) * guard, cudaMemcpyDeviceToHost);
+		if (err == cudaSuccess) {
+			err = cudaMemcpy(g.data() + guard, d_s + (size_t)n_elem * tp, sizeof(float) * guard, cudaMemcpyDeviceToHost);
+		}
+		for (uint32_t x : g) {
+			guard_ok = guard_ok && x == 0x5a5a5a5au;
+		}
+	}
 	cudaEventDestroy(e0);
 	cudaEventDestroy(e1);
 	cudaFree(d_x);
 	cudaFree(d_q);
-	cudaFree(d_s);
+	cudaFree(d_s_alloc);
 	if (err != cudaSuccess) {
 		VX_FAIL(VX_ERR_CUDA, std::string("vx_debug_ctx_sim: ") + cudaGetErrorString(err));
+	}
+	if (!guard_ok) {
+		VX_FAIL(VX_ERR_CUDA, "vx_debug_ctx_sim: a kernel wrote outside S_doc");
 	}
 	if (rc != 1) {
 		VX_FAIL(VX_ERR_INVALID, "vx_debug_ctx_sim: shape not handled by this kernel");
