@@ -43,6 +43,39 @@ __device__ __forceinline__ void load_row(const float *__restrict__ s, int32_t id
 	}
 }
 
+// Token ids of one window (one lane), read as quads: tokens 4q .. 4q+3 of a lane are one 16-byte element of the
+// tiled layout (vx_internal.cuh), so a warp fetches four token positions with one coalesced LDG.128, one quad
+// ahead of its use.  (Reading the ids one by one cost four times the L1 sectors and put the id load on the
+// critical path of every S-row gather.  Used by the linear kernel only: the affine and the multi-setting kernels
+// are register-bound and measured slower with it.)  The stream may run up to two quads past the window: that is the next
+// tile or the slack at the end of the array (VX_TOK_SLACK).
+struct IdStream {
+	const int4 *q;
+	int4 cur, nxt;
+
+	__device__ __forceinline__ explicit IdStream(const int32_t *tok_lane) {
+		q = reinterpret_cast<const int4*>(tok_lane);
+		cur = __ldg(q);
+		nxt = __ldg(q + 32);
+		q += 64;
+	}
+
+	__device__ __forceinline__ int32_t first() const {
+		return cur.x;
+	}
+
+	// id of token u; call with u = 1, 2, 3, ... in order
+	__device__ __forceinline__ int32_t next(int u) {
+		const int k = u & 3;
+		if (k == 0) {
+			cur = nxt;
+			nxt = __ldg(q);
+			q += 32;
+		}
+		return k == 0 ? cur.x : k == 1 ? cur.y : k == 2 ? cur.z : cur.w;
+	}
+};
+
 __device__ __forceinline__ float finish_score(float raw, float total, float boost) {
 	// Score::Score (cpp/match/match.h:302-307) with reference_score == total for submatch_weight == 0.
 	return (raw / total) * boost;
@@ -84,8 +117,8 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 	float last_col = 0.0f;
 
 	float row[TP];
-	int32_t id = tok[0];
-	load_row<TP>(a.s, id, row);
+	IdStream ids(tok);
+	load_row<TP>(a.s, ids.first(), row);
 
 	for (int u = 0; u < len; u++) {
 		float cur[TP];
@@ -94,8 +127,7 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 			cur[v] = row[v];
 		}
 		if (u + 1 < len) {
-			id = tok[vx_elem(0, u + 1, 0)];
-			load_row<TP>(a.s, id, row);
+			load_row<TP>(a.s, ids.next(u + 1), row);
 		}
 
 		float diag = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
