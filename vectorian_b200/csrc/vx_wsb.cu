@@ -43,7 +43,8 @@ struct WsbArgs {
 	float *score;            // by slot
 	unsigned int *counter;   // chunk counter of this launch (zeroed by the host)
 	int64_t tile_begin, tile_end;
-	int32_t chunk;           // tiles per reservation
+	int32_t chunk;           // tiles per reservation for the first n_big reservations, then one tile each
+	uint32_t n_big;
 	int32_t t;
 	int32_t cap;             // rows of history per warp in shared memory (rows rt .. rt+cap-1)
 	int32_t rt;              // rows [0, rt) of the history live in tensor memory (multiple of U)
@@ -323,11 +324,20 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 			got = atomicAdd(a.counter, 1u);
 		}
 		got = __shfl_sync(0xffffffffu, got, 0);
-		int64_t tile = a.tile_begin + (int64_t)got * a.chunk;
+		// guided schedule: large reservations first (the pipeline prologue is paid once per reservation), single
+		// tiles at the end (the shortest windows: the warps finish within one short tile of each other)
+		int64_t tile, tile_stop;
+		if (got < a.n_big) {
+			tile = a.tile_begin + (int64_t)got * a.chunk;
+			tile_stop = tile + a.chunk;
+		} else {
+			tile = a.tile_begin + (int64_t)a.n_big * a.chunk + (got - a.n_big);
+			tile_stop = tile + 1;
+		}
 		if (tile >= a.tile_end) {
 			break;
 		}
-		const int64_t tile_stop = tile + a.chunk < a.tile_end ? tile + a.chunk : a.tile_end;
+		tile_stop = tile_stop < a.tile_end ? tile_stop : a.tile_end;
 		VxTile tl = a.tiles[tile];
 		const int4 *__restrict__ quads = reinterpret_cast<const int4*>(a.tok) + (size_t)tl.base128 * 32 + lane;
 
@@ -444,10 +454,14 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	const int64_t n_tiles = a.tile_end - a.tile_begin;
 	// tiles per reservation: large enough to amortise the pipeline prologue, small enough that the
 	// last chunks balance (>= 32 chunks per warp when the class is big)
-	int64_t chunk = n_tiles / ((int64_t)sms * warps * 32);
+	const int64_t lanes = (int64_t)sms * warps;
+	const int64_t n_tail = n_tiles < 4 * lanes ? n_tiles : 4 * lanes;       // about four single tiles per warp at the end
+	int64_t chunk = (n_tiles - n_tail) / (4 * lanes);                         // >= four large reservations per warp
 	chunk = chunk < 1 ? 1 : chunk > 8 ? 8 : chunk;
+	const int64_t n_big = (n_tiles - n_tail) / chunk;
 	a.chunk = (int32_t)chunk;
-	const int64_t n_chunks = (n_tiles + chunk - 1) / chunk;
+	a.n_big = (uint32_t)n_big;
+	const int64_t n_chunks = n_big + (n_tiles - n_big * chunk);
 	const int64_t want_blocks = (n_chunks + warps - 1) / warps;
 	const int blocks = (int)(want_blocks < sms ? want_blocks : sms);
 	const size_t smem = (size_t)rows_smem * row_bytes * warps;
