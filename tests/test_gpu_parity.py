@@ -329,3 +329,50 @@ def test_gpu_scores_equal_reference_solver(engine, gap_name):
 			np.testing.assert_array_equal(g_all, expect)
 	sim.close()
 	dc.close()
+
+
+@pytest.mark.parametrize("t,dim", [(7, 32), (12, 128), (16, 64), (3, 96)])
+def test_contextual_fused_equals_unfused(engine, t, dim):
+	"""Contextual + linear gap cost: the kernel that fuses the tcgen05 similarity GEMM with the DP (ctx_mma_kernel<TP, true>)
+	gives bit for bit the scores, hits and tracebacks of the two-kernel path (GEMM, then score_linear_kernel)."""
+	import os
+	rng = np.random.default_rng(100 + t)
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=5000, t=t, seed=41)
+	n_tok = len(corpus["token_id"])
+	centroids = rng.standard_normal((50, dim)).astype(np.float32)
+	x = centroids[corpus["token_id"] % 50] + 0.4 * rng.standard_normal((n_tok, dim)).astype(np.float32)
+	q = centroids[rng.integers(0, 50, size=t)] + 0.4 * rng.standard_normal((t, dim)).astype(np.float32)
+	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"],
+		corpus["doc_span_off"], 1, 1)
+	dc.set_contextual(x)
+	boost = (0.5 + rng.random(dc.n_windows)).astype(np.float32)
+	for use_boost in (False, True):
+		if use_boost:
+			dc.set_boost(boost)
+		for locality in LOCALITIES:
+			for gap_name in ("linear0.2", "linear_st", "none"):
+				ap, keep = align_params(locality, GAPS[gap_name], dc.max_len, t)
+				qp, _ = _cabi.make_query_params(max_matches=40, min_score=-1e30)
+				out = {}
+				for mode in ("fused", "unfused"):
+					if mode == "unfused":
+						os.environ["VX_CTX_NOFUSE"] = "1"
+					try:
+						sim = engine.DeviceSim.contextual(q)
+						scores = dc.score_all(sim, ap, qp)
+						launches = dc.last_launches()
+						sim2 = engine.DeviceSim.contextual(q)
+						hits, target, dist = dc.search(sim2, ap, qp)
+						out[mode] = (scores, hits.copy(), target.copy(), dist.copy(), launches)
+						sim.close()
+						sim2.close()
+					finally:
+						os.environ.pop("VX_CTX_NOFUSE", None)
+				f, u = out["fused"], out["unfused"]
+				assert f[4] < u[4]                     # one kernel instead of two
+				np.testing.assert_array_equal(f[0], u[0])
+				for name in ("score", "score_max", "doc", "slice"):
+					np.testing.assert_array_equal(f[1][name], u[1][name])
+				np.testing.assert_array_equal(f[2], u[2])
+				np.testing.assert_array_equal(f[3], u[3])
+	dc.close()

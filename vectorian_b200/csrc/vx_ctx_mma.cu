@@ -28,16 +28,18 @@
 
 #include "vx_internal.cuh"
 #include <cuda.h>
+#include <math_constants.h>
 #include <vector>
 
 namespace {
 
 constexpr int CM_ROWS = 128;                 // tokens per tile (UMMA M)
 constexpr int CM_SUB_BYTES = CM_ROWS * 128;  // one sub-tile: 128 rows x 32 floats
-constexpr int CM_WARP_EPI = 8;               // warps 0-7 convert, 8-11 epilogue, 12 TMA, 13-16 MMA
+constexpr int CM_WARP_EPI = 8;               // warps 0-7 convert, 8-11 epilogue, 12 TMA, 13-16 MMA, 17 DP (fused)
 constexpr int CM_WARP_TMA = 12;
 constexpr int CM_WARP_MMA = 13;
-constexpr int CM_THREADS = 17 * 32;
+constexpr int CM_WARP_DP = 17;               // fused kernels: the DP warp
+constexpr int CM_THREADS = 18 * 32;
 constexpr int CM_MAX_D = 768;
 constexpr int CM_MAX_RAW = 12;
 constexpr int CM_BCHUNK_BYTES = 32 * 128;    // Qhat per 32-float chunk of K: rows 0-15 = hi, rows 16-31 = lo, 128 B each
@@ -134,6 +136,13 @@ struct CtxMmaArgs {
 	int64_t n_elem;
 	int32_t d, t, tp, n_tiles;
 	int32_t n_raw;       // stages of the raw-X ring in shared memory
+	// fused linear-gap DP (FUSED kernels only): the corpus' window tiles and the scoring parameters
+	const VxTile *tiles;
+	int32_t n_vxtiles, n_quads;
+	const float *boost;
+	float *score;
+	float gs, gt, total;
+	int32_t locality, write_sdoc;
 };
 
 // TMEM map (columns): [0, 128) accumulator set 0, [128, 256) set 1 (each: 4 x {16 hi.hi, 16 cross}),
@@ -142,7 +151,12 @@ constexpr int CM_ACC_COLS = 128;
 constexpr int CM_A_COL0 = 256;
 constexpr int CM_NA = 4;
 
-template<int TP>
+// FUSED: the similarity tiles feed the linear-gap DP (NW / SW / semiglobal) inside the same kernel.  A 128-token GEMM
+// tile is exactly one token quad of 32 windows (tokens 4q .. 4q+3 of every lane of a window tile, vx_internal.cuh), so
+// the epilogue warps drop the clipped tile into shared memory as [k][column quad][lane] float4 and ONE extra warp runs
+// the DP of the 32 windows over it (lane = window, the same arithmetic as score_linear_kernel), quad after quad.  Each
+// CTA owns a contiguous range of window tiles balanced by token quads, so S_doc never has to be read back.
+template<int TP, bool FUSED>
 __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_constant__ CUtensorMap tmap, const CtxMmaArgs a) {
 	extern __shared__ uint8_t smem_raw[];
 	const uint32_t raw = smem_u32(smem_raw);
@@ -158,6 +172,9 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 	const uint32_t bar_a_full = bar_raw_empty + 8 * 16, bar_a_empty = bar_a_full + 8 * CM_NA;
 	const uint32_t bar_acc_full = bar_a_empty + 8 * CM_NA, bar_acc_empty = bar_acc_full + 16;
 	uint32_t *const tmem_slot = reinterpret_cast<uint32_t*>(sm + off_bar + 8 * (32 + 2 * CM_NA + 4));
+	// + 384: qid[16]; + 448: s_full[2], s_empty[2]; + 480: fused tile range; + 512: fused S tiles (2 x 128 x TP floats)
+	const uint32_t bar_s_full = base + off_bar + 448, bar_s_empty = bar_s_full + 16;
+	const uint32_t off_stile = off_bar + 512;
 
 	const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -174,6 +191,29 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 			mbar_init(bar_acc_full + 8 * b, 4);            // tcgen05.commit of each MMA warp
 			mbar_init(bar_acc_empty + 8 * b, 4);           // one arrive per epilogue warp
 		}
+		for (int b = 0; b < 2; b++) {
+			mbar_init(bar_s_full + 8 * b, 4);              // fused: S tile written by the four epilogue warps
+			mbar_init(bar_s_empty + 8 * b, 1);             // fused: consumed by the DP warp
+		}
+		if (FUSED) {
+			// window tiles [i_lo, i_hi) of this CTA: boundaries at equal shares of the token quads
+			int32_t *rng = reinterpret_cast<int32_t*>(sm + off_bar + 480);
+			for (int e = 0; e < 2; e++) {
+				const int64_t target = (int64_t)a.n_quads * (blockIdx.x + e) / gridDim.x;
+				int lo = 0, hi = a.n_vxtiles;      // first tile with base128 >= target
+				while (lo < hi) {
+					const int mid = (lo + hi) >> 1;
+					if ((int64_t)a.tiles[mid].base128 < target) {
+						lo = mid + 1;
+					} else {
+						hi = mid;
+					}
+				}
+				rng[e] = blockIdx.x + e == gridDim.x ? a.n_vxtiles : lo;
+			}
+			rng[2] = rng[0] < a.n_vxtiles ? (int32_t)a.tiles[rng[0]].base128 : a.n_quads;
+			rng[3] = rng[1] < a.n_vxtiles ? (int32_t)a.tiles[rng[1]].base128 : a.n_quads;
+		}
 		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 	}
 	if (warp == CM_WARP_MMA) {
@@ -182,7 +222,7 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 	}
 	// Qhat -> one K-major SWIZZLE_128B operand of 32 rows per chunk: rows 0-15 hi, rows 16-31 lo (rows >= t zero)
 	const int d_pad = 32 * n_chunk;                        // X columns >= d read as zero (TMA out-of-bounds fill)
-	for (int i = threadIdx.x; i < 16 * d_pad; i += CM_THREADS) {
+	for (int i = threadIdx.x; i < 16 * d_pad; i += blockDim.x) {
 		const int n = i / d_pad, k = i - n * d_pad;
 		float hi = 0.0f, lo = 0.0f;
 		if (n < a.t && k < a.d) {
@@ -202,13 +242,23 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 	__syncthreads();
 	asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 	const uint32_t tmem = *tmem_slot;
-	const int my_tiles = (int)blockIdx.x < a.n_tiles ? (a.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+	int tile_first, tile_step, my_tiles;
+	if (FUSED) {
+		const int32_t *rng = reinterpret_cast<const int32_t*>(sm + off_bar + 480);
+		tile_first = rng[2];
+		tile_step = 1;
+		my_tiles = rng[3] - rng[2];
+	} else {
+		tile_first = blockIdx.x;
+		tile_step = gridDim.x;
+		my_tiles = (int)blockIdx.x < a.n_tiles ? (a.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+	}
 	const uint32_t n_sub = (uint32_t)my_tiles * n_chunk;   // sub-tiles this CTA processes, in order j = lt * n_chunk + c
 	if (warp == CM_WARP_TMA) {
 		// ---- TMA producer: raw FP32 sub-tiles of X, up to n_raw x 16 KB in flight ----
 		if (lane == 0) {
 			uint32_t s = 0, ph = 0;
-			int c = 0, tile = blockIdx.x;
+			int c = 0, tile = tile_first;
 			for (uint32_t j = 0; j < n_sub; j++) {
 				mbar_wait(bar_raw_empty + 8 * s, ph ^ 1);
 				asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
@@ -223,11 +273,11 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 				}
 				if (++c == n_chunk) {
 					c = 0;
-					tile += gridDim.x;
+					tile += tile_step;
 				}
 			}
 		}
-	} else if (warp >= CM_WARP_MMA) {
+	} else if (warp >= CM_WARP_MMA && warp < CM_WARP_MMA + 4) {
 		// ---- four MMA issuers, one per 8-float step k8 of a sub-tile: A (x_hi, x_lo) from TMEM, B (Qhat hi | lo)
 		// from shared memory.  One warp issuing all eight MMAs of a sub-tile was the bottleneck (~130 mostly
 		// uniform-datapath instructions per sub-tile); the k8 steps use disjoint accumulators, so they split cleanly.
@@ -308,12 +358,12 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 				mbar_arrive(bar_a_full + 8 * ts);
 			}
 		}
-	} else {
-		// ---- epilogue: accumulators -> clip01 -> S_doc ----
+	} else if (warp < CM_WARP_TMA) {
+		// ---- epilogue: accumulators -> clip01 -> S_doc (and, fused, the shared-memory tile of the DP warp) ----
 		const int q = warp & 3;                 // TMEM lane quarter this warp may read
 		const int32_t *const qid = reinterpret_cast<const int32_t*>(sm + off_bar + 384);   // filled before the CTA barrier
-		uint32_t lt = 0;
-		for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, lt++) {
+		for (uint32_t lt = 0; lt < (uint32_t)my_tiles; lt++) {
+			const int tile = tile_first + (int)lt * tile_step;
 			const uint32_t b = lt & 1, u = lt >> 1;
 			mbar_wait(bar_acc_full + 8 * b, u & 1);
 			asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -335,21 +385,123 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 			if (lane == 0) {
 				mbar_arrive(bar_acc_empty + 8 * b);
 			}
-			const int64_t e = (int64_t)tile * CM_ROWS + 32 * q + lane;
-			if (e < a.n_elem) {
+			const int row = 32 * q + lane;
+			const int64_t e = (int64_t)tile * CM_ROWS + row;
+			float4 o4[TP / 4];
+			#pragma unroll
+			for (int jq = 0; jq < TP / 4; jq++) {
+				float o_[4];
+				#pragma unroll
+				for (int w = 0; w < 4; w++) {
+					// identity fix-up (cpp/metric/static.cpp:58-67), then clip (cpp/metric/metric.h:28-30)
+					const float x = (int64_t)qid[4 * jq + w] == e ? 1.0f : hh[4 * jq + w] + cr[4 * jq + w];
+					o_[w] = fminf(fmaxf(x, 0.0f), 1.0f);
+				}
+				o4[jq] = make_float4(o_[0], o_[1], o_[2], o_[3]);
+			}
+			if (e < a.n_elem && (!FUSED || a.write_sdoc)) {
 				float4 *const dst = reinterpret_cast<float4*>(a.sdoc + e * TP);
 				#pragma unroll
 				for (int jq = 0; jq < TP / 4; jq++) {
-					float o_[4];
-					#pragma unroll
-					for (int w = 0; w < 4; w++) {
-						// identity fix-up (cpp/metric/static.cpp:58-67), then clip (cpp/metric/metric.h:28-30)
-						const float x = (int64_t)qid[4 * jq + w] == e ? 1.0f : hh[4 * jq + w] + cr[4 * jq + w];
-						o_[w] = fminf(fmaxf(x, 0.0f), 1.0f);
-					}
-					dst[jq] = make_float4(o_[0], o_[1], o_[2], o_[3]);
+					dst[jq] = o4[jq];
 				}
 			}
+			if (FUSED) {
+				// row = 4 * window lane + token k of the quad -> [k][jq][window lane]: the DP warp reads it conflict-free
+				const uint32_t sb = lt & 1;
+				mbar_wait(bar_s_empty + 8 * sb, ((lt >> 1) & 1) ^ 1);
+				float4 *const st = reinterpret_cast<float4*>(sm + off_stile) + sb * (CM_ROWS * TP / 4);
+				#pragma unroll
+				for (int jq = 0; jq < TP / 4; jq++) {
+					st[((row & 3) * (TP / 4) + jq) * 32 + (row >> 2)] = o4[jq];
+				}
+				__syncwarp();
+				if (lane == 0) {
+					mbar_arrive(bar_s_full + 8 * sb);
+				}
+			}
+		}
+	} else if (FUSED) {
+		// ---- DP warp: linear-gap alignment of the 32 windows of every window tile, lane = window
+		// (LinearGapCostSolver::solve, pyalign/solver.h:2817-2847; the arithmetic of score_linear_kernel, vx_align.cu) ----
+		const int32_t *rng = reinterpret_cast<const int32_t*>(sm + off_bar + 480);
+		const float4 *const st0 = reinterpret_cast<const float4*>(sm + off_stile);
+		const float gs = a.gs, gt = a.gt;
+		const int loc = a.locality, t = a.t;
+		uint32_t lt = 0;
+		for (int i = rng[0]; i < rng[1]; i++) {
+			const VxTile tl = a.tiles[i];
+			const int len = tl.len;
+			float h[TP];   // h[v] = V[u-1, v]
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				h[v] = loc == VX_GLOBAL ? -((float)(v + 1) * gt) : 0.0f;   // solver.h:2804-2806
+			}
+			float best = loc == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+			float last_col = 0.0f;
+			for (int u0 = 0; u0 < len; u0 += 4, lt++) {
+				const uint32_t sb = lt & 1;
+				mbar_wait(bar_s_full + 8 * sb, (lt >> 1) & 1);
+				const float4 *const st = st0 + sb * (CM_ROWS * TP / 4);
+				#pragma unroll
+				for (int k = 0; k < 4; k++) {
+					const int u = u0 + k;
+					if (u < len) {
+						float cur[TP];
+						#pragma unroll
+						for (int jq = 0; jq < TP / 4; jq++) {
+							const float4 x = st[(k * (TP / 4) + jq) * 32 + lane];
+							cur[4 * jq + 0] = x.x;
+							cur[4 * jq + 1] = x.y;
+							cur[4 * jq + 2] = x.z;
+							cur[4 * jq + 3] = x.w;
+						}
+						float diag = loc == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
+						float left = loc == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;  // V[u, -1]
+						#pragma unroll
+						for (int v = 0; v < TP; v++) {
+							const float up = h[v];
+							float x = fmaxf(fmaxf(diag + cur[v], up - gs), left - gt);
+							if (loc == VX_LOCAL) {
+								x = fmaxf(x, 0.0f);
+								if (v < t) {
+									best = fmaxf(best, x);
+								}
+							}
+							diag = up;
+							h[v] = x;
+							left = x;
+							if (v == t - 1) {
+								last_col = x;
+							}
+						}
+						if (loc == VX_SEMIGLOBAL) {
+							best = fmaxf(best, last_col);
+						}
+					}
+				}
+				__syncwarp();
+				if (lane == 0) {
+					mbar_arrive(bar_s_empty + 8 * sb);
+				}
+			}
+			float rawv;
+			if (loc == VX_LOCAL) {
+				rawv = best;
+			} else if (loc == VX_GLOBAL) {
+				rawv = last_col;
+			} else {
+				#pragma unroll
+				for (int v = 0; v < TP; v++) {
+					if (v < t) {
+						best = fmaxf(best, h[v]);
+					}
+				}
+				rawv = best;
+			}
+			const int64_t slot = (int64_t)i * 32 + lane;
+			const float boost = a.boost ? a.boost[slot] : 1.0f;
+			a.score[slot] = lane < tl.n_valid ? (rawv / a.total) * boost : -CUDART_INF_F;
 		}
 	}
 	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -365,10 +517,20 @@ typedef CUresult (*vx_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint3
 	const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
 	CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+struct CtxFusedParams {
+	const VxTile *tiles;
+	int32_t n_vxtiles, n_quads;
+	const float *boost;
+	float *score;
+	float gs, gt, total;
+	int32_t locality, write_sdoc;
+};
+
 // returns 1 when the tensor-core kernel was launched, 0 when the shape is outside what it handles
-// (the caller then uses the SIMT kernel), -1 on an unsupported tp or a failed tensor-map encode
-int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,
-	int32_t t, int32_t tp, float *d_sdoc, cudaStream_t st) {
+// (the caller then uses the SIMT kernel), -1 on an unsupported tp or a failed tensor-map encode.
+// fused != nullptr: the linear-gap DP of every window runs inside the same kernel (ctx_mma_kernel<TP, true>).
+static int launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,
+	int32_t t, int32_t tp, float *d_sdoc, const CtxFusedParams *fused, cudaStream_t st) {
 
 	if (d % 4 != 0 || d > CM_MAX_D || n_elem <= 0 || (reinterpret_cast<uintptr_t>(d_x) & 15) != 0) {
 		return 0;
@@ -402,6 +564,7 @@ int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *
 		return -1;
 	}
 	CtxMmaArgs a;
+	memset(&a, 0, sizeof(a));
 	a.qhat = d_qhat;
 	a.qid = d_qid;
 	a.sdoc = d_sdoc;
@@ -410,15 +573,37 @@ int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *
 	a.t = t;
 	a.tp = tp;
 	a.n_tiles = (int32_t)((n_elem + CM_ROWS - 1) / CM_ROWS);
-	const size_t fixed = 1024 + (size_t)((d + 31) / 32) * CM_BCHUNK_BYTES + 512;
+	int grid = a.n_tiles < sms ? a.n_tiles : sms;
+	size_t fixed = 1024 + (size_t)((d + 31) / 32) * CM_BCHUNK_BYTES + 512;
+	if (fused) {
+		a.tiles = fused->tiles;
+		a.n_vxtiles = fused->n_vxtiles;
+		a.n_quads = fused->n_quads;
+		a.boost = fused->boost;
+		a.score = fused->score;
+		a.gs = fused->gs;
+		a.gt = fused->gt;
+		a.total = fused->total;
+		a.locality = fused->locality;
+		a.write_sdoc = fused->write_sdoc;
+		grid = fused->n_vxtiles < sms ? fused->n_vxtiles : sms;
+		fixed += 2 * (size_t)CM_ROWS * tp * sizeof(float);   // the two S tiles of the DP warp
+	}
 	int n_raw = (int)((227 * 1024 - fixed) / CM_SUB_BYTES);
 	n_raw = n_raw > CM_MAX_RAW ? CM_MAX_RAW : n_raw;
+	if (n_raw < 2 || grid < 1) {
+		return 0;
+	}
 	a.n_raw = n_raw;
 	const size_t smem = fixed + (size_t)n_raw * CM_SUB_BYTES;
-	const int grid = a.n_tiles < sms ? a.n_tiles : sms;
 	#define VX_CM_CASE(TP) case TP: \
-		cudaFuncSetAttribute(ctx_mma_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-		ctx_mma_kernel<TP><<<grid, CM_THREADS, smem, st>>>(tmap, a); \
+		if (fused) { \
+			cudaFuncSetAttribute(ctx_mma_kernel<TP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+			ctx_mma_kernel<TP, true><<<grid, CM_THREADS, smem, st>>>(tmap, a); \
+		} else { \
+			cudaFuncSetAttribute(ctx_mma_kernel<TP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+			ctx_mma_kernel<TP, false><<<grid, CM_THREADS, smem, st>>>(tmap, a); \
+		} \
 		break;
 	switch (tp) {
 		VX_CM_CASE(4)
@@ -430,6 +615,31 @@ int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *
 	}
 	#undef VX_CM_CASE
 	return 1;
+}
+
+int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,
+	int32_t t, int32_t tp, float *d_sdoc, cudaStream_t st) {
+	return launch_ctx_mma(d_x, n_elem, d, d_qhat, d_qid, t, tp, d_sdoc, nullptr, st);
+}
+
+// Contextual query with a linear gap cost: similarity GEMM and the DP of every window in one kernel.  S_doc is still
+// written (the traceback of the k winners reads it) but never read back by the scoring pass.  Returns like above.
+int vx_launch_ctx_fused(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, float *d_sdoc) {
+	if (ap.gap_kind != VX_GAP_LINEAR || c->n_tiles <= 0 || c->n_tiles > 0x7fffffff / 64) {
+		return 0;
+	}
+	CtxFusedParams f;
+	f.tiles = c->d_tiles;
+	f.n_vxtiles = (int32_t)c->n_tiles;
+	f.n_quads = (int32_t)((c->n_tok_tiled - VX_TOK_SLACK) / 128);
+	f.boost = c->d_boost;
+	f.score = c->d_score;
+	f.gs = ap.lin_s;
+	f.gt = ap.lin_t;
+	f.total = qp.total;
+	f.locality = ap.locality;
+	f.write_sdoc = 1;
+	return launch_ctx_mma(c->d_ctx, c->n_tok_tiled, c->ctx_dim, s->d_qhat, nullptr, s->t, s->tp, d_sdoc, &f, c->stream);
 }
 
 // test hook (include/vectorian_b200.h): both contextual similarity kernels on host data

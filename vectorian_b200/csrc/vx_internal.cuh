@@ -200,6 +200,7 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 
 int vx_launch_score_multi(vx_corpus *c, const vx_sim *s, const VxQueryDev &qp, int nl, int ng,
 	const float *gs, const float *gt, float *const *score);
+int vx_launch_ctx_fused(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, float *d_sdoc);
 extern int vx_ctx_force_simt;
 int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,
 	int32_t t, int32_t tp, float *d_sdoc, cudaStream_t st);

@@ -241,7 +241,9 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 
 // Fill c->d_score for every slot; returns kernels launched or < 0.
 // S_doc = clip01(X . Qhat^T) for every token element (once per query); returns launches or < 0
-static int ensure_sdoc(vx_corpus *c, const vx_sim *s) {
+// *fused_done is set when the similarity kernel also ran the DP of every window (contextual + linear gap cost)
+static int ensure_sdoc(vx_corpus *c, const vx_sim *s, const QueryPlan *p, bool *fused_done) {
+	*fused_done = false;
 	if (c->sdoc_of == s) {
 		return 0;
 	}
@@ -256,6 +258,19 @@ static int ensure_sdoc(vx_corpus *c, const vx_sim *s) {
 		}
 		c->sdoc_bytes = need;
 	}
+	const bool no_fuse = getenv("VX_CTX_NOFUSE") != nullptr || getenv("VX_CTX_SIMT") != nullptr;   // A/B switches (read per call: the tests toggle them)
+	if (p && !no_fuse) {
+		const int nf = vx_launch_ctx_fused(c, s, p->ap, p->qp, c->d_sdoc);
+		if (nf < 0 || (nf > 0 && cudaGetLastError() != cudaSuccess)) {
+			vx_set_error("fused contextual similarity + DP kernel launch failed");
+			return -1;
+		}
+		if (nf > 0) {
+			c->sdoc_of = s;
+			*fused_done = true;
+			return nf;
+		}
+	}
 	const int n = vx_launch_ctx_sim(c->d_ctx, c->n_tok_tiled, c->ctx_dim, s->d_qhat, s->t, s->tp, c->d_sdoc, c->stream);
 	if (n < 0 || cudaGetLastError() != cudaSuccess) {
 		vx_set_error("contextual similarity kernel launch failed");
@@ -267,8 +282,9 @@ static int ensure_sdoc(vx_corpus *c, const vx_sim *s) {
 
 static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 	if (p.fast && s->contextual) {
-		const int n0 = ensure_sdoc(c, s);
-		if (n0 < 0) {
+		bool fused_done = false;
+		const int n0 = ensure_sdoc(c, s, &p, &fused_done);
+		if (n0 < 0 || fused_done) {
 			return n0;
 		}
 		vx_sim shadow = *s;
