@@ -143,6 +143,7 @@ int vx_corpus_set_boost(vx_corpus *c, const float *boost, int64_t n);
 /*
  * Contextual per-token vectors X[n_tok x d] (row-major fp32), aligned with token_id.
  * Replaces Document contextual embeddings + per-document GEMM (cpp/metric/contextual.cpp:26-63).
+ * x may be a host pointer or a device pointer of the current device (copied with cudaMemcpyDefault).
  */
 int vx_corpus_set_contextual(vx_corpus *c, const float *x, int64_t n_tok, int32_t d);
 

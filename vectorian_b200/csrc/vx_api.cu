@@ -395,7 +395,7 @@ extern "C" int vx_corpus_set_contextual(vx_corpus *c, const float *x, int64_t n_
 			vx_launch_iota(c->d_iota, c->n_tok_tiled, c->stream);
 		}
 		c->sdoc_of = nullptr;
-		cudaMemcpyAsync(d_raw, x, sizeof(float) * (size_t)n_tok * d, cudaMemcpyHostToDevice, c->stream);
+		cudaMemcpyAsync(d_raw, x, sizeof(float) * (size_t)n_tok * d, cudaMemcpyDefault, c->stream);   // x: host or device pointer (UVA)
 		cudaMemcpyAsync(d_win_tok, c->win_tok.data(), sizeof(int64_t) * (size_t)c->n_win, cudaMemcpyHostToDevice, c->stream);
 		vx_launch_normalize(d_raw, d_norm, n_tok, d, c->stream);
 		vx_launch_pack_ctx(d_norm, d_win_tok, c->d_tiles, c->d_orig, c->n_tiles, d, c->d_ctx, c->stream);

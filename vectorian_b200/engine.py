@@ -91,6 +91,13 @@ class DeviceCorpus:
 		check(self._lib.vx_corpus_set_boost(self._h, ptr(boost, C.c_float), len(boost)), self._lib)
 
 	def set_contextual(self, x):
+		"""x: [n_tokens x d] float32, a numpy array or a contiguous torch CUDA tensor (copied device to device)."""
+		if hasattr(x, "data_ptr"):
+			if not x.is_contiguous() or x.element_size() != 4:
+				raise ValueError("contextual vectors must be a contiguous float32 tensor")
+			check(self._lib.vx_corpus_set_contextual(self._h, C.cast(C.c_void_p(x.data_ptr()), C.POINTER(C.c_float)),
+				x.shape[0], x.shape[1]), self._lib)
+			return
 		x = np.ascontiguousarray(x, dtype=np.float32)
 		check(self._lib.vx_corpus_set_contextual(self._h, ptr(x, C.c_float), x.shape[0], x.shape[1]), self._lib)
 
