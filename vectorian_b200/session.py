@@ -378,33 +378,78 @@ class Session:
 			self._device_embeddings[encoder.name] = entry
 		return entry
 
-	def device_corpus(self, partition):
-		"""This rank's documents packed for one partition (vx_corpus_create), cached."""
-		key = partition.cache_key
+	def token_filter(self, options):
+		"""The query's document-side token filter: (pos bit mask, tag bit mask), or None when the options filter
+		nothing.  Query::make_token_filter + parse_filter_mask (cpp/query.cpp:220-257, cpp/query.h:8-53): bit i of a
+		mask drops every document token whose pos / tag id is i; an unknown name is an error."""
+		bits = []
+		for attr, lexicon in (('pos', self._vocab.pos), ('tag', self._vocab.tag)):
+			mask = 0
+			for name in (options.get(f'{attr}_filter') or []):
+				i = lexicon.get(name)
+				if i < 0:
+					raise RuntimeError(f"illegal value {name} for {attr}_filter")
+				mask |= 1 << i
+			bits.append(mask)
+		return tuple(bits) if any(bits) else None
+
+	@staticmethod
+	def filter_pass(token_pos, token_tag, token_filter):
+		"""TokenFilter::pass (cpp/query.h:22-28) over token columns: bool[n_tokens]."""
+		pos_bits, tag_bits = token_filter
+		drop = ((np.uint64(pos_bits) >> token_pos.astype(np.uint64)) | (np.uint64(tag_bits) >> token_tag.astype(np.uint64))) & np.uint64(1)
+		return drop == 0
+
+	def _filtered_tables(self, partition, token_filter):
+		"""Token and span columns of this rank's documents for one partition; with a token filter the tokens that do
+		not pass are removed and the span bounds are moved to the compacted coordinates -- what FilteredSliceFactory::
+		create_slice does per window with its index map (cpp/slice/static.h:365-416), done once per (partition, filter)
+		for the whole shard so that the DP kernels see dense windows again."""
+		docs = self._documents[self._doc_lo:self._doc_hi]
+		tok, pos, keeps, starts, ends, span_off, tok_off = [], [], [], [], [], [0], [0]
+		for d in docs:
+			s, e = d.span_table(partition.level)
+			s = np.asarray(s, dtype=np.int32)
+			e = np.asarray(e, dtype=np.int32)
+			if token_filter is None:
+				t_id, t_pos = d.token_id, d.token_pos
+				keep = None
+			else:
+				keep = self.filter_pass(d.token_pos, d.token_tag, token_filter)
+				cum = np.concatenate([[0], np.cumsum(keep)]).astype(np.int32)
+				n = d.n_tokens
+				s = cum[np.clip(s, 0, n)]
+				e = cum[np.clip(e, 0, n)]
+				t_id, t_pos = d.token_id[keep], d.token_pos[keep]
+			tok.append(t_id)
+			pos.append(t_pos)
+			keeps.append(keep)
+			starts.append(s)
+			ends.append(e)
+			span_off.append(span_off[-1] + len(s))
+			tok_off.append(tok_off[-1] + len(t_id))
+		cat = lambda xs, dt: np.concatenate(xs).astype(dt) if xs else np.zeros((0,), dtype=dt)
+		return dict(token_id=cat(tok, np.int32), token_pos=cat(pos, np.int8), doc_tok_off=np.array(tok_off, dtype=np.int64),
+			span_start=cat(starts, np.int32), span_end=cat(ends, np.int32), doc_span_off=np.array(span_off, dtype=np.int64),
+			keep=keeps)
+
+	def device_corpus(self, partition, token_filter=None):
+		"""This rank's documents packed for one partition (vx_corpus_create), cached -- per token filter, so that
+		queries that switch filters between calls (the reference's use case, cpp/query.h:9-11) pack once per filter."""
+		key = (partition.cache_key, token_filter)
 		dc = self._device_corpora.get(key)
 		if dc is None:
-			docs = self._documents[self._doc_lo:self._doc_hi]
-			tok = [d.token_id for d in docs]
-			pos = [d.token_pos for d in docs]
-			starts, ends, span_off, tok_off = [], [], [0], [0]
-			for d in docs:
-				s, e = d.span_table(partition.level)
-				starts.append(np.asarray(s, dtype=np.int32))
-				ends.append(np.asarray(e, dtype=np.int32))
-				span_off.append(span_off[-1] + len(s))
-				tok_off.append(tok_off[-1] + d.n_tokens)
-			cat = lambda xs, dt: np.concatenate(xs).astype(dt) if xs else np.zeros((0,), dtype=dt)
+			tb = self._filtered_tables(partition, token_filter)
 			dc = engine.DeviceCorpus(
-				cat(tok, np.int32), np.array(tok_off, dtype=np.int64),
-				cat(starts, np.int32), cat(ends, np.int32), np.array(span_off, dtype=np.int64),
-				partition.window_size, partition.window_step, token_pos=cat(pos, np.int8))
+				tb["token_id"], tb["doc_tok_off"], tb["span_start"], tb["span_end"], tb["doc_span_off"],
+				partition.window_size, partition.window_step, token_pos=tb["token_pos"])
 			self._device_corpora[key] = dc
 		return dc
 
-	def load_contextual(self, partition, embedding):
+	def load_contextual(self, partition, embedding, token_filter=None):
 		"""Make the per-token vectors of `embedding` resident next to the partition's device corpus."""
-		key = partition.cache_key
-		dc = self.device_corpus(partition)
+		key = (partition.cache_key, token_filter)
+		dc = self.device_corpus(partition, token_filter)
 		if self._contextual_loaded.get(key) != embedding.name:
 			docs = self._documents[self._doc_lo:self._doc_hi]
 			dim = embedding.dimension
@@ -412,6 +457,8 @@ class Session:
 			for d, x in zip(docs, xs):
 				if x.shape[0] != d.n_tokens:
 					raise ValueError(f"contextual embedding of document {d.id} has {x.shape[0]} rows for {d.n_tokens} tokens")
+			if token_filter is not None:
+				xs = [x[self.filter_pass(d.token_pos, d.token_tag, token_filter)] for d, x in zip(docs, xs)]
 			x = np.concatenate(xs) if xs else np.zeros((0, dim), dtype=np.float32)
 			dc.set_contextual(x)
 			self._contextual_loaded[key] = embedding.name
