@@ -166,6 +166,13 @@ int vx_sim_upload(const float *s, int64_t v, int32_t t, vx_sim **out);
 /* Contextual: only the normalised query vectors are kept; S_doc tiles are formed inside the DP kernel. */
 int vx_sim_contextual(const float *q_vec, int32_t t, int32_t d, vx_sim **out);
 
+/* Per-token similarity matrix S_tok[n_tok x T] in the token order of vx_corpus_create, for `c` only: the
+ * ContextualSimilarityMatrix a token-similarity modifier produces when one of its operands is contextual
+ * (ModifiedSimilarityMatrixFactory::create, cpp/metric/modifier.cpp:18-74), incl. the rows a static operand
+ * contributes to it (StaticEmbeddingSimilarityMatrixFactory::create, case CONTEXTUAL, cpp/metric/static.cpp:154-189),
+ * or any VectorSim evaluated by the host over contextual vectors (cpp/metric/contextual.cpp:26-63).  No clip. */
+int vx_sim_upload_tokens(vx_corpus *c, const float *s_tok, int64_t n_tok, int32_t t, vx_sim **out);
+
 int vx_sim_download(const vx_sim *s, float *out, int64_t v, int32_t t); /* debug hook "static_similarity_matrix" */
 /* Device time (CUDA events) of the kernels that built this matrix, in ms, and how many were launched. */
 float vx_sim_build_ms(const vx_sim *s);

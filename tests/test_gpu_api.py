@@ -69,14 +69,16 @@ def oracle_corpus(oracle, session, partition, boost=None):
 		partition.window_size, partition.window_step, token_pos=pos, boost=boost)
 
 
-def check_find(oracle, session, emb, index, text, n, min_score, s=None, qkw=None, contextual=False):
+def check_find(oracle, session, emb, index, text, n, min_score, s=None, qkw=None, contextual=False, oc=None, options=None):
 	from vectorian_b200 import engine
-	result = index.find(text, n=n, min_score=min_score)
-	query = index.make_query(text, n=n, min_score=min_score)
+	options = options or {}
+	result = index.find(text, n=n, min_score=min_score, options=options)
+	query = index.make_query(text, n=n, min_score=min_score, options=options)
 	p = query.prepare(whitespace_nlp)
 	t = p.n_tokens
 	partition = index.partition
-	oc = oracle_corpus(oracle, session, partition)
+	if oc is None:
+		oc = oracle_corpus(oracle, session, partition)
 	if s is None:
 		de, vv = session.device_embedding(emb)
 		q_vec = session.to_encoder(emb).encode_tokens(p.token_str).unmodified
@@ -248,3 +250,133 @@ def test_token_similarity_modifiers(oracle):
 		index = partition.index(OptimizedSpanSim(token_sim, LocalAlignment(gap=gaps.LinearGapCost(0.15))), nlp=whitespace_nlp)
 		result, _ = check_find(oracle, session, emb, index, QUERY, n=12, min_score=0.01, s=s)
 		assert len(result) > 0 and result[0].metric == token_sim.name
+
+
+def test_token_filters(oracle):
+	"""pos_filter / tag_filter query options: the document tokens that do not pass are dropped from every window before
+	the alignment (FilteredSliceFactory, cpp/slice/static.h:365-416; TokenFilter::pass, cpp/query.h:22-28).  The oracle
+	runs on a corpus filtered independently here, token by token."""
+	session, (emb,) = make_session(n_docs=5, sent_per_doc=50)
+	options = {"pos_filter": ["DET", "ADP"], "tag_filter": ["JJ"]}
+	drop_pos = {session.vocab.pos.get(x) for x in options["pos_filter"]}
+	drop_tag = {session.vocab.tag.get(x) for x in options["tag_filter"]}
+	tok, pos, starts, ends, span_off, tok_off = [], [], [], [], [0], [0]
+	index_maps = {}
+	for d in session.documents:
+		s0, e0 = d.span_table("sentence")
+		n_doc_tok = 0
+		for k in range(len(s0)):
+			keep = [i for i in range(s0[k], e0[k]) if d.token_pos[i] not in drop_pos and d.token_tag[i] not in drop_tag]
+			index_maps[(d.id, k)] = [i - s0[k] for i in keep]
+			starts.append(n_doc_tok)
+			n_doc_tok += len(keep)
+			ends.append(n_doc_tok)
+			tok.extend(int(d.token_id[i]) for i in keep)
+			pos.extend(int(d.token_pos[i]) for i in keep)
+		span_off.append(span_off[-1] + len(s0))
+		tok_off.append(tok_off[-1] + n_doc_tok)
+	assert len(tok) < sum(d.n_tokens for d in session.documents) * 0.7
+	for alignment, part_args in ((LocalAlignment(gap=gaps.smooth_gap_cost(5)), ("sentence",)),
+			(LocalAlignment(gap=gaps.AffineGapCost(u=0.2, v=0.1)), ("sentence", 3, 2))):
+		partition = session.partition(*part_args)
+		oc = oracle.OracleCorpus(np.array(tok, np.int32), np.array(tok_off), np.array(starts, np.int32), np.array(ends, np.int32),
+			np.array(span_off), partition.window_size, partition.window_step, token_pos=np.array(pos, np.int8))
+		metric = OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), alignment)
+		index = partition.index(metric, nlp=whitespace_nlp)
+		result, p = check_find(oracle, session, emb, index, QUERY, n=20, min_score=0.05, oc=oc, options=options)
+		assert len(result) > 0
+		# unfiltered search on the same index afterwards: a different device corpus, different hits
+		plain = index.find(QUERY, n=20, min_score=0.05)
+		check_find(oracle, session, emb, index, QUERY, n=20, min_score=0.05)
+		if len(part_args) == 1:
+			assert [(m.prepared_doc.id, m.slice_id, m.score) for m in plain] != [(m.prepared_doc.id, m.slice_id, m.score) for m in result]
+			# regions(): matched document tokens are reported at their UNFILTERED positions (cpp/match/flow.cpp:49-61, 95-99)
+			for m in result[:5]:
+				doc = m.prepared_doc.doc
+				s0, _ = m.prepared_doc.span_table("sentence")
+				imap = index_maps[(m.prepared_doc.id, m.slice_id)]
+				want = sorted(doc.token_text[s0[m.slice_id] + imap[u]] for u in m.flow["target"] if u >= 0)
+				got = sorted(r.s for r in m.regions(3) if r.match)
+				assert got == want
+	with pytest.raises(RuntimeError):
+		index.find(QUERY, options={"pos_filter": ["NOPE"]})
+
+
+def test_contextual_operands_in_modifiers(oracle):
+	"""A modifier with a contextual operand is a CONTEXTUAL metric (cpp/query.cpp:156-215): every operand delivers a
+	per-token matrix [n_tokens x T] -- contextual vectors through their VectorSim + clip (cpp/metric/contextual.cpp:26-63),
+	static embeddings as the rows S[id(token)] (cpp/metric/static.cpp:154-189) -- and the modifier combines them
+	(cpp/metric/modifier.cpp:18-74).  The oracle gets matrices assembled independently here; same for a contextual
+	embedding under a VectorSim the device does not evaluate itself, and for a token filter on top."""
+	from vectorian_b200 import engine
+	from vectorian_b200.embedding import Vectors
+	from vectorian_b200.sim.modifier import (MixedTokenSimilarity, MaximumTokenSimilarity, MinimumTokenSimilarity,
+		UnaryTokenSimilarityModifier)
+	from vectorian_b200.sim.kernel import Power, Threshold
+	session, (emb, ctx) = make_session(n_docs=3, sent_per_doc=30, contextual_dim=24)
+	a = EmbeddingTokenSim(emb, CosineSim())
+	b = EmbeddingTokenSim(ctx, CosineSim())
+	pn = ModifiedVectorSim(PNormDistance(p=2), Scale(0.1), DistanceToSimilarity())
+	partition = session.partition("sentence")
+	text = "w3 w17 w5 w120 w1 w9"
+	probe = partition.index(OptimizedSpanSim(a, LocalAlignment()), nlp=whitespace_nlp)
+	p = probe.make_query(text).prepare(whitespace_nlp)
+	de, vv = session.device_embedding(emb)
+	q_id = np.where(p.token_id < session.vocab.size, p.token_id, -1).astype(np.int32)
+	qv = session.to_encoder(emb).encode_tokens(p.token_str)
+	sim = engine.DeviceSim.static(de, q_id, qv.unmodified)
+	s_static = sim.download()
+	sim.close()
+	q_ctx = session.to_encoder(ctx).encode([[p.text_str[t['start']:t['end']] for t in p.tokens]])[0]
+
+	def matrices(keep):
+		tok = np.concatenate([d.token_id for d in session.documents])[keep]
+		x = np.concatenate([d.doc.contextual_embeddings["ctx"] for d in session.documents])[keep]
+		sa = s_static[tok]
+		sb = np.zeros((x.shape[0], q_ctx.shape[0]), dtype=np.float32)
+		CosineSim()(Vectors(x), Vectors(q_ctx), sb)             # the host's VectorSim, as the reference's callback
+		np.clip(sb, 0, 1, out=sb)
+		np.testing.assert_allclose(sb, oracle.sim_contextual(x, q_ctx), rtol=0, atol=1e-5)
+		sp = np.zeros_like(sb)
+		pn(Vectors(x), Vectors(q_ctx), sp)
+		np.clip(sp, 0, 1, out=sp)
+		return sa, sb, sp
+
+	n_tok = sum(d.n_tokens for d in session.documents)
+	sa, sb, sp = matrices(np.ones(n_tok, dtype=bool))
+	cases = [
+		(MixedTokenSimilarity([a, b], [1, 3]), np.average([sa, sb], axis=0, weights=[1, 3]).astype(np.float32)),
+		(MaximumTokenSimilarity([a, b]), np.maximum(sa, sb)),
+		(UnaryTokenSimilarityModifier(MinimumTokenSimilarity([b, a]), [Power(2.0), Threshold(0.1)]), None),
+		(EmbeddingTokenSim(ctx, pn), sp),
+	]
+	for token_sim, s in cases:
+		if s is None:
+			stack = np.array([sb, sa])
+			s = np.take_along_axis(stack, np.argmax(stack, axis=0)[None], axis=0)[0]   # sim/modifier.py:87-93 (argmax for both)
+			s = np.power(np.maximum(s, 0), 2.0)
+			s = np.maximum(0, s - 0.1)
+			s[s > 0] += 0.1                                     # sim/kernel.py Threshold
+		for alignment in (LocalAlignment(gap=gaps.LinearGapCost(0.15)), GlobalAlignment(gap=gaps.smooth_gap_cost(4))):
+			index = partition.index(OptimizedSpanSim(token_sim, alignment), nlp=whitespace_nlp)
+			result, _ = check_find(oracle, session, emb, index, text, n=15, min_score=-1.0, s=np.asarray(s, np.float32), contextual=True)
+			assert len(result) == 15
+			assert result[0].metric == (token_sim.name if token_sim.is_modifier else token_sim.to_args(index)['name'])
+
+	# with a token filter: rows of the filtered token table
+	options = {"pos_filter": ["DET"]}
+	det = session.vocab.pos.get("DET")
+	keep = np.concatenate([d.token_pos for d in session.documents]) != det
+	sa, sb, sp = matrices(keep)
+	tok, pos, starts, ends, span_off, tok_off = [], [], [], [], [0], [0]
+	for d in session.documents:
+		k = d.token_pos != det
+		cum = np.concatenate([[0], np.cumsum(k)])
+		s0, e0 = d.span_table("sentence")
+		tok.append(d.token_id[k]); pos.append(d.token_pos[k]); starts.append(cum[s0]); ends.append(cum[e0])
+		span_off.append(span_off[-1] + len(s0)); tok_off.append(tok_off[-1] + int(k.sum()))
+	oc = oracle.OracleCorpus(np.concatenate(tok), np.array(tok_off), np.concatenate(starts), np.concatenate(ends),
+		np.array(span_off), 1, 1, token_pos=np.concatenate(pos))
+	index = partition.index(OptimizedSpanSim(MixedTokenSimilarity([a, b], [1, 1]), LocalAlignment(gap=gaps.LinearGapCost(0.15))), nlp=whitespace_nlp)
+	check_find(oracle, session, emb, index, text, n=15, min_score=0.0, s=np.average([sa, sb], axis=0, weights=[1, 1]).astype(np.float32), contextual=True,
+		oc=oc, options=options)

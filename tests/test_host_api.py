@@ -153,3 +153,76 @@ def test_token_similarity_modifiers_host():
 	assert u.operands == [a] and "a" in u.name
 	with pytest.raises(ValueError):
 		MixedTokenSimilarity([a, b], [1])
+
+
+def test_token_filter_tables():
+	"""pos_filter / tag_filter (cpp/query.cpp:220-229, cpp/query.h:22-53, cpp/slice/static.h:365-416): bit masks over
+	the session's pos / tag ids; the filtered token table is, window by window, the list of passing tokens."""
+	docs = [
+		Document.from_sentences([["the", "cat", "sat"], ["on", "the", "mat"], ["end"]],
+			pos=[["DET", "NOUN", "VERB"], ["ADP", "DET", "NOUN"], ["NOUN"]],
+			tag=[["DT", "NN", "VBD"], ["IN", "DT", "NN"], ["NN"]]),
+		Document.from_sentences([["a", "dog"], ["the"]], pos=[["DET", "NOUN"], ["DET"]], tag=[["DT", "NN"], ["DT"]]),
+	]
+	session = Session(Corpus(docs), [])
+	assert session.token_filter({}) is None
+	assert session.token_filter({"pos_filter": []}) is None
+	with pytest.raises(RuntimeError, match="illegal value FOO for pos_filter"):
+		session.token_filter({"pos_filter": ["FOO"]})
+	tf = session.token_filter({"pos_filter": ["DET"], "tag_filter": ["VBD"]})
+	assert tf == (1 << session.vocab.pos.get("DET"), 1 << session.vocab.tag.get("VBD"))
+	part = session.partition("sentence")
+	tb = session._filtered_tables(part, tf)
+	strings = session.vocab.tokens.strings
+	words = [strings[i] for i in tb["token_id"]]
+	assert words == ["cat", "on", "mat", "end", "dog"]
+	np.testing.assert_array_equal(tb["doc_tok_off"], [0, 4, 5])
+	np.testing.assert_array_equal(tb["doc_span_off"], [0, 3, 5])
+	np.testing.assert_array_equal(tb["span_start"], [0, 1, 3, 0, 1])
+	np.testing.assert_array_equal(tb["span_end"], [1, 3, 4, 1, 1])      # the last sentence of doc 1 is emptied by the filter
+	plain = session._filtered_tables(part, None)
+	assert len(plain["token_id"]) == 10 and plain["keep"] == [None, None]
+	# per window: exactly FilteredSliceFactory::create_slice's compaction
+	for d, doc in enumerate(session.documents):
+		keep = session.filter_pass(doc.token_pos, doc.token_tag, tf)
+		s0, e0 = doc.span_table("sentence")
+		for k in range(len(s0)):
+			want = [int(doc.token_id[i]) for i in range(s0[k], e0[k]) if keep[i]]
+			lo = tb["doc_tok_off"][d] + tb["span_start"][tb["doc_span_off"][d] + k]
+			hi = tb["doc_tok_off"][d] + tb["span_end"][tb["doc_span_off"][d] + k]
+			assert list(tb["token_id"][lo:hi]) == want
+
+
+def test_host_token_matrix_mixes_static_and_contextual():
+	"""Per-token matrices of a CONTEXTUAL modifier (cpp/query.cpp:156-215, cpp/metric/static.cpp:154-189,
+	cpp/metric/contextual.cpp:26-63, cpp/metric/modifier.cpp:18-74), host side only: a static operand contributes the rows
+	S[id(token)], a contextual one clip(VectorSim(X, Q)); a token filter selects the rows of the filtered token table."""
+	from vectorian_b200.embedding import ContextualEmbedding
+	from vectorian_b200.sim.modifier import MixedTokenSimilarity
+	rng = np.random.default_rng(1)
+	sents = [["the", "cat", "sat"], ["on", "the", "mat"]]
+	pos = [["DET", "NOUN", "VERB"], ["ADP", "DET", "NOUN"]]
+	x = rng.standard_normal((6, 5)).astype(np.float32)
+	doc = Document.from_sentences(sents, pos=pos, contextual_embeddings={"ctx": x})
+	words = ["the", "cat", "sat", "on", "mat"]
+	emb = KeyedVectors("toy", (words, rng.standard_normal((5, 8)).astype(np.float32)))
+	table = {}
+	ctx = ContextualEmbedding("ctx", lambda toks: np.array([table.setdefault(t, rng.standard_normal(5).astype(np.float32)) for t in toks]), 5)
+	session = Session(Corpus([doc]), [emb, ctx])
+	a = EmbeddingTokenSim(emb, PNormDistance(p=2))          # evaluated on the host (no device needed)
+	b = EmbeddingTokenSim(ctx, CosineSim())
+	mixed = MixedTokenSimilarity([a, b], [1, 1])
+	index = session.partition("sentence").index(OptimizedSpanSim(mixed, LocalAlignment()), nlp=whitespace_nlp)
+	assert index._is_contextual(mixed) and index._is_contextual(b) and not index._is_contextual(a)
+	p = index.make_query("cat mat").prepare(whitespace_nlp)
+	sa = index._host_matrix(p, a)
+	assert sa.shape == (session.vocab.size, 2)
+	got = index._host_token_matrix(p, mixed, None)
+	q = np.array([table["cat"], table["mat"]])
+	sb = np.clip((x / np.linalg.norm(x, axis=1, keepdims=True)) @ (q / np.linalg.norm(q, axis=1, keepdims=True)).T, 0, 1)
+	ids = np.concatenate([d.token_id for d in session.documents])
+	np.testing.assert_allclose(got, (sa[ids] + sb) / 2, rtol=1e-6, atol=1e-6)
+	tf = session.token_filter({"pos_filter": ["DET"]})
+	keep = np.array([t != "DET" for s in pos for t in s])
+	got_f = index._host_token_matrix(p, mixed, tf)
+	np.testing.assert_allclose(got_f, got[keep], rtol=0, atol=0)

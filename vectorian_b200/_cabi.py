@@ -144,6 +144,7 @@ _SIGNATURES = {
 	"vx_embedding_destroy": (C.c_int, [C.c_void_p]),
 	"vx_sim_static": (C.c_int, [C.c_void_p, c_int32_p, c_float_p, C.c_int32, C.POINTER(C.c_void_p)]),
 	"vx_sim_upload": (C.c_int, [c_float_p, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),
+	"vx_sim_upload_tokens": (C.c_int, [C.c_void_p, c_float_p, C.c_int64, C.c_int32, C.POINTER(C.c_void_p)]),
 	"vx_sim_contextual": (C.c_int, [c_float_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
 	"vx_sim_download": (C.c_int, [C.c_void_p, c_float_p, C.c_int64, C.c_int32]),
 	"vx_sim_build_ms": (C.c_float, [C.c_void_p]),

@@ -646,6 +646,67 @@ extern "C" int vx_sim_upload(const float *sm, int64_t v, int32_t t, vx_sim **out
 	return VX_OK;
 }
 
+// Per-token similarity matrix S_tok[n_tok x t] supplied by the host (token order of vx_corpus_create): what a
+// ContextualSimilarityMatrix holds per document after ModifiedSimilarityMatrixFactory::create or the static-in-
+// contextual gather (vectorian/core/cpp/metric/modifier.cpp:18-74, cpp/metric/static.cpp:154-189).  The rows are packed
+// into the corpus' tiled element order once, then every DP kernel reads them like the S_doc of a contextual query.
+extern "C" int vx_sim_upload_tokens(vx_corpus *c, const float *s_tok, int64_t n_tok, int32_t t, vx_sim **out) {
+	VX_TRY(require_init());
+	if (!c || !out || t < 0 || (n_tok * t > 0 && !s_tok)) {
+		VX_FAIL(VX_ERR_INVALID, "invalid per-token similarity matrix");
+	}
+	if (n_tok != c->n_tok_raw) {
+		VX_FAIL(VX_ERR_INVALID, "per-token similarity matrix must have one row per corpus token");
+	}
+	cudaSetDevice(c->device);
+	vx_sim *s = new vx_sim();
+	s->contextual = 3;
+	s->owner = c;
+	s->rows = c->n_tok_tiled;
+	s->t = t;
+	s->tp = std::max(4, (t + 3) / 4 * 4);
+	s->nonneg = true;
+	for (int64_t i = 0; i < n_tok * t; i++) {
+		if (!(s_tok[i] >= 0.0f)) {
+			s->nonneg = false;
+			break;
+		}
+	}
+	float *d_raw = nullptr;
+	int64_t *d_win_tok = nullptr;
+	int rc = sim_alloc_s(s);
+	do {
+		if (rc != VX_OK) break;
+		if ((rc = dev_alloc(&d_raw, (size_t)std::max<int64_t>(n_tok, 1) * s->tp)) != VX_OK) break;
+		if ((rc = dev_alloc(&d_win_tok, (size_t)std::max<int64_t>(c->n_win, 1))) != VX_OK) break;
+		if (!c->d_iota) {
+			if ((rc = dev_alloc(&c->d_iota, (size_t)c->n_tok_tiled)) != VX_OK) break;
+			vx_launch_iota(c->d_iota, c->n_tok_tiled, c->stream);
+		}
+		cudaMemsetAsync(s->d_s, 0, s->s_bytes, c->stream);      // padding positions and columns >= t
+		cudaMemsetAsync(d_raw, 0, sizeof(float) * (size_t)std::max<int64_t>(n_tok, 1) * s->tp, c->stream);
+		if (n_tok * t > 0) {
+			cudaMemcpy2DAsync(d_raw, sizeof(float) * s->tp, s_tok, sizeof(float) * t, sizeof(float) * t, (size_t)n_tok,
+				cudaMemcpyHostToDevice, c->stream);
+		}
+		cudaMemcpyAsync(d_win_tok, c->win_tok.data(), sizeof(int64_t) * (size_t)c->n_win, cudaMemcpyHostToDevice, c->stream);
+		vx_launch_pack_ctx(d_raw, d_win_tok, c->d_tiles, c->d_orig, c->n_tiles, s->tp, s->d_s, c->stream);
+		const cudaError_t e = cudaStreamSynchronize(c->stream);
+		if (e != cudaSuccess) {
+			vx_set_error(std::string("per-token similarity upload failed: ") + cudaGetErrorString(e));
+			rc = VX_ERR_CUDA;
+		}
+	} while (0);
+	cudaFree(d_raw);
+	cudaFree(d_win_tok);
+	if (rc != VX_OK) {
+		sim_free(s);
+		return rc;
+	}
+	*out = s;
+	return VX_OK;
+}
+
 extern "C" int vx_sim_contextual(const float *q_vec, int32_t t, int32_t d, vx_sim **out) {
 	VX_TRY(require_init());
 	if (!out || t < 0 || d < 1 || (t > 0 && !q_vec)) {

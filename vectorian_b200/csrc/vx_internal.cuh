@@ -112,7 +112,8 @@ struct vx_sim {
 	int32_t t = 0;
 	int32_t tp = 0;                  // row stride in floats = round_up(t, 4)
 	float *d_s = nullptr;            // [rows x tp], columns >= t are zero
-	int32_t contextual = 0;
+	int32_t contextual = 0;          // 0 static [V x tp]; 1 contextual (query vectors, S_doc formed per search); 3 per-token rows in d_s (vx_sim_upload_tokens)
+	const vx_corpus *owner = nullptr; // contextual == 3: the corpus whose tiled element order d_s follows
 	bool nonneg = false;             // every entry of S is >= 0 (always true for S built on the device: clip01)
 	int32_t d = 0;
 	float *d_qhat = nullptr;         // contextual: [t x d] normalised query vectors

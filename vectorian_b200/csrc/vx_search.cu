@@ -125,7 +125,11 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 	if (need_results && qp->max_matches < 1) {
 		VX_FAIL(VX_ERR_INVALID, "max_matches must be > 0");        // PPK_ASSERT, cpp/result_set.h:27
 	}
-	if (s->contextual) {
+	if (s->contextual == 3) {
+		if (s->owner != c || !c->d_iota || s->rows != c->n_tok_tiled) {
+			VX_FAIL(VX_ERR_INVALID, "per-token similarity matrix belongs to a different corpus");
+		}
+	} else if (s->contextual) {
 		if (!c->d_ctx || c->ctx_dim != s->d) {
 			VX_FAIL(VX_ERR_INVALID, "corpus has no contextual vectors of the query's dimension");
 		}
@@ -281,6 +285,16 @@ static int ensure_sdoc(vx_corpus *c, const vx_sim *s, const QueryPlan *p, bool *
 }
 
 static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
+	if (p.fast && s->contextual == 3) {
+		// per-token rows uploaded by the host, already in tiled element order: d_iota stands in for the token ids
+		vx_sim shadow = *s;
+		shadow.contextual = 0;
+		int32_t *tok = c->d_tok;
+		c->d_tok = c->d_iota;
+		const int n1 = vx_launch_score(c, &shadow, p.ap, p.qp);
+		c->d_tok = tok;
+		return n1;
+	}
 	if (p.fast && s->contextual) {
 		bool fused_done = false;
 		const int n0 = ensure_sdoc(c, s, &p, &fused_done);

@@ -707,7 +707,9 @@ int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 		a.qhat = s->d_qhat;
 		a.ctx_dim = s->d;
 		a.contextual = s->contextual;
-		if (s->contextual && c->sdoc_of == s) {
+		if (s->contextual == 3) {
+			a.contextual = 2;        // a.s = s->d_s holds the per-token rows
+		} else if (s->contextual && c->sdoc_of == s) {
 			a.s = c->d_sdoc;
 			a.contextual = 2;
 		}
@@ -754,7 +756,9 @@ int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 	a.qhat = s->d_qhat;
 	a.ctx_dim = s->d;
 	a.contextual = s->contextual;
-	if (s->contextual && c->sdoc_of == s) {
+	if (s->contextual == 3) {
+		a.contextual = 2;        // a.s = s->d_s holds the per-token rows
+	} else if (s->contextual && c->sdoc_of == s) {
 		a.s = c->d_sdoc;
 		a.contextual = 2;
 	}

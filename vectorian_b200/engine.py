@@ -213,6 +213,16 @@ class DeviceSim:
 		return cls(h, s.shape[0], s.shape[1], lib)
 
 	@classmethod
+	def upload_tokens(cls, corpus, s_tok):
+		"""Per-token similarity rows S_tok[n_tokens x T] (token order of the corpus), valid for `corpus` only
+		(reference: ContextualSimilarityMatrix, cpp/metric/modifier.cpp:18-74, cpp/metric/static.cpp:154-189)."""
+		lib = _cabi.lib()
+		s_tok = np.ascontiguousarray(s_tok, dtype=np.float32)
+		h = C.c_void_p()
+		check(lib.vx_sim_upload_tokens(corpus.handle, ptr(s_tok, C.c_float), s_tok.shape[0], s_tok.shape[1], C.byref(h)), lib)
+		return cls(h, s_tok.shape[0], s_tok.shape[1], lib)
+
+	@classmethod
 	def contextual(cls, q_vec):
 		lib = _cabi.lib()
 		q_vec = np.ascontiguousarray(q_vec, dtype=np.float32)

@@ -206,7 +206,7 @@ class CoreMatch(Match):
 	"""A match produced by the device search; same getters as vectorian/index.py:295-379 over
 	Match / InjectiveFlow (vectorian/core/cpp/match/match.h:275-425, cpp/match/flow.cpp:190-216)."""
 
-	def __init__(self, index, query, hit, target, dist, metric_name, gap_fns):
+	def __init__(self, index, query, hit, target, dist, metric_name, gap_fns, token_filter=None):
 		self._index = index
 		self._session = index.session
 		self._query = query
@@ -218,6 +218,7 @@ class CoreMatch(Match):
 		self._dist = np.array(dist, dtype=np.float32)
 		self._metric = metric_name
 		self._gap_fns = gap_fns
+		self._token_filter = token_filter
 		self._level = "word"
 
 	@property
@@ -280,6 +281,11 @@ class CoreMatch(Match):
 		token_at, n_tok = span.start, doc.n_tokens
 		idx, ln = doc.token_idx, doc.token_len
 		edges = sorted((int(u), j) for j, u in enumerate(self._target) if u >= 0)
+		index_map = None
+		if self._token_filter is not None:
+			# targets count the tokens that pass the filter: back to window positions (cpp/match/flow.cpp:49-61, 95-99)
+			w = slice(token_at, token_at + len(span))
+			index_map = np.flatnonzero(self._session.filter_pass(pdoc.token_pos[w], pdoc.token_tag[w], self._token_filter))
 		regions = []
 		if not edges:
 			s0 = int(idx[token_at])
@@ -290,6 +296,8 @@ class CoreMatch(Match):
 		last_matched = False
 		last_source = -1
 		for target, source in edges:
+			if index_map is not None:
+				target = int(index_map[target])
 			s_i = token_at + target
 			idx0 = int(idx[last_anchor])
 			if int(idx[s_i]) > idx0:
@@ -384,8 +392,24 @@ class BruteForceIndex(Index):
 		super().__init__(*args, **kwargs)
 		self._nlp = nlp
 		self._saliency = saliency   # callable(prepared_doc, partition) -> float32[n_spans], the Booster values
-		self._boost_set = False
 		self.last_timing = None
+
+	def _set_boost(self, dc):
+		"""Booster values (cpp/document.h:175-187) by span.  Device corpora are shared by all indexes of a partition
+		(one per token filter), so the corpus remembers whose values it carries."""
+		owner = getattr(dc, "boost_owner", None)
+		if self._saliency is None:
+			if owner is not None:
+				dc.set_boost(None)
+				dc.boost_owner = None
+			return
+		if owner is self:
+			return
+		session = self.session
+		lo, hi = session.shard[2:]
+		boost = [np.asarray(self._saliency(d, self.partition), dtype=np.float32) for d in session.documents[lo:hi]]
+		dc.set_boost(np.concatenate(boost) if boost else np.zeros((0,), np.float32))
+		dc.boost_owner = self
 
 	def _host_matrix(self, p_query, token_sim):
 		"""[V x T] similarity matrix of a static token similarity in host memory: identity fix-up and clip applied
@@ -402,43 +426,83 @@ class BruteForceIndex(Index):
 		vector_sim = token_sim.similarity
 		encoder = session.to_encoder(embedding)
 		if encoder.is_contextual:
-			raise NotImplementedError("contextual embeddings inside a token similarity modifier")
-		de, vocab_vectors = session.device_embedding(embedding)
+			raise ValueError("a contextual embedding has no [V x T] matrix (use _host_token_matrix)")
 		q_vectors = encoder.encode_tokens(p_query.token_str)
 		q_id = np.where(p_query.token_id < session.vocab.size, p_query.token_id, -1).astype(np.int32)
 		if vector_sim.on_device:
+			de, _ = session.device_embedding(embedding)
 			sim = engine.DeviceSim.static(de, q_id, q_vectors.unmodified)
 			s = sim.download()
 			sim.close()
 			return s
 		# any other VectorSim: evaluated on the host exactly as the reference's callback does
 		s = np.zeros((session.vocab.size, p_query.n_tokens), dtype=np.float32)
-		vector_sim(vocab_vectors, q_vectors, s)
+		vector_sim(session.vocab_vectors(embedding), q_vectors, s)
 		for j, i in enumerate(q_id):
 			if i >= 0:
 				s[i, j] = 1.0
 		np.clip(s, 0.0, 1.0, out=s)
 		return s
 
-	def _similarity(self, p_query, metric_args):
+	def _is_contextual(self, token_sim):
+		"""Query::create_strategy (cpp/query.cpp:156-215): a modifier is CONTEXTUAL as soon as one operand is."""
+		if token_sim.is_modifier:
+			return any(self._is_contextual(op) for op in token_sim.operands)
+		return self.session.to_encoder(token_sim.embedding).is_contextual
+
+	def _query_vectors(self, p_query, encoder):
+		q_vec = encoder.encode([[p_query.text_str[t['start']:t['end']] for t in p_query.tokens]])[0]
+		if q_vec.shape[0] != p_query.n_tokens:
+			raise ValueError("contextual encoder returned a wrong number of query vectors")
+		return q_vec
+
+	def _host_token_matrix(self, p_query, token_sim, token_filter):
+		"""[n_tokens x T] per-token similarity matrix in host memory, rows in the token order of the device corpus:
+		a contextual embedding through any VectorSim + clip (cpp/metric/contextual.cpp:26-63); a static embedding as
+		the rows S[id(token)] of its matrix (cpp/metric/static.cpp:154-189); modifiers combine their operands
+		(cpp/metric/modifier.cpp:18-74).  The reference builds these per document; the shard is one block here."""
+		session = self.session
+		if token_sim.is_modifier:
+			operands = [{"similarity": self._host_token_matrix(p_query, op, token_filter)} for op in token_sim.operands]
+			if not operands:
+				raise ValueError("a token similarity modifier needs at least one operand")
+			out = {"similarity": np.zeros_like(operands[0]["similarity"])}
+			token_sim(operands, out)
+			return out["similarity"]
+		embedding = token_sim.embedding
+		encoder = session.to_encoder(embedding)
+		if encoder.is_contextual:
+			from .embedding import Vectors
+			x = session.contextual_vectors(embedding, token_filter)
+			q_vec = np.asarray(self._query_vectors(p_query, encoder), dtype=np.float32)
+			s = np.zeros((x.shape[0], p_query.n_tokens), dtype=np.float32)
+			token_sim.similarity(Vectors(x), Vectors(q_vec), s)
+			np.clip(s, 0.0, 1.0, out=s)
+			return s
+		ids = session.shard_token_ids(self.partition, token_filter)
+		return np.ascontiguousarray(self._host_matrix(p_query, token_sim)[ids])
+
+	def _similarity(self, p_query, metric_args, token_filter=None):
 		"""The query's similarity matrix on the device (cpp/metric/static.cpp:9-78, contextual.cpp:26-63)."""
 		session = self.session
 		token_sim = metric_args['token_metric']
 		if token_sim.is_modifier:
-			dc = session.device_corpus(self.partition)
+			dc = session.device_corpus(self.partition, token_filter)
+			if self._is_contextual(token_sim):
+				return dc, engine.DeviceSim.upload_tokens(dc, self._host_token_matrix(p_query, token_sim, token_filter))
 			return dc, engine.DeviceSim.upload(np.ascontiguousarray(self._host_matrix(p_query, token_sim), dtype=np.float32))
 		embedding = token_sim.embedding
 		vector_sim = token_sim.similarity
 		encoder = session.to_encoder(embedding)
 		if encoder.is_contextual:
 			if not vector_sim.on_device:
-				raise NotImplementedError("contextual embeddings support CosineSim only")
-			q_vec = encoder.encode([[p_query.text_str[t['start']:t['end']] for t in p_query.tokens]])[0]
-			if q_vec.shape[0] != p_query.n_tokens:
-				raise ValueError("contextual encoder returned a wrong number of query vectors")
-			dc = session.load_contextual(self.partition, embedding)
+				# any other VectorSim over contextual vectors: evaluated on the host like the reference's callback
+				dc = session.device_corpus(self.partition, token_filter)
+				return dc, engine.DeviceSim.upload_tokens(dc, self._host_token_matrix(p_query, token_sim, token_filter))
+			q_vec = self._query_vectors(p_query, encoder)
+			dc = session.load_contextual(self.partition, embedding, token_filter)
 			return dc, engine.DeviceSim.contextual(q_vec)
-		dc = session.device_corpus(self.partition)
+		dc = session.device_corpus(self.partition, token_filter)
 		if vector_sim.on_device:
 			de, _ = session.device_embedding(embedding)
 			q_vectors = encoder.encode_tokens(p_query.token_str)
@@ -493,12 +557,9 @@ class BruteForceIndex(Index):
 		session = self.session
 		t = p_query.n_tokens
 
-		dc, sim = self._similarity(p_query, metric_args)
-		if self._saliency is not None and not self._boost_set:
-			lo, hi = session.shard[2:]
-			boost = [np.asarray(self._saliency(d, self.partition), dtype=np.float32) for d in session.documents[lo:hi]]
-			dc.set_boost(np.concatenate(boost) if boost else np.zeros((0,), np.float32))
-			self._boost_set = True
+		token_filter = session.token_filter(options)
+		dc, sim = self._similarity(p_query, metric_args, token_filter)
+		self._set_boost(dc)
 
 		ap, keep_a, gap_fns = self._align_params(metric_args, dc, t)
 		qp, keep_q, k = self._query_params(options, metric_args, p_query)
@@ -515,7 +576,7 @@ class BruteForceIndex(Index):
 			hits["doc"] += doc_lo
 		if progress:
 			progress(1.0)
-		return [CoreMatch(self, p_query, h, tg, ds, metric_name, gap_fns) for h, tg, ds in zip(hits, target, dist)]
+		return [CoreMatch(self, p_query, h, tg, ds, metric_name, gap_fns, token_filter) for h, tg, ds in zip(hits, target, dist)]
 
 
 
@@ -532,7 +593,7 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 	session = first.session
 	queries = [[index.make_query(text, n=n, min_score=min_score, options=options) for index in indexes] for text in texts]
 	margs = [q.options.get("metric") for q in queries[0]]
-	same = all(index.partition is first.partition for index in indexes) and all(
+	same = all(index.partition is first.partition and index._saliency is None for index in indexes) and all(
 		m and m['metric'] == 'alignment-isolated' and m['token_metric'] is margs[0]['token_metric'] for m in margs)
 	if not same or session.shard[1] > 1:
 		# different partitions / token metrics, tag weights or a sharded session: one find per pair
@@ -540,11 +601,12 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 	start_time = time.time()
 	prepared, sims, live = [], [], []
 	dc = None
+	token_filter = session.token_filter(queries[0][0].options)
 	for qi, row in enumerate(queries):
 		p_query = row[0].prepare(first._nlp)
 		prepared.append(p_query)
 		if len(p_query) > 0:
-			dc, sim = first._similarity(p_query, margs[0])
+			dc, sim = first._similarity(p_query, margs[0], token_filter)
 			sims.append(sim)
 			live.append(qi)
 	results = [[session.make_result(index, [], duration=0.0) for index in indexes] for _ in texts]
@@ -557,6 +619,7 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 			keeps.append(keep)
 			gap_fns.append(fns)
 		qp, keep_q, k = first._query_params(queries[0][0].options, margs[0], prepared[live[0]])
+		first._set_boost(dc)
 		out = dc.search_batch(sims, aps, qp)
 		for sim in sims:
 			sim.close()
@@ -568,7 +631,7 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 					hits = hits.copy()
 					hits["doc"] += doc_lo
 				metric_name = index._metric_name(index, margs[ai]['token_metric'])
-				matches = [CoreMatch(index, prepared[qi], h, tg, ds, metric_name, gap_fns[ai])
+				matches = [CoreMatch(index, prepared[qi], h, tg, ds, metric_name, gap_fns[ai], token_filter)
 					for h, tg, ds in zip(hits, target, dist)]
 				results[qi][ai] = session.make_result(index, matches, duration=duration)
 	return results

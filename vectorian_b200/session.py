@@ -282,6 +282,7 @@ class Session:
 		weights = [d.n_tokens for d in self._documents]
 		self._doc_lo, self._doc_hi = shard_documents(len(self._documents), self._world, self._rank, weights)
 
+		self._vocab_vectors = {}       # encoder name -> Vectors over the vocabulary (host)
 		self._device_embeddings = {}   # encoder name -> (engine.DeviceEmbedding, Vectors over the vocabulary)
 		self._device_corpora = {}      # partition cache key -> engine.DeviceCorpus
 		self._contextual_loaded = {}   # partition cache key -> embedding name currently on the device corpus
@@ -367,13 +368,23 @@ class Session:
 		"""(rank, world size, first document id, one past the last document id) of this process."""
 		return self._rank, self._world, self._doc_lo, self._doc_hi
 
+	def vocab_vectors(self, embedding):
+		"""Static embedding vectors over the session vocabulary in host memory (cpp/vocabulary.h:439-497
+		compile_embeddings), cached until the vocabulary grows."""
+		encoder = self.to_encoder(embedding)
+		vectors = self._vocab_vectors.get(encoder.name)
+		if vectors is None or vectors.shape[0] != self._vocab.size:
+			vectors = encoder.encode_tokens(self._vocab.tokens.strings)
+			self._vocab_vectors[encoder.name] = vectors
+		return vectors
+
 	def device_embedding(self, embedding):
 		"""Static embedding matrix over the session vocabulary, normalised on the device
 		(cpp/vocabulary.h:439-497 compile_embeddings + embedding/vectors.py:71-86)."""
 		encoder = self.to_encoder(embedding)
+		vectors = self.vocab_vectors(embedding)
 		entry = self._device_embeddings.get(encoder.name)
-		if entry is None or entry[1].shape[0] != self._vocab.size:
-			vectors = encoder.encode_tokens(self._vocab.tokens.strings)
+		if entry is None or entry[1] is not vectors:
 			entry = (engine.DeviceEmbedding(vectors.unmodified), vectors)
 			self._device_embeddings[encoder.name] = entry
 		return entry
@@ -446,21 +457,28 @@ class Session:
 			self._device_corpora[key] = dc
 		return dc
 
+	def shard_token_ids(self, partition, token_filter=None):
+		"""Token ids of this rank's documents in the token order of the device corpus (after the token filter)."""
+		return self._filtered_tables(partition, token_filter)["token_id"]
+
+	def contextual_vectors(self, embedding, token_filter=None):
+		"""[n_tokens x d] per-token vectors of this rank's documents, rows aligned with shard_token_ids."""
+		docs = self._documents[self._doc_lo:self._doc_hi]
+		dim = embedding.dimension
+		xs = [np.asarray(d.doc.contextual_embeddings[embedding.name], dtype=np.float32).reshape(-1, dim) for d in docs]
+		for d, x in zip(docs, xs):
+			if x.shape[0] != d.n_tokens:
+				raise ValueError(f"contextual embedding of document {d.id} has {x.shape[0]} rows for {d.n_tokens} tokens")
+		if token_filter is not None:
+			xs = [x[self.filter_pass(d.token_pos, d.token_tag, token_filter)] for d, x in zip(docs, xs)]
+		return np.concatenate(xs) if xs else np.zeros((0, dim), dtype=np.float32)
+
 	def load_contextual(self, partition, embedding, token_filter=None):
 		"""Make the per-token vectors of `embedding` resident next to the partition's device corpus."""
 		key = (partition.cache_key, token_filter)
 		dc = self.device_corpus(partition, token_filter)
 		if self._contextual_loaded.get(key) != embedding.name:
-			docs = self._documents[self._doc_lo:self._doc_hi]
-			dim = embedding.dimension
-			xs = [np.asarray(d.doc.contextual_embeddings[embedding.name], dtype=np.float32).reshape(-1, dim) for d in docs]
-			for d, x in zip(docs, xs):
-				if x.shape[0] != d.n_tokens:
-					raise ValueError(f"contextual embedding of document {d.id} has {x.shape[0]} rows for {d.n_tokens} tokens")
-			if token_filter is not None:
-				xs = [x[self.filter_pass(d.token_pos, d.token_tag, token_filter)] for d, x in zip(docs, xs)]
-			x = np.concatenate(xs) if xs else np.zeros((0, dim), dtype=np.float32)
-			dc.set_contextual(x)
+			dc.set_contextual(self.contextual_vectors(embedding, token_filter))
 			self._contextual_loaded[key] = embedding.name
 		return dc
 
