@@ -376,3 +376,32 @@ def test_contextual_fused_equals_unfused(engine, t, dim):
 				np.testing.assert_array_equal(f[2], u[2])
 				np.testing.assert_array_equal(f[3], u[3])
 	dc.close()
+
+
+@pytest.mark.parametrize("t,dim", [(16, 64), (8, 128)])
+def test_contextual_fused_is_race_free(engine, t, dim):
+	"""The warp-specialised contextual kernel (TMA ring -> converters -> tcgen05 -> epilogue -> DP warp) gives the same
+	bits on every run.  Regression test for a shared-memory stage that was handed back to the TMA producer before the
+	converters' loads had completed (about 3 % of the runs of the (16, 64) case differed in a few windows; found with
+	scripts/stress_ctx.py)."""
+	rng = np.random.default_rng(100 + t)
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=5000, t=t, seed=41)
+	n_tok = len(corpus["token_id"])
+	centroids = rng.standard_normal((50, dim)).astype(np.float32)
+	x = centroids[corpus["token_id"] % 50] + 0.4 * rng.standard_normal((n_tok, dim)).astype(np.float32)
+	q = centroids[rng.integers(0, 50, size=t)] + 0.4 * rng.standard_normal((t, dim)).astype(np.float32)
+	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"],
+		corpus["doc_span_off"], 1, 1)
+	dc.set_contextual(x)
+	ap, keep = align_params(_cabi.VX_LOCAL, GAPS["linear0.2"], dc.max_len, t)
+	qp, _ = _cabi.make_query_params(max_matches=40, min_score=-1e30)
+	first = None
+	for rep in range(250):
+		sim = engine.DeviceSim.contextual(q)
+		scores = dc.score_all(sim, ap, qp)
+		sim.close()
+		if first is None:
+			first = scores
+		else:
+			np.testing.assert_array_equal(scores, first, err_msg=f"run {rep}")
+	dc.close()

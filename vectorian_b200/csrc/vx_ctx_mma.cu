@@ -341,16 +341,19 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 					lo[4 * kc + w] = __float_as_uint(fl);
 				}
 			}
-			__syncwarp();
-			if (lane == 0) {
-				mbar_arrive(bar_raw_empty + 8 * s);      // the values are in registers: the stage may be refilled
-			}
 			const uint32_t ts = j % CM_NA, pa = (j / CM_NA) & 1;
 			mbar_wait(bar_a_empty + 8 * ts, pa ^ 1);
 			asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 			const uint32_t taddr = tmem + ((uint32_t)(32 * q) << 16) + CM_A_COL0 + 64 * ts;
 			tmem_st32(taddr, hi);
 			tmem_st32(taddr + 32, lo);
+			// Release the raw stage only now: the tcgen05.st have read hi / lo, so the eight LDS.128 above have
+			// delivered their data.  An arrive issued right after the loads is NOT ordered behind them (SASS: LDS.128 x 8,
+			// SYNCS.ARRIVE with nothing in between) and the TMA refill of the stage could land before the loads had read
+			// it: seen as a rare wrong S row under back-pressure (fused kernel, L2-resident X; scripts/stress_ctx.py).
+			if (lane == 0) {
+				mbar_arrive(bar_raw_empty + 8 * s);
+			}
 			asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 			asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 			__syncwarp();
@@ -383,7 +386,7 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 			asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 			__syncwarp();
 			if (lane == 0) {
-				mbar_arrive(bar_acc_empty + 8 * b);
+				mbar_arrive(bar_acc_empty + 8 * b);     // after tcgen05.wait::ld: the accumulators are in registers
 			}
 			const int row = 32 * q + lane;
 			const int64_t e = (int64_t)tile * CM_ROWS + row;
@@ -442,6 +445,15 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 			for (int u0 = 0; u0 < len; u0 += 4, lt++) {
 				const uint32_t sb = lt & 1;
 				mbar_wait(bar_s_full + 8 * sb, (lt >> 1) & 1);
+				// The buffer of the PREVIOUS quad is released here, behind this wait: its loads have long been consumed
+				// by the arithmetic (an arrive right behind the loads would not be ordered after them, see the
+				// converters).  The epilogue needs that buffer one whole GEMM tile later, so nothing waits for it.
+				if (lt > 0) {
+					__syncwarp();
+					if (lane == 0) {
+						mbar_arrive(bar_s_empty + 8 * (sb ^ 1));
+					}
+				}
 				const float4 *const st = st0 + sb * (CM_ROWS * TP / 4);
 				#pragma unroll
 				for (int k = 0; k < 4; k++) {
@@ -480,10 +492,7 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 						}
 					}
 				}
-				__syncwarp();
-				if (lane == 0) {
-					mbar_arrive(bar_s_empty + 8 * sb);
-				}
+
 			}
 			float rawv;
 			if (loc == VX_LOCAL) {
@@ -591,6 +600,10 @@ static int launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const flo
 	}
 	int n_raw = (int)((227 * 1024 - fixed) / CM_SUB_BYTES);
 	n_raw = n_raw > CM_MAX_RAW ? CM_MAX_RAW : n_raw;
+	// even: sub-tile j goes to converter group j & 1 and to stage j % n_raw, so with an even ring a stage always belongs
+	// to the same group and every warp sees every phase of its barriers (with an odd ring a warp would skip every other
+	// phase and a parity wait could be satisfied by the phase before the one it means)
+	n_raw &= ~1;
 	if (n_raw < 2 || grid < 1) {
 		return 0;
 	}
