@@ -14,6 +14,46 @@ sys.path.insert(0, ROOT)
 
 from vectorian_b200 import _cabi, engine, gaps, synthetic  # noqa: E402
 
+# Multi-GPU: launched with torchrun (one process per GPU) every rank holds 1 / WORLD of the sentences (its own seeded shard),
+# runs the whole query on it, and the per-rank top-k are merged by one all-gather; times are the max over ranks.
+RANK = int(os.environ.get("RANK", "0"))
+WORLD = int(os.environ.get("WORLD_SIZE", "1"))
+DEV = "cuda:%d" % int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def dist_setup():
+	if WORLD > 1:
+		import torch
+		import torch.distributed as dist
+		torch.cuda.set_device(DEV)
+		dist.init_process_group("nccl", device_id=torch.device(DEV))
+
+
+def sync_all():
+	import torch
+	if WORLD > 1:
+		import torch.distributed as dist
+		dist.barrier()
+	torch.cuda.synchronize()
+
+
+def reduce_max(values):
+	"""max over ranks of a dict of floats"""
+	if WORLD == 1:
+		return values
+	import torch
+	import torch.distributed as dist
+	keys = sorted(values)
+	x = torch.tensor([values[k] for k in keys], dtype=torch.float64, device=DEV)
+	dist.all_reduce(x, op=dist.ReduceOp.MAX)
+	return dict(zip(keys, x.tolist()))
+
+
+def emit(out):
+	if RANK == 0:
+		out["n_gpus"] = WORLD
+		print(json.dumps(out), flush=True)
+
 
 def peaks():
 	try:
@@ -23,13 +63,15 @@ def peaks():
 
 
 def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand_per_cell=None):
-	import torch
-	tok, tables = synthetic.make_corpus_device(n_sent, vocab, device="cuda:0")
+	from vectorian_b200.distributed import gather_topk
+	n_total = n_sent
+	n_sent = n_sent // WORLD
+	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
 	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
 	del tok
 	emb = synthetic.make_embedding(vocab, dim)
 	de = engine.DeviceEmbedding(emb)
-	r = gaps.resolve_gap_costs(gap, dc.max_len, t)
+	r = gaps.resolve_gap_costs(gap, 64, t)
 	kind = r.pop("gap_kind")
 	ap, keep = _cabi.make_align_params(locality, kind, **r)
 	qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
@@ -37,9 +79,12 @@ def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand
 	tm = {"sim_ms": [], "dp_ms": [], "topk_ms": [], "traceback_ms": [], "wall_ms": []}
 	for i in range(3 + steps):
 		q = queries[i % 8]
+		sync_all()
 		t0 = time.perf_counter()
 		sim = engine.DeviceSim.static(de, q, emb[q])
 		hits, target, dist = dc.search(sim, ap, qp)
+		if WORLD > 1:
+			hits, target, dist = gather_topk(hits, target, dist, k, doc_offset=RANK * tables["n_doc"])
 		t1 = time.perf_counter()
 		if i >= 3:
 			lt = dc.last_timing()
@@ -49,45 +94,62 @@ def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand
 			tm["wall_ms"].append((t1 - t0) * 1e3)
 		sim.close()
 	p = peaks()
-	med = {kk: float(np.median(v)) for kk, v in tm.items()}
+	med = reduce_max({kk: float(np.median(v)) for kk, v in tm.items()})
 	dev_ms = med["sim_ms"] + med["dp_ms"] + med["topk_ms"] + med["traceback_ms"]
 	lens = tables["lens"].astype(np.float64)
-	cells = float((lens * t).sum())
+	cells = float((lens * t).sum()) * WORLD
+	n_sent = n_sent * WORLD
 	sms = _cabi.lib().vx_device_sm_count()
-	issue_peak = sms * 128 * p.get("sm_max_mhz", 1965.0) * 1e6
+	issue_peak = sms * 128 * p.get("sm_max_mhz", 1965.0) * 1e6 * WORLD
+	hbm_peak = p["hbm_gbs"] * WORLD
+	tok_total = float(lens.sum()) * WORLD
 	out = {
 		"config": name, "sentences": n_sent, "T": t, "V": vocab, "d": dim, "n_hits": int(len(hits)),
 		"ms": med, "device_ms": dev_ms, "sentences_per_s_device": n_sent / dev_ms * 1e3, "sentences_per_s_e2e": n_sent / med["wall_ms"] * 1e3,
 		"gcups": cells / dev_ms / 1e6,
-		"dp_hbm_frac": (4 * lens.sum() + 4 * n_sent) / (med["dp_ms"] * 1e-3) / 1e9 / p["hbm_gbs"],
+		"dp_hbm_frac": (4 * tok_total + 4 * n_sent) / (med["dp_ms"] * 1e-3) / 1e9 / hbm_peak,
 		"dp_l2_gather_gbs": cells * 4 / (med["dp_ms"] * 1e-3) / 1e9,
 		"sim_hbm_frac": (4.0 * vocab * dim + 4.0 * vocab * ((t + 3) // 4 * 4)) / (med["sim_ms"] * 1e-3) / 1e9 / p["hbm_gbs"],
 	}
 	if cand_per_cell:
 		ops = 2 * cand_per_cell * cells
 		out["dp_issue_frac"] = ops / (med["dp_ms"] * 1e-3) / issue_peak
-	print(json.dumps(out), flush=True)
+	emit(out)
 	dc.close()
 	return out
 
 
 def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
-	rng = np.random.default_rng(5)
-	corpus = synthetic.make_corpus(n_sent, 50_000)
-	n_tok = len(corpus["token_id"])
-	x = rng.standard_normal((n_tok, dim), dtype=np.float32)
-	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"], corpus["doc_span_off"])
+	import torch
+	from vectorian_b200.distributed import gather_topk
+	n_sent = n_sent // WORLD
+	tok, tables = synthetic.make_corpus_device(n_sent, 50_000, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
+	n_tok = int(tok.numel())
+	g = torch.Generator(device=DEV)
+	g.manual_seed(5 + RANK)
+	x = torch.empty((n_tok, dim), dtype=torch.float32, device=DEV)
+	chunk = 1 << 22
+	for i in range(0, n_tok, chunk):
+		x[i:i + min(chunk, n_tok - i)].normal_(generator=g)
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
 	dc.set_contextual(x)
-	r = gaps.resolve_gap_costs(gap, dc.max_len, t)
+	rng = np.random.default_rng(5)
+	qrows = x[torch.from_numpy(rng.integers(0, n_tok, size=(3 + steps, t))).to(DEV)].cpu().numpy()
+	del x, tok
+	torch.cuda.empty_cache()
+	r = gaps.resolve_gap_costs(gap, 64, t)
 	kind = r.pop("gap_kind")
 	ap, keep = _cabi.make_align_params(locality, kind, **r)
 	qp, _ = _cabi.make_query_params(max_matches=k, min_score=-1e30)
 	tm = {"dp_ms": [], "topk_ms": [], "traceback_ms": [], "wall_ms": []}
 	for i in range(3 + steps):
-		q = x[rng.integers(0, n_tok, size=t)] + 0.1 * rng.standard_normal((t, dim), dtype=np.float32)
+		q = qrows[i] + 0.1 * rng.standard_normal((t, dim), dtype=np.float32)
+		sync_all()
 		t0 = time.perf_counter()
 		sim = engine.DeviceSim.contextual(q)
 		hits, target, dist = dc.search(sim, ap, qp)
+		if WORLD > 1:
+			hits, target, dist = gather_topk(hits, target, dist, k, doc_offset=RANK * tables["n_doc"])
 		t1 = time.perf_counter()
 		if i >= 3:
 			lt = dc.last_timing()
@@ -96,23 +158,26 @@ def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
 			tm["wall_ms"].append((t1 - t0) * 1e3)
 		sim.close()
 	p = peaks()
-	med = {kk: float(np.median(v)) for kk, v in tm.items()}
+	med = reduce_max({kk: float(np.median(v)) for kk, v in tm.items()})
 	tp = (t + 3) // 4 * 4
-	lens = corpus["lens"].astype(np.float64)
-	n_pad = float((np.ceil(lens / 4) * 4).sum())   # token positions incl. quad padding (approx.: 32-lane tiles)
+	lens = tables["lens"].astype(np.float64)
+	n_pad = float((np.ceil(lens / 4) * 4).sum()) * WORLD   # token positions incl. quad padding (approx.: 32-lane tiles)
 	gemm_bytes = n_pad * (4.0 * dim + 4.0 * tp)
-	out = {"config": name, "sentences": n_sent, "tokens": n_tok, "T": t, "d": dim, "ms": med,
-		"sentences_per_s_device": n_sent / (med["dp_ms"] + med["topk_ms"] + med["traceback_ms"]) * 1e3,
-		"sentences_per_s_e2e": n_sent / med["wall_ms"] * 1e3,
-		"note": "dp_ms = contextual similarity GEMM + DP kernels",
-		"gemm_dp_hbm_frac_lower_bound": gemm_bytes / (med["dp_ms"] * 1e-3) / 1e9 / p["hbm_gbs"], "top_score": float(hits["score"][0])}
-	print(json.dumps(out), flush=True)
+	n_all = n_sent * WORLD
+	out = {"config": name, "sentences": n_all, "tokens": n_tok * WORLD, "T": t, "d": dim, "ms": med,
+		"sentences_per_s_device": n_all / (med["dp_ms"] + med["topk_ms"] + med["traceback_ms"]) * 1e3,
+		"sentences_per_s_e2e": n_all / med["wall_ms"] * 1e3,
+		"note": "dp_ms = contextual similarity GEMM + DP kernels; vectors generated on the device (random normal)",
+		"gemm_dp_hbm_frac_lower_bound": gemm_bytes / (med["dp_ms"] * 1e-3) / 1e9 / (p["hbm_gbs"] * WORLD), "top_score": float(hits["score"][0])}
+	emit(out)
 	dc.close()
 
 
 def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
 	"""C5: n_queries x 8 settings ({LinearGapCost(u), u in 0,.1,.2,.5} x {Local, Global}) without re-preprocessing."""
-	tok, tables = synthetic.make_corpus_device(n_sent, vocab, device="cuda:0")
+	from vectorian_b200.distributed import gather_topk_many
+	n_sent = n_sent // WORLD
+	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
 	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
 	del tok
 	emb = synthetic.make_embedding(vocab, dim)
@@ -120,7 +185,7 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
 	aps, keeps = [], []
 	for loc in (_cabi.VX_LOCAL, _cabi.VX_GLOBAL):
 		for u in (0.0, 0.1, 0.2, 0.5):
-			r = gaps.resolve_gap_costs(gaps.LinearGapCost(u), dc.max_len, t)
+			r = gaps.resolve_gap_costs(gaps.LinearGapCost(u), 64, t)
 			kind = r.pop("gap_kind")
 			ap, keep = _cabi.make_align_params(loc, kind, **r)
 			aps.append(ap)
@@ -129,32 +194,42 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
 	queries = [synthetic.make_query(t, vocab, seed=99 + i) for i in range(n_queries)]
 	res = {}
 	for mode in ("single", "batch"):
+		if mode == "single" and WORLD > 1:
+			continue
 		for rep in range(2):   # first repetition warms up
+			sync_all()
 			t0 = time.perf_counter()
 			sims = [engine.DeviceSim.static(de, q, emb[q]) for q in queries]
 			if mode == "single":
 				top = [[dc.search(sim, ap, qp)[0]["score"][0] for ap in aps] for sim in sims]
 			else:
 				out = dc.search_batch(sims, aps, qp)
+				if WORLD > 1:   # ONE all-gather for all queries x settings pairs
+					flat = gather_topk_many([out[q][a] for q in range(len(sims)) for a in range(len(aps))], k, doc_offset=RANK * tables["n_doc"])
+					out = [[flat[q * len(aps) + a] for a in range(len(aps))] for q in range(len(sims))]
 				top = [[out[q][a][0]["score"][0] for a in range(len(aps))] for q in range(len(sims))]
 				dev_ms = dc.last_timing()["dp_ms"]
 			t1 = time.perf_counter()
 			for sim in sims:
 				sim.close()
 		res[mode] = {"wall_ms": (t1 - t0) * 1e3, "top": top}
-	assert res["single"]["top"] == res["batch"]["top"]
+	if WORLD == 1:
+		assert res["single"]["top"] == res["batch"]["top"]
 	pairs = n_queries * len(aps)
-	out = {"config": name, "sentences": n_sent, "T": t, "queries": n_queries, "settings": len(aps),
-		"single_calls_wall_ms": res["single"]["wall_ms"], "batch_wall_ms": res["batch"]["wall_ms"], "batch_device_ms": dev_ms,
-		"ms_per_pair_batch": res["batch"]["wall_ms"] / pairs,
-		"sentence_alignments_per_s_e2e": n_sent * pairs / res["batch"]["wall_ms"] * 1e3,
+	m = reduce_max({"batch_wall_ms": res["batch"]["wall_ms"], "batch_device_ms": dev_ms})
+	out = {"config": name, "sentences": n_sent * WORLD, "T": t, "queries": n_queries, "settings": len(aps),
+		"single_calls_wall_ms": res["single"]["wall_ms"] if "single" in res else None,
+		"batch_wall_ms": m["batch_wall_ms"], "batch_device_ms": m["batch_device_ms"],
+		"ms_per_pair_batch": m["batch_wall_ms"] / pairs,
+		"sentence_alignments_per_s_e2e": n_sent * WORLD * pairs / m["batch_wall_ms"] * 1e3,
 		"launches": dc.last_launches()}
-	print(json.dumps(out), flush=True)
+	emit(out)
 	dc.close()
 
 
 def main():
 	which = sys.argv[1:] or ["c1", "c2"]
+	dist_setup()
 	if "c5" in which:
 		run_sweep("C5 sweep: 64 queries x {linear 0,.1,.2,.5} x {Local,Global}, T=12, 10M sentences (one GPU holds the whole corpus)", 10_000_000)
 	if "c1" in which:   # the reference's own CPU-runnable case, on the GPU for comparison
@@ -163,6 +238,12 @@ def main():
 		run_static("C2 SW Local linear(0.2) T=8 1M V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 1_000_000, 200_000, 300, cand_per_cell=3.5)
 	if "c2big" in which:
 		run_static("C2x SW Local linear(0.2) T=8 20M V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 20_000_000, 200_000, 300, cand_per_cell=3.5)
+	if "c4full" in which:   # BASELINE config 4 as stated: 5 M sentences (125 M tokens x 128 fp32 = 64 GB of vectors) over all GPUs
+		run_contextual("C4 (full config) NW Global linear(0.1) contextual d=128 T=8, 5M sentences over %d GPU(s)" % WORLD,
+			_cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 8, 5_000_000, 128)
+	if "c3" in which:       # the headline config with 50 M sentences in TOTAL (strong-scaling view; bench.py holds 50 M per GPU)
+		run_static("C3 (50M sentences in total) WSB Local smooth_gap_cost(5) T=12 V=50k over %d GPU(s)" % WORLD,
+			_cabi.VX_LOCAL, gaps.smooth_gap_cost(5), 12, 50_000_000, 50_000, 300)
 	if "c4" in which:
 		run_contextual("C4 NW Global linear(0.1) contextual d=128 T=8, 200k sentences (1/3 of one GPU's C4 shard)", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 8, 200_000, 128)
 		run_contextual("C4b same, T=16", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 16, 200_000, 128)
@@ -175,3 +256,6 @@ def main():
 
 if __name__ == "__main__":
 	main()
+	if WORLD > 1:
+		import torch.distributed as dist
+		dist.destroy_process_group()

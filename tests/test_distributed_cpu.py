@@ -9,7 +9,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from vectorian_b200._cabi import HIT_DTYPE
-from vectorian_b200.distributed import gather_topk, merge_hits, shard_documents
+from vectorian_b200.distributed import gather_topk, gather_topk_many, merge_hits, shard_documents
 
 
 def _free_port():
@@ -39,6 +39,9 @@ def _worker(rank, world, port, k, t, out_dir):
 	hits, target, distance = _rank_rows(rank, n_local, t)
 	g = gather_topk(hits, target, distance, k, doc_offset=rank * 5)
 	np.savez(os.path.join(out_dir, f"r{rank}.npz"), hits=g[0], target=g[1], distance=g[2])
+	# several searches (a sweep's pairs, queries of different lengths) in one collective
+	many = gather_topk_many([_rank_rows(rank, n_local, tt, k_seed=10 * i) for i, tt in enumerate((t, 3, t))], k, doc_offset=rank * 5)
+	np.savez(os.path.join(out_dir, f"m{rank}.npz"), **{f"{name}{i}": g[j] for i, g in enumerate(many) for j, name in enumerate(("hits", "target", "distance"))})
 	dist.destroy_process_group()
 
 
@@ -57,6 +60,19 @@ def test_gather_topk_world2(tmp_path):
 		np.testing.assert_array_equal(got["hits"], want[0])
 		np.testing.assert_array_equal(got["target"], want[1])      # int16 targets survive the float32 transport bit-exactly
 		np.testing.assert_array_equal(got["distance"], want[2])
+	for i, tt in enumerate((t, 3, t)):
+		parts = []
+		for rank, n_local in enumerate([7, 3]):
+			h, tg, ds = _rank_rows(rank, n_local, tt, k_seed=10 * i)
+			h = h.copy()
+			h["doc"] += rank * 5
+			parts.append((h, tg, ds))
+		want_i = merge_hits(parts, k)
+		for rank in range(world):
+			got = np.load(os.path.join(str(tmp_path), f"m{rank}.npz"))
+			np.testing.assert_array_equal(got[f"hits{i}"], want_i[0])
+			np.testing.assert_array_equal(got[f"target{i}"], want_i[1])
+			np.testing.assert_array_equal(got[f"distance{i}"], want_i[2])
 	# total order: score desc, doc desc, slice desc
 	h = want[0]
 	for a, b in zip(h[:-1], h[1:]):

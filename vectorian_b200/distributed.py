@@ -42,45 +42,71 @@ def merge_hits(parts, k):
 	return hits[order], target[order], distance[order]
 
 
-def gather_topk(hits, target, distance, k, doc_offset=0, group=None, device=None):
-	"""All-gather every rank's local top-k and merge; every rank returns the global result.
-
-	One collective: rows are packed as float32 [k, 4 + 2T] = (score, score_max, doc, slice,
-	target[T], dist[T]) plus the row count in row k.  doc/slice/target are exact in float32 only up
-	to 2^24, so they travel bit-cast, not converted.
-	"""
-	if not (dist.is_available() and dist.is_initialized()):
-		h = hits.copy()
-		h["doc"] += doc_offset
-		return merge_hits([(h, target, distance)], k)
-	world = dist.get_world_size(group)
-	t = target.shape[1] if target.ndim == 2 else 0
+def _pack_rows(hits, target, distance, k, t, doc_offset):
+	"""float32 [k + 1, 4 + 2T] = (score, score_max, doc, slice, target[T], dist[T]) rows + the row count in row k.
+	doc / slice / target travel bit-cast (exact in float32 only up to 2^24 if converted)."""
 	n = len(hits)
-	width = 4 + 2 * t
-	buf = np.zeros((k + 1, width), dtype=np.float32)
+	buf = np.zeros((k + 1, 4 + 2 * t), dtype=np.float32)
 	ibuf = buf.view(np.int32)
 	buf[:n, 0] = hits["score"]
 	buf[:n, 1] = hits["score_max"]
 	ibuf[:n, 2] = hits["doc"] + doc_offset
 	ibuf[:n, 3] = hits["slice"]
-	ibuf[:n, 4:4 + t] = target.astype(np.int32)
-	buf[:n, 4 + t:] = distance
+	if t:
+		ibuf[:n, 4:4 + t] = target[:, :t].astype(np.int32)
+		buf[:n, 4 + t:] = distance[:, :t]
 	ibuf[k, 0] = n
+	return buf
+
+
+def _unpack_rows(out, k, t):
+	iout = out.view(np.int32)
+	m = int(iout[k, 0])
+	h = np.zeros((m,), dtype=HIT_DTYPE)
+	h["score"] = out[:m, 0]
+	h["score_max"] = out[:m, 1]
+	h["doc"] = iout[:m, 2]
+	h["slice"] = iout[:m, 3]
+	return h, iout[:m, 4:4 + t].astype(np.int16), out[:m, 4 + t:].copy()
+
+
+def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
+	"""All-gather the local top-k of SEVERAL searches (e.g. the queries x settings pairs of a parameter sweep) in ONE
+	collective and merge each; `results` is a list of (hits, target, dist) triples, every rank returns the list of
+	global results."""
+	if not (dist.is_available() and dist.is_initialized()):
+		out = []
+		for hits, target, distance in results:
+			h = hits.copy()
+			h["doc"] += doc_offset
+			out.append(merge_hits([(h, target, distance)], k))
+		return out
+	if not results:
+		return []
+	world = dist.get_world_size(group)
+	t = max(r[1].shape[1] if r[1].ndim == 2 else 0 for r in results)
+	buf = np.stack([_pack_rows(h, tg, ds, k, tg.shape[1] if tg.ndim == 2 else 0, doc_offset) if (tg.ndim == 2 and tg.shape[1] == t)
+		else _pack_rows(h, np.pad(tg, ((0, 0), (0, t - tg.shape[1])), constant_values=-1), np.pad(ds, ((0, 0), (0, t - ds.shape[1])), constant_values=1.0), k, t, doc_offset)
+		for h, tg, ds in results])
 	backend = dist.get_backend(group)
 	if device is None:
 		device = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
 	send = torch.from_numpy(buf).to(device)
-	recv = torch.empty((world, k + 1, width), dtype=torch.float32, device=device)
+	recv = torch.empty((world,) + buf.shape, dtype=torch.float32, device=device)
 	dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
 	out = recv.cpu().numpy()
-	iout = out.view(np.int32)
-	parts = []
-	for r in range(world):
-		m = int(iout[r, k, 0])
-		h = np.zeros((m,), dtype=HIT_DTYPE)
-		h["score"] = out[r, :m, 0]
-		h["score_max"] = out[r, :m, 1]
-		h["doc"] = iout[r, :m, 2]
-		h["slice"] = iout[r, :m, 3]
-		parts.append((h, iout[r, :m, 4:4 + t].astype(np.int16), out[r, :m, 4 + t:].copy()))
-	return merge_hits(parts, k)
+	merged = []
+	for i, (h, tg, ds) in enumerate(results):
+		ti = tg.shape[1] if tg.ndim == 2 else 0
+		parts = []
+		for r in range(world):
+			hh, tt, dd = _unpack_rows(out[r, i], k, t)
+			parts.append((hh, tt[:, :ti], dd[:, :ti]))
+		merged.append(merge_hits(parts, k))
+	return merged
+
+
+def gather_topk(hits, target, distance, k, doc_offset=0, group=None, device=None):
+	"""All-gather every rank's local top-k and merge; every rank returns the global result (one collective of
+	k x (16 + 8T) bytes per rank)."""
+	return gather_topk_many([(hits, target, distance)], k, doc_offset=doc_offset, group=group, device=device)[0]
