@@ -200,13 +200,17 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
 			sync_all()
 			t0 = time.perf_counter()
 			sims = [engine.DeviceSim.static(de, q, emb[q]) for q in queries]
+			ta = time.perf_counter()
 			if mode == "single":
 				top = [[dc.search(sim, ap, qp)[0]["score"][0] for ap in aps] for sim in sims]
 			else:
 				out = dc.search_batch(sims, aps, qp)
+				tb = time.perf_counter()
+				host = {"sims_ms": (ta - t0) * 1e3, "search_batch_ms": (tb - ta) * 1e3}
 				if WORLD > 1:   # ONE all-gather for all queries x settings pairs
 					flat = gather_topk_many([out[q][a] for q in range(len(sims)) for a in range(len(aps))], k, doc_offset=RANK * tables["n_doc"])
 					out = [[flat[q * len(aps) + a] for a in range(len(aps))] for q in range(len(sims))]
+				host["gather_merge_ms"] = (time.perf_counter() - tb) * 1e3
 				top = [[out[q][a][0]["score"][0] for a in range(len(aps))] for q in range(len(sims))]
 				dev_ms = dc.last_timing()["dp_ms"]
 			t1 = time.perf_counter()
@@ -222,7 +226,7 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
 		"batch_wall_ms": m["batch_wall_ms"], "batch_device_ms": m["batch_device_ms"],
 		"ms_per_pair_batch": m["batch_wall_ms"] / pairs,
 		"sentence_alignments_per_s_e2e": n_sent * WORLD * pairs / m["batch_wall_ms"] * 1e3,
-		"launches": dc.last_launches()}
+		"launches": dc.last_launches(), "host_ms_rank0": host}
 	emit(out)
 	dc.close()
 

@@ -42,38 +42,11 @@ def merge_hits(parts, k):
 	return hits[order], target[order], distance[order]
 
 
-def _pack_rows(hits, target, distance, k, t, doc_offset):
-	"""float32 [k + 1, 4 + 2T] = (score, score_max, doc, slice, target[T], dist[T]) rows + the row count in row k.
-	doc / slice / target travel bit-cast (exact in float32 only up to 2^24 if converted)."""
-	n = len(hits)
-	buf = np.zeros((k + 1, 4 + 2 * t), dtype=np.float32)
-	ibuf = buf.view(np.int32)
-	buf[:n, 0] = hits["score"]
-	buf[:n, 1] = hits["score_max"]
-	ibuf[:n, 2] = hits["doc"] + doc_offset
-	ibuf[:n, 3] = hits["slice"]
-	if t:
-		ibuf[:n, 4:4 + t] = target[:, :t].astype(np.int32)
-		buf[:n, 4 + t:] = distance[:, :t]
-	ibuf[k, 0] = n
-	return buf
-
-
-def _unpack_rows(out, k, t):
-	iout = out.view(np.int32)
-	m = int(iout[k, 0])
-	h = np.zeros((m,), dtype=HIT_DTYPE)
-	h["score"] = out[:m, 0]
-	h["score_max"] = out[:m, 1]
-	h["doc"] = iout[:m, 2]
-	h["slice"] = iout[:m, 3]
-	return h, iout[:m, 4:4 + t].astype(np.int16), out[:m, 4 + t:].copy()
-
-
 def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
 	"""All-gather the local top-k of SEVERAL searches (e.g. the queries x settings pairs of a parameter sweep) in ONE
 	collective and merge each; `results` is a list of (hits, target, dist) triples, every rank returns the list of
-	global results."""
+	global results.  The merge runs where the gathered rows are (torch, on the GPU under NCCL): two sorts over
+	[pairs, world * k] keys instead of a Python loop per pair, then one copy of the pairs x k winning rows to the host."""
 	if not (dist.is_available() and dist.is_initialized()):
 		out = []
 		for hits, target, distance in results:
@@ -84,26 +57,55 @@ def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
 	if not results:
 		return []
 	world = dist.get_world_size(group)
-	t = max(r[1].shape[1] if r[1].ndim == 2 else 0 for r in results)
-	buf = np.stack([_pack_rows(h, tg, ds, k, tg.shape[1] if tg.ndim == 2 else 0, doc_offset) if (tg.ndim == 2 and tg.shape[1] == t)
-		else _pack_rows(h, np.pad(tg, ((0, 0), (0, t - tg.shape[1])), constant_values=-1), np.pad(ds, ((0, 0), (0, t - ds.shape[1])), constant_values=1.0), k, t, doc_offset)
-		for h, tg, ds in results])
+	widths = [r[1].shape[1] if r[1].ndim == 2 else 0 for r in results]
+	t = max(widths)
+	n_pairs = len(results)
+	buf = np.zeros((n_pairs, k + 1, 4 + 2 * t), dtype=np.float32)
+	ibuf = buf.view(np.int32)
+	buf[:, :, 4 + t:] = 1.0
+	ibuf[:, :, 4:4 + t] = -1
+	for i, (h, tg, ds) in enumerate(results):
+		n, ti = len(h), widths[i]
+		buf[i, :n, 0] = h["score"]
+		buf[i, :n, 1] = h["score_max"]
+		ibuf[i, :n, 2] = h["doc"] + doc_offset
+		ibuf[i, :n, 3] = h["slice"]
+		if ti:
+			ibuf[i, :n, 4:4 + ti] = tg
+			buf[i, :n, 4 + t:4 + t + ti] = ds
+		ibuf[i, k, 0] = n
 	backend = dist.get_backend(group)
 	if device is None:
 		device = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
 	send = torch.from_numpy(buf).to(device)
 	recv = torch.empty((world,) + buf.shape, dtype=torch.float32, device=device)
 	dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
-	out = recv.cpu().numpy()
-	merged = []
-	for i, (h, tg, ds) in enumerate(results):
-		ti = tg.shape[1] if tg.ndim == 2 else 0
-		parts = []
-		for r in range(world):
-			hh, tt, dd = _unpack_rows(out[r, i], k, t)
-			parts.append((hh, tt[:, :ti], dd[:, :ti]))
-		merged.append(merge_hits(parts, k))
-	return merged
+
+	# merge on the device: total order score desc, doc desc, slice desc (Match::compare_by_score made total)
+	irecv = recv.view(torch.int32)
+	count = irecv[:, :, k, 0].permute(1, 0)                                   # [pairs, world]
+	rows = recv[:, :, :k, :].permute(1, 0, 2, 3).reshape(n_pairs, world * k, -1)
+	irows = irecv[:, :, :k, :].permute(1, 0, 2, 3).reshape(n_pairs, world * k, -1)
+	valid = (torch.arange(k, device=device)[None, None, :] < count[:, :, None]).reshape(n_pairs, world * k)
+	score = torch.where(valid, rows[:, :, 0], torch.full_like(rows[:, :, 0], float("-inf")))
+	tie = irows[:, :, 2].to(torch.int64) * (1 << 32) + irows[:, :, 3].to(torch.int64)
+	tie = torch.where(valid, tie, torch.full_like(tie, -1))
+	o1 = torch.argsort(tie, dim=1, descending=True)
+	o2 = torch.sort(torch.gather(score, 1, o1), dim=1, descending=True, stable=True).indices
+	order = torch.gather(o1, 1, o2)[:, :k]
+	top = torch.gather(rows, 1, order[:, :, None].expand(-1, -1, rows.shape[2])).contiguous()
+	n_out = torch.clamp(valid.sum(dim=1), max=k)
+	top_h = top.cpu().numpy()
+	n_h = n_out.cpu().numpy()
+	itop = top_h.view(np.int32)
+	all_hits = np.zeros((n_pairs, k), dtype=HIT_DTYPE)
+	all_hits["score"] = top_h[:, :, 0]
+	all_hits["score_max"] = top_h[:, :, 1]
+	all_hits["doc"] = itop[:, :, 2]
+	all_hits["slice"] = itop[:, :, 3]
+	all_target = itop[:, :, 4:4 + t].astype(np.int16)
+	all_dist = np.ascontiguousarray(top_h[:, :, 4 + t:])
+	return [(all_hits[i, :n_h[i]], all_target[i, :n_h[i], :widths[i]], all_dist[i, :n_h[i], :widths[i]]) for i in range(n_pairs)]
 
 
 def gather_topk(hits, target, distance, k, doc_offset=0, group=None, device=None):
