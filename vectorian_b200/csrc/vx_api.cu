@@ -106,6 +106,17 @@ static void corpus_free(vx_corpus *c) {
 			cudaEventDestroy(e);
 		}
 	}
+	for (int b = 0; b < 2; b++) {
+		if (c->ev_dp[b]) {
+			cudaEventDestroy(c->ev_dp[b]);
+		}
+		if (c->ev_sel[b]) {
+			cudaEventDestroy(c->ev_sel[b]);
+		}
+	}
+	if (c->select_stream) {
+		cudaStreamDestroy(c->select_stream);
+	}
 	if (c->stream) {
 		cudaStreamDestroy(c->stream);
 	}

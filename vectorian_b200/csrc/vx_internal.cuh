@@ -81,7 +81,7 @@ struct vx_corpus {
 	size_t sdoc_bytes = 0;
 	const vx_sim *sdoc_of = nullptr; // the query d_sdoc currently holds (nullptr: none); reset at the start of every search
 	float *d_score = nullptr;        // by slot, scratch of the last search
-	float *d_score_multi = nullptr;  // 8 x n_slots, vx_search_batch: scores of the fused settings (lazily allocated)
+	float *d_score_multi = nullptr;  // 2 x 8 x n_slots, vx_search_batch: scores of the fused settings, double-buffered (lazily allocated)
 	void *d_work = nullptr;          // top-k / traceback workspace
 	size_t work_bytes = 0;
 	void *d_scratch = nullptr;       // DP scratch of the exact kernel
@@ -95,6 +95,9 @@ struct vx_corpus {
 	void *d_counters = nullptr;      // 16 x uint32 tile counters of the persistent kernels
 
 	cudaStream_t stream = nullptr;
+	cudaStream_t select_stream = nullptr;            // vx_search_batch: top-k + traceback of one group while the next group's DP runs
+	cudaEvent_t ev_dp[2] = {nullptr, nullptr};       // DP of score buffer b finished (main stream)
+	cudaEvent_t ev_sel[2] = {nullptr, nullptr};      // selects over score buffer b finished (select stream)
 	cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 	float last_ms[3] = {0, 0, 0};
 	int last_launches = 0;

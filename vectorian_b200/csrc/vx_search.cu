@@ -516,6 +516,8 @@ extern "C" int vx_search_batch(
 	cudaEventRecord(c->ev[0], c->stream);
 	int rc = VX_OK;
 	std::vector<char> live(n_pairs, 0);
+	int multi_buf = 0;
+	bool sel_pending[2] = {false, false};
 	for (int32_t q = 0; q < n_sims && rc == VX_OK; q++) {
 		const vx_sim *s = sims[q];
 		for (int32_t ai = 0; ai < n_aps && rc == VX_OK; ai++) {
@@ -540,6 +542,7 @@ extern "C" int vx_search_batch(
 				}
 			}
 		}
+		cudaStream_t const main_stream = c->stream;
 		while (rc == VX_OK) {
 			int nl = lo.size() >= 4 ? 4 : lo.size() >= 2 ? 2 : 0;
 			int ng = gl.size() >= 4 ? 4 : gl.size() >= 2 ? 2 : 0;
@@ -552,10 +555,31 @@ extern "C" int vx_search_batch(
 				break;
 			}
 			if (!c->d_score_multi) {
-				if (cudaMalloc(&c->d_score_multi, sizeof(float) * 8 * (size_t)c->n_slots) != cudaSuccess) {
+				if (cudaMalloc(&c->d_score_multi, sizeof(float) * 16 * (size_t)c->n_slots) != cudaSuccess) {
 					cudaGetLastError();
 					break;   // no room for the extra score arrays: the settings run one by one below
 				}
+			}
+			if (!c->select_stream) {
+				// the selects (top-k, traceback, result copy) are small latency-bound kernels: on a second, high-priority
+				// stream they run while the next group's DP kernel fills the machine
+				int prio_lo = 0, prio_hi = 0;
+				cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+				bool ok = cudaStreamCreateWithPriority(&c->select_stream, cudaStreamNonBlocking, prio_hi) == cudaSuccess;
+				for (int b = 0; b < 2 && ok; b++) {
+					ok = cudaEventCreateWithFlags(&c->ev_dp[b], cudaEventDisableTiming) == cudaSuccess &&
+						cudaEventCreateWithFlags(&c->ev_sel[b], cudaEventDisableTiming) == cudaSuccess;
+				}
+				if (!ok) {
+					vx_set_error("could not create the select stream");
+					rc = VX_ERR_CUDA;
+					break;
+				}
+			}
+			const int buf = multi_buf;
+			multi_buf ^= 1;
+			if (sel_pending[buf]) {
+				cudaStreamWaitEvent(main_stream, c->ev_sel[buf], 0);   // the selects that read this buffer two groups ago
 			}
 			int32_t group[8];
 			float gs[8], gt[8];
@@ -567,7 +591,7 @@ extern "C" int vx_search_batch(
 				const QueryPlan &p = plans[(size_t)q * n_aps + group[j]];
 				gs[j] = p.ap.lin_s;
 				gt[j] = p.ap.lin_t;
-				score[j] = c->d_score_multi + (size_t)j * c->n_slots;
+				score[j] = c->d_score_multi + ((size_t)buf * 8 + j) * c->n_slots;
 			}
 			const int launched = vx_launch_score_multi(c, s, plans[(size_t)q * n_aps + group[0]].qp, nl, ng, gs, gt, score);
 			if (launched <= 0) {
@@ -577,14 +601,33 @@ extern "C" int vx_search_batch(
 				break;
 			}
 			c->last_launches += launched;
+			cudaEventRecord(c->ev_dp[buf], main_stream);
+			cudaStreamWaitEvent(c->select_stream, c->ev_dp[buf], 0);
 			float *const d_score = c->d_score;
+			c->stream = c->select_stream;
 			for (int j = 0; j < nl + ng && rc == VX_OK; j++) {
 				c->d_score = score[j];
 				rc = enqueue_select(c, s, plans[(size_t)q * n_aps + group[j]], false);
 				done[group[j]] = 1;
 				live[(size_t)q * n_aps + group[j]] = 1;
 			}
+			c->stream = main_stream;
 			c->d_score = d_score;
+			cudaEventRecord(c->ev_sel[buf], c->select_stream);
+			sel_pending[buf] = true;
+		}
+		bool singles = false;
+		for (int32_t ai = 0; ai < n_aps; ai++) {
+			singles = singles || !done[ai];
+		}
+		if (singles) {
+			// these run entirely on the main stream and share the top-k workspace with the select stream: drain it first
+			for (int b = 0; b < 2; b++) {
+				if (sel_pending[b]) {
+					cudaStreamWaitEvent(main_stream, c->ev_sel[b], 0);
+					sel_pending[b] = false;
+				}
+			}
 		}
 		for (int32_t ai = 0; ai < n_aps && rc == VX_OK; ai++) {
 			if (!done[ai]) {
@@ -593,8 +636,17 @@ extern "C" int vx_search_batch(
 			}
 		}
 	}
+	for (int b = 0; b < 2; b++) {
+		if (sel_pending[b]) {
+			cudaStreamWaitEvent(c->stream, c->ev_sel[b], 0);
+		}
+	}
 	cudaEventRecord(c->ev[1], c->stream);
 	cudaError_t e = cudaStreamSynchronize(c->stream);
+	if (c->select_stream) {
+		const cudaError_t e2 = cudaStreamSynchronize(c->select_stream);
+		e = e == cudaSuccess ? e2 : e;
+	}
 	if (rc != VX_OK) {
 		return rc;
 	}
