@@ -545,7 +545,9 @@ static void sim_free(vx_sim *s) {
 		// recycle them are ordered behind this sim's own kernels on the similarity stream
 		vx_pool_free(s->d_s, s->s_bytes);
 		vx_pool_free(s->d_tmp, s->tmp_bytes);
-		cudaFree(s->d_qhat);
+		if (!s->qhat_pooled) {
+			cudaFree(s->d_qhat);
+		}
 		if (s->ev0) {
 			cudaEventDestroy(s->ev0);
 		}
@@ -738,23 +740,32 @@ extern "C" int vx_sim_contextual(const float *q_vec, int32_t t, int32_t d, vx_si
 	s->t = t;
 	s->tp = std::max(4, (t + 3) / 4 * 4);
 	s->d = d;
-	float *d_q = nullptr;
-	int rc = dev_alloc(&d_q, (size_t)t * d);
-	if (rc == VX_OK) {
-		rc = dev_alloc(&s->d_qhat, (size_t)t * d);
-	}
-	if (rc == VX_OK && t > 0) {
-		cudaMemcpyAsync(d_q, q_vec, sizeof(float) * (size_t)t * d, cudaMemcpyHostToDevice, 0);
-		vx_launch_normalize(d_q, s->d_qhat, t, d, 0);
-		if (cudaStreamSynchronize(0) != cudaSuccess) {
-			vx_set_error("contextual query normalisation failed");
-			rc = VX_ERR_CUDA;
-		}
-	}
-	cudaFree(d_q);
-	if (rc != VX_OK) {
+	// staging from the pool: q[t x d] | qhat[t x d]; normalised on the similarity stream, searches wait on ev1
+	// (no cudaMalloc / cudaFree / device-wide synchronisation per query)
+	const size_t n_q = (size_t)t * d;
+	s->tmp_bytes = (sizeof(float) * 2 * std::max<size_t>(n_q, 1) + 255) & ~(size_t)255;
+	s->d_tmp = vx_pool_alloc(s->tmp_bytes);
+	if (!s->d_tmp) {
 		sim_free(s);
-		return rc;
+		VX_FAIL(VX_ERR_CUDA, "cudaMalloc of the query staging buffer failed");
+	}
+	cudaEventCreate(&s->ev0);
+	cudaEventCreate(&s->ev1);
+	cudaStream_t st = vx_sim_stream();
+	float *d_q = (float*)s->d_tmp;
+	s->d_qhat = d_q + n_q;
+	s->qhat_pooled = true;
+	cudaEventRecord(s->ev0, st);
+	if (t > 0) {
+		cudaMemcpyAsync(d_q, q_vec, sizeof(float) * n_q, cudaMemcpyHostToDevice, st);
+		s->launches += vx_launch_normalize(d_q, s->d_qhat, t, d, st);
+	}
+	cudaEventRecord(s->ev1, st);
+	s->timed = true;
+	if (cudaGetLastError() != cudaSuccess) {
+		cudaStreamSynchronize(st);
+		sim_free(s);
+		VX_FAIL(VX_ERR_CUDA, "contextual query normalisation failed");
 	}
 	*out = s;
 	return VX_OK;

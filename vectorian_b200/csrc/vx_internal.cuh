@@ -120,6 +120,7 @@ struct vx_sim {
 	bool nonneg = false;             // every entry of S is >= 0 (always true for S built on the device: clip01)
 	int32_t d = 0;
 	float *d_qhat = nullptr;         // contextual: [t x d] normalised query vectors
+	bool qhat_pooled = false;        // d_qhat lives inside d_tmp
 	float build_ms = 0.0f;           // device time of the kernels that built d_s (resolved lazily from ev0/ev1)
 	int launches = 0;
 	size_t s_bytes = 0;              // size of the d_s allocation (returned to the pool on destroy)
