@@ -380,3 +380,23 @@ def test_contextual_operands_in_modifiers(oracle):
 	index = partition.index(OptimizedSpanSim(MixedTokenSimilarity([a, b], [1, 1]), LocalAlignment(gap=gaps.LinearGapCost(0.15))), nlp=whitespace_nlp)
 	check_find(oracle, session, emb, index, text, n=15, min_score=0.0, s=np.average([sa, sb], axis=0, weights=[1, 1]).astype(np.float32), contextual=True,
 		oc=oc, options=options)
+
+
+def test_long_query_through_find(oracle):
+	"""A 21-token query through Index.find: the similarity kernel takes 16 query columns per launch, so S is assembled from
+	two device launches and the windows are scored by the exact per-window kernel; same answers as the oracle."""
+	from vectorian_b200 import engine
+	session, (emb,) = make_session(n_docs=4, sent_per_doc=40)
+	text = " ".join(f"w{i}" for i in (3, 17, 5, 120, 1, 9, 2, 44, 8, 13, 21, 34, 55, 89, 144, 233, 377, 6, 10, 15, 28))
+	metric = OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), LocalAlignment(gap=gaps.LinearGapCost(0.2)))
+	index = session.partition("sentence").index(metric, nlp=whitespace_nlp)
+	p = index.make_query(text).prepare(whitespace_nlp)
+	assert p.n_tokens == 21
+	de, vv = session.device_embedding(emb)
+	q_vec = session.to_encoder(emb).encode_tokens(p.token_str).unmodified
+	q_id = np.where(p.token_id < session.vocab.size, p.token_id, -1).astype(np.int32)
+	s = index._device_static_matrix(de, q_id, q_vec)
+	assert s.shape == (session.vocab.size, 21)
+	np.testing.assert_allclose(s, oracle.sim_static(vv.unmodified, q_id, q_vec), rtol=0, atol=1e-5)
+	result, _ = check_find(oracle, session, emb, index, text, n=10, min_score=0.01, s=s)
+	assert len(result) == 10

@@ -14,6 +14,9 @@ from . import _cabi
 from ._cabi import ptr, check, HIT_DTYPE, Hit
 
 
+MAX_SIM_COLUMNS = 16   # query columns per vx_sim_static launch (VX_MAX_T_FAST)
+
+
 class DeviceCorpus:
 	"""Documents packed once into device-resident token tiles for one partition.
 

@@ -411,6 +411,18 @@ class BruteForceIndex(Index):
 		dc.set_boost(np.concatenate(boost) if boost else np.zeros((0,), np.float32))
 		dc.boost_owner = self
 
+	@staticmethod
+	def _device_static_matrix(de, q_id, q_vec):
+		"""S [V x T] of a static embedding, formed on the device and brought to the host.  The similarity kernel takes
+		up to 16 query columns per launch; longer queries go through it in groups of 16 (every column of S depends on
+		its own query token only, the identity fix-up included)."""
+		parts = []
+		for lo in range(0, len(q_id), engine.MAX_SIM_COLUMNS):
+			sim = engine.DeviceSim.static(de, q_id[lo:lo + engine.MAX_SIM_COLUMNS], q_vec[lo:lo + engine.MAX_SIM_COLUMNS])
+			parts.append(sim.download())
+			sim.close()
+		return np.ascontiguousarray(np.hstack(parts)) if parts else np.zeros((de.shape[0], 0), dtype=np.float32)
+
 	def _host_matrix(self, p_query, token_sim):
 		"""[V x T] similarity matrix of a static token similarity in host memory: identity fix-up and clip applied
 		(cpp/metric/static.cpp:58-75); modifiers combine their operands' matrices (cpp/metric/modifier.cpp:18-74)."""
@@ -431,10 +443,7 @@ class BruteForceIndex(Index):
 		q_id = np.where(p_query.token_id < session.vocab.size, p_query.token_id, -1).astype(np.int32)
 		if vector_sim.on_device:
 			de, _ = session.device_embedding(embedding)
-			sim = engine.DeviceSim.static(de, q_id, q_vectors.unmodified)
-			s = sim.download()
-			sim.close()
-			return s
+			return self._device_static_matrix(de, q_id, q_vectors.unmodified)
 		# any other VectorSim: evaluated on the host exactly as the reference's callback does
 		s = np.zeros((session.vocab.size, p_query.n_tokens), dtype=np.float32)
 		vector_sim(session.vocab_vectors(embedding), q_vectors, s)
@@ -507,7 +516,10 @@ class BruteForceIndex(Index):
 			de, _ = session.device_embedding(embedding)
 			q_vectors = encoder.encode_tokens(p_query.token_str)
 			q_id = np.where(p_query.token_id < session.vocab.size, p_query.token_id, -1).astype(np.int32)
-			return dc, engine.DeviceSim.static(de, q_id, q_vectors.unmodified)
+			if p_query.n_tokens <= engine.MAX_SIM_COLUMNS:
+				return dc, engine.DeviceSim.static(de, q_id, q_vectors.unmodified)
+			# long queries: S assembled from 16-column device launches, searched by the exact per-window kernel
+			return dc, engine.DeviceSim.upload(self._device_static_matrix(de, q_id, q_vectors.unmodified))
 		return dc, engine.DeviceSim.upload(self._host_matrix(p_query, token_sim))
 
 	@staticmethod
