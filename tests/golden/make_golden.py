@@ -80,6 +80,37 @@ def main():
 			s(ve, vq, res)
 		out[f"sim/{name}"] = res
 		out[f"simname/{name}"] = np.array(s.name)
+	# token-similarity modifiers (vectorian/sim/modifier.py:22-117) on two operand matrices: the operator __call__ as the
+	# reference's ModifiedSimilarityMatrixFactory invokes it (cpp/metric/modifier.cpp:18-74)
+	token = load("vectorian.sim.token", f"{REF}/vectorian/sim/token.py")
+	mod = load("vectorian.sim.modifier", f"{REF}/vectorian/sim/modifier.py")
+
+	class Operand(token.TokenSim):
+		def __init__(self, name):
+			self._n = name
+
+		@property
+		def name(self):
+			return self._n
+
+	a, b = Operand("A"), Operand("B")
+	m_a = rng.random((40, 6)).astype(np.float32)
+	m_b = rng.random((40, 6)).astype(np.float32)
+	out["mod/a"], out["mod/b"] = m_a, m_b
+	mods = {
+		"mixed_1_3": mod.MixedTokenSimilarity([a, b], [1, 3]),
+		"maximum": mod.MaximumTokenSimilarity([a, b]),
+		"minimum": mod.MinimumTokenSimilarity([a, b]),
+		"unary_pow_thr": mod.UnaryTokenSimilarityModifier(a, [kern.Power(2.0), kern.Threshold(0.3)]),
+		"unary_bias_scale": mod.UnaryTokenSimilarityModifier(b, [kern.Bias(-0.2), kern.Scale(1.5)]),
+	}
+	for name, m in mods.items():
+		res = {"similarity": np.zeros_like(m_a)}
+		operands = [{"similarity": m_a.copy()}, {"similarity": m_b.copy()}] if len(m.operands) == 2 else \
+			[{"similarity": (m_a if m.operands[0] is a else m_b).copy()}]
+		m(operands, res)
+		out[f"mod/{name}"] = res["similarity"]
+		out[f"modname/{name}"] = np.array(m.name)
 	np.savez_compressed(os.path.join(HERE, "reference_py.npz"), **out)
 	print("wrote", len(out), "arrays")
 

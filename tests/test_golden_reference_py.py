@@ -76,3 +76,36 @@ def test_oracle_similarity_matrix_against_reference_cosine():
 	want = np.clip(want, 0, 1)
 	got = oracle.sim_static(e, q_id, q)
 	np.testing.assert_allclose(got, want, rtol=1e-5, atol=2e-7)
+
+
+def test_token_similarity_modifiers_match_reference():
+	"""vectorian_b200.sim.modifier against the outputs of the reference's own operators (vectorian/sim/modifier.py:22-117,
+	invoked like ModifiedSimilarityMatrixFactory::create does, cpp/metric/modifier.cpp:18-74): bit-identical matrices and
+	the same metric names (Match::metric)."""
+	from vectorian_b200.sim import modifier as mod
+	from vectorian_b200.sim.token import TokenSim
+
+	class Operand(TokenSim):
+		def __init__(self, name):
+			self._n = name
+
+		@property
+		def name(self):
+			return self._n
+
+	a, b = Operand("A"), Operand("B")
+	m_a, m_b = G["mod/a"], G["mod/b"]
+	mods = {
+		"mixed_1_3": mod.MixedTokenSimilarity([a, b], [1, 3]),
+		"maximum": mod.MaximumTokenSimilarity([a, b]),
+		"minimum": mod.MinimumTokenSimilarity([a, b]),
+		"unary_pow_thr": mod.UnaryTokenSimilarityModifier(a, [kern.Power(2.0), kern.Threshold(0.3)]),
+		"unary_bias_scale": mod.UnaryTokenSimilarityModifier(b, [kern.Bias(-0.2), kern.Scale(1.5)]),
+	}
+	for name, m in mods.items():
+		res = {"similarity": np.zeros_like(m_a)}
+		operands = [{"similarity": m_a.copy()}, {"similarity": m_b.copy()}] if len(m.operands) == 2 else \
+			[{"similarity": (m_a if m.operands[0] is a else m_b).copy()}]
+		m(operands, res)
+		np.testing.assert_array_equal(res["similarity"], G[f"mod/{name}"], err_msg=name)
+		assert m.name == str(G[f"modname/{name}"])
