@@ -40,7 +40,14 @@ def _worker(rank, world, port, k, t, out_dir):
 	g = gather_topk(hits, target, distance, k, doc_offset=rank * 5)
 	np.savez(os.path.join(out_dir, f"r{rank}.npz"), hits=g[0], target=g[1], distance=g[2])
 	# several searches (a sweep's pairs, queries of different lengths) in one collective
-	many = gather_topk_many([_rank_rows(rank, n_local, tt, k_seed=10 * i) for i, tt in enumerate((t, 3, t))], k, doc_offset=rank * 5)
+	import vectorian_b200.distributed as vd
+	rows = [_rank_rows(rank, n_local, tt, k_seed=10 * i) for i, tt in enumerate((t, 3, t))]
+	many = gather_topk_many(rows, k, doc_offset=rank * 5)          # few rows: merged on the host
+	vd.HOST_MERGE_ROWS = 0
+	many_dev = gather_topk_many(rows, k, doc_offset=rank * 5)      # the torch merge (on the GPU under NCCL)
+	for g0, g1 in zip(many, many_dev):
+		for x0, x1 in zip(g0, g1):
+			np.testing.assert_array_equal(x0, x1)
 	np.savez(os.path.join(out_dir, f"m{rank}.npz"), **{f"{name}{i}": g[j] for i, g in enumerate(many) for j, name in enumerate(("hits", "target", "distance"))})
 	dist.destroy_process_group()
 

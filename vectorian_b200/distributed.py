@@ -14,6 +14,8 @@ import torch.distributed as dist
 
 from ._cabi import HIT_DTYPE
 
+HOST_MERGE_ROWS = 16384   # gathered rows up to which gather_topk_many merges on the host instead of the device
+
 
 def shard_documents(n_doc, world_size, rank, weights=None):
 	"""Contiguous document range [lo, hi) of `rank`, balanced by `weights` (e.g. DP cells per document)."""
@@ -80,6 +82,24 @@ def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
 	send = torch.from_numpy(buf).to(device)
 	recv = torch.empty((world,) + buf.shape, dtype=torch.float32, device=device)
 	dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
+
+	if n_pairs * world * k <= HOST_MERGE_ROWS:
+		# a single search (or a handful): one copy to the host and a lexsort per pair cost less than a dozen small kernels
+		out = recv.cpu().numpy()
+		iout = out.view(np.int32)
+		merged = []
+		for i in range(n_pairs):
+			parts = []
+			for r in range(world):
+				m = int(iout[r, i, k, 0])
+				h = np.zeros((m,), dtype=HIT_DTYPE)
+				h["score"] = out[r, i, :m, 0]
+				h["score_max"] = out[r, i, :m, 1]
+				h["doc"] = iout[r, i, :m, 2]
+				h["slice"] = iout[r, i, :m, 3]
+				parts.append((h, iout[r, i, :m, 4:4 + widths[i]].astype(np.int16), out[r, i, :m, 4 + t:4 + t + widths[i]].copy()))
+			merged.append(merge_hits(parts, k))
+		return merged
 
 	# merge on the device: total order score desc, doc desc, slice desc (Match::compare_by_score made total)
 	irecv = recv.view(torch.int32)
