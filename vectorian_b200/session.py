@@ -400,6 +400,8 @@ class Session:
 				i = lexicon.get(name)
 				if i < 0:
 					raise RuntimeError(f"illegal value {name} for {attr}_filter")
+				if i >= 64:
+					raise RuntimeError(f"{attr}_filter: id {i} of {name} does not fit the 64-bit filter mask")   # uint64_t masks, cpp/query.h:13-14
 				mask |= 1 << i
 			bits.append(mask)
 		return tuple(bits) if any(bits) else None
