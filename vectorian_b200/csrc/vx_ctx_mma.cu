@@ -151,6 +151,96 @@ constexpr int CM_ACC_COLS = 128;
 constexpr int CM_A_COL0 = 256;
 constexpr int CM_NA = 4;
 
+// The DP warp of the fused kernel (see ctx_mma_kernel): windows tiles [i_lo, i_hi), S tiles from the two shared-memory
+// buffers at st0 in quad order.
+template<int TP, int LOC>
+__device__ __forceinline__ void ctx_dp_warp(const CtxMmaArgs &a, int i_lo, int i_hi, const float4 *st0,
+	uint32_t bar_s_full, uint32_t bar_s_empty, int lane) {
+
+	const float gs = a.gs, gt = a.gt;
+	const int t = a.t;
+	uint32_t lt = 0;
+	for (int i = i_lo; i < i_hi; i++) {
+		const VxTile tl = a.tiles[i];
+		const int len = tl.len;
+		float h[TP];   // h[v] = V[u-1, v]
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			h[v] = LOC == VX_GLOBAL ? -((float)(v + 1) * gt) : 0.0f;   // solver.h:2804-2806
+		}
+		float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+		float last_col = 0.0f;
+		for (int u0 = 0; u0 < len; u0 += 4, lt++) {
+			const uint32_t sb = lt & 1;
+			mbar_wait(bar_s_full + 8 * sb, (lt >> 1) & 1);
+			// The buffer of the PREVIOUS quad is released here, behind this wait: its loads have long been consumed
+			// by the arithmetic (an arrive right behind the loads would not be ordered after them, see the
+			// converters).  The epilogue needs that buffer one whole GEMM tile later, so nothing waits for it.
+			if (lt > 0) {
+				__syncwarp();
+				if (lane == 0) {
+					mbar_arrive(bar_s_empty + 8 * (sb ^ 1));
+				}
+			}
+			const float4 *const st = st0 + sb * (CM_ROWS * TP / 4);
+			#pragma unroll
+			for (int k = 0; k < 4; k++) {
+				const int u = u0 + k;
+				if (u < len) {
+					float cur[TP];
+					#pragma unroll
+					for (int jq = 0; jq < TP / 4; jq++) {
+						const float4 x = st[(k * (TP / 4) + jq) * 32 + lane];
+						cur[4 * jq + 0] = x.x;
+						cur[4 * jq + 1] = x.y;
+						cur[4 * jq + 2] = x.z;
+						cur[4 * jq + 3] = x.w;
+					}
+					float diag = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
+					float left = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;  // V[u, -1]
+					#pragma unroll
+					for (int v = 0; v < TP; v++) {
+						const float up = h[v];
+						float x = fmaxf(fmaxf(diag + cur[v], up - gs), left - gt);
+						if (LOC == VX_LOCAL) {
+							x = fmaxf(x, 0.0f);
+							if (v < t) {
+								best = fmaxf(best, x);
+							}
+						}
+						diag = up;
+						h[v] = x;
+						left = x;
+						if (LOC != VX_LOCAL && v == t - 1) {
+							last_col = x;
+						}
+					}
+					if (LOC == VX_SEMIGLOBAL) {
+						best = fmaxf(best, last_col);
+					}
+				}
+			}
+		}
+		float rawv;
+		if (LOC == VX_LOCAL) {
+			rawv = best;
+		} else if (LOC == VX_GLOBAL) {
+			rawv = last_col;
+		} else {
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				if (v < t) {
+					best = fmaxf(best, h[v]);
+				}
+			}
+			rawv = best;
+		}
+		const int64_t slot = (int64_t)i * 32 + lane;
+		const float boost = a.boost ? a.boost[slot] : 1.0f;
+		a.score[slot] = lane < tl.n_valid ? (rawv / a.total) * boost : -CUDART_INF_F;
+	}
+}
+
 // FUSED: the similarity tiles feed the linear-gap DP (NW / SW / semiglobal) inside the same kernel.  A 128-token GEMM
 // tile is exactly one token quad of 32 windows (tokens 4q .. 4q+3 of every lane of a window tile, vx_internal.cuh), so
 // the epilogue warps drop the clipped tile into shared memory as [k][column quad][lane] float4 and ONE extra warp runs
@@ -426,91 +516,18 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 		}
 	} else if (FUSED) {
 		// ---- DP warp: linear-gap alignment of the 32 windows of every window tile, lane = window
-		// (LinearGapCostSolver::solve, pyalign/solver.h:2817-2847; the arithmetic of score_linear_kernel, vx_align.cu) ----
+		// (LinearGapCostSolver::solve, pyalign/solver.h:2817-2847; the arithmetic of score_linear_kernel, vx_align.cu).
+		// The locality is a compile-time constant of the loop (one instantiation per locality, selected once per CTA):
+		// the per-cell selects of a run-time locality cost a third of the warp's instructions, and this single warp is
+		// what bounds the kernel at T = 16.
 		const int32_t *rng = reinterpret_cast<const int32_t*>(sm + off_bar + 480);
 		const float4 *const st0 = reinterpret_cast<const float4*>(sm + off_stile);
-		const float gs = a.gs, gt = a.gt;
-		const int loc = a.locality, t = a.t;
-		uint32_t lt = 0;
-		for (int i = rng[0]; i < rng[1]; i++) {
-			const VxTile tl = a.tiles[i];
-			const int len = tl.len;
-			float h[TP];   // h[v] = V[u-1, v]
-			#pragma unroll
-			for (int v = 0; v < TP; v++) {
-				h[v] = loc == VX_GLOBAL ? -((float)(v + 1) * gt) : 0.0f;   // solver.h:2804-2806
-			}
-			float best = loc == VX_LOCAL ? 0.0f : -CUDART_INF_F;
-			float last_col = 0.0f;
-			for (int u0 = 0; u0 < len; u0 += 4, lt++) {
-				const uint32_t sb = lt & 1;
-				mbar_wait(bar_s_full + 8 * sb, (lt >> 1) & 1);
-				// The buffer of the PREVIOUS quad is released here, behind this wait: its loads have long been consumed
-				// by the arithmetic (an arrive right behind the loads would not be ordered after them, see the
-				// converters).  The epilogue needs that buffer one whole GEMM tile later, so nothing waits for it.
-				if (lt > 0) {
-					__syncwarp();
-					if (lane == 0) {
-						mbar_arrive(bar_s_empty + 8 * (sb ^ 1));
-					}
-				}
-				const float4 *const st = st0 + sb * (CM_ROWS * TP / 4);
-				#pragma unroll
-				for (int k = 0; k < 4; k++) {
-					const int u = u0 + k;
-					if (u < len) {
-						float cur[TP];
-						#pragma unroll
-						for (int jq = 0; jq < TP / 4; jq++) {
-							const float4 x = st[(k * (TP / 4) + jq) * 32 + lane];
-							cur[4 * jq + 0] = x.x;
-							cur[4 * jq + 1] = x.y;
-							cur[4 * jq + 2] = x.z;
-							cur[4 * jq + 3] = x.w;
-						}
-						float diag = loc == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
-						float left = loc == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;  // V[u, -1]
-						#pragma unroll
-						for (int v = 0; v < TP; v++) {
-							const float up = h[v];
-							float x = fmaxf(fmaxf(diag + cur[v], up - gs), left - gt);
-							if (loc == VX_LOCAL) {
-								x = fmaxf(x, 0.0f);
-								if (v < t) {
-									best = fmaxf(best, x);
-								}
-							}
-							diag = up;
-							h[v] = x;
-							left = x;
-							if (v == t - 1) {
-								last_col = x;
-							}
-						}
-						if (loc == VX_SEMIGLOBAL) {
-							best = fmaxf(best, last_col);
-						}
-					}
-				}
-
-			}
-			float rawv;
-			if (loc == VX_LOCAL) {
-				rawv = best;
-			} else if (loc == VX_GLOBAL) {
-				rawv = last_col;
-			} else {
-				#pragma unroll
-				for (int v = 0; v < TP; v++) {
-					if (v < t) {
-						best = fmaxf(best, h[v]);
-					}
-				}
-				rawv = best;
-			}
-			const int64_t slot = (int64_t)i * 32 + lane;
-			const float boost = a.boost ? a.boost[slot] : 1.0f;
-			a.score[slot] = lane < tl.n_valid ? (rawv / a.total) * boost : -CUDART_INF_F;
+		if (a.locality == VX_LOCAL) {
+			ctx_dp_warp<TP, VX_LOCAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
+		} else if (a.locality == VX_GLOBAL) {
+			ctx_dp_warp<TP, VX_GLOBAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
+		} else {
+			ctx_dp_warp<TP, VX_SEMIGLOBAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
 		}
 	}
 	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
