@@ -153,12 +153,13 @@ constexpr int CM_NA = 4;
 
 // The DP warp of the fused kernel (see ctx_mma_kernel): windows tiles [i_lo, i_hi), S tiles from the two shared-memory
 // buffers at st0 in quad order.
-template<int TP, int LOC>
+template<int TP, int LOC_>
 __device__ __forceinline__ void ctx_dp_warp(const CtxMmaArgs &a, int i_lo, int i_hi, const float4 *st0,
 	uint32_t bar_s_full, uint32_t bar_s_empty, int lane) {
 
 	const float gs = a.gs, gt = a.gt;
 	const int t = a.t;
+	const int LOC = LOC_ < 0 ? a.locality : LOC_;   // LOC_ < 0: decided at run time
 	uint32_t lt = 0;
 	for (int i = i_lo; i < i_hi; i++) {
 		const VxTile tl = a.tiles[i];
@@ -517,17 +518,23 @@ __global__ void __launch_bounds__(CM_THREADS, 1) ctx_mma_kernel(const __grid_con
 	} else if (FUSED) {
 		// ---- DP warp: linear-gap alignment of the 32 windows of every window tile, lane = window
 		// (LinearGapCostSolver::solve, pyalign/solver.h:2817-2847; the arithmetic of score_linear_kernel, vx_align.cu).
-		// The locality is a compile-time constant of the loop (one instantiation per locality, selected once per CTA):
-		// the per-cell selects of a run-time locality cost a third of the warp's instructions, and this single warp is
-		// what bounds the kernel at T = 16.
+		// For T > 8 the locality is a compile-time constant of the loop (one instantiation per locality, selected once per
+		// CTA): the per-cell selects of a run-time locality cost a third of the warp's instructions, and this single warp
+		// is what bounds the kernel at T = 16 (C4-like case: 0.55 -> 0.48 ms).
 		const int32_t *rng = reinterpret_cast<const int32_t*>(sm + off_bar + 480);
 		const float4 *const st0 = reinterpret_cast<const float4*>(sm + off_stile);
-		if (a.locality == VX_LOCAL) {
-			ctx_dp_warp<TP, VX_LOCAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
-		} else if (a.locality == VX_GLOBAL) {
-			ctx_dp_warp<TP, VX_GLOBAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
+		if constexpr (TP >= 12) {
+			if (a.locality == VX_LOCAL) {
+				ctx_dp_warp<TP, VX_LOCAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
+			} else if (a.locality == VX_GLOBAL) {
+				ctx_dp_warp<TP, VX_GLOBAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
+			} else {
+				ctx_dp_warp<TP, VX_SEMIGLOBAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
+			}
 		} else {
-			ctx_dp_warp<TP, VX_SEMIGLOBAL>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
+			// T <= 8: the warp is far from bounding the kernel, and the three copies measured slower (0.50 vs 0.44 ms
+			// on the C4-like case: the kernel is sensitive to its code size), so the locality stays a run-time value
+			ctx_dp_warp<TP, -1>(a, rng[0], rng[1], st0, bar_s_full, bar_s_empty, lane);
 		}
 	}
 	asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
