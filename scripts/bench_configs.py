@@ -236,6 +236,8 @@ def main():
 	dist_setup()
 	if "c5" in which:
 		run_sweep("C5 sweep: 64 queries x {linear 0,.1,.2,.5} x {Local,Global}, T=12, 10M sentences (one GPU holds the whole corpus)", 10_000_000)
+	if "c5s" in which:   # one GPU's share of C5 on 8 GPUs (1.25 M sentences), on a single GPU
+		run_sweep("C5 shard: 64 queries x 8 settings, T=12, 1.25M sentences (what each of 8 GPUs holds)", 1_250_000)
 	if "c1" in which:   # the reference's own CPU-runnable case, on the GPU for comparison
 		run_static("C1 NW Global linear(0.2) T=5 10k V=50k", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.2), 5, 10_000, 50_000, 300, cand_per_cell=3)
 	if "c2" in which:
