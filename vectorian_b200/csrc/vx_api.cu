@@ -96,6 +96,7 @@ static void corpus_free(vx_corpus *c) {
 	cudaFree(c->d_score);
 	cudaFree(c->d_score_multi);
 	cudaFree(c->d_work);
+	cudaFree(c->d_topk_multi);
 	cudaFree(c->d_scratch);
 	cudaFree(c->d_counters);
 	if (c->h_res) {

@@ -83,6 +83,8 @@ struct vx_corpus {
 	float *d_score = nullptr;        // by slot, scratch of the last search
 	float *d_score_multi = nullptr;  // 2 x 8 x n_slots, vx_search_batch: scores of the fused settings, double-buffered (lazily allocated)
 	void *d_work = nullptr;          // top-k / traceback workspace
+	void *d_topk_multi = nullptr;    // vx_search_batch: 8 top-k work areas (one launch for the settings of a group)
+	size_t topk_multi_stride = 0;
 	size_t work_bytes = 0;
 	void *d_scratch = nullptr;       // DP scratch of the exact kernel
 	size_t scratch_bytes = 0;
@@ -197,6 +199,8 @@ struct VxTopkOut {
 };
 size_t vx_topk_work_bytes(int32_t k);
 int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out);
+int vx_launch_topk_multi(vx_corpus *c, float min_score, int32_t k, void *work, size_t stride, int n_arrays,
+	const float *const *scores, VxTopkOut *outs);
 
 // vx_sim.cu
 int vx_launch_normalize(const float *d_in, float *d_out, int64_t rows, int32_t d, cudaStream_t st);

@@ -338,6 +338,7 @@ static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 // Enqueue one query: scores of every slot, top-k, traceback of the winners, result block to pinned host memory.
 // Nothing here waits for the device.
 static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events);
+static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, const VxTopkOut &tk, bool phase_events);
 
 static int enqueue_search(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events) {
 	cudaStream_t st = c->stream;
@@ -371,6 +372,13 @@ static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, boo
 		return VX_ERR_INVALID;
 	}
 	c->last_launches += n;
+	return enqueue_finish(c, s, p, tk, phase_events);
+}
+
+// traceback of the winners `tk`, result block to pinned host memory
+static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, const VxTopkOut &tk, bool phase_events) {
+	cudaStream_t st = c->stream;
+	int n;
 	if (phase_events) {
 		cudaEventRecord(c->ev[2], st);
 	}
@@ -605,9 +613,29 @@ extern "C" int vx_search_batch(
 			cudaStreamWaitEvent(c->select_stream, c->ev_dp[buf], 0);
 			float *const d_score = c->d_score;
 			c->stream = c->select_stream;
+			// the top-k of all settings of the group in ONE cooperative launch (they share slots, k and min_score)
+			VxTopkOut tks[8];
+			bool multi = false;
+			if (nl + ng > 1) {
+				const size_t stride = align_up(vx_topk_work_bytes(k), 256);
+				if (!c->d_topk_multi || c->topk_multi_stride != stride) {
+					cudaFree(c->d_topk_multi);
+					c->d_topk_multi = nullptr;
+					if (cudaMalloc(&c->d_topk_multi, stride * 8) == cudaSuccess) {
+						c->topk_multi_stride = stride;
+					} else {
+						cudaGetLastError();
+					}
+				}
+				if (c->d_topk_multi) {
+					multi = vx_launch_topk_multi(c, qp->min_score, k, c->d_topk_multi, stride, nl + ng, score, tks) == 1;
+					c->last_launches += multi ? 1 : 0;
+				}
+			}
 			for (int j = 0; j < nl + ng && rc == VX_OK; j++) {
 				c->d_score = score[j];
-				rc = enqueue_select(c, s, plans[(size_t)q * n_aps + group[j]], false);
+				const QueryPlan &pj = plans[(size_t)q * n_aps + group[j]];
+				rc = multi ? enqueue_finish(c, s, pj, tks[j], false) : enqueue_select(c, s, pj, false);
 				done[group[j]] = 1;
 				live[(size_t)q * n_aps + group[j]] = 1;
 			}

@@ -327,62 +327,84 @@ __device__ __forceinline__ void topk_scan_block0(TopkWork *w, int level, int k, 
 	__syncthreads();
 }
 
-__global__ void __launch_bounds__(256) topk_fused_kernel(TopkWork *w, int k, const float *__restrict__ score,
-	const uint32_t *__restrict__ orig, const uint32_t *__restrict__ slot_of, int64_t n_slots, float min_score,
-	uint32_t *__restrict__ out_slots, float *__restrict__ out_scores, int32_t *__restrict__ out_n) {
+// up to TOPK_MULTI score arrays over the same slots (the settings of one vx_search_batch group) in one launch:
+// blockIdx.y selects the array, every array has its own TopkWork, the grid-wide barriers are shared
+constexpr int TOPK_MULTI = 8;
+
+struct TopkMultiArgs {
+	TopkWork *w[TOPK_MULTI];
+	const float *score[TOPK_MULTI];
+	uint32_t *out_slots[TOPK_MULTI];
+	float *out_scores[TOPK_MULTI];
+	int32_t *out_n[TOPK_MULTI];
+	unsigned int *n_done;      // zeroed by the launcher: arrays whose survivors fit the candidate buffer
+	int n_arrays;
+};
+
+__global__ void __launch_bounds__(256) topk_fused_kernel(const __grid_constant__ TopkMultiArgs m, int k,
+	const uint32_t *__restrict__ orig, const uint32_t *__restrict__ slot_of, int64_t n_slots, float min_score) {
 
 	cg::grid_group grid = cg::this_grid();
 	extern __shared__ unsigned long long fused_smem[];   // TOPK_CAP keys (block 0's sort); histogram aliases it
 	unsigned int *h = reinterpret_cast<unsigned int*>(fused_smem);
 	__shared__ unsigned int part[8];
 	__shared__ int sel[2];
+	TopkWork *const w = m.w[blockIdx.y];
+	const float *__restrict__ const score = m.score[blockIdx.y];
 
 	for (int level = 0; level < TOPK_LEVELS; level++) {
-		// ---- histogram of the digit of this level among the keys that share the fixed prefix ----
-		for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
-			h[i] = 0;
-		}
-		__syncthreads();
-		const unsigned long long prefix = w->st.prefix;
-		const int shift = c_shift[level];
-		const int bits = c_bits[level];
-		const unsigned int mask = (1u << bits) - 1;
-		const int hi_shift = shift + bits;
-		for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_slots; p += (int64_t)gridDim.x * blockDim.x) {
-			const float sc = score[p];
-			if (!(sc > min_score)) {
-				continue;
+		// an array that is done sits out the remaining levels but keeps the barriers (they span all arrays)
+		const bool active = w->st.done == 0;
+		if (active) {
+			// ---- histogram of the digit of this level among the keys that share the fixed prefix ----
+			for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
+				h[i] = 0;
 			}
-			const unsigned int sk = score_key(sc);
-			unsigned long long key;
-			if (level < 3) {
-				key = (unsigned long long)sk << 32;
-			} else {
-				if ((unsigned long long)sk != (prefix >> (32 - hi_shift))) {
+			__syncthreads();
+			const unsigned long long prefix = w->st.prefix;
+			const int shift = c_shift[level];
+			const int bits = c_bits[level];
+			const unsigned int mask = (1u << bits) - 1;
+			const int hi_shift = shift + bits;
+			for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n_slots; p += (int64_t)gridDim.x * blockDim.x) {
+				const float sc = score[p];
+				if (!(sc > min_score)) {
 					continue;
 				}
-				key = ((unsigned long long)sk << 32) | orig[p];
+				const unsigned int sk = score_key(sc);
+				unsigned long long key;
+				if (level < 3) {
+					key = (unsigned long long)sk << 32;
+				} else {
+					if ((unsigned long long)sk != (prefix >> (32 - hi_shift))) {
+						continue;
+					}
+					key = ((unsigned long long)sk << 32) | orig[p];
+				}
+				if (level > 0 && hi_shift < 64 && (key >> hi_shift) != prefix) {
+					continue;
+				}
+				atomicAdd(&h[(unsigned int)(key >> shift) & mask], 1u);
 			}
-			if (level > 0 && hi_shift < 64 && (key >> hi_shift) != prefix) {
-				continue;
-			}
-			atomicAdd(&h[(unsigned int)(key >> shift) & mask], 1u);
-		}
-		__syncthreads();
-		for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
-			if (h[i]) {
-				atomicAdd(&w->hist[level][i], h[i]);
+			__syncthreads();
+			for (int i = threadIdx.x; i < TOPK_BINS; i += blockDim.x) {
+				if (h[i]) {
+					atomicAdd(&w->hist[level][i], h[i]);
+				}
 			}
 		}
 		__threadfence();
 		grid.sync();
-		if (blockIdx.x == 0) {
+		if (active && blockIdx.x == 0) {
 			topk_scan_block0(w, level, k, part, sel);
+			if (threadIdx.x == 0 && w->st.done) {
+				atomicAdd(m.n_done, 1u);
+			}
 			__threadfence();
 		}
 		grid.sync();
-		if (w->st.done) {
-			break;
+		if (*reinterpret_cast<volatile unsigned int*>(m.n_done) >= (unsigned int)m.n_arrays) {
+			break;   // the same value for every block of the grid: written before the barrier, read after it
 		}
 	}
 
@@ -414,24 +436,24 @@ __global__ void __launch_bounds__(256) topk_fused_kernel(TopkWork *w, int k, con
 		return;
 	}
 
-	// ---- block 0: bitonic sort (descending), emit the best k ----
+	// ---- block 0 of every array: bitonic sort (descending), emit the best k ----
 	unsigned long long *keys = fused_smem;
 	unsigned int n = w->st.n_cand;
 	if (n > TOPK_CAP) {
 		n = TOPK_CAP;
 	}
-	unsigned int m = 1;
-	while (m < n) {
-		m <<= 1;
+	unsigned int mm = 1;
+	while (mm < n) {
+		mm <<= 1;
 	}
 	__syncthreads();
-	for (unsigned int i = threadIdx.x; i < m; i += blockDim.x) {
+	for (unsigned int i = threadIdx.x; i < mm; i += blockDim.x) {
 		keys[i] = i < n ? w->cand[i] : 0ull;
 	}
 	__syncthreads();
-	for (unsigned int size = 2; size <= m; size <<= 1) {
+	for (unsigned int size = 2; size <= mm; size <<= 1) {
 		for (unsigned int stride = size >> 1; stride > 0; stride >>= 1) {
-			for (unsigned int i = threadIdx.x; i < m; i += blockDim.x) {
+			for (unsigned int i = threadIdx.x; i < mm; i += blockDim.x) {
 				const unsigned int j = i ^ stride;
 				if (j > i) {
 					const bool desc = (i & size) == 0;
@@ -445,6 +467,8 @@ __global__ void __launch_bounds__(256) topk_fused_kernel(TopkWork *w, int k, con
 			__syncthreads();
 		}
 	}
+	uint32_t *const out_slots = m.out_slots[blockIdx.y];
+	float *const out_scores = m.out_scores[blockIdx.y];
 	const unsigned int n_out = n < (unsigned int)k ? n : (unsigned int)k;
 	for (unsigned int i = threadIdx.x; i < n_out; i += blockDim.x) {
 		const unsigned long long key = keys[i];
@@ -452,7 +476,7 @@ __global__ void __launch_bounds__(256) topk_fused_kernel(TopkWork *w, int k, con
 		out_scores[i] = key_score((unsigned int)(key >> 32));
 	}
 	if (threadIdx.x == 0) {
-		*out_n = (int32_t)n_out;
+		*m.out_n[blockIdx.y] = (int32_t)n_out;
 		w->st.n_out = (int)n_out;
 	}
 }
@@ -461,16 +485,98 @@ size_t vx_topk_work_bytes(int32_t k) {
 	return sizeof(TopkWork) + (size_t)k * (sizeof(uint32_t) + sizeof(float)) + 64;
 }
 
+static void topk_carve(void *work, int32_t k, TopkWork **w, VxTopkOut *out) {
+	*w = (TopkWork*)work;
+	uint8_t *tail = (uint8_t*)work + sizeof(TopkWork);
+	out->slots = (uint32_t*)tail;
+	out->scores = (float*)(tail + (size_t)k * sizeof(uint32_t));
+	out->n = (int32_t*)(tail + (size_t)k * (sizeof(uint32_t) + sizeof(float)));
+}
+
+// the cooperative kernel over n_arrays score arrays (work areas `stride` bytes apart); returns 1, or 0 when the
+// one-launch path does not apply (no cooperative launch, more than 4 M slots: the caller takes the multi-launch path)
+static int launch_topk_fused(vx_corpus *c, float min_score, int32_t k, void *work, size_t stride, int n_arrays,
+	const float *const *scores, VxTopkOut *outs) {
+
+	static int coop = -1, max_blocks_per_sm = 0;
+	const size_t smem_f = sizeof(unsigned long long) * TOPK_CAP;
+	if (coop < 0) {
+		cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
+		cudaFuncSetAttribute(topk_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f);
+		cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_blocks_per_sm, topk_fused_kernel, 256, smem_f);
+		if (max_blocks_per_sm < 1) {
+			coop = 0;
+		}
+	}
+	// (its 3 blocks per SM cannot keep enough loads in flight for very large inputs: those keep the
+	// multi-launch path, where the passes are HBM-bound and the launch gaps do not matter)
+	if (coop <= 0 || c->n_slots > ((int64_t)4 << 20) || n_arrays < 1 || n_arrays > TOPK_MULTI) {
+		return 0;
+	}
+	int sms = 148;
+	cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+	const int per_sm = max_blocks_per_sm > 3 ? 3 : max_blocks_per_sm;
+	int64_t g = (c->n_slots + 255) / 256;
+	if (g > (int64_t)sms * per_sm / n_arrays) {
+		g = (int64_t)sms * per_sm / n_arrays;
+	}
+	if (g < 1) {
+		g = 1;
+	}
+	cudaStream_t st = c->stream;
+	TopkMultiArgs m;
+	memset(&m, 0, sizeof(m));
+	// one memset clears the states, histograms and counters of all arrays (and their outputs)
+	cudaMemsetAsync(work, 0, n_arrays > 1 ? stride * (size_t)n_arrays : sizeof(TopkState) + sizeof(unsigned int) * TOPK_LEVELS * TOPK_BINS, st);
+	for (int i = 0; i < n_arrays; i++) {
+		topk_carve((uint8_t*)work + stride * (size_t)i, k, &m.w[i], &outs[i]);
+		m.score[i] = scores[i];
+		m.out_slots[i] = outs[i].slots;
+		m.out_scores[i] = outs[i].scores;
+		m.out_n[i] = outs[i].n;
+	}
+	if (n_arrays == 1) {
+		cudaMemsetAsync(outs[0].n, 0, sizeof(int32_t), st);
+	}
+	m.n_done = reinterpret_cast<unsigned int*>(&m.w[0]->st.pad);   // zeroed with the state
+	m.n_arrays = n_arrays;
+	int k_ = k;
+	const uint32_t *orig_ = c->d_orig, *slot_of_ = c->d_slot_of;
+	int64_t n_ = c->n_slots;
+	float ms_ = min_score;
+	void *args[] = {&m, &k_, &orig_, &slot_of_, &n_, &ms_};
+	if (cudaLaunchCooperativeKernel((void*)topk_fused_kernel, dim3((unsigned)g, (unsigned)n_arrays), dim3(256), args, smem_f, st) == cudaSuccess) {
+		return 1;
+	}
+	cudaGetLastError();
+	coop = 0;
+	return 0;
+}
+
+// Top-k of several score arrays over the same slots in ONE launch (vx_search_batch: the settings of a group).
+// `work` holds n_arrays areas of vx_topk_work_bytes(k) rounded up to `stride`.  Returns 1 or 0 (not applicable).
+int vx_launch_topk_multi(vx_corpus *c, float min_score, int32_t k, void *work, size_t stride, int n_arrays,
+	const float *const *scores, VxTopkOut *outs) {
+
+	if (k > TOPK_CAP) {
+		return 0;
+	}
+	return launch_topk_fused(c, min_score, k, work, stride, n_arrays, scores, outs);
+}
+
 int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out) {
 	if (k > TOPK_CAP) {
 		vx_set_error("max_matches larger than 8192 is not supported");
 		return -1;
 	}
-	TopkWork *w = (TopkWork*)work;
-	uint8_t *tail = (uint8_t*)work + sizeof(TopkWork);
-	out->slots = (uint32_t*)tail;
-	out->scores = (float*)(tail + (size_t)k * sizeof(uint32_t));
-	out->n = (int32_t*)(tail + (size_t)k * (sizeof(uint32_t) + sizeof(float)));
+	{
+		const float *scores[1] = {c->d_score};
+		if (launch_topk_fused(c, min_score, k, work, 0, 1, scores, out) == 1) {
+			return 1;
+		}
+	}
+	TopkWork *w;
+	topk_carve(work, k, &w, out);
 
 	cudaStream_t st = c->stream;
 	int launches = 0;
@@ -485,46 +591,6 @@ int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkO
 	}
 	if (blocks < 1) {
 		blocks = 1;
-	}
-	{
-		// one cooperative launch when the device supports it (B200 does)
-		static int coop = -1, max_blocks_per_sm = 0;
-		const size_t smem_f = sizeof(unsigned long long) * TOPK_CAP;
-		if (coop < 0) {
-			cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device);
-			cudaFuncSetAttribute(topk_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f);
-			cudaOccupancyMaxActiveBlocksPerMultiprocessor(&max_blocks_per_sm, topk_fused_kernel, 256, smem_f);
-			if (max_blocks_per_sm < 1) {
-				coop = 0;
-			}
-		}
-		// (its 3 blocks per SM cannot keep enough loads in flight for very large inputs: those keep the
-		// multi-launch path, where the passes are HBM-bound and the launch gaps do not matter)
-		if (coop > 0 && c->n_slots <= ((int64_t)4 << 20)) {
-			int per_sm = max_blocks_per_sm > 3 ? 3 : max_blocks_per_sm;
-			int64_t g = (c->n_slots + 255) / 256;
-			if (g > (int64_t)sms * per_sm) {
-				g = (int64_t)sms * per_sm;
-			}
-			if (g < 1) {
-				g = 1;
-			}
-			TopkWork *w_ = w;
-			int k_ = k;
-			const float *score_ = c->d_score;
-			const uint32_t *orig_ = c->d_orig, *slot_of_ = c->d_slot_of;
-			int64_t n_ = c->n_slots;
-			float ms_ = min_score;
-			uint32_t *os_ = out->slots;
-			float *osc_ = out->scores;
-			int32_t *on_ = out->n;
-			void *args[] = {&w_, &k_, &score_, &orig_, &slot_of_, &n_, &ms_, &os_, &osc_, &on_};
-			if (cudaLaunchCooperativeKernel((void*)topk_fused_kernel, dim3((unsigned)g), dim3(256), args, smem_f, st) == cudaSuccess) {
-				return 1;
-			}
-			cudaGetLastError();
-			coop = 0;
-		}
 	}
 	for (int level = 0; level < TOPK_LEVELS; level++) {
 		topk_hist_kernel<<<(unsigned)blocks, 256, 0, st>>>(w, level, c->d_score, c->d_orig, c->n_slots, min_score);
