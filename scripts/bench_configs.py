@@ -204,11 +204,11 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
 			if mode == "single":
 				top = [[dc.search(sim, ap, qp)[0]["score"][0] for ap in aps] for sim in sims]
 			else:
-				out = dc.search_batch(sims, aps, qp)
+				out = dc.search_batch(sims, aps, qp, raw=WORLD > 1)
 				tb = time.perf_counter()
 				host = {"sims_ms": (ta - t0) * 1e3, "search_batch_ms": (tb - ta) * 1e3}
 				if WORLD > 1:   # ONE all-gather for all queries x settings pairs
-					flat = gather_topk_many([out[q][a] for q in range(len(sims)) for a in range(len(aps))], k, doc_offset=RANK * tables["n_doc"])
+					flat = gather_topk_many(out, k, doc_offset=RANK * tables["n_doc"])
 					out = [[flat[q * len(aps) + a] for a in range(len(aps))] for q in range(len(sims))]
 				host["gather_merge_ms"] = (time.perf_counter() - tb) * 1e3
 				top = [[out[q][a][0]["score"][0] for a in range(len(aps))] for q in range(len(sims))]

@@ -48,6 +48,21 @@ def _worker(rank, world, port, k, t, out_dir):
 	for g0, g1 in zip(many, many_dev):
 		for x0, x1 in zip(g0, g1):
 			np.testing.assert_array_equal(x0, x1)
+	# the unsplit arrays of a batched search (engine.search_batch(raw=True)) take the vectorised packing
+	rows3 = [_rank_rows(rank, n_local, t, k_seed=10 * i) for i in range(3)]
+	kk = 8
+	hits = np.zeros((3, kk), dtype=HIT_DTYPE)
+	target = np.full((3, kk, t), -1, dtype=np.int16)
+	distance = np.ones((3, kk, t), dtype=np.float32)
+	for i, (h, tg, ds) in enumerate(rows3):
+		hits[i, :len(h)], target[i, :len(h)], distance[i, :len(h)] = h, tg, ds
+	for limit in (1 << 20, 0):
+		vd.HOST_MERGE_ROWS = limit
+		want = gather_topk_many(rows3, kk, doc_offset=rank * 5)
+		got = gather_topk_many(vd.BatchRows(hits, target, distance, [len(r[0]) for r in rows3], [t] * 3), kk, doc_offset=rank * 5)
+		for g0, g1 in zip(want, got):
+			for x0, x1 in zip(g0, g1):
+				np.testing.assert_array_equal(x0, x1)
 	np.savez(os.path.join(out_dir, f"m{rank}.npz"), **{f"{name}{i}": g[j] for i, g in enumerate(many) for j, name in enumerate(("hits", "target", "distance"))})
 	dist.destroy_process_group()
 

@@ -44,6 +44,17 @@ def merge_hits(parts, k):
 	return hits[order], target[order], distance[order]
 
 
+class BatchRows:
+	"""The result arrays of one vx_search_batch call, unsplit: hits [P, k] (HIT_DTYPE), target [P, k, T] int16,
+	dist [P, k, T] float32, n [P] valid rows per pair, widths [P] query length of every pair (engine.search_batch(raw=True))."""
+
+	def __init__(self, hits, target, dist, n, widths):
+		self.hits, self.target, self.dist, self.n, self.widths = hits, target, dist, np.asarray(n), list(widths)
+
+	def triples(self):
+		return [(self.hits[i, :m], self.target[i, :m, :w], self.dist[i, :m, :w]) for i, (m, w) in enumerate(zip(self.n, self.widths))]
+
+
 def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
 	"""All-gather the local top-k of SEVERAL searches (e.g. the queries x settings pairs of a parameter sweep) in ONE
 	collective and merge each; `results` is a list of (hits, target, dist) triples, every rank returns the list of
@@ -51,31 +62,46 @@ def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
 	[pairs, world * k] keys instead of a Python loop per pair, then one copy of the pairs x k winning rows to the host."""
 	if not (dist.is_available() and dist.is_initialized()):
 		out = []
-		for hits, target, distance in results:
+		for hits, target, distance in (results.triples() if isinstance(results, BatchRows) else results):
 			h = hits.copy()
 			h["doc"] += doc_offset
 			out.append(merge_hits([(h, target, distance)], k))
 		return out
-	if not results:
+	if not isinstance(results, BatchRows) and not results:
 		return []
 	world = dist.get_world_size(group)
-	widths = [r[1].shape[1] if r[1].ndim == 2 else 0 for r in results]
-	t = max(widths)
-	n_pairs = len(results)
-	buf = np.zeros((n_pairs, k + 1, 4 + 2 * t), dtype=np.float32)
-	ibuf = buf.view(np.int32)
-	buf[:, :, 4 + t:] = 1.0
-	ibuf[:, :, 4:4 + t] = -1
-	for i, (h, tg, ds) in enumerate(results):
-		n, ti = len(h), widths[i]
-		buf[i, :n, 0] = h["score"]
-		buf[i, :n, 1] = h["score_max"]
-		ibuf[i, :n, 2] = h["doc"] + doc_offset
-		ibuf[i, :n, 3] = h["slice"]
-		if ti:
-			ibuf[i, :n, 4:4 + ti] = tg
-			buf[i, :n, 4 + t:4 + t + ti] = ds
-		ibuf[i, k, 0] = n
+	if isinstance(results, BatchRows):
+		# the arrays of vx_search_batch as they are: packed with a handful of whole-array copies
+		n_pairs, t = results.hits.shape[0], results.target.shape[2]
+		widths = list(results.widths)
+		buf = np.zeros((n_pairs, k + 1, 4 + 2 * t), dtype=np.float32)
+		ibuf = buf.view(np.int32)
+		live = np.arange(k)[None, :] < results.n[:, None]
+		buf[:, :k, 0] = np.where(live, results.hits["score"], 0.0)
+		buf[:, :k, 1] = np.where(live, results.hits["score_max"], 0.0)
+		ibuf[:, :k, 2] = np.where(live, results.hits["doc"] + doc_offset, 0)
+		ibuf[:, :k, 3] = np.where(live, results.hits["slice"], 0)
+		ibuf[:, :k, 4:4 + t] = results.target
+		buf[:, :k, 4 + t:] = results.dist
+		ibuf[:, k, 0] = results.n
+	else:
+		widths = [r[1].shape[1] if r[1].ndim == 2 else 0 for r in results]
+		t = max(widths)
+		n_pairs = len(results)
+		buf = np.zeros((n_pairs, k + 1, 4 + 2 * t), dtype=np.float32)
+		ibuf = buf.view(np.int32)
+		buf[:, :, 4 + t:] = 1.0
+		ibuf[:, :, 4:4 + t] = -1
+		for i, (h, tg, ds) in enumerate(results):
+			n, ti = len(h), widths[i]
+			buf[i, :n, 0] = h["score"]
+			buf[i, :n, 1] = h["score_max"]
+			ibuf[i, :n, 2] = h["doc"] + doc_offset
+			ibuf[i, :n, 3] = h["slice"]
+			if ti:
+				ibuf[i, :n, 4:4 + ti] = tg
+				buf[i, :n, 4 + t:4 + t + ti] = ds
+			ibuf[i, k, 0] = n
 	backend = dist.get_backend(group)
 	if device is None:
 		device = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")

@@ -119,7 +119,7 @@ class DeviceCorpus:
 			hits.ctypes.data_as(C.POINTER(Hit)), ptr(target, C.c_int16), ptr(dist, C.c_float), C.byref(n)), self._lib)
 		return hits[:n.value], target[:n.value, :sim.t], dist[:n.value, :sim.t]
 
-	def search_batch(self, sims, aps, qp):
+	def search_batch(self, sims, aps, qp, raw=False):
 		"""Parameter sweep (vx_search_batch): every query in `sims` against every alignment setting in `aps` in one
 		call.  Returns a list over queries of lists over settings of (hits, target, dist) as `search` returns them."""
 		n_q, n_a = len(sims), len(aps)
@@ -136,6 +136,10 @@ class DeviceCorpus:
 			C.memmove(C.byref(ap_arr[i]), C.byref(a), C.sizeof(_cabi.AlignParams))   # keeps pointers into the caller's tables
 		check(self._lib.vx_search_batch(self._h, handles, n_q, ap_arr, n_a, C.byref(qp), t_stride,
 			hits.ctypes.data_as(C.POINTER(Hit)), ptr(target, C.c_int16), ptr(dist, C.c_float), ptr(n, C.c_int32)), self._lib)
+		if raw:
+			# unsplit arrays for distributed.gather_topk_many (pair p = q * len(aps) + a)
+			from .distributed import BatchRows
+			return BatchRows(hits, target, dist, n[:n_pairs], [sims[p // max(n_a, 1)].t for p in range(n_pairs)])
 		out = []
 		for q in range(n_q):
 			row = []
