@@ -607,8 +607,8 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 	margs = [q.options.get("metric") for q in queries[0]]
 	same = all(index.partition is first.partition and index._saliency is None for index in indexes) and all(
 		m and m['metric'] == 'alignment-isolated' and m['token_metric'] is margs[0]['token_metric'] for m in margs)
-	if not same or session.shard[1] > 1:
-		# different partitions / token metrics, tag weights or a sharded session: one find per pair
+	if not same:
+		# different partitions / token metrics or tag weights: one find per pair
 		return [[index.find(text, n=n, min_score=min_score, options=options) for index in indexes] for text in texts]
 	start_time = time.time()
 	prepared, sims, live = [], [], []
@@ -632,10 +632,17 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 			gap_fns.append(fns)
 		qp, keep_q, k = first._query_params(queries[0][0].options, margs[0], prepared[live[0]])
 		first._set_boost(dc)
-		out = dc.search_batch(sims, aps, qp)
+		rank, world, doc_lo, _ = session.shard
+		if world > 1:
+			# sharded session: ONE all-gather for all (query, setting) pairs, document ids made global inside it
+			from .distributed import gather_topk_many
+			flat = gather_topk_many(dc.search_batch(sims, aps, qp, raw=True), k, doc_offset=doc_lo)
+			out = [[flat[q * len(aps) + a] for a in range(len(aps))] for q in range(len(sims))]
+			doc_lo = 0
+		else:
+			out = dc.search_batch(sims, aps, qp)
 		for sim in sims:
 			sim.close()
-		doc_lo = session.shard[2]
 		duration = (time.time() - start_time) / (len(sims) * len(indexes))
 		for row, qi in zip(out, live):
 			for ai, (index, (hits, target, dist)) in enumerate(zip(indexes, row)):
