@@ -189,6 +189,8 @@ struct VxTraceOut {
 };
 int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp,
 	const uint32_t *d_slots, int64_t slot_base, const int32_t *d_n_items, int32_t max_items, VxTraceOut out);
+int vx_launch_trace_multi(vx_corpus *c, const vx_sim *s, const VxAlignDev *aps, const VxQueryDev &qp, int n,
+	const uint32_t *const *d_slots, const int32_t *const *d_n_items, int32_t max_items, const VxTraceOut *outs);
 size_t vx_trace_scratch_bytes(int32_t max_len, int32_t t, int32_t max_items, int32_t gap_kind);
 
 // vx_topk.cu -- exact top-k of d_score under (score desc, window index desc).

@@ -632,10 +632,41 @@ extern "C" int vx_search_batch(
 					c->last_launches += multi ? 1 : 0;
 				}
 			}
+			// ... and so are their tracebacks (same query constants, per-setting gap costs and result blocks)
+			bool traced = false;
+			if (multi) {
+				VxAlignDev aps_dev[8];
+				VxTraceOut outs[8];
+				const uint32_t *slots_[8];
+				const int32_t *n_[8];
+				for (int j = 0; j < nl + ng; j++) {
+					const QueryPlan &pj = plans[(size_t)q * n_aps + group[j]];
+					aps_dev[j] = pj.ap;
+					outs[j].score = (float*)(pj.res + pj.off_score);
+					outs[j].score_max = (float*)(pj.res + pj.off_score_max);
+					outs[j].win = (uint32_t*)(pj.res + pj.off_win);
+					outs[j].target = (int16_t*)(pj.res + pj.off_target);
+					outs[j].dist = (float*)(pj.res + pj.off_dist);
+					slots_[j] = tks[j].slots;
+					n_[j] = tks[j].n;
+				}
+				const QueryPlan &p0 = plans[(size_t)q * n_aps + group[0]];
+				const int nt = vx_launch_trace_multi(c, s, aps_dev, p0.qp, nl + ng, slots_, n_, p0.k, outs);
+				if (nt < 0) {
+					rc = VX_ERR_CUDA;
+				}
+				traced = nt == 1;
+				c->last_launches += traced ? 1 : 0;
+			}
 			for (int j = 0; j < nl + ng && rc == VX_OK; j++) {
 				c->d_score = score[j];
 				const QueryPlan &pj = plans[(size_t)q * n_aps + group[j]];
-				rc = multi ? enqueue_finish(c, s, pj, tks[j], false) : enqueue_select(c, s, pj, false);
+				if (traced) {
+					cudaMemcpyAsync(pj.res + pj.off_n, tks[j].n, sizeof(int32_t), cudaMemcpyDeviceToDevice, c->stream);
+					cudaMemcpyAsync(pj.h_res, pj.res, pj.res_bytes, cudaMemcpyDeviceToHost, c->stream);
+				} else {
+					rc = multi ? enqueue_finish(c, s, pj, tks[j], false) : enqueue_select(c, s, pj, false);
+				}
 				done[group[j]] = 1;
 				live[(size_t)q * n_aps + group[j]] = 1;
 			}

@@ -391,7 +391,7 @@ struct SAcc {
 	}
 };
 
-__global__ void __launch_bounds__(32) trace_warp_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
+__device__ __forceinline__ void trace_warp_body(const TraceArgs &a, const VxAlignDev &ap, const VxQueryDev &qp) {
 	extern __shared__ float tw_smem[];
 	const int item = blockIdx.x;
 	const int lane = threadIdx.x;
@@ -671,6 +671,23 @@ __global__ void __launch_bounds__(32) trace_warp_kernel(TraceArgs a, VxAlignDev 
 	}
 }
 
+__global__ void __launch_bounds__(32) trace_warp_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
+	trace_warp_body(a, ap, qp);
+}
+
+// The winners of several alignment settings of ONE query (a group of vx_search_batch) in one launch: blockIdx.y selects
+// the setting's arguments (own winner list, gap costs and result block), the query constants are shared.
+constexpr int VX_TRACE_MULTI = 8;
+
+struct TraceMulti {
+	TraceArgs a[VX_TRACE_MULTI];
+	VxAlignDev ap[VX_TRACE_MULTI];
+};
+
+__global__ void __launch_bounds__(32) trace_warp_multi_kernel(const __grid_constant__ TraceMulti m, const __grid_constant__ VxQueryDev qp) {
+	trace_warp_body(m.a[blockIdx.y], m.ap[blockIdx.y], qp);
+}
+
 static size_t trace_warp_smem(int32_t max_len, int32_t t, int32_t gap_kind) {
 	const size_t n_layers = gap_kind == VX_GAP_AFFINE ? 3 : 1;
 	const size_t n_cell = (size_t)(max_len + 1) * (t + 1);
@@ -685,6 +702,72 @@ size_t vx_trace_scratch_bytes(int32_t max_len, int32_t t, int32_t max_items, int
 		+ sizeof(int16_t) * (size_t)t;
 	per_item = (per_item + 15) & ~(size_t)15;
 	return per_item * (size_t)max_items;
+}
+
+static void fill_trace_args(TraceArgs &a, const vx_corpus *c, const vx_sim *s, const uint32_t *d_slots, int64_t slot_base,
+	const int32_t *d_n_items, int32_t max_items, const VxTraceOut &out) {
+
+	a.tiles = c->d_tiles;
+	a.tok = c->d_tok;
+	a.pos = c->d_pos;
+	a.boost = c->d_boost;
+	a.s = s->d_s;
+	a.tp = s->tp;
+	a.ctx = c->d_ctx;
+	a.qhat = s->d_qhat;
+	a.ctx_dim = s->d;
+	a.contextual = s->contextual;
+	if (s->contextual == 3) {
+		a.contextual = 2;        // a.s = s->d_s holds the per-token rows
+	} else if (s->contextual && c->sdoc_of == s) {
+		a.s = c->d_sdoc;
+		a.contextual = 2;
+	}
+	a.scratch = nullptr;
+	a.scratch_per_item = 0;
+	a.max_len = c->max_len;
+	a.slots = d_slots;
+	a.slot_base = slot_base;
+	a.orig = c->d_orig;
+	a.n_items = d_n_items;
+	a.max_items = max_items;
+	a.out = out;
+}
+
+// Tracebacks of the winners of n settings of one query in ONE launch (same gap kind, same query constants); returns 1,
+// or 0 when the shared-memory kernel does not apply (the caller then launches per setting).
+int vx_launch_trace_multi(vx_corpus *c, const vx_sim *s, const VxAlignDev *aps, const VxQueryDev &qp, int n,
+	const uint32_t *const *d_slots, const int32_t *const *d_n_items, int32_t max_items, const VxTraceOut *outs) {
+
+	if (max_items <= 0 || n < 1 || n > VX_TRACE_MULTI) {
+		return 0;
+	}
+	for (int j = 1; j < n; j++) {
+		if (aps[j].gap_kind != aps[0].gap_kind) {
+			return 0;
+		}
+	}
+	const size_t warp_smem = trace_warp_smem(c->max_len, qp.t, aps[0].gap_kind);
+	if (warp_smem > 200 * 1024) {
+		return 0;
+	}
+	TraceMulti m;
+	memset(&m, 0, sizeof(m));
+	for (int j = 0; j < n; j++) {
+		fill_trace_args(m.a[j], c, s, d_slots[j], 0, d_n_items[j], max_items, outs[j]);
+		m.ap[j] = aps[j];
+	}
+	static size_t smem_set = 48 * 1024;
+	if (warp_smem > smem_set) {
+		cudaFuncSetAttribute(trace_warp_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)warp_smem);
+		smem_set = warp_smem;
+	}
+	trace_warp_multi_kernel<<<dim3((unsigned)max_items, (unsigned)n), 32, warp_smem, c->stream>>>(m, qp);
+	if (cudaGetLastError() != cudaSuccess) {
+		vx_set_error("trace (warp, multi) kernel launch failed");
+		return -1;
+	}
+	return 1;
 }
 
 int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp,
