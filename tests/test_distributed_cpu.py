@@ -116,3 +116,26 @@ def test_merge_empty_and_shards():
 		b = [shard_documents(5, world, r) for r in range(world)]
 		assert b[0][0] == 0 and b[-1][1] == 5
 		assert all(x[1] == y[0] for x, y in zip(b[:-1], b[1:]))
+
+
+def test_gather_without_process_group():
+	"""No process group (one GPU): gather_topk / gather_topk_many only make the document ids global and keep the order."""
+	import vectorian_b200.distributed as vd
+	assert not dist.is_initialized()
+	h, tg, ds = _rank_rows(0, 6, 4)
+	g = gather_topk(h, tg, ds, 4, doc_offset=7)
+	want = merge_hits([(np.array([(s, m, d + 7, sl) for s, m, d, sl in h.tolist()], dtype=HIT_DTYPE), tg, ds)], 4)
+	np.testing.assert_array_equal(g[0], want[0])
+	np.testing.assert_array_equal(g[1], want[1])
+	k = 8
+	hits = np.zeros((2, k), dtype=HIT_DTYPE)
+	target = np.full((2, k, 4), -1, dtype=np.int16)
+	distance = np.ones((2, k, 4), dtype=np.float32)
+	rows = [_rank_rows(0, 6, 4), _rank_rows(1, 3, 4)]
+	for i, (hh, tt, dd) in enumerate(rows):
+		hits[i, :len(hh)], target[i, :len(hh)], distance[i, :len(hh)] = hh, tt, dd
+	a = gather_topk_many(vd.BatchRows(hits, target, distance, [6, 3], [4, 4]), k, doc_offset=2)
+	b = gather_topk_many(rows, k, doc_offset=2)
+	for x, y in zip(a, b):
+		for u, v in zip(x, y):
+			np.testing.assert_array_equal(u, v)
