@@ -176,7 +176,7 @@ def run_reference(args):
 		"e2e": {"value": value, "unit": "sentences/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
 		"gcups": value * 25 * T_QUERY / 1e9,
 	}
-	print(json.dumps(line), flush=True)
+	emit_line(json.dumps(line))
 
 
 def workload_name(args):
@@ -348,11 +348,24 @@ def main():
 			rp, dtp, _ = cpu_port_rate(args.cpu_sample, threads)
 			line["cpu_port"] = {"value": rp, "unit": "sentences/s", "cores": threads,
 				"what": "oracle/vx_oracle.c (optimised C restatement), same sample"}
-		print(json.dumps(line), flush=True)
+		emit_line(json.dumps(line))
 
 	if world > 1:
 		dist.destroy_process_group()
 
 
+def emit_line(text):
+	"""The JSON line goes to the REAL stdout; everything else written to fd 1 while the bench runs (e.g. the
+	"NCCL version ..." banner NCCL prints on stdout under NCCL_DEBUG=VERSION) has been redirected to stderr, so that
+	stdout holds exactly one line."""
+	os.write(_REAL_STDOUT, (text + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 if __name__ == "__main__":
+	sys.stdout.flush()
+	_REAL_STDOUT = os.dup(1)
+	os.dup2(2, 1)
 	main()
