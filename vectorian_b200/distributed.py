@@ -124,11 +124,29 @@ def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
 		pin_recv.copy_(recv, non_blocking=True)
 		torch.cuda.current_stream(device).synchronize()
 		recv_host = pin_recv.numpy()
+		pin_top = None
+	elif device.type == "cuda":
+		# sweeps: the same staging (pinned send buffer, cached device buffers); the merge below stays on the device
+		key = ("sweep", buf.shape, world, device.index)
+		st = _staging.get(key)
+		if st is None:
+			st = (torch.empty(buf.shape, dtype=torch.float32).pin_memory(), torch.empty(buf.shape, dtype=torch.float32, device=device),
+				torch.empty((world,) + buf.shape, dtype=torch.float32, device=device),
+				torch.empty((n_pairs, k, buf.shape[2]), dtype=torch.float32).pin_memory())
+			if len(_staging) > 32:
+				_staging.clear()
+			_staging[key] = st
+		pin_send, send, recv, pin_top = st
+		pin_send.numpy()[...] = buf
+		send.copy_(pin_send, non_blocking=True)
+		dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
+		recv_host = None
 	else:
 		send = torch.from_numpy(buf).to(device)
 		recv = torch.empty((world,) + buf.shape, dtype=torch.float32, device=device)
 		dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
 		recv_host = None
+		pin_top = None
 
 	if host_merge:
 		# a single search (or a handful): one copy to the host and a lexsort per pair cost less than a dozen small kernels
@@ -162,8 +180,13 @@ def gather_topk_many(results, k, doc_offset=0, group=None, device=None):
 	order = torch.gather(o1, 1, o2)[:, :k]
 	top = torch.gather(rows, 1, order[:, :, None].expand(-1, -1, rows.shape[2])).contiguous()
 	n_out = torch.clamp(valid.sum(dim=1), max=k)
-	top_h = top.cpu().numpy()
-	n_h = n_out.cpu().numpy()
+	if device.type == "cuda" and pin_top is not None:
+		pin_top.copy_(top, non_blocking=True)
+		n_h = n_out.cpu().numpy()             # synchronises the stream: the pinned copy above has landed
+		top_h = pin_top.numpy()
+	else:
+		top_h = top.cpu().numpy()
+		n_h = n_out.cpu().numpy()
 	itop = top_h.view(np.int32)
 	all_hits = np.zeros((n_pairs, k), dtype=HIT_DTYPE)
 	all_hits["score"] = top_h[:, :, 0]
