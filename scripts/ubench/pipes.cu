@@ -7,6 +7,7 @@
 #define ITERS 2048
 
 __constant__ float c_w[64];
+__constant__ float2 c_w2[32];
 
 template<int MODE>
 __global__ void __launch_bounds__(128) bench(float *out, float seed, long long *cycles) {
@@ -74,6 +75,32 @@ __global__ void __launch_bounds__(128) bench(float *out, float seed, long long *
 				xi = max(max(xi, __float_as_int(y) + i), __float_as_int(z) + it);
 				x[i] = __int_as_float(xi);
 			}
+		} else if (MODE == 10) {  // FADD2 r, UR pair (gap-cost pair from the parameter bank, as in the WSB kernel)
+			#pragma unroll
+			for (int i = 0; i < N_CHAIN; i += 2) {
+				const float2 w = c_w2[(i / 2 + it) & 31];
+				asm("{ .reg .b64 a, b; mov.b64 a, {%0, %1}; mov.b64 b, {%2, %3}; add.rn.f32x2 a, a, b; mov.b64 {%0, %1}, a; }"
+					: "+f"(x[i]), "+f"(x[i + 1]) : "f"(w.x), "f"(w.y));
+			}
+		} else if (MODE == 11) {  // the WSB inner loop after the rewrite: 2 FADD2 (r, UR) + 2 FMNMX3 per 4 candidates
+			#pragma unroll
+			for (int i = 0; i < N_CHAIN; i += 2) {
+				const int p = (i + 2) % N_CHAIN, q = (i + 4) % N_CHAIN;
+				const float2 w0 = c_w2[(i / 2 + it) & 31], w1 = c_w2[(i / 2 + it + 7) & 31];
+				float a0, a1, b0, b1;
+				asm("{ .reg .b64 a, b; mov.b64 a, {%2, %3}; mov.b64 b, {%4, %5}; add.rn.f32x2 a, a, b; mov.b64 {%0, %1}, a; }"
+					: "=f"(a0), "=f"(a1) : "f"(x[p]), "f"(x[p + 1]), "f"(w0.x), "f"(w0.y));
+				asm("{ .reg .b64 a, b; mov.b64 a, {%2, %3}; mov.b64 b, {%4, %5}; add.rn.f32x2 a, a, b; mov.b64 {%0, %1}, a; }"
+					: "=f"(b0), "=f"(b1) : "f"(x[q]), "f"(x[q + 1]), "f"(w1.x), "f"(w1.y));
+				asm("max.f32 %0, %0, %1, %2;" : "+f"(x[i]) : "f"(a0), "f"(b0));
+				asm("max.f32 %0, %0, %1, %2;" : "+f"(x[i + 1]) : "f"(a1), "f"(b1));
+			}
+		} else if (MODE == 12) {  // FFMA2 for reference (fma.rn.f32x2)
+			#pragma unroll
+			for (int i = 0; i < N_CHAIN; i += 2) {
+				asm("{ .reg .b64 a, b; mov.b64 a, {%0, %1}; mov.b64 b, {%2, %3}; fma.rn.f32x2 a, a, b, b; mov.b64 {%0, %1}, a; }"
+					: "+f"(x[i]), "+f"(x[i + 1]) : "f"(y), "f"(z));
+			}
 		} else if (MODE == 9) {   // 2 FADD(reg,const) + FMNMX3
 			#pragma unroll
 			for (int i = 0; i < N_CHAIN; i++) {
@@ -117,7 +144,9 @@ void run(const char *name, int instr_per_iter, int cand_per_iter, int warps_per_
 int main() {
 	float w[64]; for (int i = 0; i < 64; i++) w[i] = 0.01f * i;
 	cudaMemcpyToSymbol(c_w, w, sizeof(w));
-	for (int wps : {4, 8, 16}) {
+	float2 w2[32]; for (int i = 0; i < 32; i++) w2[i] = make_float2(-0.01f * i, -0.01f * i);
+	cudaMemcpyToSymbol(c_w2, w2, sizeof(w2));
+	for (int wps : {4, 8, 12, 16}) {
 		run<0>("FADD r,r", N_CHAIN, 0, wps);
 		run<1>("FADD r,c", N_CHAIN, 0, wps);
 		run<2>("FMNMX", N_CHAIN, 0, wps);
@@ -128,6 +157,9 @@ int main() {
 		run<7>("FADD2 + FMNMX3", N_CHAIN * 2, N_CHAIN * 2, wps);
 		run<8>("VIMNMX3 (+2 IADD)", N_CHAIN * 3, 0, wps);
 		run<9>("2 FADD r,c + FMNMX3", N_CHAIN * 3, N_CHAIN * 2, wps);
+		run<10>("FADD2 r,UR", N_CHAIN / 2, 0, wps);
+		run<11>("2 FADD2 r,UR + 2 FMNMX3 (4 cand)", N_CHAIN * 2, N_CHAIN * 2, wps);
+		run<12>("FFMA2", N_CHAIN / 2, 0, wps);
 	}
 	return 0;
 }
