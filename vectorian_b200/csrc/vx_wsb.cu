@@ -52,11 +52,26 @@ struct WsbArgs {
 	float total;
 	float ws[VX_WSB_MAX_LEN + 4];   // w_s[0..64], gap cost along the sentence
 	float wt[VX_MAX_T_FAST + 4];    // w_t[0..16], gap cost along the query
+	// the same tables negated and paired for the packed adds (add.rn.f32x2 -> FADD2, one issue slot for two
+	// candidates; x - w == x + (-w) bit for bit):
+	float2 nws2[VX_WSB_MAX_LEN + 4];   // {-w_s[d], -w_s[d]}: two neighbouring columns of one finished row
+	float2 nwt2[VX_MAX_T_FAST + 4];    // {-w_t[d], -w_t[d-1]}: two neighbouring cells (k, k+1) left of column k + d
 };
 
 __device__ __forceinline__ float max3(float a, float b, float c) {
 	float r;
 	asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+	return r;
+}
+
+// Packed fp32 add (sm_100: add.rn.f32x2 -> SASS FADD2 Rd, Ra.F32x2, URb.F32x2): both halves are ordinary
+// round-to-nearest adds.  The register pairs are formed by the allocator (the tcgen05.ld / LDS.128
+// destinations and the accumulator rows are consecutive registers), the gap-cost pair comes from the
+// parameter bank through a uniform register pair.
+__device__ __forceinline__ float2 add2(float x0, float x1, float2 w) {
+	float2 r;
+	asm("{ .reg .b64 ra, rb, rc; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; add.rn.f32x2 rc, ra, rb; mov.b64 {%0, %1}, rc; }"
+		: "=f"(r.x), "=f"(r.y) : "f"(x0), "f"(x1), "f"(w.x), "f"(w.y));
 	return r;
 }
 
@@ -100,6 +115,14 @@ struct Fold {
 			has = true;
 		}
 	}
+	__device__ __forceinline__ void push2(float c0, float c1) {
+		if (has) {
+			x = max3(x, p, c0);
+			p = c1;
+		} else {
+			x = max3(x, c0, c1);
+		}
+	}
 	__device__ __forceinline__ float done() const {
 		return has ? fmaxf(x, p) : x;
 	}
@@ -121,11 +144,42 @@ __device__ __forceinline__ int32_t quad_get(const int4 &q, int i) {
 	return i == 0 ? q.x : i == 1 ? q.y : i == 2 ? q.z : q.w;
 }
 
+// Vertical candidates of the NR rows of a block from two finished rows k, k+1 (h0, h1); d = u0 - k.
+//   acc[i][v] = max(acc[i][v], h0[v] - w_s[d + i], h1[v] - w_s[d + i - 1])
+// F2: one FADD2 forms the candidates of two neighbouring columns, so 4 candidates cost 2 FADD2 + 2 FMNMX3
+// (4 issue slots instead of 6).
+template<int TP, int NR, bool F2>
+__device__ __forceinline__ void wsb_history_pair(const WsbArgs &a, const int d, float (&acc)[NR][TP],
+	const float (&h0)[TP], const float (&h1)[TP]) {
+
+	#pragma unroll
+	for (int i = 0; i < NR; i++) {
+		if (F2) {
+			const float2 w0 = a.nws2[d + i];
+			const float2 w1 = a.nws2[d + i - 1];
+			#pragma unroll
+			for (int v = 0; v < TP; v += 2) {
+				const float2 p = add2(h0[v], h0[v + 1], w0);
+				const float2 q = add2(h1[v], h1[v + 1], w1);
+				acc[i][v] = max3(acc[i][v], p.x, q.x);
+				acc[i][v + 1] = max3(acc[i][v + 1], p.y, q.y);
+			}
+		} else {
+			const float w0 = a.ws[d + i];
+			const float w1 = a.ws[d + i - 1];
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				acc[i][v] = max3(acc[i][v], h0[v] - w0, h1[v] - w1);
+			}
+		}
+	}
+}
+
 // One block of NR rows u0 .. u0+NR-1 of one tile.
 //   prev[v]  in: V[u0-1, v]  out: V[u0+NR-1, v]
 //   sim      in: S rows of this block; out: S rows of the NEXT block of the warp's token stream
 //            (each row is re-loaded as soon as it has been consumed, ids from idq_next)
-template<int TP, int LOC, bool BORD, int NR>
+template<int TP, int LOC, bool BORD, int NR, bool F2>
 __device__ __forceinline__ void wsb_block(
 	const WsbArgs &a, const uint32_t tmem, float4 *__restrict__ hist, const int u0, const int t,
 	float (&prev)[TP], float &best, float &last_col,
@@ -163,15 +217,7 @@ __device__ __forceinline__ void wsb_block(
 			tmem_ld4(tmem + (uint32_t)((k + 1) * TP + 4 * q), h1 + 4 * q);
 		}
 		tmem_wait_ld();
-		#pragma unroll
-		for (int i = 0; i < NR; i++) {
-			const float w0 = a.ws[u0 + i - k];
-			const float w1 = a.ws[u0 + i - k - 1];
-			#pragma unroll
-			for (int v = 0; v < TP; v++) {
-				acc[i][v] = max3(acc[i][v], h0[v] - w0, h1[v] - w1);
-			}
-		}
+		wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, h0, h1);
 	}
 	#pragma unroll 1
 	for (int k = rt; k < u0; k += 2) {
@@ -183,15 +229,7 @@ __device__ __forceinline__ void wsb_block(
 			h0[4 * q + 0] = x.x; h0[4 * q + 1] = x.y; h0[4 * q + 2] = x.z; h0[4 * q + 3] = x.w;
 			h1[4 * q + 0] = y.x; h1[4 * q + 1] = y.y; h1[4 * q + 2] = y.z; h1[4 * q + 3] = y.w;
 		}
-		#pragma unroll
-		for (int i = 0; i < NR; i++) {
-			const float w0 = a.ws[u0 + i - k];
-			const float w1 = a.ws[u0 + i - k - 1];
-			#pragma unroll
-			for (int v = 0; v < TP; v++) {
-				acc[i][v] = max3(acc[i][v], h0[v] - w0, h1[v] - w1);
-			}
-		}
+		wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, h0, h1);
 	}
 
 	// token ids: idq_next (ids of the next block, loaded one block ago) is consumed by the row-wise
@@ -207,23 +245,68 @@ __device__ __forceinline__ void wsb_block(
 		// V[u, -1] and V[u-1, -1]
 		const float left = BORD ? (LOC == VX_GLOBAL ? -a.ws[u + 1] : 0.0f) : 0.0f;
 		float diag = BORD ? (LOC == VX_GLOBAL ? (u == 0 ? -a.wt[0] : -a.ws[u]) : 0.0f) : 0.0f;
-		#pragma unroll
-		for (int v = 0; v < TP; v++) {
-			Fold f(acc[i][v]);
+		if (F2) {
+			// rows of this block above row i: pairs of rows and pairs of columns per FADD2; an odd row is left
+			// pending and folds with the diagonal candidate below
+			float pend[TP];
 			#pragma unroll
-			for (int j = 0; j < i; j++) {
-				f.push(acc[j][v] - a.ws[i - j]);          // rows of this block
+			for (int j = 0; j + 1 < i; j += 2) {
+				#pragma unroll
+				for (int v = 0; v < TP; v += 2) {
+					const float2 p = add2(acc[j][v], acc[j][v + 1], a.nws2[i - j]);
+					const float2 q = add2(acc[j + 1][v], acc[j + 1][v + 1], a.nws2[i - j - 1]);
+					acc[i][v] = max3(acc[i][v], p.x, q.x);
+					acc[i][v + 1] = max3(acc[i][v + 1], p.y, q.y);
+				}
 			}
-			f.push(diag + sim[i][v]);
-			diag = i == 0 ? prev[v] : acc[i - 1][v];
-			if (BORD) {
-				f.push(left - a.wt[v + 1]);
+			if (i & 1) {
+				#pragma unroll
+				for (int v = 0; v < TP; v += 2) {
+					const float2 p = add2(acc[i - 1][v], acc[i - 1][v + 1], a.nws2[1]);
+					pend[v] = p.x;
+					pend[v + 1] = p.y;
+				}
 			}
 			#pragma unroll
-			for (int k = 0; k < v; k++) {
-				f.push(acc[i][k] - a.wt[v - k]);          // cells to the left
+			for (int v = 0; v < TP; v++) {
+				Fold f(acc[i][v]);
+				if (i & 1) {
+					f.push(pend[v]);
+				}
+				f.push(diag + sim[i][v]);
+				diag = i == 0 ? prev[v] : acc[i - 1][v];
+				if (BORD) {
+					f.push(left - a.wt[v + 1]);
+				}
+				#pragma unroll
+				for (int k = 0; k + 1 < v; k += 2) {
+					const float2 p = add2(acc[i][k], acc[i][k + 1], a.nwt2[v - k]);   // cells k, k+1 to the left
+					f.push2(p.x, p.y);
+				}
+				if (v & 1) {
+					f.push(acc[i][v - 1] - a.wt[1]);
+				}
+				acc[i][v] = f.done();
 			}
-			acc[i][v] = f.done();
+		} else {
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				Fold f(acc[i][v]);
+				#pragma unroll
+				for (int j = 0; j < i; j++) {
+					f.push(acc[j][v] - a.ws[i - j]);          // rows of this block
+				}
+				f.push(diag + sim[i][v]);
+				diag = i == 0 ? prev[v] : acc[i - 1][v];
+				if (BORD) {
+					f.push(left - a.wt[v + 1]);
+				}
+				#pragma unroll
+				for (int k = 0; k < v; k++) {
+					f.push(acc[i][k] - a.wt[v - k]);          // cells to the left
+				}
+				acc[i][v] = f.done();
+			}
 		}
 		// this row of S has been consumed: fetch the same row of the next block
 		load_sim_row<TP>(s4, quad_get(idq_use, i), sim[i]);
@@ -287,7 +370,7 @@ __device__ __forceinline__ void wsb_block(
 	}
 }
 
-template<int TP, int LOC, bool BORD>
+template<int TP, int LOC, bool BORD, bool F2>
 __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant__ WsbArgs a) {
 	extern __shared__ float4 wsb_smem[];
 	__shared__ uint32_t tmem_base_sh;
@@ -369,18 +452,18 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 			int u0 = 0;
 			#pragma unroll 1
 			for (; u0 + U <= len; u0 += U) {
-				wsb_block<TP, LOC, BORD, U>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+				wsb_block<TP, LOC, BORD, U, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 			}
 			if (u0 < len) {
 				switch (len - u0) {
 					case 1:
-						wsb_block<TP, LOC, BORD, 1>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 1, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 					case 2:
-						wsb_block<TP, LOC, BORD, 2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 2, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 					default:
-						wsb_block<TP, LOC, BORD, 3>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 3, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 				}
 			}
@@ -437,7 +520,7 @@ static void wsb_plan(int tp, int cap, int *warps, int *rt, int *tmem_cols, int *
 	}
 }
 
-template<int TP, int LOC, bool BORD>
+template<int TP, int LOC, bool BORD, bool F2>
 static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap) {
 	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
 	// SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a TMEM lane quarter
@@ -467,7 +550,7 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	const size_t smem = (size_t)rows_smem * row_bytes * warps;
 	static bool attr_set = false;
 	if (!attr_set) {
-		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
+		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD, F2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
 		attr_set = true;
 	}
 	// Every launch after the first of a query is a programmatic dependent launch: the kernels of one query do not
@@ -484,21 +567,28 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	attr[0].val.programmaticStreamSerializationAllowed = 1;
 	cfg.attrs = attr;
 	cfg.numAttrs = overlap ? 1 : 0;
-	if (cudaLaunchKernelEx(&cfg, wsb_score_kernel<TP, LOC, BORD>, a) != cudaSuccess) {
+	if (cudaLaunchKernelEx(&cfg, wsb_score_kernel<TP, LOC, BORD, F2>, a) != cudaSuccess) {
 		return -1;
 	}
 	return 1;
 }
 
-template<int TP>
-static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
+template<int TP, bool F2>
+static int launch_class_f(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
 	if (loc == VX_LOCAL) {
-		return bord ? launch_class<TP, VX_LOCAL, true>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false>(c, a, cap, sms, overlap);
+		return bord ? launch_class<TP, VX_LOCAL, true, F2>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false, F2>(c, a, cap, sms, overlap);
 	}
 	if (loc == VX_GLOBAL) {
-		return launch_class<TP, VX_GLOBAL, true>(c, a, cap, sms, overlap);
+		return launch_class<TP, VX_GLOBAL, true, F2>(c, a, cap, sms, overlap);
 	}
-	return launch_class<TP, VX_SEMIGLOBAL, true>(c, a, cap, sms, overlap);
+	return launch_class<TP, VX_SEMIGLOBAL, true, F2>(c, a, cap, sms, overlap);
+}
+
+template<int TP>
+static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
+	// packed adds (FADD2) by default; VX_WSB_NO_F2 keeps the scalar-add variant for A/B measurements (read once)
+	static const bool f2 = getenv("VX_WSB_NO_F2") == nullptr;
+	return f2 ? launch_class_f<TP, true>(c, a, cap, sms, loc, bord, overlap) : launch_class_f<TP, false>(c, a, cap, sms, loc, bord, overlap);
 }
 
 // Scores every tile whose windows are at most VX_WSB_MAX_LEN long; *first_tile receives the index of
@@ -532,6 +622,12 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	for (int i = 0; i <= qp.t && i < ap.n_w_t; i++) {
 		a.wt[i] = h_wt[i];
 		nonneg = nonneg && h_wt[i] >= 0.0f;
+	}
+	for (int i = 0; i < VX_WSB_MAX_LEN + 4; i++) {
+		a.nws2[i] = make_float2(-a.ws[i], -a.ws[i]);
+	}
+	for (int i = 1; i < VX_MAX_T_FAST + 4; i++) {
+		a.nwt2[i] = make_float2(-a.wt[i], -a.wt[i - 1]);
 	}
 	// With non-negative gap costs the border candidates of a Local alignment (0 - w) never beat the
 	// Local zero, so the kernel variant without them gives the same maxima.
