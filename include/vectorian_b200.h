@@ -203,6 +203,28 @@ int vx_search_batch(
 	const vx_align_params *aps, int32_t n_aps, const vx_query_params *qp, int32_t t_stride,
 	vx_hit *hits, int16_t *target, float *dist, int32_t *n_hits);
 
+/*
+ * vx_search_topk_noalloc -- NO COUNTERPART IN THE REFERENCE.
+ * For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it): the score -> top-k part of vx_search without any allocation -- no cudaMalloc / cudaMallocHost / cudaFree, on
+ * the first call or any later one.  The top-k kernel's scratch (radix histograms, candidate buffer, winner list) and
+ * the result rows live in ONE file-scope static device array of VX_NOALLOC_SCRATCH_BYTES per GPU that loads the
+ * library (held until the process exits).  Returns the same hits (score, score_max, doc, slice; same order) vx_search
+ * returns, without tracebacks (no target / dist).
+ * Limits: max_matches <= VX_NOALLOC_MAX_K; static or uploaded similarity matrix with at most 16 query tokens; no
+ * tag weighting, submatch_weight == 0; general gap costs only with windows of at most 64 tokens (the other paths
+ * need scratch sized by the input).  Anything beyond fails with VX_ERR_INVALID and a message; nothing is truncated.
+ * Every call on a GPU shares the array and finds the last call's contents in it: what must start at zero is cleared
+ * at the start of each call.  Calls that overlap on one GPU would race on it; within a process they cannot (the
+ * entry point holds a lock and waits for its stream before returning).
+ */
+#define VX_NOALLOC_MAX_K 1024
+#define VX_NOALLOC_SCRATCH_BYTES 147456   /* 144 KiB */
+int vx_search_topk_noalloc(
+	vx_corpus *c, const vx_sim *s,
+	const vx_align_params *ap, const vx_query_params *qp,
+	vx_hit *hits, int32_t *n_hits);
+
 /* Score every window (debug hook "alignment" / tests): score[n_windows] in window order, 0-filled where len<1. */
 int vx_score_all(
 	vx_corpus *c, const vx_sim *s,

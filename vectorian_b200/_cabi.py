@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libvectorian_b200.so")
 VX_LOCAL, VX_GLOBAL, VX_SEMIGLOBAL = 0, 1, 2
 VX_GAP_LINEAR, VX_GAP_AFFINE, VX_GAP_GENERAL = 0, 1, 2
 VX_MAX_LEN = 16383
+VX_NOALLOC_MAX_K = 1024
 
 c_float_p = C.POINTER(C.c_float)
 c_int8_p = C.POINTER(C.c_int8)
@@ -153,6 +154,8 @@ _SIGNATURES = {
 	"vx_search": (C.c_int, [
 		C.c_void_p, C.c_void_p, C.POINTER(AlignParams), C.POINTER(QueryParams),
 		C.POINTER(Hit), c_int16_p, c_float_p, c_int32_p]),
+	"vx_search_topk_noalloc": (C.c_int, [
+		C.c_void_p, C.c_void_p, C.POINTER(AlignParams), C.POINTER(QueryParams), C.POINTER(Hit), c_int32_p]),
 	"vx_search_batch": (C.c_int, [
 		C.c_void_p, C.POINTER(C.c_void_p), C.c_int32, C.POINTER(AlignParams), C.c_int32, C.POINTER(QueryParams), C.c_int32,
 		C.POINTER(Hit), c_int16_p, c_float_p, c_int32_p]),

@@ -119,6 +119,17 @@ class DeviceCorpus:
 			hits.ctypes.data_as(C.POINTER(Hit)), ptr(target, C.c_int16), ptr(dist, C.c_float), C.byref(n)), self._lib)
 		return hits[:n.value], target[:n.value, :sim.t], dist[:n.value, :sim.t]
 
+	def search_topk_noalloc(self, sim, ap, qp):
+		"""vx_search_topk_noalloc: the hits of `search` (no tracebacks) through the entry point that allocates nothing
+		(scratch in a static device array; max_matches <= VX_NOALLOC_MAX_K, fast paths only).  No counterpart in the
+		reference."""
+		k = max(int(qp.max_matches), 1)
+		hits = np.zeros((k,), dtype=HIT_DTYPE)
+		n = C.c_int32(0)
+		check(self._lib.vx_search_topk_noalloc(self._h, sim.handle, C.byref(ap), C.byref(qp),
+			hits.ctypes.data_as(C.POINTER(Hit)), C.byref(n)), self._lib)
+		return hits[:n.value]
+
 	def search_batch(self, sims, aps, qp, raw=False):
 		"""Parameter sweep (vx_search_batch): every query in `sims` against every alignment setting in `aps` in one
 		call.  Returns a list over queries of lists over settings of (hits, target, dist) as `search` returns them."""
