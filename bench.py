@@ -1,14 +1,17 @@
 #!/usr/bin/env python
 """Headline benchmark: Waterman-Smith-Beyer brute-force search (BASELINE.json configs[2]).
 
-One step = one query through the whole hot path over the resident corpus shard:
+One step = one query through the whole hot path over the resident corpus:
 similarity GEMM (query x vocabulary) -> per-sentence WSB alignment -> device top-k ->
-traceback of the winners -> (N > 1) all-gather + merge of the per-rank top-k.
+traceback of the winners -> (N > 1) all-gather + device merge of the per-rank top-k.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--sentences S]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--sentences S] [--weak]
 
-N > 1 is launched by torchrun (one rank per GPU, NCCL).  Weak scaling: every rank holds
-`--sentences` sentences (default 50M = the named corpus on one GPU).
+N > 1 is launched by torchrun (one rank per GPU, NCCL).  STRONG scaling, as configs[2] names it: `--sentences`
+(default 50M) is the corpus IN TOTAL, sharded by documents over the N ranks (50M / N sentences per GPU); every rank
+generates the same global corpus and keeps its own documents.  `--weak` keeps `--sentences` per GPU instead.
+After the timed loop the sharded result of one query is checked on the hardware against a merge built from every
+rank's vx_score_all scores ("sharded_parity").
 """
 
 import argparse
@@ -167,7 +170,7 @@ def run_reference(args):
 	line = {
 		"impl": "reference", "metric": "sentences/sec (WSB alignment, 12-token query, top-100)",
 		"value": value, "unit": "sentences/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-		"ms_per_step": float(np.mean([dt for _, dt in rates]) * 1e3), "higher_is_better": True, "scaling": "weak",
+		"ms_per_step": float(np.mean([dt for _, dt in rates]) * 1e3), "higher_is_better": True, "scaling": "weak" if args.weak else "strong",
 		"vs_baseline": None, "dtype": "f32", "data": "synthetic",
 		"config": {"workload": workload_name(args), "sample_sentences_per_step": sample},
 		"cpu_baseline": {"value": value, "unit": "sentences/s", "cores": threads, "kind": kind,
@@ -180,8 +183,57 @@ def run_reference(args):
 
 
 def workload_name(args):
+	world = max(int(getattr(args, "gpus", 1) or 1), 1)
+	if getattr(args, "weak", False):
+		size = f"{args.sentences} sentences per GPU"
+	elif world > 1:
+		size = f"{args.sentences} sentences in total, {args.sentences // world} per GPU (sharded by documents over {world} GPUs)"
+	else:
+		size = f"{args.sentences} sentences in total"
 	return (f"C3: Waterman-Smith-Beyer Local, smooth_gap_cost(5), T={T_QUERY}, V={VOCAB}x{DIM} static embedding, "
-		f"top-{TOPK}, {args.sentences} sentences per GPU (~25 tokens each, Zipf ids)")
+		f"top-{TOPK}, {size} (~25 tokens each, Zipf ids)")
+
+
+def shard_tables(tok, tables, lo, hi):
+	"""The documents [lo, hi) of a corpus made by synthetic.make_corpus_device: (token view, span tables)."""
+	t0, t1 = int(tables["doc_tok_off"][lo]), int(tables["doc_tok_off"][hi])
+	s0, s1 = int(tables["doc_span_off"][lo]), int(tables["doc_span_off"][hi])
+	sub = dict(doc_tok_off=tables["doc_tok_off"][lo:hi + 1] - t0, span_start=tables["span_start"][s0:s1],
+		span_end=tables["span_end"][s0:s1], doc_span_off=tables["doc_span_off"][lo:hi + 1] - s0,
+		lens=tables["lens"][s0:s1], n_doc=hi - lo)
+	return tok[t0:t1], sub
+
+
+def sharded_parity(dc, sim, ap, qp, hits, rank, world, doc_lo, sentences_per_doc=1000):
+	"""On-hardware check of 'N shards + NCCL gather + device merge' (ResultSet::extend + best_n, reference:
+	vectorian/core/cpp/result_set.h:70-93, cpp/result_set.cpp:3-21): every rank scores ALL its windows (vx_score_all,
+	independent of the device top-k and of the merge), keeps its best k under (score desc, doc desc, slice desc) with
+	numpy, the lists are gathered as Python objects and merged on rank 0; the result must equal the hits the timed
+	path returned -- scores, document ids and slice ids, in order."""
+	import torch.distributed as dist
+	score = dc.score_all(sim, ap, qp)
+	k = int(qp.max_matches)
+	ok = score > np.float32(qp.min_score)
+	idx = np.nonzero(ok)[0]
+	if len(idx) > k:
+		part = np.argpartition(-score[idx], k - 1)[:k]
+		kth = score[idx][part].min()
+		idx = idx[score[idx] >= kth]          # everything tied with the k-th score stays in
+	doc = idx // sentences_per_doc + doc_lo    # synthetic corpus: every sentence is one window, 1000 per document
+	sl = idx % sentences_per_doc
+	rows = list(zip(score[idx].tolist(), doc.tolist(), sl.tolist()))
+	gathered = [None] * world
+	if world > 1:
+		dist.all_gather_object(gathered, rows)
+	else:
+		gathered = [rows]
+	if rank != 0:
+		return None
+	allrows = sorted((r for part in gathered for r in part), key=lambda r: (-r[0], -r[1], -r[2]))[:k]
+	got = [(float(h["score"]), int(h["doc"]), int(h["slice"])) for h in hits]
+	if got == [(float(np.float32(a)), b, c) for a, b, c in allrows]:
+		return "ok"
+	return "MISMATCH: %d rows, first difference at %s" % (len(got), next((i for i, (x, y) in enumerate(zip(got, allrows)) if x != (float(np.float32(y[0])), y[1], y[2])), "length"))
 
 
 def main():
@@ -194,6 +246,8 @@ def main():
 	ap_.add_argument("--cpu-sample", type=int, default=1_000_000)
 	ap_.add_argument("--no-cpu-baseline", action="store_true")
 	ap_.add_argument("--no-clocks", action="store_true")
+	ap_.add_argument("--weak", action="store_true", help="--sentences per GPU instead of in total")
+	ap_.add_argument("--no-secondary", action="store_true")
 	args = ap_.parse_args()
 	args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
 
@@ -204,29 +258,40 @@ def main():
 	import torch
 	import torch.distributed as dist
 	from vectorian_b200 import _cabi, engine, synthetic
-	from vectorian_b200.distributed import gather_topk
+	from vectorian_b200.distributed import device_comm
 
 	rank = int(os.environ.get("RANK", "0"))
 	world = int(os.environ.get("WORLD_SIZE", "1"))
 	local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+	args.gpus = world
 	torch.cuda.set_device(local_rank)
 	if world > 1:
 		dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
 	# ---- resident state: corpus shard + embedding (setup, untimed) ----
 	t_setup = time.perf_counter()
-	tok, tables = synthetic.make_corpus_device(args.sentences, VOCAB, seed=synthetic.CORPUS_SEED + rank,
-		device=f"cuda:{local_rank}")
+	if args.weak or world == 1:
+		tok, tables = synthetic.make_corpus_device(args.sentences, VOCAB, seed=synthetic.CORPUS_SEED + (rank if args.weak else 0),
+			device=f"cuda:{local_rank}")
+		doc_lo = rank * tables["n_doc"]
+	else:
+		# strong scaling: the SAME global corpus on every rank, this rank keeps a contiguous range of its documents
+		tok_all, tables_all = synthetic.make_corpus_device(args.sentences, VOCAB, seed=synthetic.CORPUS_SEED, device=f"cuda:{local_rank}")
+		n_doc_all = tables_all["n_doc"]
+		doc_lo, doc_hi = n_doc_all * rank // world, n_doc_all * (rank + 1) // world
+		tok, tables = shard_tables(tok_all, tables_all, doc_lo, doc_hi)
+		del tok_all
 	torch.cuda.synchronize()
 	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"],
 		tables["doc_span_off"], on_device=True)
 	lens = tables["lens"]
-	n_doc_local = tables["n_doc"]
 	del tok
 	torch.cuda.empty_cache()
+	if world > 1:
+		comm = device_comm()
+		dc.set_shard(comm, doc_lo)      # vx_search now returns the global top-k on every rank
 	emb = synthetic.make_embedding(VOCAB, DIM)
 	de = engine.DeviceEmbedding(emb)
-	rng = np.random.default_rng(synthetic.QUERY_SEED)
 	queries = [synthetic.make_query(T_QUERY, VOCAB, seed=synthetic.QUERY_SEED + i) for i in range(N_QUERIES)]
 	# per-step inputs live in pinned host memory: query token ids + their (unnormalised) vectors
 	q_ids = [torch.from_numpy(q).pin_memory() for q in queries]
@@ -236,15 +301,14 @@ def main():
 	setup_s = time.perf_counter() - t_setup
 
 	def step(i):
-		"""The public-API call a user makes; inputs from pinned host memory, results back on the host."""
+		"""The public-API call a user makes; inputs from pinned host memory, results back on the host.  With N > 1 the
+		all-gather of the ranks' result rows and their merge happen inside vx_search (device time in gather_merge_ms)."""
 		j = i % N_QUERIES
 		sim = engine.DeviceSim.static(de, q_ids[j].numpy(), q_vecs[j].numpy())
 		hits, target, distance = dc.search(sim, ap, qp)
 		dev_ms = sim.build_ms + sum(dc.last_timing().values())
 		launches = sim.launches + dc.last_launches()
 		sim.close()
-		if world > 1:
-			hits, target, distance = gather_topk(hits, target, distance, TOPK, doc_offset=rank * n_doc_local)
 		return hits, dev_ms, launches
 
 	def barrier():
@@ -260,14 +324,26 @@ def main():
 	t0 = time.perf_counter()
 	dev_ms_total, dp_ms_total, launches_total = 0.0, 0.0, 0
 	last_hits = None
+	gather_ms_total = 0.0
 	for i in range(args.steps):
 		last_hits, dev_ms, launches = step(args.warmup + i)
 		dev_ms_total += dev_ms
 		dp_ms_total += dc.last_timing()["dp_ms"]
+		gather_ms_total += dc.last_timing()["gather_merge_ms"]
 		launches_total += launches
 	barrier()
 	t1 = time.perf_counter()
 	clocks = sampler.stop(t0, t1) if sampler else None
+
+	# ---- on-hardware check of the sharded path (untimed): the hits of one more query vs. every rank's vx_score_all ----
+	j = (args.warmup + args.steps) % N_QUERIES
+	sim = engine.DeviceSim.static(de, q_ids[j].numpy(), q_vecs[j].numpy())
+	check_hits = dc.search(sim, ap, qp)[0]
+	dc.set_shard(None, 0)                     # score_all and the local lists are per rank
+	parity = sharded_parity(dc, sim, ap, qp, check_hits, rank, world, doc_lo)
+	if world > 1:
+		dc.set_shard(comm, doc_lo)
+	sim.close()
 
 	wall_s = t1 - t0
 	times = torch.tensor([wall_s, dev_ms_total / 1e3, dp_ms_total / 1e3], dtype=torch.float64, device="cuda")
@@ -312,14 +388,16 @@ def main():
 		line = {
 			"metric": "sentences/sec (WSB alignment, 12-token query, top-100)",
 			"value": value, "unit": "sentences/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-			"ms_per_step": dev_s * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak",
+			"ms_per_step": dev_s * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak" if args.weak else "strong",
 			"vs_baseline": None, "dtype": "f32", "data": "synthetic",
 			"config": {"workload": workload_name(args), "l2": "inputs larger than L2 (token tiles %.1f GB per GPU)" % (4.0 * dc.n_cells / 1e9),
-				"queries": f"{N_QUERIES} distinct queries in rotation", "parallelism": f"sentence shards x{world}, top-k all-gather"},
+				"queries": f"{N_QUERIES} distinct queries in rotation", "parallelism": f"sentence shards x{world}, one NCCL all-gather of the k result rows + device merge inside vx_search" if world > 1 else "1 GPU"},
+			"sharded_parity": parity,
+			"value_includes": "device time (CUDA events) of similarity build + DP + top-k + traceback" + (" + all-gather + merge" if world > 1 else ""),
 			"gcups": n_cells * T_QUERY * args.steps / dev_s / 1e9,
 			"e2e": {"value": e2e, "unit": "sentences/s",
 				"h2d_bytes_per_step": int(T_QUERY * 4 + T_QUERY * DIM * 4 + (dc.max_len + 1 + T_QUERY + 1) * 4),
-				"d2h_bytes_per_step": int(TOPK * (16 + 6 * T_QUERY) + 16), "ms_per_step": wall_s * 1e3 / args.steps},
+				"d2h_bytes_per_step": int(TOPK * (24 + 6 * T_QUERY) + 16), "ms_per_step": wall_s * 1e3 / args.steps},
 			"gpu_launches": int(launches_all),
 			# for the static-embedding configs the binding roofline of the DP kernel is FP32 issue
 			# (achieved = algorithmic FP32 add / max operations per second, peak = SMs x 128 lanes x clock); the HBM view of the
@@ -333,7 +411,7 @@ def main():
 				"note": "not HBM-bound and no tensor-core work: HBM view in hbm_roofline"},
 			"hbm_roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
 				"traffic": traffic, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src},
-			"phases_ms": {k: v for k, v in dc.last_timing().items()},
+			"phases_ms": dict({k: v for k, v in dc.last_timing().items()}, gather_merge_ms_mean=gather_ms_total / args.steps),
 			"setup_s": setup_s,
 			"top_score": float(last_hits["score"][0]) if len(last_hits) else None,
 		}

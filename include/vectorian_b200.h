@@ -89,10 +89,14 @@ typedef struct {
 typedef struct vx_corpus vx_corpus;   /* packed device corpus: replaces core.Document[] + Spans (cpp/document.h) */
 typedef struct vx_embedding vx_embedding; /* replaces StaticEmbedding / Vectors (cpp/embedding/static.h) */
 typedef struct vx_sim vx_sim;         /* replaces SimilarityMatrix (cpp/metric/metric.h:9-52) */
+typedef struct vx_comm vx_comm;       /* ranks of a sentence-sharded corpus; replaces the document thread pool's shared
+                                         ResultSet (vectorian/index.py:544-555) */
 
 /* ---- library ---- */
 
-/* Select the CUDA device for this process (one process per GPU). Fails loudly without sm_100. */
+/* Select the CUDA device for this process.  ONE process drives ONE device: the library keeps per-process state
+ * (device index, SM count, kernel attributes, buffer pool) and is not meant to be re-initialised for a second GPU.
+ * Fails loudly without sm_100. */
 int vx_init(int device);
 const char *vx_last_error(void);
 const char *vx_build_info(void);      /* replaces backend_build_time (cpp/module.cpp:20-22) */
@@ -224,6 +228,31 @@ int vx_search_topk_noalloc(
 	vx_corpus *c, const vx_sim *s,
 	const vx_align_params *ap, const vx_query_params *qp,
 	vx_hit *hits, int32_t *n_hits);
+
+/* ---- sentence shards over the GPUs of one box: replaces the fan-out over documents + ResultSet::extend
+ *      (vectorian/index.py:544-555, cpp/result_set.h:70-93, cpp/result_set.cpp:3-21) ----
+ * One process per GPU; each rank holds a contiguous range of documents in its own vx_corpus.  With a communicator
+ * attached, vx_search and vx_search_batch return the GLOBAL result on every rank: the per-rank result rows stay on
+ * the device, ONE NCCL all-gather on the corpus stream collects them (k x (24 + 6T) bytes per rank and pair), one
+ * kernel merges them under (score desc, doc desc, slice desc), k rows are copied to the host.  Every rank must make
+ * the same calls in the same order (they are collectives).  NCCL is bound at run time (dlopen of libnccl.so.2). */
+
+/* rank 0: a fresh 128-byte NCCL unique id, to be handed to every rank by the host's own channel */
+int vx_comm_unique_id(uint8_t *id128);
+/* collective over all ranks of the job */
+int vx_comm_create(const uint8_t *id128, int32_t world, int32_t rank, vx_comm **out);
+int vx_comm_destroy(vx_comm *m);
+/* this corpus is the shard of rank `rank` of m; doc_offset = global id of its first document.  m == NULL detaches. */
+int vx_corpus_set_shard(vx_corpus *c, vx_comm *m, int32_t doc_offset);
+/* device time (CUDA events) of the all-gather + merge of the last search on this corpus, in ms */
+float vx_last_gather_ms(const vx_corpus *c);
+
+/* Layout of one result block of k rows for a query of t tokens (what the ranks exchange): byte offsets of
+ * score[k] f32, score_max[k] f32, win[k] u32, doc[k] i32, slice[k] i32, target[k x t] i16, dist[k x t] f32, n i32;
+ * returns the block size.  Test hook: vx_debug_merge merges `world` such blocks (host memory, back to back) with the
+ * device merge kernel of the sharded search, no communicator needed. */
+int64_t vx_res_block_bytes(int32_t t, int32_t k, int64_t *offsets8);
+int vx_debug_merge(const uint8_t *blocks, int32_t world, int32_t t, int32_t k, uint8_t *merged_out);
 
 /* Score every window (debug hook "alignment" / tests): score[n_windows] in window order, 0-filled where len<1. */
 int vx_score_all(

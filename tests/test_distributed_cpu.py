@@ -42,13 +42,8 @@ def _worker(rank, world, port, k, t, out_dir):
 	# several searches (a sweep's pairs, queries of different lengths) in one collective
 	import vectorian_b200.distributed as vd
 	rows = [_rank_rows(rank, n_local, tt, k_seed=10 * i) for i, tt in enumerate((t, 3, t))]
-	many = gather_topk_many(rows, k, doc_offset=rank * 5)          # few rows: merged on the host
-	vd.HOST_MERGE_ROWS = 0
-	many_dev = gather_topk_many(rows, k, doc_offset=rank * 5)      # the torch merge (on the GPU under NCCL)
-	for g0, g1 in zip(many, many_dev):
-		for x0, x1 in zip(g0, g1):
-			np.testing.assert_array_equal(x0, x1)
-	# the unsplit arrays of a batched search (engine.search_batch(raw=True)) take the vectorised packing
+	many = gather_topk_many(rows, k, doc_offset=rank * 5)
+	# the unsplit arrays of a batched search (engine.search_batch(raw=True)) give the same answer
 	rows3 = [_rank_rows(rank, n_local, t, k_seed=10 * i) for i in range(3)]
 	kk = 8
 	hits = np.zeros((3, kk), dtype=HIT_DTYPE)
@@ -56,13 +51,11 @@ def _worker(rank, world, port, k, t, out_dir):
 	distance = np.ones((3, kk, t), dtype=np.float32)
 	for i, (h, tg, ds) in enumerate(rows3):
 		hits[i, :len(h)], target[i, :len(h)], distance[i, :len(h)] = h, tg, ds
-	for limit in (1 << 20, 0):
-		vd.HOST_MERGE_ROWS = limit
-		want = gather_topk_many(rows3, kk, doc_offset=rank * 5)
-		got = gather_topk_many(vd.BatchRows(hits, target, distance, [len(r[0]) for r in rows3], [t] * 3), kk, doc_offset=rank * 5)
-		for g0, g1 in zip(want, got):
-			for x0, x1 in zip(g0, g1):
-				np.testing.assert_array_equal(x0, x1)
+	want = gather_topk_many(rows3, kk, doc_offset=rank * 5)
+	got = gather_topk_many(vd.BatchRows(hits, target, distance, [len(r[0]) for r in rows3], [t] * 3), kk, doc_offset=rank * 5)
+	for g0, g1 in zip(want, got):
+		for x0, x1 in zip(g0, g1):
+			np.testing.assert_array_equal(x0, x1)
 	np.savez(os.path.join(out_dir, f"m{rank}.npz"), **{f"{name}{i}": g[j] for i, g in enumerate(many) for j, name in enumerate(("hits", "target", "distance"))})
 	dist.destroy_process_group()
 

@@ -163,6 +163,13 @@ _SIGNATURES = {
 		C.c_void_p, C.c_void_p, C.POINTER(AlignParams), C.POINTER(QueryParams),
 		c_float_p, C.c_int64]),
 	"vx_abort": (C.c_int, [C.c_void_p]),
+	"vx_comm_unique_id": (C.c_int, [C.c_void_p]),
+	"vx_comm_create": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+	"vx_comm_destroy": (C.c_int, [C.c_void_p]),
+	"vx_corpus_set_shard": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32]),
+	"vx_last_gather_ms": (C.c_float, [C.c_void_p]),
+	"vx_res_block_bytes": (C.c_int64, [C.c_int32, C.c_int32, c_int64_p]),
+	"vx_debug_merge": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
 	"vx_last_timing": (C.c_int, [C.c_void_p, c_float_p]),
 	"vx_last_launches": (C.c_int, [C.c_void_p]),
 	"vx_debug_ctx_sim": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,

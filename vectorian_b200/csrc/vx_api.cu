@@ -3,6 +3,8 @@
 
 #include <algorithm>
 #include <cmath>
+#include <climits>
+#include <cstdint>
 #include <cstring>
 
 static thread_local std::string g_error;
@@ -99,6 +101,10 @@ static void corpus_free(vx_corpus *c) {
 	cudaFree(c->d_topk_multi);
 	cudaFree(c->d_scratch);
 	cudaFree(c->d_counters);
+	cudaFree(c->d_win_doc);
+	cudaFree(c->d_win_slice);
+	cudaFree(c->d_res);
+	cudaFree(c->d_gather);
 	if (c->h_res) {
 		cudaFreeHost(c->h_res);
 	}
@@ -292,6 +298,10 @@ static int corpus_create_impl(
 			if ((rc = dev_alloc(&c->d_pos, (size_t)c->n_tok_tiled)) != VX_OK) break;
 		}
 		if ((rc = dev_alloc(&c->d_score, (size_t)c->n_slots)) != VX_OK) break;
+		if ((rc = dev_alloc(&c->d_win_doc, (size_t)c->n_win)) != VX_OK) break;
+		if ((rc = dev_alloc(&c->d_win_slice, (size_t)c->n_win)) != VX_OK) break;
+		cudaMemcpyAsync(c->d_win_doc, c->win_doc.data(), sizeof(int32_t) * (size_t)c->n_win, cudaMemcpyHostToDevice, c->stream);
+		cudaMemcpyAsync(c->d_win_slice, c->win_slice.data(), sizeof(int32_t) * (size_t)c->n_win, cudaMemcpyHostToDevice, c->stream);
 		{
 			unsigned int *ctr = nullptr;
 			if ((rc = dev_alloc(&ctr, 16)) != VX_OK) break;
@@ -302,11 +312,27 @@ static int corpus_create_impl(
 		cudaMemcpyAsync(c->d_orig, orig.data(), sizeof(uint32_t) * (size_t)c->n_slots, cudaMemcpyHostToDevice, c->stream);
 		cudaMemcpyAsync(c->d_slot_of, slot_of.data(), sizeof(uint32_t) * (size_t)c->n_win, cudaMemcpyHostToDevice, c->stream);
 		vx_launch_pack(d_tok_raw, d_pos_raw, d_win_tok, c->d_tiles, c->d_orig, c->n_tiles, c->d_tok, c->d_pos, c->stream);
+		int32_t h_minmax[2] = {0, -1};
+		if (on_device && n_tok > 0) {
+			// the host path scans the ids above; a device-resident corpus gets the same bounds check from a reduction,
+			// so that make_plan can reject a similarity matrix with too few rows instead of gathering out of bounds
+			int32_t *d_mm = (int32_t*)c->d_counters;   // 16 words, rewritten by every search
+			vx_launch_minmax(d_tok_raw, n_tok, d_mm, c->stream);
+			cudaMemcpyAsync(h_minmax, d_mm, sizeof(h_minmax), cudaMemcpyDeviceToHost, c->stream);
+		}
 		cudaError_t e = cudaStreamSynchronize(c->stream);
 		if (e != cudaSuccess) {
 			vx_set_error(std::string("corpus pack failed: ") + cudaGetErrorString(e));
 			rc = VX_ERR_CUDA;
 			break;
+		}
+		if (on_device && n_tok > 0) {
+			if (h_minmax[0] < 0) {
+				vx_set_error("negative token id in corpus");
+				rc = VX_ERR_INVALID;
+				break;
+			}
+			c->max_token_id = h_minmax[1];
 		}
 		// keep the window -> token offsets for later vx_corpus_set_contextual calls
 		c->win_tok.swap(hw.tok);
@@ -390,6 +416,9 @@ extern "C" int vx_corpus_set_contextual(vx_corpus *c, const float *x, int64_t n_
 	}
 	if (n_tok != c->n_tok_raw) {
 		VX_FAIL(VX_ERR_INVALID, "contextual vectors must have one row per corpus token");
+	}
+	if (c->n_tok_tiled > (int64_t)INT32_MAX) {
+		VX_FAIL(VX_ERR_INVALID, "more than 2^31 tiled token positions per GPU with contextual vectors: shard the corpus");
 	}
 	float *d_raw = nullptr, *d_norm = nullptr;
 	int64_t *d_win_tok = nullptr;
@@ -680,6 +709,9 @@ extern "C" int vx_sim_upload_tokens(vx_corpus *c, const float *s_tok, int64_t n_
 	}
 	if (n_tok != c->n_tok_raw) {
 		VX_FAIL(VX_ERR_INVALID, "per-token similarity matrix must have one row per corpus token");
+	}
+	if (c->n_tok_tiled > (int64_t)INT32_MAX) {
+		VX_FAIL(VX_ERR_INVALID, "more than 2^31 tiled token positions per GPU with a per-token similarity matrix: shard the corpus");
 	}
 	cudaSetDevice(c->device);
 	vx_sim *s = new vx_sim();

@@ -3,6 +3,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -90,7 +91,17 @@ struct vx_corpus {
 	size_t scratch_bytes = 0;
 	void *h_res = nullptr;           // pinned host mirror of the result block
 	size_t h_res_bytes = 0;
-	int32_t max_token_id = -1;       // -1 = unknown (corpus created from device memory)
+	int32_t max_token_id = -1;       // largest token id (host scan, or a device reduction for vx_corpus_create_dev)
+	int32_t *d_win_doc = nullptr;    // window index -> document id (local to this corpus) / slice id, for the k winners
+	int32_t *d_win_slice = nullptr;
+	// sentence shard of a multi-GPU corpus (vx_corpus_set_shard): results of vx_search / vx_search_batch are
+	// all-gathered over `comm` on `stream` and merged on the device, document ids made global with doc_offset
+	struct vx_comm *comm = nullptr;
+	int32_t doc_offset = 0;
+	uint8_t *d_res = nullptr;        // result blocks of the running call, back to back (the all-gather's send buffer)
+	size_t res_bytes = 0;
+	uint8_t *d_gather = nullptr;     // [world x res bytes] gathered blocks | [res bytes] merged blocks
+	size_t gather_bytes = 0;
 	// tiles are sorted by descending length: class_first[i] = first tile whose windows are <= 4*i long
 	// (class_first[0] = n_tiles); the WSB kernel is launched once per run of classes with equal occupancy
 	int64_t class_first[VX_N_CLASS + 1] = {0};
@@ -100,10 +111,10 @@ struct vx_corpus {
 	cudaStream_t select_stream = nullptr;            // vx_search_batch: top-k + traceback of one group while the next group's DP runs
 	cudaEvent_t ev_dp[2] = {nullptr, nullptr};       // DP of score buffer b finished (main stream)
 	cudaEvent_t ev_sel[2] = {nullptr, nullptr};      // selects over score buffer b finished (select stream)
-	cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-	float last_ms[3] = {0, 0, 0};
+	cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // phase marks: DP, top-k, traceback, end | gather begin, end
+	float last_ms[4] = {0, 0, 0, 0};   // DP, top-k, traceback, all-gather + merge
 	int last_launches = 0;
-	volatile int aborted = 0;
+	std::atomic<int> aborted{0};     // vx_abort (any thread) -> consumed by the searching thread with exchange(0)
 };
 
 struct vx_embedding {
@@ -186,6 +197,8 @@ struct VxTraceOut {
 	int16_t *target;    // [n x t]
 	float *dist;        // [n x t]
 	uint32_t *win;      // [n] window index of each item
+	int32_t *doc;       // [n] global document id = win_doc[win] + doc_offset (nullptr: not wanted)
+	int32_t *slice;     // [n] slice id
 };
 int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp,
 	const uint32_t *d_slots, int64_t slot_base, const int32_t *d_n_items, int32_t max_items, VxTraceOut out);
@@ -218,6 +231,40 @@ int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *
 int vx_launch_ctx_sim(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, int32_t t, int32_t tp,
 	float *d_sdoc, cudaStream_t st);
 int vx_launch_iota(int32_t *d_out, int64_t n, cudaStream_t st);
+
+// vx_shard.cu -- NCCL communicator (dlopen'ed libnccl) + merge of the gathered per-rank result blocks
+struct vx_comm;
+// offsets of the arrays inside one result block of k rows for a query of t tokens
+struct VxResLayout {
+	size_t off_score, off_score_max, off_win, off_doc, off_slice, off_target, off_dist, off_n, bytes;
+};
+__host__ __device__ inline VxResLayout vx_res_layout(int32_t t, int32_t k) {
+	VxResLayout b;
+	const size_t tt = (size_t)(t > 1 ? t : 1), kk = (size_t)k;
+	size_t r = 0;
+	b.off_score = r;      r = (r + 4 * kk + 15) & ~(size_t)15;
+	b.off_score_max = r;  r = (r + 4 * kk + 15) & ~(size_t)15;
+	b.off_win = r;        r = (r + 4 * kk + 15) & ~(size_t)15;
+	b.off_doc = r;        r = (r + 4 * kk + 15) & ~(size_t)15;
+	b.off_slice = r;      r = (r + 4 * kk + 15) & ~(size_t)15;
+	b.off_target = r;     r = (r + 2 * kk * tt + 15) & ~(size_t)15;
+	b.off_dist = r;       r = (r + 4 * kk * tt + 15) & ~(size_t)15;
+	b.off_n = r;          r = (r + 4 + 15) & ~(size_t)15;
+	b.bytes = (r + 255) & ~(size_t)255;
+	return b;
+}
+struct VxPairDesc {
+	uint64_t off;     // byte offset of the pair's result block inside a rank's buffer
+	int32_t t;        // query length of the pair
+	int32_t pad;
+};
+int vx_comm_world(const vx_comm *m);
+// all-gather `bytes` per rank from `send` into `recv` [world x bytes] on stream st; returns VX_OK or an error
+int vx_comm_all_gather(vx_comm *m, const void *send, void *recv, size_t bytes, cudaStream_t st);
+// merge the gathered blocks of n_pairs pairs (descs: device array, or nullptr with `one` for a single pair)
+int vx_launch_merge(const uint8_t *d_gathered, size_t rank_stride, int world, uint8_t *d_merged,
+	const VxPairDesc *d_descs, VxPairDesc one, int n_pairs, int32_t k, cudaStream_t st);
+int vx_launch_minmax(const int32_t *d_tok, int64_t n, int32_t *d_out2, cudaStream_t st);
 
 // vx_pack.cu
 int vx_launch_pack(const int32_t *d_tok_raw, const int8_t *d_pos_raw, const int64_t *d_win_tok,

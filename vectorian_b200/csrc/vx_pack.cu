@@ -5,6 +5,8 @@
 // tag-weighted similarity) reach the DP, so those are all that is kept on the device.
 #include "vx_internal.cuh"
 
+#include <cstdint>
+
 // One warp per tile.  Lane l owns window orig[tile*32+l]; the warp walks the quads of the tile and
 // writes 32 x (4 elements) contiguously per quad (512 bytes of ids, 128 bytes of POS tags).
 template<typename T>
@@ -97,4 +99,37 @@ int vx_launch_unpermute(const float *d_score, const uint32_t *d_slot_of, int64_t
 	}
 	unpermute_kernel<<<(unsigned)((n_win + 255) / 256), 256, 0, st>>>(d_score, d_slot_of, n_win, d_out);
 	return 1;
+}
+
+// min / max of the token ids of a device-resident corpus: out2[0] = min, out2[1] = max
+__global__ void minmax_init_kernel(int32_t *out2) {
+	out2[0] = INT32_MAX;
+	out2[1] = INT32_MIN;
+}
+
+__global__ void __launch_bounds__(256) minmax_kernel(const int32_t *__restrict__ tok, int64_t n, int32_t *out2) {
+	int32_t lo = INT32_MAX, hi = INT32_MIN;
+	for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+		const int32_t x = tok[i];
+		lo = x < lo ? x : lo;
+		hi = x > hi ? x : hi;
+	}
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		const int32_t l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+		lo = l2 < lo ? l2 : lo;
+		hi = h2 > hi ? h2 : hi;
+	}
+	if ((threadIdx.x & 31) == 0) {
+		atomicMin(out2, lo);
+		atomicMax(out2 + 1, hi);
+	}
+}
+
+int vx_launch_minmax(const int32_t *d_tok, int64_t n, int32_t *d_out2, cudaStream_t st) {
+	minmax_init_kernel<<<1, 1, 0, st>>>(d_out2);
+	int64_t blocks = (n + 255) / 256;
+	blocks = blocks > 148 * 16 ? 148 * 16 : blocks < 1 ? 1 : blocks;
+	minmax_kernel<<<(unsigned)blocks, 256, 0, st>>>(d_tok, n, d_out2);
+	return 2;
 }

@@ -33,16 +33,17 @@ struct QueryPlan {
 	uint8_t *res;
 	uint8_t *h_res;      // pinned host copy of the result block
 	size_t res_bytes;
-	size_t off_score, off_score_max, off_win, off_target, off_dist, off_n;
+	size_t res_off;      // offset of the result block inside c->d_res / c->h_res
+	size_t off_score, off_score_max, off_win, off_doc, off_slice, off_target, off_dist, off_n;
 };
 
-// device block of one plan: gap tables, tag weights, result rows
+// device block of the per-query constants of one plan (gap tables, tag weights); the result rows of a plan live in
+// c->d_res (vx_res_layout), all plans of a call back to back: that buffer is what a sharded corpus all-gathers
 struct BlockLayout {
-	size_t off_gs, off_gt, off_tw, off_tpos, off_res, bytes;
-	size_t off_score, off_score_max, off_win, off_target, off_dist, off_n, res_bytes;
+	size_t off_gs, off_gt, off_tw, off_tpos, bytes;
 };
 
-static BlockLayout block_layout(int32_t t, int32_t k, size_t n_ws, size_t n_wt) {
+static BlockLayout block_layout(int32_t t, size_t n_ws, size_t n_wt) {
 	BlockLayout b;
 	const size_t tt = (size_t)std::max(t, 1);
 	size_t off = 0;
@@ -54,28 +55,13 @@ static BlockLayout block_layout(int32_t t, int32_t k, size_t n_ws, size_t n_wt) 
 	off = align_up(off + sizeof(float) * tt, 256);
 	b.off_tpos = off;
 	off = align_up(off + tt, 256);
-	b.off_res = off;
-	size_t r = 0;
-	b.off_score = r;
-	r = align_up(r + sizeof(float) * k, 16);
-	b.off_score_max = r;
-	r = align_up(r + sizeof(float) * k, 16);
-	b.off_win = r;
-	r = align_up(r + sizeof(uint32_t) * k, 16);
-	b.off_target = r;
-	r = align_up(r + sizeof(int16_t) * (size_t)k * tt, 16);
-	b.off_dist = r;
-	r = align_up(r + sizeof(float) * (size_t)k * tt, 16);
-	b.off_n = r;
-	r = align_up(r + sizeof(int32_t), 16);
-	b.res_bytes = r;
-	b.bytes = align_up(off + r, 256);
+	b.bytes = off;
 	return b;
 }
 
 // position of one (query, setting) pair of vx_search_batch inside the shared work / pinned host buffers
 struct BatchSlot {
-	size_t work_off, host_off;
+	size_t work_off, res_off;
 };
 
 static int ensure_work(vx_corpus *c, size_t bytes) {
@@ -101,6 +87,31 @@ static int ensure_host(vx_corpus *c, size_t bytes) {
 	c->h_res_bytes = 0;
 	VX_CUDA(cudaMallocHost(&c->h_res, bytes));
 	c->h_res_bytes = bytes;
+	return VX_OK;
+}
+
+static int ensure_res(vx_corpus *c, size_t bytes) {
+	if (c->res_bytes >= bytes) {
+		return VX_OK;
+	}
+	cudaFree(c->d_res);
+	c->d_res = nullptr;
+	c->res_bytes = 0;
+	VX_CUDA(cudaMalloc((void**)&c->d_res, bytes));
+	c->res_bytes = bytes;
+	return VX_OK;
+}
+
+// [world x bytes] gathered blocks | [bytes] merged blocks | pair descriptors
+static int ensure_gather(vx_corpus *c, size_t bytes) {
+	if (c->gather_bytes >= bytes) {
+		return VX_OK;
+	}
+	cudaFree(c->d_gather);
+	c->d_gather = nullptr;
+	c->gather_bytes = 0;
+	VX_CUDA(cudaMalloc((void**)&c->d_gather, bytes));
+	c->gather_bytes = bytes;
 	return VX_OK;
 }
 
@@ -169,18 +180,23 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 	// ---- workspace layout: [top-k area | block of plan 0 | block of plan 1 | ...] ----
 	const size_t n_ws = ap->gap_kind == VX_GAP_GENERAL ? (size_t)ap->n_w_s : 0;
 	const size_t n_wt = ap->gap_kind == VX_GAP_GENERAL ? (size_t)ap->n_w_t : 0;
-	const BlockLayout bl = block_layout(t, p->k, n_ws, n_wt);
-	p->off_score = bl.off_score;
-	p->off_score_max = bl.off_score_max;
-	p->off_win = bl.off_win;
-	p->off_target = bl.off_target;
-	p->off_dist = bl.off_dist;
-	p->off_n = bl.off_n;
-	p->res_bytes = bl.res_bytes;
+	const BlockLayout bl = block_layout(t, n_ws, n_wt);
+	const VxResLayout rl = vx_res_layout(t, p->k);
+	p->off_score = rl.off_score;
+	p->off_score_max = rl.off_score_max;
+	p->off_win = rl.off_win;
+	p->off_doc = rl.off_doc;
+	p->off_slice = rl.off_slice;
+	p->off_target = rl.off_target;
+	p->off_dist = rl.off_dist;
+	p->off_n = rl.off_n;
+	p->res_bytes = rl.bytes;
+	p->res_off = batch ? batch->res_off : 0;
 	const size_t topk_bytes = align_up(vx_topk_work_bytes(p->k), 256);
 	if (!batch) {
 		VX_TRY(ensure_work(c, topk_bytes + bl.bytes));
-		VX_TRY(ensure_host(c, bl.res_bytes));
+		VX_TRY(ensure_res(c, rl.bytes));
+		VX_TRY(ensure_host(c, rl.bytes));
 	}
 	uint8_t *w = (uint8_t*)c->d_work;
 	p->topk = w;
@@ -189,8 +205,8 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 	p->gap_t = (float*)(w + bl.off_gt);
 	p->tw = (float*)(w + bl.off_tw);
 	p->tpos = (int8_t*)(w + bl.off_tpos);
-	p->res = w + bl.off_res;
-	p->h_res = (uint8_t*)c->h_res + (batch ? batch->host_off : 0);
+	p->res = c->d_res + p->res_off;
+	p->h_res = (uint8_t*)c->h_res + p->res_off;
 
 	// ---- per-query constants ----
 	VxAlignDev &a = p->ap;
@@ -321,7 +337,7 @@ static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 	chunk = chunk / 32 * 32;
 	int launches = 0;
 	for (int64_t base = 0; base < c->n_slots; base += chunk) {
-		if (c->aborted) {
+		if (c->aborted.load()) {
 			break;
 		}
 		const int32_t n = (int32_t)std::min<int64_t>(chunk, c->n_slots - base);
@@ -333,6 +349,46 @@ static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 		launches += rc;
 	}
 	return launches;
+}
+
+// where the traceback kernels put the rows of plan p
+static VxTraceOut plan_out(const QueryPlan &p) {
+	VxTraceOut out;
+	out.score = (float*)(p.res + p.off_score);
+	out.score_max = (float*)(p.res + p.off_score_max);
+	out.win = (uint32_t*)(p.res + p.off_win);
+	out.doc = (int32_t*)(p.res + p.off_doc);
+	out.slice = (int32_t*)(p.res + p.off_slice);
+	out.target = (int16_t*)(p.res + p.off_target);
+	out.dist = (float*)(p.res + p.off_dist);
+	return out;
+}
+
+// Sentence shards (vx_corpus_set_shard): all-gather the result blocks of this call (c->d_res[0, bytes), identical
+// layout on every rank) on the corpus stream, merge them per pair on the device and copy the merged blocks to the
+// pinned host mirror.  Replaces ResultSet::extend across the reference's per-document result sets
+// (vectorian/index.py:551-555, cpp/result_set.h:70-93).  Nothing here waits for the device.
+static int enqueue_gather_merge(vx_corpus *c, size_t bytes, const std::vector<VxPairDesc> &descs, int32_t k) {
+	const int world = vx_comm_world(c->comm);
+	const size_t desc_bytes = align_up(sizeof(VxPairDesc) * descs.size(), 256);
+	VX_TRY(ensure_gather(c, (size_t)(world + 1) * bytes + desc_bytes));
+	cudaStream_t st = c->stream;
+	cudaEventRecord(c->ev[4], st);
+	VX_TRY(vx_comm_all_gather(c->comm, c->d_res, c->d_gather, bytes, st));
+	uint8_t *merged = c->d_gather + (size_t)world * bytes;
+	const VxPairDesc *d_descs = nullptr;
+	if (descs.size() > 1) {
+		d_descs = (const VxPairDesc*)(merged + bytes);
+		cudaMemcpyAsync((void*)d_descs, descs.data(), sizeof(VxPairDesc) * descs.size(), cudaMemcpyHostToDevice, st);
+	}
+	const int n = vx_launch_merge(c->d_gather, bytes, world, merged, d_descs, descs[0], (int)descs.size(), k, st);
+	if (n < 0) {
+		return VX_ERR_CUDA;
+	}
+	c->last_launches += n;
+	cudaEventRecord(c->ev[5], st);
+	cudaMemcpyAsync(c->h_res, merged, bytes, cudaMemcpyDeviceToHost, st);
+	return VX_OK;
 }
 
 // Enqueue one query: scores of every slot, top-k, traceback of the winners, result block to pinned host memory.
@@ -360,8 +416,7 @@ static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, boo
 	if (phase_events) {
 		cudaEventRecord(c->ev[1], st);
 	}
-	if (c->aborted) {
-		c->aborted = 0;
+	if (c->aborted.exchange(0)) {
 		cudaStreamSynchronize(st);
 		VX_FAIL(VX_ERR_ABORTED, "query aborted");
 	}
@@ -383,12 +438,7 @@ static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, con
 		cudaEventRecord(c->ev[2], st);
 	}
 
-	VxTraceOut out;
-	out.score = (float*)(p.res + p.off_score);
-	out.score_max = (float*)(p.res + p.off_score_max);
-	out.win = (uint32_t*)(p.res + p.off_win);
-	out.target = (int16_t*)(p.res + p.off_target);
-	out.dist = (float*)(p.res + p.off_dist);
+	VxTraceOut out = plan_out(p);
 	n = vx_launch_trace(c, s, p.ap, p.qp, tk.slots, 0, tk.n, p.k, out);
 	if (n < 0) {
 		return VX_ERR_CUDA;
@@ -398,27 +448,29 @@ static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, con
 	if (phase_events) {
 		cudaEventRecord(c->ev[3], st);
 	}
-	cudaMemcpyAsync(p.h_res, p.res, p.res_bytes, cudaMemcpyDeviceToHost, st);
+	if (!c->comm) {
+		cudaMemcpyAsync(p.h_res, p.res, p.res_bytes, cudaMemcpyDeviceToHost, st);   // sharded: after the gather + merge
+	}
 	return VX_OK;
 }
 
 // hits / target / dist rows of one finished query from its pinned result block
-static void unpack_results(const vx_corpus *c, const QueryPlan &p, vx_hit *hits, int16_t *target, float *dist,
+static void unpack_results(const QueryPlan &p, vx_hit *hits, int16_t *target, float *dist,
 	int32_t *n_hits, int32_t t_stride) {
 
 	const uint8_t *h = p.h_res;
 	const int32_t found = *(const int32_t*)(h + p.off_n);
 	const float *h_score = (const float*)(h + p.off_score);
 	const float *h_score_max = (const float*)(h + p.off_score_max);
-	const uint32_t *h_win = (const uint32_t*)(h + p.off_win);
+	const int32_t *h_doc = (const int32_t*)(h + p.off_doc);
+	const int32_t *h_slice = (const int32_t*)(h + p.off_slice);
 	const int16_t *h_target = (const int16_t*)(h + p.off_target);
 	const float *h_dist = (const float*)(h + p.off_dist);
 	for (int32_t i = 0; i < found; i++) {
-		const uint32_t w = h_win[i];
 		hits[i].score = h_score[i];
 		hits[i].score_max = h_score_max[i];
-		hits[i].doc = c->win_doc[w];
-		hits[i].slice = c->win_slice[w];
+		hits[i].doc = h_doc[i];        // global document id (window table + shard offset, written by the traceback kernel)
+		hits[i].slice = h_slice[i];
 		memcpy(target + (size_t)i * t_stride, h_target + (size_t)i * p.t, sizeof(int16_t) * p.t);
 		memcpy(dist + (size_t)i * t_stride, h_dist + (size_t)i * p.t, sizeof(float) * p.t);
 	}
@@ -439,20 +491,33 @@ extern "C" int vx_search(
 	VX_TRY(make_plan(c, s, ap, qp, true, &p));
 	c->sdoc_of = nullptr;   // a new vx_sim may reuse the address of a destroyed one: never trust a stale S_doc
 	c->last_launches = 0;
-	c->last_ms[0] = c->last_ms[1] = c->last_ms[2] = 0.0f;
-	if (p.t < 1 || c->n_win == 0) {
-		return VX_OK;   // no matches (cpp/match/matcher_impl.h:80-83; vectorian/index.py:533-534)
-	}
+	c->last_ms[0] = c->last_ms[1] = c->last_ms[2] = c->last_ms[3] = 0.0f;
+	c->last_ms[3] = 0.0f;
 	if (!hits || !target || !dist) {
 		VX_FAIL(VX_ERR_INVALID, "output arrays are NULL");
 	}
-	if (c->aborted) {
-		c->aborted = 0;
+	if (p.t < 1 || (c->n_win == 0 && !c->comm)) {
+		return VX_OK;   // no matches (cpp/match/matcher_impl.h:80-83; vectorian/index.py:533-534); t is the same on every rank
+	}
+	if (c->n_win == 0) {
+		// an empty shard still takes part in the collective: an empty result block
+		cudaMemsetAsync(p.res + p.off_n, 0, sizeof(int32_t), c->stream);
+		VX_TRY(enqueue_gather_merge(c, p.res_bytes, std::vector<VxPairDesc>(1, VxPairDesc{0, p.t, 0}), p.k));
+		if (cudaStreamSynchronize(c->stream) != cudaSuccess) {
+			VX_FAIL(VX_ERR_CUDA, "sharded search failed");
+		}
+		unpack_results(p, hits, target, dist, n_hits, p.t);
+		return VX_OK;
+	}
+	if (c->aborted.exchange(0)) {
 		VX_FAIL(VX_ERR_ABORTED, "query aborted");
 	}
 
 	cudaEventRecord(c->ev[0], c->stream);
 	VX_TRY(enqueue_search(c, s, p, true));
+	if (c->comm) {
+		VX_TRY(enqueue_gather_merge(c, p.res_bytes, std::vector<VxPairDesc>(1, VxPairDesc{0, p.t, 0}), p.k));
+	}
 	cudaError_t e = cudaStreamSynchronize(c->stream);
 	if (e != cudaSuccess) {
 		vx_set_error(std::string("search failed: ") + cudaGetErrorString(e));
@@ -461,7 +526,10 @@ extern "C" int vx_search(
 	for (int i = 0; i < 3; i++) {
 		cudaEventElapsedTime(&c->last_ms[i], c->ev[i], c->ev[i + 1]);
 	}
-	unpack_results(c, p, hits, target, dist, n_hits, p.t);
+	if (c->comm) {
+		cudaEventElapsedTime(&c->last_ms[3], c->ev[4], c->ev[5]);   // all-gather + merge
+	}
+	unpack_results(p, hits, target, dist, n_hits, p.t);
 	return VX_OK;
 }
 
@@ -494,6 +562,7 @@ extern "C" int vx_search_batch(
 	const int32_t k = qp->max_matches;
 	// buffer positions of every pair, then one allocation
 	std::vector<BatchSlot> slots(n_pairs);
+	std::vector<VxPairDesc> descs(n_pairs);
 	size_t work = 0, host = 0;
 	for (int32_t q = 0; q < n_sims; q++) {
 		if (!sims[q]) {
@@ -504,20 +573,25 @@ extern "C" int vx_search_batch(
 		}
 		for (int32_t ai = 0; ai < n_aps; ai++) {
 			const bool gen = aps[ai].gap_kind == VX_GAP_GENERAL;
-			const BlockLayout bl = block_layout(sims[q]->t, k, gen ? (size_t)std::max(aps[ai].n_w_s, 0) : 0,
+			const BlockLayout bl = block_layout(sims[q]->t, gen ? (size_t)std::max(aps[ai].n_w_s, 0) : 0,
 				gen ? (size_t)std::max(aps[ai].n_w_t, 0) : 0);
 			slots[(size_t)q * n_aps + ai] = BatchSlot{work, host};
+			descs[(size_t)q * n_aps + ai] = VxPairDesc{(uint64_t)host, sims[q]->t, 0};
 			work += bl.bytes;
-			host += align_up(bl.res_bytes, 256);
+			host += vx_res_layout(sims[q]->t, k).bytes;
 		}
 	}
 	VX_TRY(ensure_work(c, align_up(vx_topk_work_bytes(k), 256) + work));
+	VX_TRY(ensure_res(c, host));
 	VX_TRY(ensure_host(c, host));
+	if (c->comm) {
+		// pairs that launch nothing (empty query, empty shard) still ship a block: zero rows
+		cudaMemsetAsync(c->d_res, 0, host, c->stream);
+	}
 	c->sdoc_of = nullptr;
 	c->last_launches = 0;
-	c->last_ms[0] = c->last_ms[1] = c->last_ms[2] = 0.0f;
-	if (c->aborted) {
-		c->aborted = 0;
+	c->last_ms[0] = c->last_ms[1] = c->last_ms[2] = c->last_ms[3] = 0.0f;
+	if (c->aborted.exchange(0)) {
 		VX_FAIL(VX_ERR_ABORTED, "query aborted");
 	}
 	std::vector<QueryPlan> plans(n_pairs);
@@ -642,11 +716,7 @@ extern "C" int vx_search_batch(
 				for (int j = 0; j < nl + ng; j++) {
 					const QueryPlan &pj = plans[(size_t)q * n_aps + group[j]];
 					aps_dev[j] = pj.ap;
-					outs[j].score = (float*)(pj.res + pj.off_score);
-					outs[j].score_max = (float*)(pj.res + pj.off_score_max);
-					outs[j].win = (uint32_t*)(pj.res + pj.off_win);
-					outs[j].target = (int16_t*)(pj.res + pj.off_target);
-					outs[j].dist = (float*)(pj.res + pj.off_dist);
+					outs[j] = plan_out(pj);
 					slots_[j] = tks[j].slots;
 					n_[j] = tks[j].n;
 				}
@@ -663,7 +733,9 @@ extern "C" int vx_search_batch(
 				const QueryPlan &pj = plans[(size_t)q * n_aps + group[j]];
 				if (traced) {
 					cudaMemcpyAsync(pj.res + pj.off_n, tks[j].n, sizeof(int32_t), cudaMemcpyDeviceToDevice, c->stream);
-					cudaMemcpyAsync(pj.h_res, pj.res, pj.res_bytes, cudaMemcpyDeviceToHost, c->stream);
+					if (!c->comm) {
+						cudaMemcpyAsync(pj.h_res, pj.res, pj.res_bytes, cudaMemcpyDeviceToHost, c->stream);
+					}
 				} else {
 					rc = multi ? enqueue_finish(c, s, pj, tks[j], false) : enqueue_select(c, s, pj, false);
 				}
@@ -701,6 +773,11 @@ extern "C" int vx_search_batch(
 		}
 	}
 	cudaEventRecord(c->ev[1], c->stream);
+	if (c->comm && rc == VX_OK) {
+		// ONE all-gather for all (query, setting) pairs, one merge launch (a block per pair), one copy to the host
+		rc = enqueue_gather_merge(c, host, descs, k);
+		live.assign(n_pairs, 1);
+	}
 	cudaError_t e = cudaStreamSynchronize(c->stream);
 	if (c->select_stream) {
 		const cudaError_t e2 = cudaStreamSynchronize(c->select_stream);
@@ -714,9 +791,12 @@ extern "C" int vx_search_batch(
 		return VX_ERR_CUDA;
 	}
 	cudaEventElapsedTime(&c->last_ms[0], c->ev[0], c->ev[1]);   // the whole batch
+	if (c->comm) {
+		cudaEventElapsedTime(&c->last_ms[3], c->ev[4], c->ev[5]);
+	}
 	for (size_t i = 0; i < n_pairs; i++) {
 		if (live[i]) {
-			unpack_results(c, plans[i], hits + i * k, target + i * (size_t)k * t_stride,
+			unpack_results(plans[i], hits + i * k, target + i * (size_t)k * t_stride,
 				dist + i * (size_t)k * t_stride, &n_hits[i], t_stride);
 		}
 	}
@@ -766,7 +846,7 @@ extern "C" int vx_score_all(
 
 extern "C" int vx_abort(vx_corpus *c) {
 	if (c) {
-		c->aborted = 1;
+		c->aborted.store(1);
 	}
 	return VX_OK;
 }
@@ -779,6 +859,10 @@ extern "C" int vx_last_timing(const vx_corpus *c, float *ms3) {
 	ms3[1] = c->last_ms[1];
 	ms3[2] = c->last_ms[2];
 	return VX_OK;
+}
+
+extern "C" float vx_last_gather_ms(const vx_corpus *c) {
+	return c ? c->last_ms[3] : 0.0f;
 }
 
 extern "C" int vx_last_launches(const vx_corpus *c) {

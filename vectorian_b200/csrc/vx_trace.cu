@@ -86,6 +86,9 @@ struct TraceArgs {
 	const uint32_t *orig;
 	const int32_t *n_items;   // device count (may be nullptr -> max_items)
 	int32_t max_items;
+	const int32_t *win_doc;   // window index -> local document id / slice id
+	const int32_t *win_slice;
+	int32_t doc_offset;       // + doc_offset = global document id (sentence shards)
 	VxTraceOut out;
 };
 
@@ -334,6 +337,11 @@ __global__ void trace_kernel(TraceArgs a, VxAlignDev ap, VxQueryDev qp) {
 	}
 	if (a.out.win) {
 		a.out.win[item] = a.orig[slot];
+	}
+	if (a.out.doc) {
+		const uint32_t w = a.orig[slot];
+		a.out.doc[item] = a.win_doc[w] + a.doc_offset;
+		a.out.slice[item] = a.win_slice[w];
 	}
 
 	// ---- ScoreComputer: dist = 1 - unmodified_similarity(target, j) ----
@@ -653,6 +661,11 @@ __device__ __forceinline__ void trace_warp_body(const TraceArgs &a, const VxAlig
 		if (a.out.win) {
 			a.out.win[item] = a.orig[slot];
 		}
+		if (a.out.doc) {
+			const uint32_t w = a.orig[slot];
+			a.out.doc[item] = a.win_doc[w] + a.doc_offset;
+			a.out.slice[item] = a.win_slice[w];
+		}
 	}
 	__syncwarp();
 	for (int j = lane; j < len_t; j += 32) {
@@ -731,6 +744,9 @@ static void fill_trace_args(TraceArgs &a, const vx_corpus *c, const vx_sim *s, c
 	a.orig = c->d_orig;
 	a.n_items = d_n_items;
 	a.max_items = max_items;
+	a.win_doc = c->d_win_doc;
+	a.win_slice = c->d_win_slice;
+	a.doc_offset = c->doc_offset;
 	a.out = out;
 }
 
@@ -780,31 +796,7 @@ int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 	if (d_slots && warp_smem <= 200 * 1024) {
 		// the k winners: one warp each, matrices in shared memory
 		TraceArgs a;
-		a.tiles = c->d_tiles;
-		a.tok = c->d_tok;
-		a.pos = c->d_pos;
-		a.boost = c->d_boost;
-		a.s = s->d_s;
-		a.tp = s->tp;
-		a.ctx = c->d_ctx;
-		a.qhat = s->d_qhat;
-		a.ctx_dim = s->d;
-		a.contextual = s->contextual;
-		if (s->contextual == 3) {
-			a.contextual = 2;        // a.s = s->d_s holds the per-token rows
-		} else if (s->contextual && c->sdoc_of == s) {
-			a.s = c->d_sdoc;
-			a.contextual = 2;
-		}
-		a.scratch = nullptr;
-		a.scratch_per_item = 0;
-		a.max_len = c->max_len;
-		a.slots = d_slots;
-		a.slot_base = slot_base;
-		a.orig = c->d_orig;
-		a.n_items = d_n_items;
-		a.max_items = max_items;
-		a.out = out;
+		fill_trace_args(a, c, s, d_slots, slot_base, d_n_items, max_items, out);
 		if (warp_smem > 48 * 1024) {
 			cudaFuncSetAttribute(trace_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)warp_smem);
 		}
@@ -829,31 +821,9 @@ int vx_launch_trace(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 		c->scratch_bytes = need;
 	}
 	TraceArgs a;
-	a.tiles = c->d_tiles;
-	a.tok = c->d_tok;
-	a.pos = c->d_pos;
-	a.boost = c->d_boost;
-	a.s = s->d_s;
-	a.tp = s->tp;
-	a.ctx = c->d_ctx;
-	a.qhat = s->d_qhat;
-	a.ctx_dim = s->d;
-	a.contextual = s->contextual;
-	if (s->contextual == 3) {
-		a.contextual = 2;        // a.s = s->d_s holds the per-token rows
-	} else if (s->contextual && c->sdoc_of == s) {
-		a.s = c->d_sdoc;
-		a.contextual = 2;
-	}
+	fill_trace_args(a, c, s, d_slots, slot_base, d_n_items, max_items, out);
 	a.scratch = (uint8_t*)c->d_scratch;
 	a.scratch_per_item = need / (size_t)max_items;
-	a.max_len = c->max_len;
-	a.slots = d_slots;
-	a.slot_base = slot_base;
-	a.orig = c->d_orig;
-	a.n_items = d_n_items;
-	a.max_items = max_items;
-	a.out = out;
 	const int threads = 32;
 	trace_kernel<<<(max_items + threads - 1) / threads, threads, 0, c->stream>>>(a, ap, qp);
 	if (cudaGetLastError() != cudaSuccess) {

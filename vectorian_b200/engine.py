@@ -17,6 +17,69 @@ from ._cabi import ptr, check, HIT_DTYPE, Hit
 MAX_SIM_COLUMNS = 16   # query columns per vx_sim_static launch (VX_MAX_T_FAST)
 
 
+class Comm:
+	"""The ranks of a sentence-sharded corpus (vx_comm: an NCCL communicator bound inside the C ABI).  The reference's
+	counterpart is the document thread pool sharing one ResultSet (vectorian/index.py:544-555)."""
+
+	def __init__(self, unique_id, world, rank):
+		lib = _cabi.lib()
+		self._lib = lib
+		self._h = C.c_void_p()
+		uid = np.ascontiguousarray(unique_id, dtype=np.uint8)
+		assert uid.shape == (128,)
+		self.world, self.rank = int(world), int(rank)
+		check(lib.vx_comm_create(uid.ctypes.data_as(C.c_void_p), self.world, self.rank, C.byref(self._h)), lib)
+
+	@staticmethod
+	def unique_id():
+		lib = _cabi.lib()
+		uid = np.zeros((128,), dtype=np.uint8)
+		check(lib.vx_comm_unique_id(uid.ctypes.data_as(C.c_void_p)), lib)
+		return uid
+
+	@property
+	def handle(self):
+		return self._h
+
+	def close(self):
+		if self._h:
+			self._lib.vx_comm_destroy(self._h)
+			self._h = C.c_void_p()
+
+
+def merge_blocks(blocks, t, k):
+	"""vx_debug_merge: merge per-rank (hits, target, dist) triples with the DEVICE merge kernel of the sharded search
+	(test hook; document ids must already be global).  Returns the merged triple."""
+	lib = _cabi.lib()
+	off = np.zeros((8,), dtype=np.int64)
+	nbytes = int(lib.vx_res_block_bytes(t, k, ptr(off, C.c_int64)))
+	o_score, o_max, o_win, o_doc, o_slice, o_target, o_dist, o_n = [int(x) for x in off]
+	buf = np.zeros((len(blocks), nbytes), dtype=np.uint8)
+	for r, (h, tg, ds) in enumerate(blocks):
+		n = len(h)
+		assert n <= k
+		row = buf[r]
+		row[o_score:o_score + 4 * n].view(np.float32)[:] = h["score"]
+		row[o_max:o_max + 4 * n].view(np.float32)[:] = h["score_max"]
+		row[o_doc:o_doc + 4 * n].view(np.int32)[:] = h["doc"]
+		row[o_slice:o_slice + 4 * n].view(np.int32)[:] = h["slice"]
+		if t:
+			row[o_target:o_target + 2 * n * t].view(np.int16)[:] = np.asarray(tg, dtype=np.int16).reshape(-1)
+			row[o_dist:o_dist + 4 * n * t].view(np.float32)[:] = np.asarray(ds, dtype=np.float32).reshape(-1)
+		row[o_n:o_n + 4].view(np.int32)[0] = n
+	out = np.zeros((nbytes,), dtype=np.uint8)
+	check(lib.vx_debug_merge(buf.ctypes.data_as(C.c_void_p), len(blocks), t, k, out.ctypes.data_as(C.c_void_p)), lib)
+	n = int(out[o_n:o_n + 4].view(np.int32)[0])
+	hits = np.zeros((n,), dtype=HIT_DTYPE)
+	hits["score"] = out[o_score:o_score + 4 * n].view(np.float32)
+	hits["score_max"] = out[o_max:o_max + 4 * n].view(np.float32)
+	hits["doc"] = out[o_doc:o_doc + 4 * n].view(np.int32)
+	hits["slice"] = out[o_slice:o_slice + 4 * n].view(np.int32)
+	target = out[o_target:o_target + 2 * n * t].view(np.int16).reshape(n, t).copy()
+	dist = out[o_dist:o_dist + 4 * n * t].view(np.float32).reshape(n, t).copy()
+	return hits, target, dist
+
+
 class DeviceCorpus:
 	"""Documents packed once into device-resident token tiles for one partition.
 
@@ -54,6 +117,13 @@ class DeviceCorpus:
 				int(window_size), int(window_step), C.byref(self._h)), lib)
 		self.n_doc = n_doc
 		self.n_spans = int(doc_span_off[-1])
+		self.sharded = False     # set_shard: search / search_batch return the GLOBAL result on every rank
+
+	def set_shard(self, comm, doc_offset):
+		"""vx_corpus_set_shard: this corpus is one rank's shard; doc_offset = global id of its first document."""
+		check(self._lib.vx_corpus_set_shard(self._h, comm.handle if comm is not None else None, int(doc_offset)), self._lib)
+		self.sharded = comm is not None
+		self._comm = comm
 
 	def close(self):
 		if self._h:
@@ -170,7 +240,8 @@ class DeviceCorpus:
 	def last_timing(self):
 		ms = np.zeros((3,), dtype=np.float32)
 		check(self._lib.vx_last_timing(self._h, ptr(ms, C.c_float)), self._lib)
-		return dict(dp_ms=float(ms[0]), topk_ms=float(ms[1]), traceback_ms=float(ms[2]))
+		return dict(dp_ms=float(ms[0]), topk_ms=float(ms[1]), traceback_ms=float(ms[2]),
+			gather_merge_ms=float(self._lib.vx_last_gather_ms(self._h)))
 
 	def last_launches(self):
 		return int(self._lib.vx_last_launches(self._h))

@@ -581,8 +581,10 @@ class BruteForceIndex(Index):
 		self.last_timing = dict(dc.last_timing(), sim_ms=sim.build_ms)
 		sim.close()
 		rank, world, doc_lo, _ = session.shard
-		if world > 1:
-			hits, target, dist = gather_topk(hits, target, dist, k, doc_offset=doc_lo)
+		if dc.sharded:
+			pass    # vx_search has already gathered and merged the ranks' rows on the device; document ids are global
+		elif world > 1:
+			hits, target, dist = gather_topk(hits, target, dist, k, doc_offset=doc_lo)   # process group without NCCL
 		elif doc_lo:
 			hits = hits.copy()
 			hits["doc"] += doc_lo
@@ -633,9 +635,12 @@ def sweep(indexes, texts, n=10, min_score=0.0, options: dict = dict()):
 		qp, keep_q, k = first._query_params(queries[0][0].options, margs[0], prepared[live[0]])
 		first._set_boost(dc)
 		rank, world, doc_lo, _ = session.shard
-		if world > 1:
-			# sharded session: ONE all-gather for all (query, setting) pairs, document ids made global inside it
-			from .distributed import gather_topk_many
+		if dc.sharded:
+			# sharded session: ONE all-gather + ONE merge launch for all (query, setting) pairs inside vx_search_batch
+			out = dc.search_batch(sims, aps, qp)
+			doc_lo = 0
+		elif world > 1:
+			from .distributed import gather_topk_many   # process group without NCCL: host path
 			flat = gather_topk_many(dc.search_batch(sims, aps, qp, raw=True), k, doc_offset=doc_lo)
 			out = [[flat[q * len(aps) + a] for a in range(len(aps))] for q in range(len(sims))]
 			doc_lo = 0

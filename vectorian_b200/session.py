@@ -456,6 +456,11 @@ class Session:
 			dc = engine.DeviceCorpus(
 				tb["token_id"], tb["doc_tok_off"], tb["span_start"], tb["span_end"], tb["doc_span_off"],
 				partition.window_size, partition.window_step, token_pos=tb["token_pos"])
+			if self._world > 1:
+				from .distributed import device_comm
+				comm = device_comm()      # NCCL process groups: gather + merge inside vx_search (csrc/vx_shard.cu)
+				if comm is not None:
+					dc.set_shard(comm, self._doc_lo)
 			self._device_corpora[key] = dc
 		return dc
 
