@@ -29,15 +29,26 @@ def params(locality, gap, max_len, t):
 	return _cabi.make_align_params(locality, kind, **r)
 
 
-def main():
-	n_sent = int(sys.argv[1]) if len(sys.argv) > 1 else 60000
-	local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-	torch.cuda.set_device(local_rank)
-	dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-	rank, world = dist.get_rank(), dist.get_world_size()
-	vocab, dim = 3000, 32
-	corpus = synthetic.make_corpus(n_sent, vocab, seed=5, sentences_per_doc=53)
-	emb = synthetic.make_embedding(vocab, dim, seed=6, n_centroids=20)   # few centroids: many exact score ties
+def tiled_corpus(base_sentences, reps, vocab, sentences_per_doc=53):
+	"""`reps` copies of one small corpus back to back: every sentence -- hence every score -- occurs `reps` times, in
+	different documents and (sharded) on different ranks, so the top-k is full of exact ties."""
+	base = synthetic.make_corpus(base_sentences, vocab, seed=5, sentences_per_doc=sentences_per_doc)
+	lens = np.tile(base["lens"], reps)
+	token_id = np.tile(base["token_id"], reps)
+	n = len(lens)
+	n_doc = (n + sentences_per_doc - 1) // sentences_per_doc
+	doc_span_off = np.minimum(np.arange(n_doc + 1, dtype=np.int64) * sentences_per_doc, n)
+	ends = np.cumsum(lens.astype(np.int64))
+	starts = ends - lens
+	doc_tok_off = np.concatenate([starts[doc_span_off[:-1]], [len(token_id)]]).astype(np.int64)
+	doc_of = np.repeat(np.arange(n_doc), np.diff(doc_span_off))
+	return dict(token_id=token_id, doc_tok_off=doc_tok_off, span_start=(starts - doc_tok_off[doc_of]).astype(np.int32),
+		span_end=(ends - doc_tok_off[doc_of]).astype(np.int32), doc_span_off=doc_span_off, lens=lens, n_doc=n_doc)
+
+
+def check_corpus(vocab, dim, cent, n_sent, rank, world, tiled=False):
+	corpus = tiled_corpus(n_sent // 30, 30, vocab) if tiled else synthetic.make_corpus(n_sent, vocab, seed=5, sentences_per_doc=53)
+	emb = synthetic.make_embedding(vocab, dim, seed=6, n_centroids=cent)   # few centroids: many exact score ties
 	whole = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"], corpus["doc_span_off"])
 	n_doc = corpus["n_doc"]
 	lo, hi = shard_documents(n_doc, world, rank, np.diff(corpus["doc_tok_off"]))
@@ -91,11 +102,38 @@ def main():
 			n_checked += 1
 	ties = int(np.sum(np.diff(whole.search(sims[0], params(_cabi.VX_LOCAL, gaps.LinearGapCost(0.0), max_len, 12)[0],
 		_cabi.make_query_params(max_matches=100, min_score=0.0)[0])[0]["score"]) == 0))
+	ms = shard.last_timing()["gather_merge_ms"]
+	for sim in sims:
+		sim.close()
+	de.close()
+	shard.set_shard(None, 0)
+	shard.close()
+	whole.close()
+	return ok, n_checked, ties, ms
+
+
+def main():
+	n_sent = int(sys.argv[1]) if len(sys.argv) > 1 else 60000
+	local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+	torch.cuda.set_device(local_rank)
+	dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+	rank, world = dist.get_rank(), dist.get_world_size()
+	ok = True
+	n_checked = 0
+	ties = 0
+	last_ms = 0.0
+	# a varied corpus, then 30 copies of a small one: every score occurs 30 times, spread over the ranks, so the top-k
+	# and its order are decided by (doc desc, slice desc) across ranks
+	for vocab, dim, cent, n_here, tiled in ((3000, 32, 20, n_sent, False), (3000, 32, 20, min(n_sent, 60000), True)):
+		ok_c, n_c, ties_c, last_ms = check_corpus(vocab, dim, cent, n_here, rank, world, tiled)
+		ok = ok and ok_c
+		n_checked += n_c
+		ties += ties_c
 	flag = torch.tensor([1 if ok else 0], device="cuda")
 	dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 	if rank == 0:
-		print("sharded == unsharded on every rank: %s (%d searches, world %d, %d sentences, %d equal neighbours in one top-100, gather+merge %.3f ms)" % (
-			bool(flag.item()), n_checked, world, n_sent, ties, shard.last_timing()["gather_merge_ms"]), flush=True)
+		print("sharded == unsharded on every rank: %s (%d searches, world %d, %d sentences, %d equal neighbours in two top-100 lists, gather+merge %.3f ms)" % (
+			bool(flag.item()), n_checked, world, n_sent, ties, last_ms), flush=True)
 	dist.destroy_process_group()
 	sys.exit(0 if flag.item() else 1)
 

@@ -45,10 +45,8 @@ def main():
 		for ai, index in enumerate(indexes):
 			want = index.find(text, n=15, min_score=-10.0)
 			ok = ok and rows(got[qi][ai]) == rows(want)
-	# the same sweep with the merge forced onto the device (what large sweeps use), twice: the cached pinned staging
-	# buffers are reused by the second call and must not alias the results of the first
-	import vectorian_b200.distributed as vd
-	vd.HOST_MERGE_ROWS = 0
+	# twice more, the second time with the queries reversed: the result buffers (send / gather / merged / pinned) are
+	# reused from call to call and must not alias the results of an earlier one
 	dev1 = sweep(indexes, texts, n=15, min_score=-10.0)
 	dev1_rows = [[rows(r) for r in row] for row in dev1]
 	dev2 = sweep(indexes, list(reversed(texts)), n=15, min_score=-10.0)
@@ -56,6 +54,7 @@ def main():
 		for ai in range(len(indexes)):
 			ok = ok and dev1_rows[qi][ai] == rows(got[qi][ai]) and rows(dev1[qi][ai]) == dev1_rows[qi][ai]
 			ok = ok and rows(dev2[len(texts) - 1 - qi][ai]) == rows(got[qi][ai])
+	assert indexes[0].session.device_corpus(partition).sharded
 	docs_seen = {r[0] for row in got for res in row for r in rows(res)}
 	flag = torch.tensor([1 if ok else 0], device="cuda")
 	dist.all_reduce(flag, op=dist.ReduceOp.MIN)

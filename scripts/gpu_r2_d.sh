@@ -1,0 +1,17 @@
+#!/bin/bash
+# Round 2, visit D (N GPUs): sharded == unsharded on the hardware, sharded sweep through the Python API, strong-scaling bench.
+set -u
+N=${1:-2}
+OUT=gpurun_out/r2_d_n$N
+mkdir -p $OUT
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+timeout 600 $TR --master-port 29611 scripts/check_sharded.py > $OUT/check_sharded.log 2>&1; echo "check_sharded rc=$?"; grep -E "sharded ==|MISMATCH|Error|error" $OUT/check_sharded.log | head -5
+timeout 600 $TR --master-port 29612 scripts/check_sharded.py 2000000 > $OUT/check_sharded_2m.log 2>&1; echo "check_sharded 2M rc=$?"; grep -E "sharded ==|MISMATCH" $OUT/check_sharded_2m.log | head -5
+timeout 600 $TR --master-port 29613 scripts/check_sweep_sharded.py > $OUT/check_sweep.log 2>&1; echo "check_sweep rc=$?"; grep -E "sharded sweep|Error" $OUT/check_sweep.log | head -3
+timeout 600 python -m pytest tests/test_gpu_shard.py -m gpu -x -q > $OUT/pytest_shard.log 2>&1; echo "pytest shard rc=$?"; tail -2 $OUT/pytest_shard.log
+timeout 900 $TR --master-port 29614 bench.py --gpus $N --steps 20 --warmup 5 > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?"; tail -3 $OUT/bench.err
+python - $OUT <<'PY'
+import json, sys
+d = json.load(open(sys.argv[1] + "/bench.json"))
+print("N=%d value %.4g e2e %.4g (%.3f ms/step e2e, %.3f device) frac %.4f parity %s scaling %s\nphases %s" % (d["n_gpus"], d["value"], d["e2e"]["value"], d["e2e"]["ms_per_step"], d["ms_per_step"], d["roofline"]["frac"], d["sharded_parity"], d["scaling"], d["phases_ms"]))
+PY
