@@ -406,7 +406,7 @@ def main():
 				"achieved": issue_ach / 1e12, "peak": issue_peak / 1e12, "unit": "TFLOP/s", "frac": issue_ach / issue_peak,
 				"traffic": traffic, "traffic_note": traffic_note,
 				"ops_per_launch": lane_ops, "ops_definition": "2 FP32 ops per DP candidate + 1 per Local cell (SURVEY.md 8d): 12600 per 25 x 12 sentence",
-				"peak_source": "SMs (%d) x 128 FP32 lanes x %.0f MHz (MEASURED_PEAKS.json sm_max_mhz); the kernel issues 1.5 slots per candidate (2 FADD + 1/2 FMNMX3), so 1.33 is the hard ceiling of this fraction" % (sms, sm_max),
+				"peak_source": "SMs (%d) x 128 FP32 lanes x %.0f MHz (MEASURED_PEAKS.json sm_max_mhz); the definition counts 2 lane-ops per candidate, the kernel spends one FADD2 + one FMNMX3 per TWO candidates (packed add.rn.f32x2), so the fraction can exceed 1: its ceiling is 2.0 (alu pipe: one FMNMX3 per scheduler every 2 cycles; measured 2.2-2.3 cycles, i.e. about 1.8)" % (sms, sm_max),
 				"ms_per_launch": dp_ms,
 				"note": "not HBM-bound and no tensor-core work: HBM view in hbm_roofline"},
 			"hbm_roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,

@@ -144,6 +144,28 @@ __device__ __forceinline__ int32_t quad_get(const int4 &q, int i) {
 	return i == 0 ? q.x : i == 1 ? q.y : i == 2 ? q.z : q.w;
 }
 
+// rows k, k+1 of the column history from tensor memory (asynchronous until tmem_wait_ld) / shared memory
+template<int TP>
+__device__ __forceinline__ void tmem_ld_pair(const uint32_t tmem, const int k, float (&h0)[TP], float (&h1)[TP]) {
+	#pragma unroll
+	for (int q = 0; q < TP / 4; q++) {
+		tmem_ld4(tmem + (uint32_t)(k * TP + 4 * q), h0 + 4 * q);
+		tmem_ld4(tmem + (uint32_t)((k + 1) * TP + 4 * q), h1 + 4 * q);
+	}
+}
+
+template<int TP>
+__device__ __forceinline__ void smem_ld_pair(const float4 *__restrict__ hist, const int k, float (&h0)[TP], float (&h1)[TP]) {
+	constexpr int Q = TP / 4;
+	#pragma unroll
+	for (int q = 0; q < Q; q++) {
+		const float4 x = hist[((size_t)k * Q + q) * 32];
+		const float4 y = hist[((size_t)(k + 1) * Q + q) * 32];
+		h0[4 * q + 0] = x.x; h0[4 * q + 1] = x.y; h0[4 * q + 2] = x.z; h0[4 * q + 3] = x.w;
+		h1[4 * q + 0] = y.x; h1[4 * q + 1] = y.y; h1[4 * q + 2] = y.z; h1[4 * q + 3] = y.w;
+	}
+}
+
 // Vertical candidates of the NR rows of a block from two finished rows k, k+1 (h0, h1); d = u0 - k.
 //   acc[i][v] = max(acc[i][v], h0[v] - w_s[d + i], h1[v] - w_s[d + i - 1])
 // F2: one FADD2 forms the candidates of two neighbouring columns, so 4 candidates cost 2 FADD2 + 2 FMNMX3
@@ -179,7 +201,7 @@ __device__ __forceinline__ void wsb_history_pair(const WsbArgs &a, const int d, 
 //   prev[v]  in: V[u0-1, v]  out: V[u0+NR-1, v]
 //   sim      in: S rows of this block; out: S rows of the NEXT block of the warp's token stream
 //            (each row is re-loaded as soon as it has been consumed, ids from idq_next)
-template<int TP, int LOC, bool BORD, int NR, bool F2>
+template<int TP, int LOC, bool BORD, int NR, bool F2, bool PIPE>
 __device__ __forceinline__ void wsb_block(
 	const WsbArgs &a, const uint32_t tmem, float4 *__restrict__ hist, const int u0, const int t,
 	float (&prev)[TP], float &best, float &last_col,
@@ -204,32 +226,55 @@ __device__ __forceinline__ void wsb_block(
 		}
 	}
 
-	// vertical candidates from the finished rows k = 0 .. u0-1 (u0 and rt are multiples of U, U even):
-	// rows [0, rt) from tensor memory, rows [rt, u0) from shared memory
+	// vertical candidates from the finished rows k = 0 .. u0-1: rows [0, rt) from tensor memory, rows [rt, u0) from
+	// shared memory.  u0 and rt are multiples of U = 4, so both ranges hold an even number of row PAIRS; the loops are
+	// double-buffered by hand: the loads of the next pair are in flight while the 8 * TP candidates of this pair are
+	// evaluated (with two warps per scheduler the load latency -- ~52 cycles for tcgen05.ld -- was exposed in every
+	// iteration: 14-25 % long-scoreboard stalls in these loops, profiles/r2_wsb_f2).
 	const int rt = a.rt;
 	const int k_tmem = u0 < rt ? u0 : rt;
-	#pragma unroll 1
-	for (int k = 0; k < k_tmem; k += 2) {
-		float h0[TP], h1[TP];
-		#pragma unroll
-		for (int q = 0; q < Q; q++) {
-			tmem_ld4(tmem + (uint32_t)(k * TP + 4 * q), h0 + 4 * q);
-			tmem_ld4(tmem + (uint32_t)((k + 1) * TP + 4 * q), h1 + 4 * q);
+	if (PIPE) {
+		float hA0[TP], hA1[TP], hB0[TP], hB1[TP];
+		if (k_tmem > 0) {
+			tmem_ld_pair<TP>(tmem, 0, hA0, hA1);
 		}
-		tmem_wait_ld();
-		wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, h0, h1);
-	}
-	#pragma unroll 1
-	for (int k = rt; k < u0; k += 2) {
-		float h0[TP], h1[TP];
-		#pragma unroll
-		for (int q = 0; q < Q; q++) {
-			const float4 x = hist[((size_t)(k - rt) * Q + q) * 32];
-			const float4 y = hist[((size_t)(k - rt + 1) * Q + q) * 32];
-			h0[4 * q + 0] = x.x; h0[4 * q + 1] = x.y; h0[4 * q + 2] = x.z; h0[4 * q + 3] = x.w;
-			h1[4 * q + 0] = y.x; h1[4 * q + 1] = y.y; h1[4 * q + 2] = y.z; h1[4 * q + 3] = y.w;
+		#pragma unroll 1
+		for (int k = 0; k < k_tmem; k += 4) {
+			tmem_wait_ld();                                   // pair A = rows k, k+1
+			tmem_ld_pair<TP>(tmem, k + 2, hB0, hB1);          // in flight during A
+			wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, hA0, hA1);
+			tmem_wait_ld();                                   // pair B = rows k+2, k+3
+			if (k + 4 < k_tmem) {
+				tmem_ld_pair<TP>(tmem, k + 4, hA0, hA1);      // in flight during B
+			}
+			wsb_history_pair<TP, NR, F2>(a, u0 - k - 2, acc, hB0, hB1);
 		}
-		wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, h0, h1);
+		if (rt < u0) {
+			smem_ld_pair<TP>(hist, 0, hA0, hA1);
+		}
+		#pragma unroll 1
+		for (int k = rt; k < u0; k += 4) {
+			smem_ld_pair<TP>(hist, k - rt + 2, hB0, hB1);
+			wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, hA0, hA1);
+			if (k + 4 < u0) {
+				smem_ld_pair<TP>(hist, k - rt + 4, hA0, hA1);
+			}
+			wsb_history_pair<TP, NR, F2>(a, u0 - k - 2, acc, hB0, hB1);
+		}
+	} else {
+		#pragma unroll 1
+		for (int k = 0; k < k_tmem; k += 2) {
+			float h0[TP], h1[TP];
+			tmem_ld_pair<TP>(tmem, k, h0, h1);
+			tmem_wait_ld();
+			wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, h0, h1);
+		}
+		#pragma unroll 1
+		for (int k = rt; k < u0; k += 2) {
+			float h0[TP], h1[TP];
+			smem_ld_pair<TP>(hist, k - rt, h0, h1);
+			wsb_history_pair<TP, NR, F2>(a, u0 - k, acc, h0, h1);
+		}
 	}
 
 	// token ids: idq_next (ids of the next block, loaded one block ago) is consumed by the row-wise
@@ -370,7 +415,7 @@ __device__ __forceinline__ void wsb_block(
 	}
 }
 
-template<int TP, int LOC, bool BORD, bool F2>
+template<int TP, int LOC, bool BORD, bool F2, bool PIPE>
 __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant__ WsbArgs a) {
 	extern __shared__ float4 wsb_smem[];
 	__shared__ uint32_t tmem_base_sh;
@@ -452,18 +497,18 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 			int u0 = 0;
 			#pragma unroll 1
 			for (; u0 + U <= len; u0 += U) {
-				wsb_block<TP, LOC, BORD, U, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+				wsb_block<TP, LOC, BORD, U, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 			}
 			if (u0 < len) {
 				switch (len - u0) {
 					case 1:
-						wsb_block<TP, LOC, BORD, 1, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 1, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 					case 2:
-						wsb_block<TP, LOC, BORD, 2, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 2, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 					default:
-						wsb_block<TP, LOC, BORD, 3, F2>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 3, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
 						break;
 				}
 			}
@@ -520,7 +565,7 @@ static void wsb_plan(int tp, int cap, int *warps, int *rt, int *tmem_cols, int *
 	}
 }
 
-template<int TP, int LOC, bool BORD, bool F2>
+template<int TP, int LOC, bool BORD, bool F2, bool PIPE>
 static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap) {
 	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
 	// SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a TMEM lane quarter
@@ -550,7 +595,7 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	const size_t smem = (size_t)rows_smem * row_bytes * warps;
 	static bool attr_set = false;
 	if (!attr_set) {
-		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD, F2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
+		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD, F2, PIPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
 		attr_set = true;
 	}
 	// Every launch after the first of a query is a programmatic dependent launch: the kernels of one query do not
@@ -567,28 +612,39 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	attr[0].val.programmaticStreamSerializationAllowed = 1;
 	cfg.attrs = attr;
 	cfg.numAttrs = overlap ? 1 : 0;
-	if (cudaLaunchKernelEx(&cfg, wsb_score_kernel<TP, LOC, BORD, F2>, a) != cudaSuccess) {
+	if (cudaLaunchKernelEx(&cfg, wsb_score_kernel<TP, LOC, BORD, F2, PIPE>, a) != cudaSuccess) {
 		return -1;
 	}
 	return 1;
 }
 
-template<int TP, bool F2>
+template<int TP, bool F2, bool PIPE>
 static int launch_class_f(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
 	if (loc == VX_LOCAL) {
-		return bord ? launch_class<TP, VX_LOCAL, true, F2>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false, F2>(c, a, cap, sms, overlap);
+		return bord ? launch_class<TP, VX_LOCAL, true, F2, PIPE>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false, F2, PIPE>(c, a, cap, sms, overlap);
 	}
 	if (loc == VX_GLOBAL) {
-		return launch_class<TP, VX_GLOBAL, true, F2>(c, a, cap, sms, overlap);
+		return launch_class<TP, VX_GLOBAL, true, F2, PIPE>(c, a, cap, sms, overlap);
 	}
-	return launch_class<TP, VX_SEMIGLOBAL, true, F2>(c, a, cap, sms, overlap);
+	return launch_class<TP, VX_SEMIGLOBAL, true, F2, PIPE>(c, a, cap, sms, overlap);
 }
 
 template<int TP>
 static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
-	// packed adds (FADD2) by default; VX_WSB_NO_F2 keeps the scalar-add variant for A/B measurements (read once)
+	// A/B switches for measurements (read once): VX_WSB_NO_F2 = scalar adds instead of FADD2 (and the round-1 loop
+	// structure), VX_WSB_NO_PIPE = packed adds without the double-buffered history loops
 	static const bool f2 = getenv("VX_WSB_NO_F2") == nullptr;
-	return f2 ? launch_class_f<TP, true>(c, a, cap, sms, loc, bord, overlap) : launch_class_f<TP, false>(c, a, cap, sms, loc, bord, overlap);
+	static const bool pipe = getenv("VX_WSB_NO_PIPE") == nullptr;
+	if (!f2) {
+		return launch_class_f<TP, false, false>(c, a, cap, sms, loc, bord, overlap);
+	}
+	// the second row-pair buffer costs 2 * TP registers: 249 at TP = 12 (fits 8 warps per SM exactly), spills at TP = 16
+	if constexpr (TP <= 12) {
+		if (pipe) {
+			return launch_class_f<TP, true, true>(c, a, cap, sms, loc, bord, overlap);
+		}
+	}
+	return launch_class_f<TP, true, false>(c, a, cap, sms, loc, bord, overlap);
 }
 
 // Scores every tile whose windows are at most VX_WSB_MAX_LEN long; *first_tile receives the index of
