@@ -1,0 +1,20 @@
+#!/bin/bash
+# Round 2, visit F: pruned top-k + value-first traceback: whole GPU suite, phases at 50 M / 6.25 M / 1 M / 10 k sentences,
+# A/B against the radix top-k (VX_TOPK_RADIX=1).
+set -u
+OUT=gpurun_out/${1:-r2_f}
+mkdir -p $OUT
+timeout 1800 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest gpu rc=$?"; tail -4 $OUT/pytest_gpu.log
+for n in 50000000 6250000 1000000 10000; do
+	timeout 600 python bench.py --sentences $n --steps 20 --warmup 5 --no-cpu-baseline --no-secondary --no-clocks > $OUT/bench_$n.json 2> $OUT/bench_$n.err; echo "bench $n rc=$?"
+done
+VX_TOPK_RADIX=1 timeout 600 python bench.py --sentences 6250000 --steps 20 --warmup 5 --no-cpu-baseline --no-secondary --no-clocks > $OUT/bench_radix_6250000.json 2> $OUT/bench_radix.err
+python - $OUT <<'PY'
+import json, sys, glob
+for f in sorted(glob.glob(sys.argv[1] + "/bench_*.json")):
+    try:
+        d = json.load(open(f))
+        print("%-32s dev %.3f ms e2e %.3f ms frac %.3f parity %s launches/step %.1f phases %s" % (f.split("/")[-1], d["ms_per_step"], d["e2e"]["ms_per_step"], d["roofline"]["frac"], d["sharded_parity"], d["gpu_launches"] / d["steps"], {k: round(v, 3) for k, v in d["phases_ms"].items() if "gather" not in k}))
+    except Exception as e:
+        print(f, "failed", e)
+PY

@@ -101,6 +101,7 @@ static void corpus_free(vx_corpus *c) {
 	cudaFree(c->d_topk_multi);
 	cudaFree(c->d_scratch);
 	cudaFree(c->d_counters);
+	cudaFree(c->d_group_max);
 	cudaFree(c->d_win_doc);
 	cudaFree(c->d_win_slice);
 	cudaFree(c->d_res);

@@ -106,6 +106,8 @@ struct vx_corpus {
 	// (class_first[0] = n_tiles); the WSB kernel is launched once per run of classes with equal occupancy
 	int64_t class_first[VX_N_CLASS + 1] = {0};
 	void *d_counters = nullptr;      // 16 x uint32 tile counters of the persistent kernels
+	float *d_group_max = nullptr;    // pruned top-k: maximum score of every group of slots (vx_topk.cu)
+	size_t group_max_bytes = 0;
 
 	cudaStream_t stream = nullptr;
 	cudaStream_t select_stream = nullptr;            // vx_search_batch: top-k + traceback of one group while the next group's DP runs
@@ -214,6 +216,7 @@ struct VxTopkOut {
 };
 size_t vx_topk_work_bytes(int32_t k);
 int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out);
+int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out, const unsigned int **overflow_flag_dev);
 int vx_launch_topk_multi(vx_corpus *c, float min_score, int32_t k, void *work, size_t stride, int n_arrays,
 	const float *const *scores, VxTopkOut *outs);
 

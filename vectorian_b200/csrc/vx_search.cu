@@ -393,10 +393,11 @@ static int enqueue_gather_merge(vx_corpus *c, size_t bytes, const std::vector<Vx
 
 // Enqueue one query: scores of every slot, top-k, traceback of the winners, result block to pinned host memory.
 // Nothing here waits for the device.
-static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events);
-static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, const VxTopkOut &tk, bool phase_events);
+static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events, bool pruned = false);
+static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, const VxTopkOut &tk, bool phase_events,
+	const unsigned int *overflow_dev = nullptr);
 
-static int enqueue_search(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events) {
+static int enqueue_search(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events, bool pruned = false) {
 	cudaStream_t st = c->stream;
 	if (s->ev1) {
 		cudaStreamWaitEvent(st, s->ev1, 0);   // S may still be under construction on the similarity stream
@@ -406,11 +407,11 @@ static int enqueue_search(vx_corpus *c, const vx_sim *s, const QueryPlan &p, boo
 		return VX_ERR_CUDA;
 	}
 	c->last_launches += n;
-	return enqueue_select(c, s, p, phase_events);
+	return enqueue_select(c, s, p, phase_events, pruned);
 }
 
 // top-k over c->d_score, traceback of the winners, result block to pinned host memory
-static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events) {
+static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, bool phase_events, bool pruned) {
 	cudaStream_t st = c->stream;
 	int n;
 	if (phase_events) {
@@ -422,16 +423,24 @@ static int enqueue_select(vx_corpus *c, const vx_sim *s, const QueryPlan &p, boo
 	}
 
 	VxTopkOut tk;
-	n = vx_launch_topk(c, p.qp.min_score, p.k, p.topk, &tk);
+	const unsigned int *overflow_dev = nullptr;
+	// single searches: group maxima -> threshold -> candidates (no grid barriers); when masses of equal scores overflow
+	// its candidate buffer it says so in the result block and vx_search repeats the selection with the radix select
+	n = pruned ? vx_launch_topk_pruned(c, p.qp.min_score, p.k, p.topk, &tk, &overflow_dev) : 0;
+	if (n == 0) {
+		overflow_dev = nullptr;
+		n = vx_launch_topk(c, p.qp.min_score, p.k, p.topk, &tk);
+	}
 	if (n < 0) {
 		return VX_ERR_INVALID;
 	}
 	c->last_launches += n;
-	return enqueue_finish(c, s, p, tk, phase_events);
+	return enqueue_finish(c, s, p, tk, phase_events, overflow_dev);
 }
 
 // traceback of the winners `tk`, result block to pinned host memory
-static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, const VxTopkOut &tk, bool phase_events) {
+static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, const VxTopkOut &tk, bool phase_events,
+	const unsigned int *overflow_dev) {
 	cudaStream_t st = c->stream;
 	int n;
 	if (phase_events) {
@@ -445,6 +454,11 @@ static int enqueue_finish(vx_corpus *c, const vx_sim *s, const QueryPlan &p, con
 	}
 	c->last_launches += n;
 	cudaMemcpyAsync(p.res + p.off_n, tk.n, sizeof(int32_t), cudaMemcpyDeviceToDevice, st);
+	if (overflow_dev) {
+		cudaMemcpyAsync(p.res + p.off_n + 4, overflow_dev, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st);
+	} else {
+		cudaMemsetAsync(p.res + p.off_n + 4, 0, sizeof(uint32_t), st);
+	}
 	if (phase_events) {
 		cudaEventRecord(c->ev[3], st);
 	}
@@ -501,7 +515,7 @@ extern "C" int vx_search(
 	}
 	if (c->n_win == 0) {
 		// an empty shard still takes part in the collective: an empty result block
-		cudaMemsetAsync(p.res + p.off_n, 0, sizeof(int32_t), c->stream);
+		cudaMemsetAsync(p.res + p.off_n, 0, 2 * sizeof(int32_t), c->stream);
 		VX_TRY(enqueue_gather_merge(c, p.res_bytes, std::vector<VxPairDesc>(1, VxPairDesc{0, p.t, 0}), p.k));
 		if (cudaStreamSynchronize(c->stream) != cudaSuccess) {
 			VX_FAIL(VX_ERR_CUDA, "sharded search failed");
@@ -514,11 +528,21 @@ extern "C" int vx_search(
 	}
 
 	cudaEventRecord(c->ev[0], c->stream);
-	VX_TRY(enqueue_search(c, s, p, true));
+	VX_TRY(enqueue_search(c, s, p, true, true));
 	if (c->comm) {
 		VX_TRY(enqueue_gather_merge(c, p.res_bytes, std::vector<VxPairDesc>(1, VxPairDesc{0, p.t, 0}), p.k));
 	}
 	cudaError_t e = cudaStreamSynchronize(c->stream);
+	if (e == cudaSuccess && *(const uint32_t*)(p.h_res + p.off_n + 4) != 0) {
+		// the pruned top-k met more equal scores than its candidate buffer holds (on this rank or, sharded, on any rank:
+		// the merge kernel ORs the flags, so every rank takes this branch together): select again with the radix
+		// select over the scores that are still in c->d_score
+		VX_TRY(enqueue_select(c, s, p, false, false));
+		if (c->comm) {
+			VX_TRY(enqueue_gather_merge(c, p.res_bytes, std::vector<VxPairDesc>(1, VxPairDesc{0, p.t, 0}), p.k));
+		}
+		e = cudaStreamSynchronize(c->stream);
+	}
 	if (e != cudaSuccess) {
 		vx_set_error(std::string("search failed: ") + cudaGetErrorString(e));
 		return VX_ERR_CUDA;

@@ -236,6 +236,12 @@ __global__ void __launch_bounds__(256) merge_gathered_kernel(const uint8_t *__re
 	}
 	if (threadIdx.x == 0) {
 		*(int32_t*)(out + L.off_n) = total < k ? total : k;
+		// word 1 of the header: "this rank's top-k overflowed, select again" -- ORed so that all ranks agree
+		uint32_t again = 0;
+		for (int r = 0; r < world; r++) {
+			again |= *(const uint32_t*)(gathered + (size_t)r * rank_stride + d.off + L.off_n + 4);
+		}
+		*(uint32_t*)(out + L.off_n + 4) = again;
 	}
 }
 

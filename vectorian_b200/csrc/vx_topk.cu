@@ -13,6 +13,8 @@
 // sorted by one block (bitonic, shared memory).  No host round trip until the final copy.
 #include "vx_internal.cuh"
 
+#include <math_constants.h>
+
 constexpr int TOPK_LEVELS = 6;
 constexpr int TOPK_BINS = 2048;
 constexpr int TOPK_CAP = 8192;
@@ -481,10 +483,328 @@ __global__ void __launch_bounds__(256) topk_fused_kernel(const __grid_constant__
 	}
 }
 
+static void topk_carve(void *work, int32_t k, TopkWork **w, VxTopkOut *out);
+
+// ---------------------------------------------------------------------------
+// Pruned top-k for a single search: no grid-wide barriers, no radix levels over the scores.
+//   K1  group maxima: one pass over the scores, one float per group of G slots (G = 32 .. 1024, chosen so that there
+//       are many more groups than k);
+//   K2  ONE block: tau = the k-th largest group maximum (exact 3-level radix select over the n / G maxima, in shared
+//       memory).  The k largest group maxima are k distinct scores >= tau, so the k-th best score overall is >= tau:
+//       every member of the top-k has a score >= tau and sits in a group whose maximum is >= tau;
+//   K3  grid: groups with maximum >= tau are scanned, scores >= tau (and > min_score) become candidate keys; the last
+//       block to finish sorts the candidates (bitonic, shared memory) and emits the best k.
+// If more than TOPK_CAP scores reach tau (masses of equal scores), K3 raises `overflow` in the state and the caller
+// re-runs the exact radix path after its normal synchronisation -- a rare second round trip instead of a cost on
+// every query.  Same total order as above: (score desc, window index desc).
+// ---------------------------------------------------------------------------
+
+__device__ __forceinline__ float warp_max(float x) {
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		x = fmaxf(x, __shfl_xor_sync(0xffffffffu, x, o));
+	}
+	return x;
+}
+
+// one warp per group of G slots (G a multiple of 32)
+__global__ void __launch_bounds__(256) topk_group_max_kernel(const float *__restrict__ score, int64_t n_slots, int g_slots,
+	float *__restrict__ gmax, int64_t n_groups) {
+
+	const int lane = threadIdx.x & 31;
+	const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+	for (int64_t g = warp0; g < n_groups; g += n_warps) {
+		const int64_t base = g * g_slots;
+		float m = -CUDART_INF_F;
+		if ((g_slots & 127) == 0 && base + g_slots <= n_slots) {
+			const float4 *p4 = reinterpret_cast<const float4*>(score + base);
+			for (int i = lane; i < g_slots / 4; i += 32) {
+				const float4 x = __ldg(p4 + i);
+				m = fmaxf(fmaxf(m, fmaxf(x.x, x.y)), fmaxf(x.z, x.w));
+			}
+		} else {
+			for (int64_t i = base + lane; i < base + g_slots && i < n_slots; i += 32) {
+				m = fmaxf(m, score[i]);
+			}
+		}
+		m = warp_max(m);
+		if (lane == 0) {
+			gmax[g] = m;
+		}
+	}
+}
+
+struct PrunedState {
+	float tau;
+	unsigned int n_cand;
+	unsigned int ticket;
+	unsigned int overflow;
+};
+
+__global__ void __launch_bounds__(1024) topk_tau_kernel(const float *__restrict__ gmax, int64_t n_groups, int k, float min_score,
+	PrunedState *st) {
+
+	__shared__ unsigned int hist[2048];
+	__shared__ unsigned int sh_prefix, sh_remaining, sh_stop;
+	const int tid = threadIdx.x;
+	if (tid == 0) {
+		sh_prefix = 0;
+		sh_remaining = (unsigned int)k;
+		sh_stop = 0;
+	}
+	const int shifts[3] = {21, 10, 0};
+	const int bitsv[3] = {11, 11, 10};
+	for (int level = 0; level < 3; level++) {
+		for (int i = tid; i < 2048; i += blockDim.x) {
+			hist[i] = 0;
+		}
+		__syncthreads();
+		const unsigned int prefix = sh_prefix;
+		const int shift = shifts[level], bits = bitsv[level];
+		const unsigned int mask = (1u << bits) - 1;
+		for (int64_t i = tid; i < n_groups; i += blockDim.x) {
+			const float x = gmax[i];
+			if (!(x > min_score)) {
+				continue;
+			}
+			const unsigned int key = score_key(x);
+			if (level > 0 && (key >> (shift + bits)) != prefix) {
+				continue;
+			}
+			atomicAdd(&hist[(key >> shift) & mask], 1u);
+		}
+		__syncthreads();
+		{
+			// thread t owns the two bins 2047 - 2t, 2046 - 2t (from the top); inclusive block scan of their counts
+			__shared__ unsigned int warp_sum[32];
+			const int b0 = 2047 - 2 * tid;
+			const unsigned int c0 = hist[b0], c1 = hist[b0 - 1];
+			unsigned int incl = c0 + c1;
+			const int lane = tid & 31, wid = tid >> 5;
+			#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const unsigned int y = __shfl_up_sync(0xffffffffu, incl, o);
+				if (lane >= o) {
+					incl += y;
+				}
+			}
+			if (lane == 31) {
+				warp_sum[wid] = incl;
+			}
+			__syncthreads();
+			if (wid == 0) {
+				unsigned int ws = warp_sum[lane];
+				#pragma unroll
+				for (int o = 1; o < 32; o <<= 1) {
+					const unsigned int y = __shfl_up_sync(0xffffffffu, ws, o);
+					if (lane >= o) {
+						ws += y;
+					}
+				}
+				warp_sum[lane] = ws;
+			}
+			__syncthreads();
+			incl += wid > 0 ? warp_sum[wid - 1] : 0;
+			const unsigned int excl = incl - c0 - c1;
+			const unsigned int remaining = sh_remaining;
+			const unsigned int total = warp_sum[31];
+			__syncthreads();
+			if (total < remaining) {
+				if (tid == 0) {
+					sh_stop = 1;      // fewer than k groups above min_score: everything qualifies
+				}
+			} else if (excl < remaining && excl + c0 >= remaining) {
+				sh_prefix = (prefix << bits) | (unsigned int)b0;
+				sh_remaining = remaining - excl;
+			} else if (excl + c0 < remaining && incl >= remaining) {
+				sh_prefix = (prefix << bits) | (unsigned int)(b0 - 1);
+				sh_remaining = remaining - excl - c0;
+			}
+		}
+		__syncthreads();
+		if (sh_stop) {
+			break;
+		}
+	}
+	if (tid == 0) {
+		st->tau = sh_stop ? -CUDART_INF_F : key_score(sh_prefix);
+		st->n_cand = 0;
+		st->ticket = 0;
+		st->overflow = 0;
+	}
+}
+
+__global__ void __launch_bounds__(256) topk_collect_sort_kernel(const float *__restrict__ score, const uint32_t *__restrict__ orig,
+	const uint32_t *__restrict__ slot_of, int64_t n_slots, int g_slots, const float *__restrict__ gmax, int64_t n_groups,
+	float min_score, int k, PrunedState *st, unsigned long long *__restrict__ cand,
+	uint32_t *__restrict__ out_slots, float *__restrict__ out_scores, int32_t *__restrict__ out_n) {
+
+	extern __shared__ unsigned long long ps_keys[];   // TOPK_CAP keys (the last block's sort)
+	__shared__ unsigned int is_last;
+	const float tau = st->tau;
+	const int lane = threadIdx.x & 31;
+	const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+	// a warp looks at 32 group maxima at a time, then scans the qualifying groups together
+	for (int64_t g0 = warp0 * 32; g0 < n_groups; g0 += n_warps * 32) {
+		const int64_t g = g0 + lane;
+		const bool hit = g < n_groups && gmax[g] >= tau && gmax[g] > min_score;
+		unsigned int hits = __ballot_sync(0xffffffffu, hit);
+		while (hits) {
+			const int b = __ffs(hits) - 1;
+			hits &= hits - 1;
+			const int64_t base = (g0 + b) * g_slots;
+			if ((g_slots & 127) == 0 && base + g_slots <= n_slots) {
+				// four independent 16-byte loads per lane and step: the whole group is in flight at once
+				const float4 *p4 = reinterpret_cast<const float4*>(score + base);
+				for (int i0 = 0; i0 < g_slots / 4; i0 += 128) {
+					float4 x[4];
+					#pragma unroll
+					for (int r = 0; r < 4; r++) {
+						const int i = i0 + r * 32 + lane;
+						x[r] = i < g_slots / 4 ? __ldg(p4 + i) : make_float4(-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F);
+					}
+					#pragma unroll
+					for (int r = 0; r < 4; r++) {
+						const float e[4] = {x[r].x, x[r].y, x[r].z, x[r].w};
+						#pragma unroll
+						for (int q = 0; q < 4; q++) {
+							if (e[q] >= tau && e[q] > min_score) {
+								const int64_t i = base + 4 * (int64_t)(i0 + r * 32 + lane) + q;
+								const unsigned int at = atomicAdd(&st->n_cand, 1u);
+								if (at < TOPK_CAP) {
+									cand[at] = ((unsigned long long)score_key(e[q]) << 32) | orig[i];
+								}
+							}
+						}
+					}
+				}
+			} else {
+				for (int64_t i = base + lane; i < base + g_slots && i < n_slots; i += 32) {
+					const float sc = score[i];
+					if (sc >= tau && sc > min_score) {
+						const unsigned int at = atomicAdd(&st->n_cand, 1u);
+						if (at < TOPK_CAP) {
+							cand[at] = ((unsigned long long)score_key(sc) << 32) | orig[i];
+						}
+					}
+				}
+			}
+		}
+	}
+	__threadfence();
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		is_last = atomicAdd(&st->ticket, 1u) == gridDim.x - 1;
+	}
+	__syncthreads();
+	if (!is_last) {
+		return;
+	}
+	__threadfence();
+	unsigned int n = *reinterpret_cast<volatile unsigned int*>(&st->n_cand);
+	if (n > TOPK_CAP) {
+		if (threadIdx.x == 0) {
+			st->overflow = 1;
+			*out_n = 0;
+		}
+		return;
+	}
+	unsigned int mm = 1;
+	while (mm < n) {
+		mm <<= 1;
+	}
+	for (unsigned int i = threadIdx.x; i < mm; i += blockDim.x) {
+		ps_keys[i] = i < n ? __ldcg(cand + i) : 0ull;
+	}
+	__syncthreads();
+	for (unsigned int size = 2; size <= mm; size <<= 1) {
+		for (unsigned int stride = size >> 1; stride > 0; stride >>= 1) {
+			for (unsigned int i = threadIdx.x; i < mm; i += blockDim.x) {
+				const unsigned int j = i ^ stride;
+				if (j > i) {
+					const bool desc = (i & size) == 0;
+					const unsigned long long a = ps_keys[i], b = ps_keys[j];
+					if (desc ? a < b : a > b) {
+						ps_keys[i] = b;
+						ps_keys[j] = a;
+					}
+				}
+			}
+			__syncthreads();
+		}
+	}
+	const unsigned int n_out = n < (unsigned int)k ? n : (unsigned int)k;
+	for (unsigned int i = threadIdx.x; i < n_out; i += blockDim.x) {
+		const unsigned long long key = ps_keys[i];
+		out_slots[i] = slot_of[(uint32_t)(key & 0xffffffffull)];
+		out_scores[i] = key_score((unsigned int)(key >> 32));
+	}
+	if (threadIdx.x == 0) {
+		*out_n = (int32_t)n_out;
+	}
+}
+
+// Returns the number of launches (3), or 0 when the pruned path does not apply.  *overflow_flag_dev receives the
+// device address of the flag the caller must look at after synchronising (copy it with the results).
+int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out, const unsigned int **overflow_flag_dev) {
+	static const bool off = getenv("VX_TOPK_RADIX") != nullptr;   // A/B switch (read once)
+	if (off || k > TOPK_CAP / 4 || c->n_slots < 1) {
+		return 0;
+	}
+	// group size: many more groups than k, at most 1024 slots each
+	int g_slots = 1024;
+	while (g_slots > 32 && c->n_slots / g_slots < (int64_t)64 * k) {
+		g_slots >>= 1;
+	}
+	const int64_t n_groups = (c->n_slots + g_slots - 1) / g_slots;
+	const size_t need = sizeof(float) * (size_t)n_groups;
+	if (c->group_max_bytes < need) {
+		cudaFree(c->d_group_max);
+		c->d_group_max = nullptr;
+		c->group_max_bytes = 0;
+		if (cudaMalloc((void**)&c->d_group_max, need) != cudaSuccess) {
+			cudaGetLastError();
+			return 0;
+		}
+		c->group_max_bytes = need;
+	}
+	TopkWork *w;
+	topk_carve(work, k, &w, out);
+	PrunedState *st = reinterpret_cast<PrunedState*>(&w->hist[0][0]);   // the radix histograms are not used by this path
+	static int sms = 0;
+	static bool attr = false;
+	if (!sms) {
+		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+	}
+	const size_t smem = sizeof(unsigned long long) * TOPK_CAP;
+	if (!attr) {
+		cudaFuncSetAttribute(topk_collect_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		attr = true;
+	}
+	cudaStream_t st_ = c->stream;
+	int64_t blocks = (n_groups * 32 + 255) / 256;
+	blocks = blocks > (int64_t)sms * 8 ? (int64_t)sms * 8 : blocks < 1 ? 1 : blocks;
+	topk_group_max_kernel<<<(unsigned)blocks, 256, 0, st_>>>(c->d_score, c->n_slots, g_slots, c->d_group_max, n_groups);
+	topk_tau_kernel<<<1, 1024, 0, st_>>>(c->d_group_max, n_groups, k, min_score, st);
+	int64_t cblocks = (n_groups + 255) / 256;          // a warp takes 32 groups per step
+	cblocks = cblocks > sms ? sms : cblocks < 1 ? 1 : cblocks;
+	topk_collect_sort_kernel<<<(unsigned)cblocks, 256, smem, st_>>>(c->d_score, c->d_orig, c->d_slot_of, c->n_slots, g_slots,
+		c->d_group_max, n_groups, min_score, k, st, w->cand, out->slots, out->scores, out->n);
+	if (cudaGetLastError() != cudaSuccess) {
+		vx_set_error("pruned top-k launch failed");
+		return -1;
+	}
+	*overflow_flag_dev = &st->overflow;
+	return 3;
+}
+
 size_t vx_topk_work_bytes(int32_t k) {
 	return sizeof(TopkWork) + (size_t)k * (sizeof(uint32_t) + sizeof(float)) + 64;
 }
 
+static void topk_carve(void *work, int32_t k, TopkWork **w, VxTopkOut *out);
 static void topk_carve(void *work, int32_t k, TopkWork **w, VxTopkOut *out) {
 	*w = (TopkWork*)work;
 	uint8_t *tail = (uint8_t*)work + sizeof(TopkWork);

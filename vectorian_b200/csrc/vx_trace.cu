@@ -433,16 +433,29 @@ __device__ __forceinline__ void trace_warp_body(const TraceArgs &a, const VxAlig
 	SLayer P{vals + n_cell, tbs + 2 * n_cell, tbs + 3 * n_cell, ld};
 	SLayer Q{vals + 2 * n_cell, tbs + 4 * n_cell, tbs + 5 * n_cell, ld};
 
-	// similarity of the slice (same arithmetic as trace_kernel)
+	// similarity of the slice (same arithmetic as trace_kernel).  The token ids (and POS ids) of the window go to
+	// shared memory first, so that the S loads of the fill loop do not each wait for their own id load: the loop's
+	// iterations are then independent and pipeline (this fill was the longest serial chain of the kernel).
+	int32_t *ids_sh = reinterpret_cast<int32_t*>(vals);          // the value area is written after the fill
+	int8_t *pos_sh = reinterpret_cast<int8_t*>(ids_sh + len_s);
+	for (int u = lane; u < len_s; u += 32) {
+		const size_t ti = vx_elem(tl.base128, u, wlane);
+		ids_sh[u] = a.tok[ti];
+		if (qp.tag_weighted) {
+			pos_sh[u] = a.pos[ti];
+		}
+	}
+	__syncwarp();
+	#pragma unroll 4
 	for (int c = lane; c < len_s * len_t; c += 32) {
 		const int u = c / len_t, j = c - u * len_t;
 		const size_t ti = vx_elem(tl.base128, u, wlane);
-		float x = raw_sim(a, ti, a.tok[ti], j);
+		float x = raw_sim(a, ti, ids_sh[u], j);
 		if (qp.tag_weighted) {
 			const float tw = len_t <= VX_MAX_T_MASK ? qp.t_weights[j] : qp.t_weights_dev[j];
 			const int8_t tpos = len_t <= VX_MAX_T_MASK ? qp.t_pos[j] : qp.t_pos_dev[j];
 			float weight = tw;
-			if (a.pos[ti] != tpos) {
+			if (pos_sh[u] != tpos) {
 				weight *= 1.0f - qp.pos_mismatch_penalty;
 			}
 			const float sc = x * weight;
@@ -450,6 +463,7 @@ __device__ __forceinline__ void trace_warp_body(const TraceArgs &a, const VxAlig
 		}
 		sim[c] = x;
 	}
+	__syncwarp();
 
 	// borders
 	const float ninf = -CUDART_INF_F;
@@ -505,10 +519,59 @@ __device__ __forceinline__ void trace_warp_body(const TraceArgs &a, const VxAlig
 	}
 	__syncwarp();
 
+	// ---- general gap costs: VALUES first, predecessors only along the path ----
+	// The value of a cell is the maximum of its candidates, which does not depend on their order; only the
+	// predecessor does (first candidate in the reference's order that attains the maximum, solver.h:1320-1340,
+	// 3145-3173).  So the matrix is filled with plain maxima -- per row: the vertical scans of all columns in
+	// parallel (lane = column), then the horizontal scan along the row -- and the traceback below recomputes the
+	// candidates of the <= L + T cells it visits, in order, across the lanes.  Same fp32 operations on the same
+	// operands as the per-cell accumulator: identical values, identical pointers; ~6x faster than carrying
+	// (value, u, v) triples through L * T * (L + T) / 2 compare-select chains.
+	const bool fast_general = ap.gap_kind == VX_GAP_GENERAL && len_t <= 32;
+	float *gw_s = reinterpret_cast<float*>(tbs);     // gap tables in the (unused) traceback area: n_cell >= L + T + 2 floats
+	float *gw_t = gw_s + (len_s + 1);
+	if (fast_general) {
+		for (int i = lane; i <= len_s; i += 32) {
+			gw_s[i] = ap.w_s[i];
+		}
+		for (int i = lane; i <= len_t; i += 32) {
+			gw_t[i] = ap.w_t[i];
+		}
+		__syncwarp();
+		// lane v owns column v of the current row
+		const bool col = lane < len_t;
+		const int v = col ? lane : 0;
+		for (int u = 0; u < len_s; u++) {
+			// vertical candidates (k = -1 .. u-1), the diagonal, the left border, the Local zero
+			float acc = D.val[D.at(-1, v)] - gw_s[u + 1];
+			#pragma unroll 4
+			for (int k = 0; k < u; k++) {
+				acc = fmaxf(acc, D.val[D.at(k, v)] - gw_s[u - k]);
+			}
+			acc = fmaxf(acc, D.val[D.at(u - 1, v - 1)] + sim[u * len_t + v]);
+			acc = fmaxf(acc, D.val[D.at(u, -1)] - gw_t[v + 1]);
+			if (local) {
+				acc = fmaxf(acc, 0.0f);
+			}
+			// horizontal candidates: cell k of this row is final once the cells before it have been folded in; it is
+			// broadcast and every later column takes cell_k - w_t[v - k]
+			for (int k = 0; k + 1 < len_t; k++) {
+				const float ck = __shfl_sync(0xffffffffu, acc, k);
+				if (col && lane > k) {
+					acc = fmaxf(acc, ck - gw_t[lane - k]);
+				}
+			}
+			if (col) {
+				D.val[D.at(u, v)] = acc;
+			}
+			__syncwarp();
+		}
+	}
+
 	// ---- solve: anti-diagonals ----
 	const float w1s = ap.aff_ext_s + ap.aff_open_s;
 	const float w1t = ap.aff_ext_t + ap.aff_open_t;
-	for (int d = 0; d <= len_s + len_t - 2; d++) {
+	for (int d = 0; d <= len_s + len_t - 2 && !fast_general; d++) {
 		const int u_lo = d - (len_t - 1) > 0 ? d - (len_t - 1) : 0;
 		const int u_hi = d < len_s - 1 ? d : len_s - 1;
 		for (int u = u_lo + lane; u <= u_hi; u += 32) {
@@ -624,10 +687,70 @@ __device__ __forceinline__ void trace_warp_body(const TraceArgs &a, const VxAlig
 	}
 	__syncwarp();
 
+	// ---- traceback of the value-only matrix: all lanes walk, the candidates of each visited cell are spread over the
+	// lanes; winner = greatest value, on equal values the EARLIEST candidate in the reference's order:
+	//   0: diagonal; 1 .. u+1: (k, v) for k = -1 .. u-1; u+2 .. u+v+2: (u, k) for k = -1 .. v-1
+	// (the Local zero precedes them all but never wins here: a Local walk only visits cells with a value > 0)
+	float raw_fast = -CUDART_INF_F;
+	if (fast_general && have_seed) {
+		int u = su, v = sv;
+		raw_fast = D.val[D.at(u, v)];
+		int last_u = u, last_v = v;
+		while (u >= 0 && v >= 0 && (!local || D.val[D.at(u, v)] > 0.0f)) {
+			const int n_cand = u + v + 3;
+			float best = -CUDART_INF_F;
+			int best_i = 0x7fffffff;
+			for (int i = lane; i < n_cand; i += 32) {
+				float x;
+				if (i == 0) {
+					x = D.val[D.at(u - 1, v - 1)] + sim[u * len_t + v];
+				} else if (i <= u + 1) {
+					const int k = i - 2;
+					x = D.val[D.at(k, v)] - gw_s[u - k];
+				} else {
+					const int k = i - u - 3;
+					x = D.val[D.at(u, k)] - gw_t[v - k];
+				}
+				if (best_i == 0x7fffffff || x > best) {
+					best = x;
+					best_i = i;
+				}
+			}
+			#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) {
+				const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+				const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+				if (oi != 0x7fffffff && (best_i == 0x7fffffff || ob > best || (ob == best && oi < best_i))) {
+					best = ob;
+					best_i = oi;
+				}
+			}
+			int nu, nv;
+			if (best_i == 0) {
+				nu = u - 1;
+				nv = v - 1;
+			} else if (best_i <= u + 1) {
+				nu = best_i - 2;
+				nv = v;
+			} else {
+				nu = u;
+				nv = best_i - u - 3;
+			}
+			u = nu;
+			v = nv;
+			if (u != last_u && v != last_v && last_u >= 0 && last_v >= 0 && lane == 0) {
+				target_sh[last_v] = (int16_t)last_u;
+			}
+			last_u = u;
+			last_v = v;
+		}
+		__syncwarp();
+	}
+
 	// ---- traceback (lane 0), score, flow ----
 	if (lane == 0) {
-		float raw = -CUDART_INF_F;
-		if (have_seed) {
+		float raw = raw_fast;
+		if (have_seed && !fast_general) {
 			int u = su, v = sv;
 			raw = D.val[D.at(u, v)];
 			int last_u = u, last_v = v;
