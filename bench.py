@@ -426,10 +426,42 @@ def main():
 			rp, dtp, _ = cpu_port_rate(args.cpu_sample, threads)
 			line["cpu_port"] = {"value": rp, "unit": "sentences/s", "cores": threads,
 				"what": "oracle/vx_oracle.c (optimised C restatement), same sample"}
+		if world == 1 and not args.no_secondary:
+			line["secondary"] = secondary_configs(emb)
 		emit_line(json.dumps(line))
 
 	if world > 1:
 		dist.destroy_process_group()
+
+
+def secondary_configs(emb50k):
+	"""The other BASELINE.json configs on this GPU, a few steps each (scripts/bench_configs.py): so that the driver sees
+	them too.  Times are medians of device phases (CUDA events); each entry names its own bound."""
+	import importlib.util
+	spec = importlib.util.spec_from_file_location("bench_configs", os.path.join(ROOT, "scripts", "bench_configs.py"))
+	bc = importlib.util.module_from_spec(spec)
+	spec.loader.exec_module(bc)
+	from vectorian_b200 import _cabi, gaps
+	bc.COLLECT = []
+	out = {}
+	try:
+		bc.run_static("C2 SW Local linear(0.2) T=8 1M V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 1_000_000, 200_000, 300, steps=8, cand_per_cell=3.5)
+		r = bc.COLLECT[-1]
+		out["c2"] = {"workload": r["config"], "sentences_per_s_device": r["sentences_per_s_device"], "sentences_per_s_e2e": r["sentences_per_s_e2e"],
+			"device_ms": r["device_ms"], "phases_ms": r["ms"], "roofline": {"bound": "fp32-issue (SURVEY 8d currency; the kernel itself sits at the L1TEX wavefront limit of the S gather, profiles/r1_linear)",
+			"frac": r["dp_issue_frac"]}, "sim_hbm_frac": r["sim_hbm_frac"]}
+		bc.run_contextual("C4 shard: NW Global linear(0.1) contextual d=128 T=8, 200k sentences (5 M tokens; 768->128 PCA taken as given)", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.1), 8, 200_000, 128, steps=8)
+		r = bc.COLLECT[-1]
+		out["c4_shard"] = {"workload": r["config"], "sentences_per_s_device": r["sentences_per_s_device"], "sentences_per_s_e2e": r["sentences_per_s_e2e"],
+			"phases_ms": r["ms"], "roofline": {"bound": "hbm", "frac": r["gemm_dp_hbm_frac_lower_bound"],
+			"note": "fused tcgen05 GEMM + DP kernel: algorithmic bytes tokens x (4 d + 4 TP) / kernel time vs MEASURED_PEAKS hbm_gbs"}}
+		bc.run_sweep("C5 on one GPU: 64 queries x {linear 0,.1,.2,.5} x {Local,Global}, T=12, 10M sentences", 10_000_000, embedding=emb50k)
+		r = bc.COLLECT[-1]
+		out["c5_1gpu"] = {"workload": r["config"], "batch_wall_ms": r["batch_wall_ms"], "batch_device_ms": r["batch_device_ms"],
+			"single_calls_wall_ms": r["single_calls_wall_ms"], "sentence_alignments_per_s_e2e": r["sentence_alignments_per_s_e2e"], "launches": r["launches"]}
+	except Exception as e:   # the headline line must not depend on the secondary block
+		out["error"] = repr(e)
+	return out
 
 
 def emit_line(text):

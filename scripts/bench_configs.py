@@ -49,10 +49,23 @@ def reduce_max(values):
 	return dict(zip(keys, x.tolist()))
 
 
+COLLECT = None   # bench.py sets this to a list: results are collected instead of printed
+
+
 def emit(out):
 	if RANK == 0:
 		out["n_gpus"] = WORLD
-		print(json.dumps(out), flush=True)
+		if COLLECT is not None:
+			COLLECT.append(out)
+		else:
+			print(json.dumps(out), flush=True)
+
+
+def attach_shard(dc, n_doc):
+	"""Multi-GPU: gather + merge of the ranks' result rows happen inside vx_search / vx_search_batch (csrc/vx_shard.cu)."""
+	if WORLD > 1:
+		from vectorian_b200.distributed import device_comm
+		dc.set_shard(device_comm(), RANK * n_doc)
 
 
 def peaks():
@@ -62,14 +75,13 @@ def peaks():
 		return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}
 
 
-def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand_per_cell=None):
-	from vectorian_b200.distributed import gather_topk
-	n_total = n_sent
+def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand_per_cell=None, embedding=None):
 	n_sent = n_sent // WORLD
 	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
 	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	attach_shard(dc, tables["n_doc"])
 	del tok
-	emb = synthetic.make_embedding(vocab, dim)
+	emb = embedding if embedding is not None else synthetic.make_embedding(vocab, dim)
 	de = engine.DeviceEmbedding(emb)
 	r = gaps.resolve_gap_costs(gap, 64, t)
 	kind = r.pop("gap_kind")
@@ -83,8 +95,6 @@ def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand
 		t0 = time.perf_counter()
 		sim = engine.DeviceSim.static(de, q, emb[q])
 		hits, target, dist = dc.search(sim, ap, qp)
-		if WORLD > 1:
-			hits, target, dist = gather_topk(hits, target, dist, k, doc_offset=RANK * tables["n_doc"])
 		t1 = time.perf_counter()
 		if i >= 3:
 			lt = dc.last_timing()
@@ -121,7 +131,6 @@ def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand
 
 def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
 	import torch
-	from vectorian_b200.distributed import gather_topk
 	n_sent = n_sent // WORLD
 	tok, tables = synthetic.make_corpus_device(n_sent, 50_000, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
 	n_tok = int(tok.numel())
@@ -133,6 +142,7 @@ def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
 		x[i:i + min(chunk, n_tok - i)].normal_(generator=g)
 	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
 	dc.set_contextual(x)
+	attach_shard(dc, tables["n_doc"])
 	rng = np.random.default_rng(5)
 	qrows = x[torch.from_numpy(rng.integers(0, n_tok, size=(3 + steps, t))).to(DEV)].cpu().numpy()
 	del x, tok
@@ -148,8 +158,6 @@ def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
 		t0 = time.perf_counter()
 		sim = engine.DeviceSim.contextual(q)
 		hits, target, dist = dc.search(sim, ap, qp)
-		if WORLD > 1:
-			hits, target, dist = gather_topk(hits, target, dist, k, doc_offset=RANK * tables["n_doc"])
 		t1 = time.perf_counter()
 		if i >= 3:
 			lt = dc.last_timing()
@@ -173,14 +181,14 @@ def run_contextual(name, locality, gap, t, n_sent, dim, k=100, steps=10):
 	dc.close()
 
 
-def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
+def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100, embedding=None):
 	"""C5: n_queries x 8 settings ({LinearGapCost(u), u in 0,.1,.2,.5} x {Local, Global}) without re-preprocessing."""
-	from vectorian_b200.distributed import gather_topk_many
 	n_sent = n_sent // WORLD
 	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
 	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	attach_shard(dc, tables["n_doc"])
 	del tok
-	emb = synthetic.make_embedding(vocab, dim)
+	emb = embedding if embedding is not None else synthetic.make_embedding(vocab, dim)
 	de = engine.DeviceEmbedding(emb)
 	aps, keeps = [], []
 	for loc in (_cabi.VX_LOCAL, _cabi.VX_GLOBAL):
@@ -204,13 +212,10 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100):
 			if mode == "single":
 				top = [[dc.search(sim, ap, qp)[0]["score"][0] for ap in aps] for sim in sims]
 			else:
-				out = dc.search_batch(sims, aps, qp, raw=WORLD > 1)
+				out = dc.search_batch(sims, aps, qp)   # WORLD > 1: ONE all-gather + ONE merge launch for all pairs, inside the call
 				tb = time.perf_counter()
-				host = {"sims_ms": (ta - t0) * 1e3, "search_batch_ms": (tb - ta) * 1e3}
-				if WORLD > 1:   # ONE all-gather for all queries x settings pairs
-					flat = gather_topk_many(out, k, doc_offset=RANK * tables["n_doc"])
-					out = [[flat[q * len(aps) + a] for a in range(len(aps))] for q in range(len(sims))]
-				host["gather_merge_ms"] = (time.perf_counter() - tb) * 1e3
+				host = {"sims_ms": (ta - t0) * 1e3, "search_batch_ms": (tb - ta) * 1e3,
+					"gather_merge_ms": dc.last_timing()["gather_merge_ms"]}
 				top = [[out[q][a][0]["score"][0] for a in range(len(aps))] for q in range(len(sims))]
 				dev_ms = dc.last_timing()["dp_ms"]
 			t1 = time.perf_counter()
