@@ -400,3 +400,39 @@ def test_long_query_through_find(oracle):
 	np.testing.assert_allclose(s, oracle.sim_static(vv.unmodified, q_id, q_vec), rtol=0, atol=1e-5)
 	result, _ = check_find(oracle, session, emb, index, text, n=10, min_score=0.01, s=s)
 	assert len(result) == 10
+
+
+def test_debug_hook_reports_matrix_and_every_slice():
+	"""The `debug` option (cpp/query.cpp:73-74): one "static_similarity_matrix" call, then one "alignment" call per slice
+	with {slice, similarity, flow, score} (cpp/metric/alignment.h:144-173) -- the flows of the slices that make the result
+	equal the result's, the raw score is score * score_max."""
+	session, (emb,) = make_session(n_docs=3, sent_per_doc=25)
+	index = session.partition("sentence").index(
+		OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), LocalAlignment(gap=gaps.smooth_gap_cost(5))), nlp=whitespace_nlp)
+	calls = []
+	result = index.find("w3 w17 w5 w9", n=10, min_score=0.0, debug=lambda name, data: calls.append((name, data)))
+	names = [c[0] for c in calls]
+	assert names[0] == "static_similarity_matrix" and names.count("static_similarity_matrix") == 1
+	m = calls[0][1]
+	assert m["similarity"].shape == (session.vocab.size, 4) and m["columns"]() == ["w3", "w17", "w5", "w9"]
+	assert len(m["rows"]()) == session.vocab.size
+	per_slice = [c[1] for c in calls if c[0] == "alignment"]
+	assert len(per_slice) == 3 * 25          # every slice of every document, slice ids ascending per document
+	assert [d["slice"] for d in per_slice[:25]] == list(range(25))
+	by_key = {}
+	doc = -1
+	for d in per_slice:
+		if d["slice"] == 0:
+			doc += 1
+		by_key[(doc, d["slice"])] = d
+	assert len(result) > 0
+	for match in result:
+		d = by_key[(match.prepared_doc.id, match.slice_id)]
+		np.testing.assert_array_equal(d["flow"]["target"], match.flow["target"])
+		assert d["similarity"].shape[1] == 4 and d["similarity"].shape[0] >= 1
+		np.testing.assert_allclose(d["score"], match.score * match.score_max, rtol=1e-6)
+	big = session.partition("sentence").index(
+		OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), LocalAlignment()), nlp=whitespace_nlp)
+	big.DEBUG_MAX_WINDOWS = 10
+	with pytest.raises(NotImplementedError, match="debug hook"):
+		big.find("w3 w17", debug=lambda name, data: None)

@@ -526,7 +526,7 @@ static int launch_score_tl(vx_corpus *c, const vx_sim *s, const ScoreArgs &a, co
 		default: {
 			// windows up to 64 tokens: shared-memory kernel (vx_wsb.cu); the rest: global scratch
 			int64_t first = 0;
-			const int n_fast = vx_launch_wsb(c, s, ap, qp, &first);
+			const int n_fast = vx_launch_wsb(c, s, ap, qp, &first, a.tok);
 			if (n_fast < 0) {
 				return -1;
 			}
@@ -632,14 +632,14 @@ int vx_launch_score_multi(vx_corpus *c, const vx_sim *s, const VxQueryDev &qp, i
 // Fast path preconditions: static similarity, T <= 16, plain (isolated) scoring with
 // submatch_weight == 0, so that reference_score == T exactly.  Everything else is scored by the
 // exact kernel in vx_trace.cu (the caller decides).
-int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp) {
+int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, const int32_t *ids) {
 	if (c->n_tiles == 0) {
 		return 0;
 	}
 	ScoreArgs a;
 	a.tiles = c->d_tiles;
 	a.n_tiles = c->n_tiles;
-	a.tok = c->d_tok;
+	a.tok = ids ? ids : c->d_tok;
 	a.s = s->d_s;
 	a.boost = c->d_boost;
 	a.score = c->d_score;

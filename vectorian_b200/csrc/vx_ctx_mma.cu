@@ -635,10 +635,18 @@ static int launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const flo
 	const size_t smem = fixed + (size_t)n_raw * CM_SUB_BYTES;
 	#define VX_CM_CASE(TP) case TP: \
 		if (fused) { \
-			cudaFuncSetAttribute(ctx_mma_kernel<TP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+			static size_t smem_set = 0; \
+			if (smem > smem_set) { \
+				cudaFuncSetAttribute(ctx_mma_kernel<TP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+				smem_set = smem; \
+			} \
 			ctx_mma_kernel<TP, true><<<grid, CM_THREADS, smem, st>>>(tmap, a); \
 		} else { \
-			cudaFuncSetAttribute(ctx_mma_kernel<TP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+			static size_t smem_set = 0; \
+			if (smem > smem_set) { \
+				cudaFuncSetAttribute(ctx_mma_kernel<TP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+				smem_set = smem; \
+			} \
 			ctx_mma_kernel<TP, false><<<grid, CM_THREADS, smem, st>>>(tmap, a); \
 		} \
 		break;

@@ -186,11 +186,12 @@ struct VxQueryDev {
 // ---------------------------------------------------------------------------
 
 // vx_align.cu -- score-only DP over every tile; writes c->d_score[slot].
-int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp);
+// `ids` = the token-id stream the kernels gather S rows with: c->d_tok, or c->d_iota for per-token rows (S_doc)
+int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, const int32_t *ids = nullptr);
 
 // vx_wsb.cu -- general gap cost, windows up to 64 tokens, history in shared memory.  Handles the
 // tiles [*first_tile, n_tiles); the longer ones are left to the scratch kernel of vx_align.cu.
-int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, int64_t *first_tile);
+int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, int64_t *first_tile, const int32_t *ids);
 
 // vx_trace.cu -- exact DP with traceback for a list of slots (device array), one thread per item.
 struct VxTraceOut {

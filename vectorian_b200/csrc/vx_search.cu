@@ -305,11 +305,7 @@ static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 		// per-token rows uploaded by the host, already in tiled element order: d_iota stands in for the token ids
 		vx_sim shadow = *s;
 		shadow.contextual = 0;
-		int32_t *tok = c->d_tok;
-		c->d_tok = c->d_iota;
-		const int n1 = vx_launch_score(c, &shadow, p.ap, p.qp);
-		c->d_tok = tok;
-		return n1;
+		return vx_launch_score(c, &shadow, p.ap, p.qp, c->d_iota);
 	}
 	if (p.fast && s->contextual) {
 		bool fused_done = false;
@@ -321,10 +317,7 @@ static int score_everything(vx_corpus *c, const vx_sim *s, const QueryPlan &p) {
 		shadow.contextual = 0;
 		shadow.d_s = c->d_sdoc;
 		shadow.rows = c->n_tok_tiled;
-		int32_t *tok = c->d_tok;
-		c->d_tok = c->d_iota;               // "token id" = element index -> row of S_doc
-		const int n1 = vx_launch_score(c, &shadow, p.ap, p.qp);
-		c->d_tok = tok;
+		const int n1 = vx_launch_score(c, &shadow, p.ap, p.qp, c->d_iota);   // "token id" = element index -> row of S_doc
 		return n1 < 0 ? n1 : n0 + n1;
 	}
 	if (p.fast) {

@@ -55,61 +55,6 @@ int vx_launch_normalize(const float *d_in, float *d_out, int64_t rows, int32_t d
 	return 1;
 }
 
-// S row per warp.  Qhat[t x d] is staged in shared memory once per block; each lane keeps TP partial
-// dot products over its strided slice of the row, then the warp reduces them.
-template<int TP>
-__global__ void sim_static_kernel(const float *__restrict__ ehat, int64_t v, int32_t d,
-	const float *__restrict__ qhat, const int32_t *__restrict__ qid, int32_t t,
-	float *__restrict__ s) {
-
-	extern __shared__ float q_sh[];   // [t x d]
-	for (int i = threadIdx.x; i < t * d; i += blockDim.x) {
-		q_sh[i] = qhat[i];
-	}
-	__syncthreads();
-
-	const int lane = threadIdx.x & 31;
-	const int warps_per_block = blockDim.x / 32;
-	for (int64_t row = (int64_t)blockIdx.x * warps_per_block + threadIdx.x / 32; row < v;
-		row += (int64_t)gridDim.x * warps_per_block) {
-
-		const float *src = ehat + row * d;
-		float acc[TP];
-		#pragma unroll
-		for (int j = 0; j < TP; j++) {
-			acc[j] = 0.0f;
-		}
-		for (int k = lane; k < d; k += 32) {
-			const float x = src[k];
-			#pragma unroll
-			for (int j = 0; j < TP; j++) {
-				if (j < t) {
-					acc[j] = fmaf(x, q_sh[j * d + k], acc[j]);
-				}
-			}
-		}
-		#pragma unroll
-		for (int j = 0; j < TP; j++) {
-			acc[j] = warp_sum(acc[j]);
-		}
-		if (lane == 0) {
-			#pragma unroll
-			for (int j = 0; j < TP; j++) {
-				float x = 0.0f;
-				if (j < t) {
-					x = acc[j];
-					if (qid[j] == row) {
-						x = 1.0f;                     // identity fix-up, cpp/metric/static.cpp:58-67
-					}
-					x = fminf(fmaxf(x, 0.0f), 1.0f);  // clip, cpp/metric/metric.h:28-30
-				}
-				s[row * TP + j] = x;
-			}
-		}
-	}
-}
-
-
 // 8 lanes per row, 2 rows per lane group: lane `sub` of a group takes the dimensions k = 8m + sub, so
 // the group reads 32 contiguous bytes of each row per step and -- with Qhat staged k-major in shared
 // memory ([d][TPS], TPS padded so that the 8 lanes hit 8 different bank quads) -- one LDS.128 feeds
@@ -220,8 +165,13 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 		if (blocks4 > cap4) {
 			blocks4 = cap4;
 		}
-		#define VX_SIM4_CASE(TP) case TP: \
-			cudaFuncSetAttribute(sim_static_g8_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4); \
+		// the attribute is raised once per instantiation and only ever grows (one process drives one device)
+		#define VX_SIM4_CASE(TP) case TP: { \
+			static size_t smem_set = 0; \
+			if (smem4 > smem_set) { \
+				cudaFuncSetAttribute(sim_static_g8_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4); \
+				smem_set = smem4; \
+			} } \
 			sim_static_g8_kernel<TP><<<(unsigned)blocks4, warps * 32, smem4, st>>>(d_ehat, v, d, d_qhat, d_qid, t, d_s); \
 			return 1;
 		switch (tp) {
@@ -234,25 +184,6 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 		}
 		#undef VX_SIM4_CASE
 	}
-	const size_t smem = sizeof(float) * (size_t)t * d;
-	int64_t blocks = (v + warps - 1) / warps;
-	if (blocks > 148 * 16) {
-		blocks = 148 * 16;
-	}
-	#define VX_SIM_CASE(TP) case TP: \
-		cudaFuncSetAttribute(sim_static_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-		sim_static_kernel<TP><<<(unsigned)blocks, warps * 32, smem, st>>>(d_ehat, v, d, d_qhat, d_qid, t, d_s); \
-		break;
-	switch (tp) {
-		VX_SIM_CASE(4)
-		VX_SIM_CASE(8)
-		VX_SIM_CASE(12)
-		VX_SIM_CASE(16)
-		default:
-			return -1;
-	}
-	#undef VX_SIM_CASE
-	return 1;
 }
 
 
@@ -377,7 +308,11 @@ int vx_launch_ctx_sim(const float *d_x, int64_t n_elem, int32_t d, const float *
 	}
 	#define VX_CTX_CASE(TP) case TP: \
 		if (vec) { \
-			cudaFuncSetAttribute(ctx_sim_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+			static size_t smem_set = 0; \
+			if (smem > smem_set) { \
+				cudaFuncSetAttribute(ctx_sim_kernel<TP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+				smem_set = smem; \
+			} \
 			ctx_sim_kernel<TP><<<(unsigned)blocks, 128, smem, st>>>(d_x, n_elem, d, d_qhat, t, d_sdoc); \
 		} else { \
 			ctx_sim_scalar_kernel<TP><<<(unsigned)((n_elem + 127) / 128), 128, 0, st>>>(d_x, n_elem, d, d_qhat, t, d_sdoc); \

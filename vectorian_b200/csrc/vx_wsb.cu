@@ -650,7 +650,7 @@ static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, b
 // Scores every tile whose windows are at most VX_WSB_MAX_LEN long; *first_tile receives the index of
 // the first tile handled (tiles are sorted by descending length, so [0, *first_tile) are the long ones
 // left to the scratch kernel).  Returns launches or < 0.
-int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, int64_t *first_tile) {
+int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, int64_t *first_tile, const int32_t *ids) {
 	const float *h_ws = ap.h_w_s, *h_wt = ap.h_w_t;
 
 	*first_tile = c->n_tiles;
@@ -663,7 +663,7 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	WsbArgs a;
 	memset(&a, 0, sizeof(a));
 	a.tiles = c->d_tiles;
-	a.tok = c->d_tok;
+	a.tok = ids;
 	a.s = s->d_s;
 	a.boost = c->d_boost;
 	a.score = c->d_score;

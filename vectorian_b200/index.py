@@ -402,13 +402,15 @@ class BruteForceIndex(Index):
 			if owner is not None:
 				dc.set_boost(None)
 				dc.boost_owner = None
+				dc.boost_values = None
 			return
 		if owner is self:
 			return
 		session = self.session
 		lo, hi = session.shard[2:]
 		boost = [np.asarray(self._saliency(d, self.partition), dtype=np.float32) for d in session.documents[lo:hi]]
-		dc.set_boost(np.concatenate(boost) if boost else np.zeros((0,), np.float32))
+		dc.boost_values = np.concatenate(boost) if boost else np.zeros((0,), np.float32)
+		dc.set_boost(dc.boost_values)
 		dc.boost_owner = self
 
 	@staticmethod
@@ -555,6 +557,68 @@ class BruteForceIndex(Index):
 			submatch_weight=options.get("submatch_weight", 0.0), **qkw)
 		return qp, keep_q, k
 
+	DEBUG_MAX_WINDOWS = 8192   # the traceback of every window comes from ONE search with max_matches = #windows
+
+	def _call_debug_hook(self, hook, dc, sim, ap, metric_args, options, p_query, token_filter):
+		"""The `debug` query option (cpp/query.cpp:73-74): the reference calls the hook once with the static similarity
+		matrix ("static_similarity_matrix": similarity, rows, columns; cpp/metric/static.cpp:196-231, cpp/query.cpp:132-134)
+		and then for EVERY slice with {"slice", "similarity" [len_s x len_t], "flow", "score" (raw aligner score)} under the
+		name "alignment" (cpp/metric/alignment.h:144-173, 279-282, 472).  Here the per-slice data comes from one extra search
+		with max_matches = number of windows and no score floor; windows are reported in document order, slice ascending.
+		A debugging aid for small corpora: more than DEBUG_MAX_WINDOWS windows per shard are refused."""
+		session = self.session
+		s_matrix = None
+		if sim.rows > 0:
+			s_matrix = sim.download()
+			if not metric_args['token_metric'].is_modifier:
+				vocab = session.vocab
+				hook("static_similarity_matrix", {
+					"similarity": s_matrix,
+					"rows": lambda: list(vocab.tokens.strings),
+					"columns": lambda: list(p_query.token_str)})
+		n_win = dc.n_windows
+		if n_win > self.DEBUG_MAX_WINDOWS:
+			raise NotImplementedError(
+				f"the debug hook reports every slice; {n_win} windows exceed the {self.DEBUG_MAX_WINDOWS} a debug search can trace")
+		if n_win == 0:
+			return
+		d_opts = dict(options, max_matches=n_win, min_score=-np.inf)
+		qp_all, keep_all, _ = self._query_params(d_opts, metric_args, p_query)
+		was_sharded = dc.sharded
+		comm = getattr(dc, "_comm", None)
+		if was_sharded:
+			dc.set_shard(None, 0)       # the hook reports this rank's slices
+		try:
+			hits, target, dist = dc.search(sim, ap, qp_all)
+		finally:
+			if was_sharded:
+				dc.set_shard(comm, session.shard[2])
+		tb = session._filtered_tables(self.partition, token_filter)
+		ids = tb["token_id"]
+		boost = getattr(dc, "boost_values", None)
+		size, step = self.partition.window_size, self.partition.window_step
+		rows = {(int(h["doc"]), int(h["slice"])): i for i, h in enumerate(hits)}
+		for d in range(len(tb["doc_tok_off"]) - 1):
+			st = tb["span_start"][tb["doc_span_off"][d]:tb["doc_span_off"][d + 1]]
+			en = tb["span_end"][tb["doc_span_off"][d]:tb["doc_span_off"][d + 1]]
+			n = len(st)
+			token_at = 0
+			for slice_id in range(0, n, step):              # Spans::iterate, cpp/document.h:147-169
+				len_s = int(en[min(slice_id + size - 1, n - 1)]) - int(st[slice_id])
+				if len_s >= 1 and (d, slice_id) in rows:
+					i = rows[(d, slice_id)]
+					t0 = int(tb["doc_tok_off"][d]) + token_at
+					sim_ij = s_matrix[ids[t0:t0 + len_s]] if s_matrix is not None else None
+					t = sim.t
+					b = float(boost[int(tb["doc_span_off"][d]) + slice_id]) if boost is not None else 1.0
+					hook("alignment", {
+						"slice": slice_id,
+						"similarity": sim_ij,
+						"flow": {"type": "injective", "target": target[i].copy(),
+							"flow": (target[i] >= 0).astype(np.float32), "dist": dist[i].copy()},
+						"score": float(hits["score"][i]) * float(hits["score_max"][i]) / (b if b else 1.0)})
+				token_at += int(en[min(slice_id + step - 1, n - 1)]) - int(st[slice_id])
+
 	def _find(self, query, n_threads=None, progress=None):
 		p_query = query.prepare(self._nlp)
 		if len(p_query) == 0:
@@ -577,6 +641,8 @@ class BruteForceIndex(Index):
 		qp, keep_q, k = self._query_params(options, metric_args, p_query)
 		metric_name = self._metric_name(self, metric_args['token_metric'])
 
+		if options.get("debug") is not None:
+			self._call_debug_hook(options["debug"], dc, sim, ap, metric_args, options, p_query, token_filter)
 		hits, target, dist = dc.search(sim, ap, qp)
 		self.last_timing = dict(dc.last_timing(), sim_ms=sim.build_ms)
 		sim.close()
