@@ -38,7 +38,9 @@ def main():
 	names = demangle(list(counts))
 	rows = []
 	for k, c in counts.items():
-		name = re.sub(r"\(.*", "", names.get(k, k)).replace("void ", "").replace("(anonymous namespace)::", "")
+		name = names.get(k, k).replace("void ", "").replace("(anonymous namespace)::", "")
+		name = re.sub(r"_GLOBAL__N__\w+::", "", name)
+		name = re.sub(r"\(.*", "", name)
 		rows.append((name, c))
 	rows.sort(key=lambda r: r[0])
 	with open(dst, "w") as f:
