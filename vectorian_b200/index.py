@@ -280,7 +280,8 @@ class CoreMatch(Match):
 		span = pdoc.span(part, self._slice_id)
 		token_at, n_tok = span.start, doc.n_tokens
 		idx, ln = doc.token_idx, doc.token_len
-		edges = sorted((int(u), j) for j, u in enumerate(self._target) if u >= 0)
+		# InjectiveFlow::to_edges + the sort of flow.cpp:32-41 (by target; all flows of an injective alignment are 1)
+		edges = sorted(((int(u), j) for j, u in enumerate(self._target) if u >= 0), key=lambda e: e[0])
 		index_map = None
 		if self._token_filter is not None:
 			# targets count the tokens that pass the filter: back to window positions (cpp/match/flow.cpp:49-61, 95-99)
@@ -295,7 +296,9 @@ class CoreMatch(Match):
 		last_anchor = max(0, token_at + edges[0][0] - context_size)
 		last_matched = False
 		last_source = -1
-		for target, source in edges:
+		i = 0
+		while i < len(edges):
+			target = edges[i][0]
 			if index_map is not None:
 				target = int(index_map[target])
 			s_i = token_at + target
@@ -303,18 +306,26 @@ class CoreMatch(Match):
 			if int(idx[s_i]) > idx0:
 				p = gap_s(s_i - last_anchor) if last_matched else 0.0
 				regions.append(Region(s=s_text[idx0:int(idx[s_i])], match=None, gap_penalty=p))
-			if last_source >= 0:
-				p = gap_t(source - last_source - 1)
-				if p > 0.0:
-					regions.append(Region(s="", match=None, gap_penalty=p))
-			last_source = source
-			t = self._query.tokens[source]
-			edge = TokenMatchEdge(
-				t=TokenMatchT(text=t_text[t['start']:t['end']], index=source, pos=t.get('pos', 'X')),
-				flow=1.0, distance=float(self._dist[source]), metric=self._metric)
+			region_edges = []
+			while True:
+				source = edges[i][1]
+				if last_source >= 0:
+					p = gap_t(source - last_source - 1)
+					if p > 0.0:
+						regions.append(Region(s="", match=None, gap_penalty=p))
+				last_source = source
+				t = self._query.tokens[source]
+				region_edges.append(TokenMatchEdge(
+					t=TokenMatchT(text=t_text[t['start']:t['end']], index=source, pos=t.get('pos', 'X')),
+					flow=1.0, distance=float(self._dist[source]), metric=self._metric))
+				i += 1
+				# flow.cpp:143 groups the following edges whose RAW target equals this edge's MAPPED target; without a
+				# token filter the two coincide and an injective flow never repeats a target.  Kept as the reference has it.
+				if not (i < len(edges) and edges[i][0] == target):
+					break
 			regions.append(Region(
 				s=s_text[int(idx[s_i]):int(idx[s_i]) + int(ln[s_i])],
-				match=TokenMatch(pos_s=doc.token_pos[s_i], edges=[edge]), gap_penalty=0.0))
+				match=TokenMatch(pos_s=doc.token_pos[s_i], edges=region_edges), gap_penalty=0.0))
 			last_anchor = s_i + 1
 			last_matched = True
 		up_to = min(last_anchor + context_size, n_tok - 1)
