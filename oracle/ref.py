@@ -115,3 +115,38 @@ def corpus_scores(locality, resolved, s, token_id, sent_off, max_len_s, n_thread
 	if rc != 0:
 		raise RuntimeError("reference solver failed: " + lib().ref_last_error().decode())
 	return out
+
+
+# ---- the reference's own ResultSet (oracle/ref/resultset_driver.cpp) ----
+
+RS_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libresultset_ref.so")
+_rs_lib = None
+
+
+def result_set_available():
+	return os.path.exists(RS_LIB_PATH)
+
+
+def result_set(raw, score_max, doc, slice_id, max_matches, min_score, boost=None):
+	"""Windows (document-major, slice ascending) through the reference's unmodified result_set.h / result_set.cpp /
+	match_impl.h the way _find drives them: a ResultSet per document (`score > worst_score()` admission), extend() in
+	document order, best_n.  Returns (doc, slice, score) arrays of the winners, best first."""
+	global _rs_lib
+	if _rs_lib is None:
+		_rs_lib = C.CDLL(RS_LIB_PATH)
+		_rs_lib.ref_result_set.restype = C.c_int
+		_rs_lib.ref_result_set.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+			C.c_int32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+	raw = np.ascontiguousarray(raw, dtype=np.float32)
+	score_max = np.ascontiguousarray(score_max, dtype=np.float32)
+	doc = np.ascontiguousarray(doc, dtype=np.int32)
+	slice_id = np.ascontiguousarray(slice_id, dtype=np.int32)
+	b = None if boost is None else np.ascontiguousarray(boost, dtype=np.float32)
+	k = int(max_matches)
+	o_doc = np.zeros((k,), np.int32)
+	o_slice = np.zeros((k,), np.int32)
+	o_score = np.zeros((k,), np.float32)
+	n = C.c_int32(0)
+	_rs_lib.ref_result_set(raw.ctypes.data, score_max.ctypes.data, None if b is None else b.ctypes.data, doc.ctypes.data,
+		slice_id.ctypes.data, len(raw), k, float(min_score), o_doc.ctypes.data, o_slice.ctypes.data, o_score.ctypes.data, C.byref(n))
+	return o_doc[:n.value], o_slice[:n.value], o_score[:n.value]

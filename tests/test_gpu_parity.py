@@ -405,3 +405,27 @@ def test_contextual_fused_is_race_free(engine, t, dim):
 		else:
 			np.testing.assert_array_equal(scores, first, err_msg=f"run {rep}")
 	dc.close()
+
+
+@pytest.mark.parametrize("k,min_score", [(100, 0.0), (7, 0.0), (40, 0.5), (500, 0.0), (2000, 0.9)])
+def test_gpu_top_k_equals_reference_result_set(engine, k, min_score):
+	"""a12 pinned to the reference itself: the device top-k (pruned selection, or the radix select it falls back to) returns
+	the winners of the reference's own, unmodified ResultSet + Match::compare_by_score (oracle/ref/resultset_driver.cpp)
+	on an input full of score ties across documents -- same scores, same documents, same slices, same order."""
+	from oracle import ref
+	from tests.test_oracle_vs_ref import tie_problem
+	if not ref.result_set_available():
+		pytest.skip("oracle/_ref/libresultset_ref.so not built")
+	corpus, s, raw, doc, slice_id = tie_problem()
+	want_doc, want_slice, want_score = ref.result_set(raw, np.ones_like(raw), doc, slice_id, k, min_score)
+	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"], corpus["doc_span_off"])
+	sim = engine.DeviceSim.upload(s)
+	ap, _ = _cabi.make_align_params(_cabi.VX_LOCAL, _cabi.VX_GAP_LINEAR, lin=(0.0, 0.0))
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=min_score)
+	hits, _, _ = dc.search(sim, ap, qp)
+	np.testing.assert_array_equal(hits["score"], want_score)
+	np.testing.assert_array_equal(hits["doc"], want_doc)
+	np.testing.assert_array_equal(hits["slice"], want_slice)
+	np.testing.assert_array_equal(dc.search_topk_noalloc(sim, ap, qp)["doc"] if k <= _cabi.VX_NOALLOC_MAX_K else want_doc, want_doc)
+	sim.close()
+	dc.close()

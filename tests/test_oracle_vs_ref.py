@@ -79,3 +79,41 @@ def test_oracle_equals_reference_solver(oracle, locality, gap_name):
 		n_ties += mode == 1
 	solver.close()
 	assert n_ties > 0 and n_flip <= 6   # a last-bit difference may flip a tie; it must stay rare
+
+
+# ---- heap order pinned to the reference's own ResultSet (oracle/ref/resultset_driver.cpp) ----
+
+def tie_problem(n_doc=40, per_doc=37, seed=0):
+	"""One-token windows and a one-token query: the score of a window is S[its token id, 0], i.e. any value we like.
+	Every document carries the SAME per_doc distinct scores (in a shuffled slice order): every score is tied n_doc times
+	ACROSS documents and never inside one -- the case Match::compare_by_score orders (score, then document id); ties
+	inside a document fall through to a comparison of flow POINTERS in the reference (match_impl.h:20-24) and are exempt."""
+	rng = np.random.default_rng(seed)
+	base = (rng.permutation(per_doc).astype(np.float32) + 1) / np.float32(per_doc + 3)
+	n = n_doc * per_doc
+	token_id = np.concatenate([rng.permutation(per_doc) for _ in range(n_doc)]).astype(np.int32)
+	doc_span_off = np.arange(0, n + 1, per_doc, dtype=np.int64)
+	span_start = (np.arange(n) % per_doc).astype(np.int32)
+	corpus = dict(token_id=token_id, doc_tok_off=doc_span_off.copy(), span_start=span_start, span_end=span_start + 1,
+		doc_span_off=doc_span_off)
+	s = base.reshape(per_doc, 1).copy()
+	raw = base[token_id]
+	doc = np.repeat(np.arange(n_doc, dtype=np.int32), per_doc)
+	return corpus, s, raw, doc, span_start.copy()
+
+
+@pytest.mark.skipif(not ref.result_set_available(), reason="oracle/_ref/libresultset_ref.so not built")
+@pytest.mark.parametrize("k,min_score", [(100, 0.0), (7, 0.0), (40, 0.5), (500, 0.0), (2000, 0.9), (1, 0.0)])
+def test_oracle_result_set_equals_reference_result_set(oracle, k, min_score):
+	from vectorian_b200 import _cabi
+	corpus, s, raw, doc, slice_id = tie_problem()
+	want_doc, want_slice, want_score = ref.result_set(raw, np.ones_like(raw), doc, slice_id, k, min_score)
+	oc = oracle.OracleCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"], corpus["doc_span_off"])
+	ap, _ = _cabi.make_align_params(_cabi.VX_LOCAL, _cabi.VX_GAP_LINEAR, lin=(0.0, 0.0))
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=min_score)
+	hits, _, _ = oc.search(s, ap, qp, n_threads=3)
+	assert len(hits) == len(want_doc) > 0
+	np.testing.assert_array_equal(hits["score"], want_score)
+	np.testing.assert_array_equal(hits["doc"], want_doc)          # equal scores: the HIGHER document id first
+	np.testing.assert_array_equal(hits["slice"], want_slice)
+	assert k == 1 or np.sum(np.diff(want_score) == 0) > 1       # the winners really are full of ties
