@@ -75,18 +75,29 @@ def peaks():
 		return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}
 
 
-def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand_per_cell=None, embedding=None):
+def run_static(name, locality, gap, t, n_sent, vocab, dim, k=100, steps=10, cand_per_cell=None, embedding=None, tag_weights=None):
 	n_sent = n_sent // WORLD
 	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
-	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	pos = None
+	if tag_weights is not None:
+		import torch
+		g = torch.Generator(device=DEV)
+		g.manual_seed(7 + RANK)
+		pos = torch.randint(0, 17, (int(tok.numel()),), generator=g, device=DEV, dtype=torch.int8)   # 17 universal POS tags
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True,
+		token_pos=pos)
 	attach_shard(dc, tables["n_doc"])
-	del tok
+	del tok, pos
 	emb = embedding if embedding is not None else synthetic.make_embedding(vocab, dim)
 	de = engine.DeviceEmbedding(emb)
 	r = gaps.resolve_gap_costs(gap, 64, t)
 	kind = r.pop("gap_kind")
 	ap, keep = _cabi.make_align_params(locality, kind, **r)
-	qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
+	if tag_weights is not None:
+		qp, _keep_q = _cabi.make_query_params(max_matches=k, min_score=0.0, t_weights=np.asarray(tag_weights, np.float32),
+			t_pos=(np.arange(t) % 17).astype(np.int8), pos_mismatch_penalty=0.3, similarity_threshold=0.1)
+	else:
+		qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
 	queries = [synthetic.make_query(t, vocab, seed=99 + i) for i in range(8)]
 	tm = {"sim_ms": [], "dp_ms": [], "topk_ms": [], "traceback_ms": [], "wall_ms": []}
 	for i in range(3 + steps):
@@ -185,9 +196,16 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100, em
 	"""C5: n_queries x 8 settings ({LinearGapCost(u), u in 0,.1,.2,.5} x {Local, Global}) without re-preprocessing."""
 	n_sent = n_sent // WORLD
 	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
-	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	pos = None
+	if tag_weights is not None:
+		import torch
+		g = torch.Generator(device=DEV)
+		g.manual_seed(7 + RANK)
+		pos = torch.randint(0, 17, (int(tok.numel()),), generator=g, device=DEV, dtype=torch.int8)   # 17 universal POS tags
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True,
+		token_pos=pos)
 	attach_shard(dc, tables["n_doc"])
-	del tok
+	del tok, pos
 	emb = embedding if embedding is not None else synthetic.make_embedding(vocab, dim)
 	de = engine.DeviceEmbedding(emb)
 	aps, keeps = [], []
@@ -261,6 +279,11 @@ def main():
 	if "wsbloc" in which:
 		for loc, nm in ((_cabi.VX_LOCAL, "Local"), (_cabi.VX_GLOBAL, "Global"), (_cabi.VX_SEMIGLOBAL, "Semiglobal")):
 			run_static("WSB %s smooth_gap_cost(5) T=12 10M V=50k" % nm, loc, gaps.smooth_gap_cost(5), 12, 10_000_000, 50_000, 300)
+	if "tag" in which:    # tag-weighted similarity on the fast kernels vs the per-window scorer (weights that are not exact in fp32)
+		w = [1.0, 0.5, 1.5, 1.0, 2.0, 0.25, 1.0, 1.0, 0.75, 1.0, 1.25, 1.0]
+		run_static("C3-tag: WSB Local smooth_gap_cost(5) T=12 tag-weighted (dyadic weights, fast kernel), 10M", _cabi.VX_LOCAL, gaps.smooth_gap_cost(5), 12, 10_000_000, 50_000, 300, tag_weights=w)
+		run_static("C2-tag: SW Local linear(0.2) T=12 tag-weighted (dyadic weights, fast kernel), 10M", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 12, 10_000_000, 50_000, 300, cand_per_cell=3.5, tag_weights=w)
+		run_static("C3-tag-exact: same, weights 0.3 .. 1.3 (per-window scorer), 200k", _cabi.VX_LOCAL, gaps.smooth_gap_cost(5), 12, 200_000, 50_000, 300, steps=3, tag_weights=[0.3 + 0.1 * i for i in range(12)])
 	if "gotoh" in which:
 		run_static("Gotoh Local affine(0.3,0.1) T=8 20M V=50k", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1), 8, 20_000_000, 50_000, 300, cand_per_cell=7.5)
 

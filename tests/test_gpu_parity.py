@@ -166,6 +166,34 @@ def test_tag_weighted_and_submatch(engine, oracle):
 			run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], 7, submatch_weight=0.5)
 
 
+def test_tag_weighted_on_the_fast_kernels(engine, oracle):
+	"""Tag-weighted similarity with weights whose sums are exact in fp32 (multiples of 2^-10; the default 1 among them)
+	takes the fast DP kernels -- the weighting is applied to the gathered S row (TagWeightedSlice::similarity,
+	cpp/slice/static.h:236-263) --, other weights keep the per-window scorer; both are bit-identical to the oracle,
+	for every locality x gap kind, with windows, a boost and a long (> 64 tokens) sentence in the corpus."""
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=1500, t=12, seed=78, with_pos=True)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	rng = np.random.default_rng(2)
+	t_pos = rng.integers(0, 17, size=12).astype(np.int8)
+	dyadic = (rng.integers(1, 12, size=12) / 4.0).astype(np.float32)            # 0.25 .. 2.75
+	ones = np.ones(12, np.float32)
+	ragged = rng.uniform(0.2, 2.0, size=12).astype(np.float32)                  # not exact: per-window scorer
+	boost = rng.uniform(0.5, 1.5, size=len(corpus["span_start"])).astype(np.float32)
+	dc, oc = make_both(engine, oracle, corpus, with_pos=True, boost=boost)
+	for name, w in (("dyadic", dyadic), ("ones", ones), ("ragged", ragged)):
+		for locality in LOCALITIES:
+			for gap_name in ("linear0.2", "affine", "smooth5"):
+				run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], 12,
+					t_weights=w, t_pos=t_pos, pos_mismatch_penalty=0.4, similarity_threshold=0.15)
+	dc.close()
+	# windows of three sentences, step two
+	dc, oc = make_both(engine, oracle, corpus, window_size=3, window_step=2, with_pos=True)
+	for gap_name in ("linear0.2", "smooth5"):
+		run_case(engine, oracle, dc, oc, s, _cabi.VX_LOCAL, GAPS[gap_name], 12,
+			t_weights=dyadic, t_pos=t_pos, pos_mismatch_penalty=0.25, similarity_threshold=0.0)
+	dc.close()
+
+
 def test_edge_cases(engine, oracle):
 	# ragged: empty document, empty spans, single-token sentences, a sentence longer than 64 tokens
 	token_id = np.arange(200, dtype=np.int32) % 50

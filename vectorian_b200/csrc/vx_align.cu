@@ -90,6 +90,8 @@ struct ScoreArgs {
 	float *score;          // by slot
 	int32_t t;
 	float total;
+	const int8_t *pos;     // tiled POS ids (tag-weighted similarity only)
+	VxTagArgs tag;
 };
 
 // ---------------------------------------------------------------------------
@@ -128,6 +130,9 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 		}
 		if (u + 1 < len) {
 			load_row<TP>(a.s, ids.next(u + 1), row);
+		}
+		if (a.tag.on) {
+			vx_apply_tag<TP>(a.tag, a.pos[vx_elem(tl.base128, u, lane)], cur);
 		}
 
 		float diag = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
@@ -327,6 +332,9 @@ __global__ void __launch_bounds__(128) score_affine_kernel(ScoreArgs a, AffineAr
 		if (u + 1 < len) {
 			id = tok[vx_elem(0, u + 1, 0)];
 			load_row<TP>(a.s, id, row);
+		}
+		if (a.tag.on) {
+			vx_apply_tag<TP>(a.tag, a.pos[vx_elem(tl.base128, u, lane)], cur);
 		}
 
 		float diag = LOC == VX_GLOBAL ? -affine_w(g.ext_s, g.open_s, u) : 0.0f;       // D[u-1, -1]
@@ -608,6 +616,8 @@ int vx_launch_score_multi(vx_corpus *c, const vx_sim *s, const VxQueryDev &qp, i
 	a.score = nullptr;
 	a.t = qp.t;
 	a.total = qp.total;
+	a.pos = nullptr;
+	memset(&a.tag, 0, sizeof(a.tag));   // the multi-setting kernel has no tag weighting: the caller keeps such settings out
 	MultiArgs m;
 	memset(&m, 0, sizeof(m));
 	for (int i = 0; i < nl + ng; i++) {
@@ -645,6 +655,8 @@ int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 	a.score = c->d_score;
 	a.t = qp.t;
 	a.total = qp.total;
+	a.pos = c->d_pos;
+	a.tag = vx_make_tag_args(qp);
 	int n;
 	switch (s->tp) {
 		case 4:

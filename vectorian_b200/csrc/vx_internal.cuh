@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <atomic>
 #include <string>
+#include <cstring>
 #include <vector>
 
 #include "../../include/vectorian_b200.h"
@@ -180,6 +181,46 @@ struct VxQueryDev {
 	const float *t_weights_dev;          // device copies for t > 32
 	const int8_t *t_pos_dev;
 };
+
+// Tag-weighted similarity on the fast score kernels (TagWeightedSlice::similarity, cpp/slice/static.h:236-263):
+//   x = S[id(s_u), v] * w_v * (pos(s_u) != pos(t_v) ? 1 - pos_mismatch_penalty : 1);   x <= threshold -> 0
+// with the two possible weights of every query column precomputed in fp32 exactly as the per-window scorer forms them
+// (weight = w_v; weight *= 1.0f - pmp), so that x is bit-identical.
+struct VxTagArgs {
+	int32_t on;
+	float thr;
+	float w_same[VX_MAX_T_FAST];   // pos(s) == pos(t_v)
+	float w_diff[VX_MAX_T_FAST];   // pos(s) != pos(t_v)
+	int8_t tpos[VX_MAX_T_FAST];
+};
+
+inline VxTagArgs vx_make_tag_args(const VxQueryDev &qp) {
+	VxTagArgs g;
+	memset(&g, 0, sizeof(g));
+	g.on = qp.tag_weighted ? 1 : 0;
+	g.thr = qp.similarity_threshold;
+	const float miss = 1.0f - qp.pos_mismatch_penalty;
+	for (int v = 0; v < VX_MAX_T_FAST && v < qp.t; v++) {
+		float w = qp.t_weights[v];
+		g.w_same[v] = w;
+		w *= miss;
+		g.w_diff[v] = w;
+		g.tpos[v] = qp.t_pos[v];
+	}
+	return g;
+}
+
+#ifdef __CUDACC__
+template<int TP>
+__device__ __forceinline__ void vx_apply_tag(const VxTagArgs &g, int8_t pos, float (&x)[TP]) {
+	#pragma unroll
+	for (int v = 0; v < TP; v++) {
+		const float w = pos == g.tpos[v] ? g.w_same[v] : g.w_diff[v];
+		const float y = x[v] * w;
+		x[v] = y <= g.thr ? 0.0f : y;
+	}
+}
+#endif
 
 // ---------------------------------------------------------------------------
 // kernels (launchers); each returns the number of kernels it launched or < 0 on error

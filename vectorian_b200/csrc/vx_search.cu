@@ -175,7 +175,23 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 	p->t = t;
 	p->k = std::max(qp->max_matches, 1);
 	// contextual queries take the same fast kernels: S_doc is formed first, d_iota stands in for the ids
-	p->fast = (!s->contextual || c->d_iota) && s->tp <= VX_MAX_T_FAST && !qp->tag_weighted && qp->submatch_weight == 0.0f;
+	// Tag-weighted similarity runs on the fast kernels too (the weighting is applied to the gathered S row), provided the
+	// normalisation stays exact: the per-window scorer divides by matched + (total - matched), which equals total in
+	// fp32 only if every partial sum of the tag weights is exactly representable -- true when all weights are
+	// multiples of 2^-10 and their sum stays below 2^13 (the default weight 1 included).  Other weights, and general gap
+	// costs over windows the tensor-memory kernel does not take (> 64 tokens), keep the exact scorer.
+	bool tag_fast = true;
+	if (qp->tag_weighted) {
+		float sum = 0.0f;
+		for (int32_t j = 0; j < t; j++) {
+			const float w = qp->t_weights[j];
+			tag_fast = tag_fast && w >= 0.0f && w * 1024.0f == floorf(w * 1024.0f);
+			sum += w;
+		}
+		tag_fast = tag_fast && sum > 0.0f && sum < 8192.0f && t <= VX_MAX_T_FAST;
+		tag_fast = tag_fast && !(ap->gap_kind == VX_GAP_GENERAL && c->max_len > 64);
+	}
+	p->fast = (!s->contextual || c->d_iota) && s->tp <= VX_MAX_T_FAST && tag_fast && qp->submatch_weight == 0.0f;
 
 	// ---- workspace layout: [top-k area | block of plan 0 | block of plan 1 | ...] ----
 	const size_t n_ws = ap->gap_kind == VX_GAP_GENERAL ? (size_t)ap->n_w_s : 0;
@@ -279,7 +295,7 @@ static int ensure_sdoc(vx_corpus *c, const vx_sim *s, const QueryPlan *p, bool *
 		c->sdoc_bytes = need;
 	}
 	const bool no_fuse = getenv("VX_CTX_NOFUSE") != nullptr || getenv("VX_CTX_SIMT") != nullptr;   // A/B switches (read per call: the tests toggle them)
-	if (p && !no_fuse) {
+	if (p && !no_fuse && !p->qp.tag_weighted) {   // the fused GEMM + DP kernel has no tag weighting
 		const int nf = vx_launch_ctx_fused(c, s, p->ap, p->qp, c->d_sdoc);
 		if (nf < 0 || (nf > 0 && cudaGetLastError() != cudaSuccess)) {
 			vx_set_error("fused contextual similarity + DP kernel launch failed");
@@ -633,7 +649,7 @@ extern "C" int vx_search_batch(
 		std::vector<char> done(n_aps, 0);
 		for (int32_t ai = 0; ai < n_aps; ai++) {
 			const QueryPlan &p = plans[(size_t)q * n_aps + ai];
-			if (p.fast && !s->contextual && p.ap.gap_kind == VX_GAP_LINEAR) {
+			if (p.fast && !s->contextual && p.ap.gap_kind == VX_GAP_LINEAR && !p.qp.tag_weighted) {
 				if (p.ap.locality == VX_LOCAL) {
 					lo.push_back(ai);
 				} else if (p.ap.locality == VX_GLOBAL) {

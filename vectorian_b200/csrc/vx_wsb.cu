@@ -56,6 +56,8 @@ struct WsbArgs {
 	// candidates; x - w == x + (-w) bit for bit):
 	float2 nws2[VX_WSB_MAX_LEN + 4];   // {-w_s[d], -w_s[d]}: two neighbouring columns of one finished row
 	float2 nwt2[VX_MAX_T_FAST + 4];    // {-w_t[d], -w_t[d-1]}: two neighbouring cells (k, k+1) left of column k + d
+	const int8_t *pos;                 // tiled POS ids, same element order as tok (tag-weighted similarity only)
+	VxTagArgs tag;
 };
 
 __device__ __forceinline__ float max3(float a, float b, float c) {
@@ -201,11 +203,15 @@ __device__ __forceinline__ void wsb_history_pair(const WsbArgs &a, const int d, 
 //   prev[v]  in: V[u0-1, v]  out: V[u0+NR-1, v]
 //   sim      in: S rows of this block; out: S rows of the NEXT block of the warp's token stream
 //            (each row is re-loaded as soon as it has been consumed, ids from idq_next)
-template<int TP, int LOC, bool BORD, int NR, bool F2, bool PIPE>
+// TAG: tag-weighted similarity.  `posq` holds the POS bytes of this block's four tokens (applied to the S rows when
+// they are consumed, so that the prefetch of the rows is not disturbed); the POS quad of the next block is requested
+// through `pquads`, which runs one block ahead, and handed back in `posq` when the block is done.
+template<int TP, int LOC, bool BORD, int NR, bool F2, bool PIPE, bool TAG>
 __device__ __forceinline__ void wsb_block(
 	const WsbArgs &a, const uint32_t tmem, float4 *__restrict__ hist, const int u0, const int t,
 	float (&prev)[TP], float &best, float &last_col,
-	float (&sim)[VX_WSB_U][TP], int4 &idq_next, const int4 *__restrict__ &quads) {
+	float (&sim)[VX_WSB_U][TP], int4 &idq_next, const int4 *__restrict__ &quads,
+	uint32_t &posq, const uint32_t *__restrict__ &pquads) {
 
 	constexpr int Q = TP / 4;
 	constexpr int U = VX_WSB_U;
@@ -282,6 +288,11 @@ __device__ __forceinline__ void wsb_block(
 	const int4 idq_use = idq_next;
 	idq_next = __ldg(quads);
 	quads += 32;
+	uint32_t posq_next = 0;
+	if (TAG) {
+		posq_next = __ldg(pquads);
+		pquads += 32;
+	}
 
 	// the rows of the block, in order
 	#pragma unroll
@@ -290,6 +301,9 @@ __device__ __forceinline__ void wsb_block(
 		// V[u, -1] and V[u-1, -1]
 		const float left = BORD ? (LOC == VX_GLOBAL ? -a.ws[u + 1] : 0.0f) : 0.0f;
 		float diag = BORD ? (LOC == VX_GLOBAL ? (u == 0 ? -a.wt[0] : -a.ws[u]) : 0.0f) : 0.0f;
+		if (TAG) {
+			vx_apply_tag<TP>(a.tag, (int8_t)((posq >> (8 * i)) & 0xffu), sim[i]);
+		}
 		if (F2) {
 			// rows of this block above row i: pairs of rows and pairs of columns per FADD2; an odd row is left
 			// pending and folds with the diagonal candidate below
@@ -413,9 +427,12 @@ __device__ __forceinline__ void wsb_block(
 	for (int v = 0; v < TP; v++) {
 		prev[v] = acc[NR - 1][v];
 	}
+	if (TAG) {
+		posq = posq_next;
+	}
 }
 
-template<int TP, int LOC, bool BORD, bool F2, bool PIPE>
+template<int TP, int LOC, bool BORD, bool F2, bool PIPE, bool TAG>
 __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant__ WsbArgs a) {
 	extern __shared__ float4 wsb_smem[];
 	__shared__ uint32_t tmem_base_sh;
@@ -481,6 +498,14 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 			}
 		}
 		quads += 64;
+		// POS bytes: this block's quad now, the next block's quad is requested inside wsb_block
+		uint32_t posq = 0;
+		const uint32_t *__restrict__ pquads = nullptr;
+		if (TAG) {
+			pquads = reinterpret_cast<const uint32_t*>(a.pos) + (size_t)tl.base128 * 32 + lane;
+			posq = __ldg(pquads);
+			pquads += 32;
+		}
 
 		for (; tile < tile_stop; tile++) {
 			const VxTile tl_next = a.tiles[tile + 1];   // d_tiles has one padding entry
@@ -497,18 +522,18 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 			int u0 = 0;
 			#pragma unroll 1
 			for (; u0 + U <= len; u0 += U) {
-				wsb_block<TP, LOC, BORD, U, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+				wsb_block<TP, LOC, BORD, U, F2, PIPE, TAG>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads, posq, pquads);
 			}
 			if (u0 < len) {
 				switch (len - u0) {
 					case 1:
-						wsb_block<TP, LOC, BORD, 1, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 1, F2, PIPE, TAG>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads, posq, pquads);
 						break;
 					case 2:
-						wsb_block<TP, LOC, BORD, 2, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 2, F2, PIPE, TAG>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads, posq, pquads);
 						break;
 					default:
-						wsb_block<TP, LOC, BORD, 3, F2, PIPE>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads);
+						wsb_block<TP, LOC, BORD, 3, F2, PIPE, TAG>(a, tmem, hist, u0, t, prev, best, last_col, sim, idq_next, quads, posq, pquads);
 						break;
 				}
 			}
@@ -565,7 +590,7 @@ static void wsb_plan(int tp, int cap, int *warps, int *rt, int *tmem_cols, int *
 	}
 }
 
-template<int TP, int LOC, bool BORD, bool F2, bool PIPE>
+template<int TP, int LOC, bool BORD, bool F2, bool PIPE, bool TAG>
 static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap) {
 	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
 	// SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a TMEM lane quarter
@@ -595,7 +620,7 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	const size_t smem = (size_t)rows_smem * row_bytes * warps;
 	static bool attr_set = false;
 	if (!attr_set) {
-		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD, F2, PIPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
+		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD, F2, PIPE, TAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
 		attr_set = true;
 	}
 	// Every launch after the first of a query is a programmatic dependent launch: the kernels of one query do not
@@ -612,21 +637,21 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	attr[0].val.programmaticStreamSerializationAllowed = 1;
 	cfg.attrs = attr;
 	cfg.numAttrs = overlap ? 1 : 0;
-	if (cudaLaunchKernelEx(&cfg, wsb_score_kernel<TP, LOC, BORD, F2, PIPE>, a) != cudaSuccess) {
+	if (cudaLaunchKernelEx(&cfg, wsb_score_kernel<TP, LOC, BORD, F2, PIPE, TAG>, a) != cudaSuccess) {
 		return -1;
 	}
 	return 1;
 }
 
-template<int TP, bool F2, bool PIPE>
+template<int TP, bool F2, bool PIPE, bool TAG>
 static int launch_class_f(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
 	if (loc == VX_LOCAL) {
-		return bord ? launch_class<TP, VX_LOCAL, true, F2, PIPE>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false, F2, PIPE>(c, a, cap, sms, overlap);
+		return bord ? launch_class<TP, VX_LOCAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false, F2, PIPE, TAG>(c, a, cap, sms, overlap);
 	}
 	if (loc == VX_GLOBAL) {
-		return launch_class<TP, VX_GLOBAL, true, F2, PIPE>(c, a, cap, sms, overlap);
+		return launch_class<TP, VX_GLOBAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap);
 	}
-	return launch_class<TP, VX_SEMIGLOBAL, true, F2, PIPE>(c, a, cap, sms, overlap);
+	return launch_class<TP, VX_SEMIGLOBAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap);
 }
 
 template<int TP>
@@ -635,16 +660,19 @@ static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, b
 	// structure), VX_WSB_NO_PIPE = packed adds without the double-buffered history loops
 	static const bool f2 = getenv("VX_WSB_NO_F2") == nullptr;
 	static const bool pipe = getenv("VX_WSB_NO_PIPE") == nullptr;
+	if (a.tag.on) {
+		return launch_class_f<TP, true, false, true>(c, a, cap, sms, loc, bord, overlap);   // tag weighting: packed adds, single-buffered
+	}
 	if (!f2) {
-		return launch_class_f<TP, false, false>(c, a, cap, sms, loc, bord, overlap);
+		return launch_class_f<TP, false, false, false>(c, a, cap, sms, loc, bord, overlap);
 	}
 	// the second row-pair buffer costs 2 * TP registers: 249 at TP = 12 (fits 8 warps per SM exactly), spills at TP = 16
 	if constexpr (TP <= 12) {
 		if (pipe) {
-			return launch_class_f<TP, true, true>(c, a, cap, sms, loc, bord, overlap);
+			return launch_class_f<TP, true, true, false>(c, a, cap, sms, loc, bord, overlap);
 		}
 	}
-	return launch_class_f<TP, true, false>(c, a, cap, sms, loc, bord, overlap);
+	return launch_class_f<TP, true, false, false>(c, a, cap, sms, loc, bord, overlap);
 }
 
 // Scores every tile whose windows are at most VX_WSB_MAX_LEN long; *first_tile receives the index of
@@ -669,6 +697,8 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	a.score = c->d_score;
 	a.t = qp.t;
 	a.total = qp.total;
+	a.pos = c->d_pos;
+	a.tag = vx_make_tag_args(qp);
 	const int n_ws = ap.n_w_s < VX_WSB_MAX_LEN + 1 ? ap.n_w_s : VX_WSB_MAX_LEN + 1;
 	bool nonneg = true;
 	for (int i = 0; i < n_ws; i++) {
