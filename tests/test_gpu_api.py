@@ -290,14 +290,28 @@ def test_token_filters(oracle):
 		check_find(oracle, session, emb, index, QUERY, n=20, min_score=0.05)
 		if len(part_args) == 1:
 			assert [(m.prepared_doc.id, m.slice_id, m.score) for m in plain] != [(m.prepared_doc.id, m.slice_id, m.score) for m in result]
-			# regions(): matched document tokens are reported at their UNFILTERED positions (cpp/match/flow.cpp:49-61, 95-99)
+			# regions(): matched document tokens are reported at their UNFILTERED positions (cpp/match/flow.cpp:49-61, 95-99),
+			# exactly as the reference's Flow::py_regions does it -- including its grouping of edges at flow.cpp:143, which
+			# compares a raw (filtered) target with a mapped one (oracle/render.py restates it; tests/test_render_oracle.py)
+			from oracle import render
 			for m in result[:5]:
 				doc = m.prepared_doc.doc
-				s0, _ = m.prepared_doc.span_table("sentence")
+				s0, s1 = m.prepared_doc.span_table("sentence")
 				imap = index_maps[(m.prepared_doc.id, m.slice_id)]
-				want = sorted(doc.token_text[s0[m.slice_id] + imap[u]] for u in m.flow["target"] if u >= 0)
-				got = sorted(r.s for r in m.regions(3) if r.match)
+				token_at, slice_len = int(s0[m.slice_id]), int(s1[m.slice_id]) - int(s0[m.slice_id])
+				keep = [i in set(int(x) for x in imap) for i in range(slice_len)]
+				s_tokens = [{'idx': int(doc.token_idx[i]), 'len': int(doc.token_len[i]), 'pos': doc.token_pos[i]} for i in range(doc.n_tokens)]
+				t_tokens = [{'idx': t['start'], 'len': t['end'] - t['start'], 'pos': t.get('pos', 'X')} for t in m.query.tokens]
+				edges = [(int(u), j, 1.0, float(m.flow["dist"][j])) for j, u in enumerate(m.flow["target"]) if u >= 0]
+				gap_s, gap_t = m._gap_fns
+				want = render.render(doc.text_str, m.query.text_str,
+					render.py_regions(s_tokens, t_tokens, token_at, slice_len, edges, 3, filter_pass=keep, gap_cost_s=gap_s, gap_cost_t=gap_t), m.metric)
+				got = [(r.s, None if r.match is None else (r.match.pos_s, [((e.t.text, e.t.index, e.t.pos), e.flow, e.distance, e.metric) for e in r.match.edges]),
+					r.gap_penalty) for r in m.regions(3)]
 				assert got == want
+				# every matched region shows a document token that passed the filter
+				passed = {doc.token_text[token_at + int(i)] for i in imap}
+				assert all(r.s in passed for r in m.regions(3) if r.match)
 	with pytest.raises(RuntimeError):
 		index.find(QUERY, options={"pos_filter": ["NOPE"]})
 
