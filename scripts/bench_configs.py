@@ -254,6 +254,46 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100, em
 	dc.close()
 
 
+def run_multi_query(name, locality, gap, t, n_sent, vocab, dim, n_queries=8, k=100, reps=5):
+	"""Several queries against ONE linear-gap setting: n_queries single vx_search calls vs one
+	vx_search_batch (score_linear_mq_kernel), same results."""
+	n_sent = n_sent // WORLD
+	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	attach_shard(dc, tables["n_doc"])
+	del tok
+	emb = synthetic.make_embedding(vocab, dim)
+	de = engine.DeviceEmbedding(emb)
+	r = gaps.resolve_gap_costs(gap, 64, t)
+	kind = r.pop("gap_kind")
+	ap, keep = _cabi.make_align_params(locality, kind, **r)
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
+	queries = [synthetic.make_query(t, vocab, seed=99 + i) for i in range(n_queries)]
+	res = {}
+	for mode in ("single", "batch"):
+		best = None
+		for rep in range(reps):
+			sync_all()
+			t0 = time.perf_counter()
+			sims = [engine.DeviceSim.static(de, q, emb[q]) for q in queries]
+			if mode == "single":
+				top = [dc.search(sim, ap, qp)[0] for sim in sims]
+			else:
+				top = [row[0][0] for row in dc.search_batch(sims, [ap], qp)]
+			dt = (time.perf_counter() - t0) * 1e3
+			for sim in sims:
+				sim.close()
+			best = dt if best is None or dt < best else best
+		res[mode] = (best, top)
+	same = all(np.array_equal(a, b) for a, b in zip(res["single"][1], res["batch"][1]))
+	m = reduce_max({"single_ms": res["single"][0], "batch_ms": res["batch"][0]})
+	emit({"config": name, "sentences": n_sent * WORLD, "T": t, "queries": n_queries, "single_calls_wall_ms": m["single_ms"],
+		"batch_wall_ms": m["batch_ms"], "speedup": m["single_ms"] / m["batch_ms"],
+		"sentence_queries_per_s_single": n_sent * WORLD * n_queries / m["single_ms"] * 1e3,
+		"sentence_queries_per_s_batch": n_sent * WORLD * n_queries / m["batch_ms"] * 1e3, "identical_results": bool(same)})
+	dc.close()
+
+
 def main():
 	which = sys.argv[1:] or ["c1", "c2"]
 	dist_setup()
@@ -279,6 +319,10 @@ def main():
 	if "wsbloc" in which:
 		for loc, nm in ((_cabi.VX_LOCAL, "Local"), (_cabi.VX_GLOBAL, "Global"), (_cabi.VX_SEMIGLOBAL, "Semiglobal")):
 			run_static("WSB %s smooth_gap_cost(5) T=12 10M V=50k" % nm, loc, gaps.smooth_gap_cost(5), 12, 10_000_000, 50_000, 300)
+	if "mq" in which:
+		run_multi_query("C2-mq: 8 SW Local linear(0.2) queries, T=8, 20M sentences, V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 20_000_000, 200_000, 300)
+		run_multi_query("C2-mq12: 8 NW Global linear(0.2) queries, T=12, 20M sentences, V=50k", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.2), 12, 20_000_000, 50_000, 300)
+		run_multi_query("C2-mq4: 4 SW Local linear(0.2) queries, T=8, 1M sentences, V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 1_000_000, 200_000, 300, n_queries=4)
 	if "tag" in which:    # tag-weighted similarity on the fast kernels vs the per-window scorer (weights that are not exact in fp32)
 		w = [1.0, 0.5, 1.5, 1.0, 2.0, 0.25, 1.0, 1.0, 0.75, 1.0, 1.25, 1.0]
 		run_static("C3-tag: WSB Local smooth_gap_cost(5) T=12 tag-weighted (dyadic weights, fast kernel), 10M", _cabi.VX_LOCAL, gaps.smooth_gap_cost(5), 12, 10_000_000, 50_000, 300, tag_weights=w)

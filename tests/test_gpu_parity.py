@@ -327,6 +327,46 @@ def test_search_batch_equals_single_searches(engine, oracle):
 	assert dc.search_batch([], aps, qp) == []
 
 
+@pytest.mark.parametrize("n_queries", [2, 3, 8, 13])
+def test_search_batch_several_queries_per_pass(engine, oracle, n_queries):
+	"""vx_search_batch with several queries and ONE linear-gap setting per locality: groups of 8 / 4 / 2 queries share a
+	pass over the corpus (score_linear_mq_kernel: interleaved similarity matrices, a lane per (window, query) pair), the
+	rest run alone -- every pair returns exactly the rows of its own vx_search, for queries of different lengths, an
+	uploaded matrix with negative entries, a boost, and a setting (affine) that is not fused."""
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=3100, t=8, seed=12)
+	rng = np.random.default_rng(4 + n_queries)
+	boost = rng.uniform(0.5, 1.5, size=len(corpus["span_start"])).astype(np.float32)
+	dc, oc = make_both(engine, oracle, corpus, boost=boost)
+	de = engine.DeviceEmbedding(emb)
+	sims = []
+	for i in range(n_queries):
+		t = int(rng.integers(1, 13))
+		if i == 1:
+			sims.append(engine.DeviceSim.upload((rng.random((emb.shape[0], t)) * 1.3 - 0.3).astype(np.float32)))
+		else:
+			ids = rng.choice(emb.shape[0], size=t, replace=False).astype(np.int32)
+			sims.append(engine.DeviceSim.static(de, ids, emb[ids]))
+	aps, keeps = [], []
+	for locality, gap_name in ((_cabi.VX_LOCAL, "linear0.2"), (_cabi.VX_GLOBAL, "linear_st"), (_cabi.VX_SEMIGLOBAL, "none"), (_cabi.VX_LOCAL, "affine")):
+		ap, keep = align_params(locality, GAPS[gap_name], dc.max_len, 12)
+		aps.append(ap)
+		keeps.append(keep)
+	qp, _ = _cabi.make_query_params(max_matches=30, min_score=0.0)
+	batch = dc.search_batch(sims, aps, qp)
+	for q, sim in enumerate(sims):
+		for a, ap in enumerate(aps):
+			hits, target, dist = dc.search(sim, ap, qp)
+			b_hits, b_target, b_dist = batch[q][a]
+			assert len(b_hits) == len(hits), (q, a)
+			for f in ("score", "score_max", "doc", "slice"):
+				np.testing.assert_array_equal(b_hits[f], hits[f], err_msg=f"{q} {a} {f}")
+			np.testing.assert_array_equal(b_target, target)
+			np.testing.assert_array_equal(b_dist, dist)
+	for sim in sims:
+		sim.close()
+	dc.close()
+
+
 @pytest.mark.parametrize("gap_name", ["linear0.2", "affine", "smooth5", "mixed"])
 def test_gpu_scores_equal_reference_solver(engine, gap_name):
 	"""The CUDA path against the REFERENCE'S OWN solver (oracle/_ref: unmodified pyalign solver.h, oracle/ref/):

@@ -284,6 +284,125 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 }
 
 // ---------------------------------------------------------------------------
+// linear gap cost, several QUERIES at once (vx_search_batch with more than one query and one setting):
+// the reference runs index.find once per query (vectorian/index.py:481-501).  The single-query kernel sits at the
+// L1TEX wavefront limit: its 32 lanes gather 32 different S rows, so every load instruction touches 32 lines.
+// Here the similarity matrices of K queries are interleaved into S_multi[V][K][TP] and a lane is a (window, query)
+// pair: lane = w * K + k.  The K lanes of a window read ONE contiguous K * TP * 4-byte row, an instruction touches
+// 32 / K windows' rows (1-2 lines each) instead of 32, and the per-lane DP state is as small as in the single-query
+// kernel.  A warp takes 32 / K windows of a tile; the cells are the same fp32 maxima of the same candidates.
+// ---------------------------------------------------------------------------
+
+struct MqArgs {
+	const float *s_multi;            // [V][K][TP]
+	float gs, gt;
+	float *score[VX_MULTI_MAX];      // per query, by slot
+	int32_t t[VX_MULTI_MAX];
+	float total[VX_MULTI_MAX];
+};
+
+template<int TP, int K, int LOC>
+__global__ void __launch_bounds__(128) score_linear_mq_kernel(ScoreArgs a, const __grid_constant__ MqArgs m) {
+	constexpr int W = 32 / K;        // windows per warp
+	const int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int64_t tile = unit / K;
+	const int sub = (int)(unit - tile * K);
+	if (tile >= a.n_tiles) {
+		return;
+	}
+	const int lane = threadIdx.x & 31;
+	const int k = lane % K;
+	const int wl = sub * W + lane / K;          // window (lane of the tile) this thread works on
+	const VxTile tl = a.tiles[tile];
+	const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + wl) * 4;
+	const int len = tl.len;
+	const int t = m.t[k];
+	const float gs = m.gs, gt = m.gt;
+
+	float h[TP];   // h[v] = V[u-1, v]
+	#pragma unroll
+	for (int v = 0; v < TP; v++) {
+		h[v] = LOC == VX_GLOBAL ? -((float)(v + 1) * gt) : 0.0f;
+	}
+	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
+	float last_col = 0.0f;
+
+	float row[TP];
+	IdStream ids(tok);
+	load_row<TP>(m.s_multi, ids.first() * K + k, row);
+
+	for (int u = 0; u < len; u++) {
+		float cur[TP];
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			cur[v] = row[v];
+		}
+		if (u + 1 < len) {
+			load_row<TP>(m.s_multi, ids.next(u + 1) * K + k, row);
+		}
+		float diag = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;
+		float left = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			const float up = h[v];
+			float x = fmaxf(fmaxf(diag + cur[v], up - gs), left - gt);
+			if (LOC == VX_LOCAL) {
+				x = fmaxf(x, 0.0f);
+				if (v < t) {
+					best = fmaxf(best, x);
+				}
+			}
+			diag = up;
+			h[v] = x;
+			left = x;
+			if (v == t - 1) {
+				last_col = x;
+			}
+		}
+		if (LOC == VX_SEMIGLOBAL) {
+			best = fmaxf(best, last_col);
+		}
+	}
+
+	float raw;
+	if (LOC == VX_LOCAL) {
+		raw = best;
+	} else if (LOC == VX_GLOBAL) {
+		raw = last_col;
+	} else {
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			if (v < t) {
+				best = fmaxf(best, h[v]);
+			}
+		}
+		raw = best;
+	}
+	const int64_t slot = tile * 32 + wl;
+	const float boost = a.boost ? a.boost[slot] : 1.0f;
+	m.score[k][slot] = wl < tl.n_valid ? finish_score(raw, m.total[k], boost) : -CUDART_INF_F;
+}
+
+// S_multi[row][k][0..TP) = S_k[row][0..tp_k), zero beyond the query's own columns
+struct InterleaveArgs {
+	const float *s[VX_MULTI_MAX];
+	int32_t tp[VX_MULTI_MAX];
+};
+
+__global__ void __launch_bounds__(256) interleave_sim_kernel(const __grid_constant__ InterleaveArgs g, int64_t rows, int k_n, int tp,
+	float *__restrict__ out) {
+
+	const int64_t n = rows * k_n * tp;
+	for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+		const int j = (int)(i % tp);
+		const int64_t rk = i / tp;
+		const int k = (int)(rk % k_n);
+		const int64_t r = rk / k_n;
+		out[i] = j < g.tp[k] ? g.s[k][r * g.tp[k] + j] : 0.0f;
+	}
+}
+
+// ---------------------------------------------------------------------------
 // affine gap cost: Gotoh
 // ---------------------------------------------------------------------------
 
@@ -680,4 +799,103 @@ int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 		return -1;
 	}
 	return n;
+}
+
+template<int TP, int K>
+static int launch_mq_tk(const ScoreArgs &a, const MqArgs &m, int locality, cudaStream_t st) {
+	const int warps = 4;
+	const unsigned grid = (unsigned)((a.n_tiles * K + warps - 1) / warps);
+	switch (locality) {
+		case VX_LOCAL:
+			score_linear_mq_kernel<TP, K, VX_LOCAL><<<grid, warps * 32, 0, st>>>(a, m);
+			return 1;
+		case VX_GLOBAL:
+			score_linear_mq_kernel<TP, K, VX_GLOBAL><<<grid, warps * 32, 0, st>>>(a, m);
+			return 1;
+		default:
+			score_linear_mq_kernel<TP, K, VX_SEMIGLOBAL><<<grid, warps * 32, 0, st>>>(a, m);
+			return 1;
+	}
+}
+
+template<int TP>
+static int launch_mq_t(const ScoreArgs &a, const MqArgs &m, int k_n, int locality, cudaStream_t st) {
+	switch (k_n) {
+		case 8:
+			return launch_mq_tk<TP, 8>(a, m, locality, st);
+		case 4:
+			return launch_mq_tk<TP, 4>(a, m, locality, st);
+		case 2:
+			return launch_mq_tk<TP, 2>(a, m, locality, st);
+		default:
+			return 0;
+	}
+}
+
+// K = 2, 4 or 8 queries (static similarity matrices over the same vocabulary) against ONE linear-gap setting in one
+// pass over the corpus: interleaves their S into d_s_multi [rows x K x tp] and scores every (window, query) pair.
+// Returns launches (2) or 0 when the shape has no kernel.
+int vx_launch_score_mq(vx_corpus *c, const vx_sim *const *sims, int k_n, int locality, float gs, float gt,
+	float *d_s_multi, float *const *score) {
+
+	if (c->n_tiles == 0 || (k_n != 2 && k_n != 4 && k_n != 8)) {
+		return 0;
+	}
+	int tp = 4;
+	InterleaveArgs g;
+	memset(&g, 0, sizeof(g));
+	MqArgs m;
+	memset(&m, 0, sizeof(m));
+	for (int k = 0; k < k_n; k++) {
+		tp = sims[k]->tp > tp ? sims[k]->tp : tp;
+		g.s[k] = sims[k]->d_s;
+		g.tp[k] = sims[k]->tp;
+		m.score[k] = score[k];
+		m.t[k] = sims[k]->t;
+		m.total[k] = (float)sims[k]->t;
+	}
+	const int64_t rows = sims[0]->rows;
+	if (tp > VX_MAX_T_FAST || rows * k_n >= ((int64_t)1 << 31)) {
+		return 0;
+	}
+	m.s_multi = d_s_multi;
+	m.gs = gs;
+	m.gt = gt;
+	const int64_t n = rows * k_n * tp;
+	int64_t blocks = (n + 255) / 256;
+	blocks = blocks > 148 * 16 ? 148 * 16 : blocks < 1 ? 1 : blocks;
+	interleave_sim_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(g, rows, k_n, tp, d_s_multi);
+	ScoreArgs a;
+	a.tiles = c->d_tiles;
+	a.n_tiles = c->n_tiles;
+	a.tok = c->d_tok;
+	a.s = nullptr;
+	a.boost = c->d_boost;
+	a.score = nullptr;
+	a.t = 0;
+	a.total = 0.0f;
+	a.pos = nullptr;
+	memset(&a.tag, 0, sizeof(a.tag));
+	int launched;
+	switch (tp) {
+		case 4:
+			launched = launch_mq_t<4>(a, m, k_n, locality, c->stream);
+			break;
+		case 8:
+			launched = launch_mq_t<8>(a, m, k_n, locality, c->stream);
+			break;
+		case 12:
+			launched = launch_mq_t<12>(a, m, k_n, locality, c->stream);
+			break;
+		case 16:
+			launched = launch_mq_t<16>(a, m, k_n, locality, c->stream);
+			break;
+		default:
+			launched = 0;
+	}
+	if (launched && cudaGetLastError() != cudaSuccess) {
+		vx_set_error("multi-query score kernel launch failed");
+		return -1;
+	}
+	return launched ? launched + 1 : 0;
 }

@@ -269,6 +269,8 @@ int vx_launch_sim_static(const float *d_ehat, int64_t v, int32_t d, const float 
 
 int vx_launch_score_multi(vx_corpus *c, const vx_sim *s, const VxQueryDev &qp, int nl, int ng,
 	const float *gs, const float *gt, float *const *score);
+int vx_launch_score_mq(vx_corpus *c, const vx_sim *const *sims, int k_n, int locality, float gs, float gt,
+	float *d_s_multi, float *const *score);
 int vx_launch_ctx_fused(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, float *d_sdoc);
 extern int vx_ctx_force_simt;
 int vx_launch_ctx_mma(const float *d_x, int64_t n_elem, int32_t d, const float *d_qhat, const int32_t *d_qid,

@@ -634,11 +634,132 @@ extern "C" int vx_search_batch(
 	int multi_buf = 0;
 	bool sel_pending[2] = {false, false};
 	for (int32_t q = 0; q < n_sims && rc == VX_OK; q++) {
-		const vx_sim *s = sims[q];
 		for (int32_t ai = 0; ai < n_aps && rc == VX_OK; ai++) {
-			rc = make_plan(c, s, &aps[ai], qp, true, &plans[(size_t)q * n_aps + ai], &slots[(size_t)q * n_aps + ai]);
+			rc = make_plan(c, sims[q], &aps[ai], qp, true, &plans[(size_t)q * n_aps + ai], &slots[(size_t)q * n_aps + ai]);
 		}
-		if (rc != VX_OK || s->t < 1 || c->n_win == 0) {
+	}
+	std::vector<char> done_pair(n_pairs, 0);
+	std::vector<std::pair<void*, size_t>> mq_buffers;   // interleaved similarity matrices, returned to the pool after the wait
+
+	// ---- several QUERIES per pass (score_linear_mq_kernel): for every linear-gap setting, groups of 8 / 4 / 2 queries
+	// with static similarity matrices over the same vocabulary.  Taken when the settings of a query cannot be fused
+	// instead (fewer than two Local and fewer than two Global linear settings): then one gathered row of the interleaved
+	// S feeds K queries' columns.
+	if (rc == VX_OK && n_sims >= 2 && c->n_win > 0 && getenv("VX_NO_MQ") == nullptr) {
+		int n_lo = 0, n_gl = 0;
+		for (int32_t ai = 0; ai < n_aps; ai++) {
+			if (aps[ai].gap_kind == VX_GAP_LINEAR) {
+				n_lo += aps[ai].locality == VX_LOCAL;
+				n_gl += aps[ai].locality == VX_GLOBAL;
+			}
+		}
+		for (int32_t ai = 0; ai < n_aps && rc == VX_OK && n_lo < 2 && n_gl < 2; ai++) {
+			if (aps[ai].gap_kind != VX_GAP_LINEAR) {
+				continue;
+			}
+			std::vector<int32_t> qs;
+			for (int32_t q = 0; q < n_sims; q++) {
+				const QueryPlan &p = plans[(size_t)q * n_aps + ai];
+				if (p.fast && !sims[q]->contextual && !p.qp.tag_weighted && sims[q]->t >= 1 && sims[q]->rows == sims[0]->rows && sims[q]->rows > 0) {
+					qs.push_back(q);
+				}
+			}
+			size_t at = 0;
+			while (rc == VX_OK && qs.size() - at >= 2) {
+				const int k_n = qs.size() - at >= 8 ? 8 : qs.size() - at >= 4 ? 4 : 2;
+				if (!c->d_score_multi && cudaMalloc(&c->d_score_multi, sizeof(float) * 16 * (size_t)c->n_slots) != cudaSuccess) {
+					cudaGetLastError();
+					break;
+				}
+				if (!c->select_stream) {
+					int prio_lo = 0, prio_hi = 0;
+					cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+					bool ok = cudaStreamCreateWithPriority(&c->select_stream, cudaStreamNonBlocking, prio_hi) == cudaSuccess;
+					for (int b = 0; b < 2 && ok; b++) {
+						ok = cudaEventCreateWithFlags(&c->ev_dp[b], cudaEventDisableTiming) == cudaSuccess &&
+							cudaEventCreateWithFlags(&c->ev_sel[b], cudaEventDisableTiming) == cudaSuccess;
+					}
+					if (!ok) {
+						vx_set_error("could not create the select stream");
+						rc = VX_ERR_CUDA;
+						break;
+					}
+				}
+				const vx_sim *group[8];
+				int tp = 4;
+				for (int j = 0; j < k_n; j++) {
+					group[j] = sims[qs[at + j]];
+					tp = std::max(tp, group[j]->tp);
+					if (group[j]->ev1) {
+						cudaStreamWaitEvent(c->stream, group[j]->ev1, 0);
+					}
+				}
+				const size_t bytes = align_up(sizeof(float) * (size_t)group[0]->rows * k_n * tp, 256);
+				float *d_s_multi = (float*)vx_pool_alloc(bytes);
+				if (!d_s_multi) {
+					break;   // no room: these queries run one by one below
+				}
+				mq_buffers.push_back(std::make_pair((void*)d_s_multi, bytes));
+				const int buf = multi_buf;
+				multi_buf ^= 1;
+				if (sel_pending[buf]) {
+					cudaStreamWaitEvent(c->stream, c->ev_sel[buf], 0);
+				}
+				float *score[8];
+				for (int j = 0; j < k_n; j++) {
+					score[j] = c->d_score_multi + ((size_t)buf * 8 + j) * c->n_slots;
+				}
+				const int launched = vx_launch_score_mq(c, group, k_n, aps[ai].locality, aps[ai].lin_s, aps[ai].lin_t, d_s_multi, score);
+				if (launched < 0) {
+					rc = VX_ERR_CUDA;
+					break;
+				}
+				if (launched == 0) {
+					break;
+				}
+				c->last_launches += launched;
+				cudaEventRecord(c->ev_dp[buf], c->stream);
+				cudaStreamWaitEvent(c->select_stream, c->ev_dp[buf], 0);
+				cudaStream_t const main_stream = c->stream;
+				float *const d_score = c->d_score;
+				c->stream = c->select_stream;
+				VxTopkOut tks[8];
+				bool multi = false;
+				{
+					const size_t stride = align_up(vx_topk_work_bytes(k), 256);
+					if (!c->d_topk_multi || c->topk_multi_stride != stride) {
+						cudaFree(c->d_topk_multi);
+						c->d_topk_multi = nullptr;
+						if (cudaMalloc(&c->d_topk_multi, stride * 8) == cudaSuccess) {
+							c->topk_multi_stride = stride;
+						} else {
+							cudaGetLastError();
+						}
+					}
+					if (c->d_topk_multi) {
+						multi = vx_launch_topk_multi(c, qp->min_score, k, c->d_topk_multi, stride, k_n, score, tks) == 1;
+						c->last_launches += multi ? 1 : 0;
+					}
+				}
+				for (int j = 0; j < k_n && rc == VX_OK; j++) {
+					const size_t pi = (size_t)qs[at + j] * n_aps + ai;
+					c->d_score = score[j];
+					rc = multi ? enqueue_finish(c, group[j], plans[pi], tks[j], false) : enqueue_select(c, group[j], plans[pi], false);
+					done_pair[pi] = 1;
+					live[pi] = 1;
+				}
+				c->stream = main_stream;
+				c->d_score = d_score;
+				cudaEventRecord(c->ev_sel[buf], c->select_stream);
+				sel_pending[buf] = true;
+				at += k_n;
+			}
+		}
+	}
+
+	for (int32_t q = 0; q < n_sims && rc == VX_OK; q++) {
+		const vx_sim *s = sims[q];
+		if (s->t < 1 || c->n_win == 0) {
 			continue;
 		}
 		if (s->ev1) {
@@ -648,8 +769,11 @@ extern "C" int vx_search_batch(
 		std::vector<int32_t> lo, gl;
 		std::vector<char> done(n_aps, 0);
 		for (int32_t ai = 0; ai < n_aps; ai++) {
+			done[ai] = done_pair[(size_t)q * n_aps + ai];
+		}
+		for (int32_t ai = 0; ai < n_aps; ai++) {
 			const QueryPlan &p = plans[(size_t)q * n_aps + ai];
-			if (p.fast && !s->contextual && p.ap.gap_kind == VX_GAP_LINEAR && !p.qp.tag_weighted) {
+			if (!done[ai] && p.fast && !s->contextual && p.ap.gap_kind == VX_GAP_LINEAR && !p.qp.tag_weighted) {
 				if (p.ap.locality == VX_LOCAL) {
 					lo.push_back(ai);
 				} else if (p.ap.locality == VX_GLOBAL) {
@@ -815,6 +939,9 @@ extern "C" int vx_search_batch(
 	if (c->select_stream) {
 		const cudaError_t e2 = cudaStreamSynchronize(c->select_stream);
 		e = e == cudaSuccess ? e2 : e;
+	}
+	for (const auto &b : mq_buffers) {
+		vx_pool_free(b.first, b.second);
 	}
 	if (rc != VX_OK) {
 		return rc;
