@@ -196,16 +196,9 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100, em
 	"""C5: n_queries x 8 settings ({LinearGapCost(u), u in 0,.1,.2,.5} x {Local, Global}) without re-preprocessing."""
 	n_sent = n_sent // WORLD
 	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED + RANK, device=DEV)
-	pos = None
-	if tag_weights is not None:
-		import torch
-		g = torch.Generator(device=DEV)
-		g.manual_seed(7 + RANK)
-		pos = torch.randint(0, 17, (int(tok.numel()),), generator=g, device=DEV, dtype=torch.int8)   # 17 universal POS tags
-	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True,
-		token_pos=pos)
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
 	attach_shard(dc, tables["n_doc"])
-	del tok, pos
+	del tok
 	emb = embedding if embedding is not None else synthetic.make_embedding(vocab, dim)
 	de = engine.DeviceEmbedding(emb)
 	aps, keeps = [], []

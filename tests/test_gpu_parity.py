@@ -264,6 +264,44 @@ def test_many_ties_topk(engine, oracle):
 	assert [(int(h["doc"]), int(h["slice"])) for h in hits] == want
 
 
+def test_more_ties_than_the_candidate_buffer_holds(engine):
+	"""12 000 identical windows: every score ties, the pruned top-k overflows its 8192-key candidate buffer and the search
+	(single, setting-fused batch, query-fused batch) must fall back to the exact radix select: the order is still
+	(doc desc, slice desc)."""
+	n, per_doc = 12000, 100
+	token_id = np.zeros(n * 4, np.int32)
+	starts = (np.arange(n) % per_doc) * 4
+	doc_span_off = np.arange(0, n + 1, per_doc)
+	dc = engine.DeviceCorpus(token_id, doc_span_off * 4, starts, starts + 4, doc_span_off)
+	sims = [engine.DeviceSim.upload(np.full((1, 3), 0.5, np.float32)), engine.DeviceSim.upload(np.full((1, 2), 0.25, np.float32))]
+	qp, _ = _cabi.make_query_params(max_matches=130, min_score=0.0)
+	want = [(n // per_doc - 1 - i // per_doc, per_doc - 1 - i % per_doc) for i in range(130)]
+	aps, keeps = [], []
+	for locality, gap_name in ((_cabi.VX_LOCAL, "none"), (_cabi.VX_LOCAL, "linear0.2"), (_cabi.VX_GLOBAL, "none"), (_cabi.VX_GLOBAL, "linear0.2")):
+		ap, keep = align_params(locality, GAPS[gap_name], 4, 3)
+		aps.append(ap)
+		keeps.append(keep)
+	for sim in sims:
+		hits, _, _ = dc.search(sim, aps[0], qp)
+		assert len(hits) == 130 and np.all(hits["score"] == hits["score"][0])
+		assert [(int(h["doc"]), int(h["slice"])) for h in hits] == want
+	batch = dc.search_batch(sims, aps, qp)             # settings of a query fused
+	mq = dc.search_batch(sims, aps[:1], qp)            # queries of a setting fused
+	for q, sim in enumerate(sims):
+		for a, ap in enumerate(aps):
+			single = dc.search(sim, ap, qp)
+			for got in ([batch[q][a]] + ([mq[q][0]] if a == 0 else [])):
+				assert len(got[0]) == len(single[0])
+				for f in ("score", "doc", "slice"):
+					np.testing.assert_array_equal(got[0][f], single[0][f])
+				np.testing.assert_array_equal(got[1], single[1])
+			if len(single[0]):
+				assert [(int(h["doc"]), int(h["slice"])) for h in single[0]] == want[:len(single[0])]
+	for sim in sims:
+		sim.close()
+	dc.close()
+
+
 @pytest.mark.parametrize("gap_name", ["linear0.2", "affine", "smooth5"])
 def test_contextual_fast_path(engine, oracle, gap_name):
 	"""Per-token contextual vectors: S_doc formed on the device (ctx_sim_kernel), then the same DP kernels.

@@ -200,9 +200,23 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
 	return r;
 }
 
+// packed fp32 add (add.rn.f32x2 -> FADD2): two independent round-to-nearest adds in one issue slot
+__device__ __forceinline__ float2 add2(float2 a, float2 b) {
+	float2 r;
+	asm("{ .reg .b64 ra, rb, rc; mov.b64 ra, {%2, %3}; mov.b64 rb, {%4, %5}; add.rn.f32x2 rc, ra, rb; mov.b64 {%0, %1}, rc; }"
+		: "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+	return r;
+}
+
+// Settings are processed in PAIRS (i, i + 1) of the same locality (NL and NG are even): the three adds of a cell --
+// diag + S, up - g_s, left - g_t -- are three FADD2 over the pair, with {-g_s[i], -g_s[i+1]} / {-g_t[i], -g_t[i+1]} from the
+// parameter bank (x - g == x + (-g) bit for bit); the maximum is one FMNMX3 per setting.  5 issue slots per cell and
+// setting pair instead of 8.
 template<int TP, int NL, int NG, bool ZC>
 __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, const __grid_constant__ MultiArgs m) {
 	constexpr int NS = NL + NG;
+	constexpr int NP = NS / 2, NLP = NL / 2;
+	static_assert(NL % 2 == 0 && NG % 2 == 0, "settings are paired");
 	const int64_t tile = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (tile >= a.n_tiles) {
 		return;
@@ -212,16 +226,17 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 	const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + lane) * 4;
 	const int len = tl.len;
 
-	float h[NS][TP];              // h[i][v] = V_i[u-1, v]
-	float best[NL > 0 ? NL : 1];  // Local: running maximum (padded columns v >= t only repeat or lower values)
+	float2 h[NP][TP];                 // h[p][v] = {V_2p[u-1, v], V_2p+1[u-1, v]}
+	float2 best[NLP > 0 ? NLP : 1];   // Local: running maxima (padded columns v >= t only repeat or lower values)
 	#pragma unroll
-	for (int i = 0; i < NS; i++) {
+	for (int p = 0; p < NP; p++) {
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
-			h[i][v] = i < NL ? 0.0f : -((float)(v + 1) * m.gt[i]);   // solver.h:2804-2806
+			h[p][v] = p < NLP ? make_float2(0.0f, 0.0f)
+				: make_float2(-((float)(v + 1) * m.gt[2 * p]), -((float)(v + 1) * m.gt[2 * p + 1]));   // solver.h:2804-2806
 		}
-		if (i < NL) {
-			best[i] = 0.0f;
+		if (p < NLP) {
+			best[p] = make_float2(0.0f, 0.0f);
 		}
 	}
 
@@ -230,35 +245,42 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 	load_row<TP>(a.s, id, row);
 
 	for (int u = 0; u < len; u++) {
-		float cur[TP];
+		float2 cur[TP];
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
-			cur[v] = row[v];
+			cur[v] = make_float2(row[v], row[v]);
 		}
 		if (u + 1 < len) {
 			id = tok[vx_elem(0, u + 1, 0)];
 			load_row<TP>(a.s, id, row);
 		}
 		#pragma unroll
-		for (int i = 0; i < NS; i++) {
-			const float gs = m.gs[i], gt = m.gt[i];
-			float diag = i < NL ? 0.0f : -((float)u * gs);        // V[u-1, -1]
-			float left = i < NL ? 0.0f : -((float)(u + 1) * gs);  // V[u, -1]
+		for (int p = 0; p < NP; p++) {
+			const float2 ngs = make_float2(-m.gs[2 * p], -m.gs[2 * p + 1]);
+			const float2 ngt = make_float2(-m.gt[2 * p], -m.gt[2 * p + 1]);
+			// V[u-1, -1] and V[u, -1]
+			float2 diag = p < NLP ? make_float2(0.0f, 0.0f) : make_float2(-((float)u * m.gs[2 * p]), -((float)u * m.gs[2 * p + 1]));
+			float2 left = p < NLP ? make_float2(0.0f, 0.0f) : make_float2(-((float)(u + 1) * m.gs[2 * p]), -((float)(u + 1) * m.gs[2 * p + 1]));
 			#pragma unroll
 			for (int v = 0; v < TP; v++) {
-				const float up = h[i][v];
-				float x = fmax3(diag + cur[v], up - gs, left - gt);
-				if (i < NL && ZC) {
-					x = fmaxf(x, 0.0f);   // Local zero; with S >= 0 it never wins: diag + S >= 0 already (ZC = false)
+				const float2 up = h[p][v];
+				const float2 c0 = add2(diag, cur[v]);
+				const float2 c1 = add2(up, ngs);
+				const float2 c2 = add2(left, ngt);
+				float2 x = make_float2(fmax3(c0.x, c1.x, c2.x), fmax3(c0.y, c1.y, c2.y));
+				if (p < NLP && ZC) {
+					x.x = fmaxf(x.x, 0.0f);   // Local zero; with S >= 0 it never wins: diag + S >= 0 already (ZC = false)
+					x.y = fmaxf(x.y, 0.0f);
 				}
 				diag = up;
-				h[i][v] = x;
+				h[p][v] = x;
 				left = x;
 			}
-			if (i < NL) {
+			if (p < NLP) {
 				#pragma unroll
 				for (int v = 0; v + 1 < TP; v += 2) {
-					best[i] = fmax3(best[i], h[i][v], h[i][v + 1]);
+					best[p].x = fmax3(best[p].x, h[p][v].x, h[p][v + 1].x);
+					best[p].y = fmax3(best[p].y, h[p][v].y, h[p][v + 1].y);
 				}
 			}
 		}
@@ -268,15 +290,16 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 	const float boost = a.boost ? a.boost[slot] : 1.0f;
 	#pragma unroll
 	for (int i = 0; i < NS; i++) {
+		const int p = i / 2;
 		float raw;
 		if (i < NL) {
-			raw = best[i];
+			raw = (i & 1) ? best[p].y : best[p].x;
 		} else {
-			raw = h[i][0];                       // V[len-1, t-1]; the selects are opaque to the compiler, which would
-			#pragma unroll                       // otherwise turn the chain into a dynamically indexed local-memory array
+			raw = (i & 1) ? h[p][0].y : h[p][0].x;   // V[len-1, t-1]; the selects are opaque to the compiler, which would
+			#pragma unroll                           // otherwise turn the chain into a dynamically indexed local-memory array
 			for (int v = 1; v < TP; v++) {
 				asm("{ .reg .pred p; setp.eq.s32 p, %2, %3; selp.f32 %0, %1, %0, p; }"
-					: "+f"(raw) : "f"(h[i][v]), "r"(v), "r"(a.t - 1));
+					: "+f"(raw) : "f"((i & 1) ? h[p][v].y : h[p][v].x), "r"(v), "r"(a.t - 1));
 			}
 		}
 		m.score[i][slot] = lane < tl.n_valid ? finish_score(raw, a.total, boost) : -CUDART_INF_F;

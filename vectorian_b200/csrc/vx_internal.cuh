@@ -259,6 +259,8 @@ struct VxTopkOut {
 size_t vx_topk_work_bytes(int32_t k);
 int vx_launch_topk(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out);
 int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out, const unsigned int **overflow_flag_dev);
+int vx_launch_topk_pruned_multi(vx_corpus *c, float min_score, int32_t k, void *work, size_t stride, int n_arrays,
+	const float *const *scores, VxTopkOut *outs, const unsigned int **overflow_flags_dev);
 int vx_launch_topk_multi(vx_corpus *c, float min_score, int32_t k, void *work, size_t stride, int n_arrays,
 	const float *const *scores, VxTopkOut *outs);
 

@@ -115,6 +115,42 @@ static int ensure_gather(vx_corpus *c, size_t bytes) {
 	return VX_OK;
 }
 
+// top-k of the score arrays of one vx_search_batch group in ONE set of launches: the pruned selection (any size, 3
+// launches), else the cooperative radix kernel (<= 4 M slots).  ovf[i] = device flag "array i overflowed" or nullptr.
+static bool batch_topk(vx_corpus *c, float min_score, int32_t k, int n_arrays, const float *const *score, VxTopkOut *tks,
+	const unsigned int **ovf) {
+
+	const size_t stride = align_up(vx_topk_work_bytes(k), 256);
+	if (!c->d_topk_multi || c->topk_multi_stride != stride) {
+		cudaFree(c->d_topk_multi);
+		c->d_topk_multi = nullptr;
+		if (cudaMalloc(&c->d_topk_multi, stride * 8) == cudaSuccess) {
+			c->topk_multi_stride = stride;
+		} else {
+			cudaGetLastError();
+		}
+	}
+	for (int i = 0; i < n_arrays; i++) {
+		ovf[i] = nullptr;
+	}
+	if (!c->d_topk_multi) {
+		return false;
+	}
+	const int n = vx_launch_topk_pruned_multi(c, min_score, k, c->d_topk_multi, stride, n_arrays, score, tks, ovf);
+	if (n > 0) {
+		c->last_launches += n;
+		return true;
+	}
+	for (int i = 0; i < n_arrays; i++) {
+		ovf[i] = nullptr;
+	}
+	if (vx_launch_topk_multi(c, min_score, k, c->d_topk_multi, stride, n_arrays, score, tks) == 1) {
+		c->last_launches += 1;
+		return true;
+	}
+	return false;
+}
+
 // Validates like the reference does and stages the per-query constants on the device.
 static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, const vx_query_params *qp,
 	bool need_results, QueryPlan *p, const BatchSlot *batch = nullptr) {
@@ -724,27 +760,12 @@ extern "C" int vx_search_batch(
 				float *const d_score = c->d_score;
 				c->stream = c->select_stream;
 				VxTopkOut tks[8];
-				bool multi = false;
-				{
-					const size_t stride = align_up(vx_topk_work_bytes(k), 256);
-					if (!c->d_topk_multi || c->topk_multi_stride != stride) {
-						cudaFree(c->d_topk_multi);
-						c->d_topk_multi = nullptr;
-						if (cudaMalloc(&c->d_topk_multi, stride * 8) == cudaSuccess) {
-							c->topk_multi_stride = stride;
-						} else {
-							cudaGetLastError();
-						}
-					}
-					if (c->d_topk_multi) {
-						multi = vx_launch_topk_multi(c, qp->min_score, k, c->d_topk_multi, stride, k_n, score, tks) == 1;
-						c->last_launches += multi ? 1 : 0;
-					}
-				}
+				const unsigned int *ovf[8];
+				const bool multi = batch_topk(c, qp->min_score, k, k_n, score, tks, ovf);
 				for (int j = 0; j < k_n && rc == VX_OK; j++) {
 					const size_t pi = (size_t)qs[at + j] * n_aps + ai;
 					c->d_score = score[j];
-					rc = multi ? enqueue_finish(c, group[j], plans[pi], tks[j], false) : enqueue_select(c, group[j], plans[pi], false);
+					rc = multi ? enqueue_finish(c, group[j], plans[pi], tks[j], false, ovf[j]) : enqueue_select(c, group[j], plans[pi], false);
 					done_pair[pi] = 1;
 					live[pi] = 1;
 				}
@@ -844,24 +865,12 @@ extern "C" int vx_search_batch(
 			cudaStreamWaitEvent(c->select_stream, c->ev_dp[buf], 0);
 			float *const d_score = c->d_score;
 			c->stream = c->select_stream;
-			// the top-k of all settings of the group in ONE cooperative launch (they share slots, k and min_score)
+			// the top-k of all settings of the group in ONE set of launches (they share slots, k and min_score)
 			VxTopkOut tks[8];
+			const unsigned int *ovf[8];
 			bool multi = false;
 			if (nl + ng > 1) {
-				const size_t stride = align_up(vx_topk_work_bytes(k), 256);
-				if (!c->d_topk_multi || c->topk_multi_stride != stride) {
-					cudaFree(c->d_topk_multi);
-					c->d_topk_multi = nullptr;
-					if (cudaMalloc(&c->d_topk_multi, stride * 8) == cudaSuccess) {
-						c->topk_multi_stride = stride;
-					} else {
-						cudaGetLastError();
-					}
-				}
-				if (c->d_topk_multi) {
-					multi = vx_launch_topk_multi(c, qp->min_score, k, c->d_topk_multi, stride, nl + ng, score, tks) == 1;
-					c->last_launches += multi ? 1 : 0;
-				}
+				multi = batch_topk(c, qp->min_score, k, nl + ng, score, tks, ovf);
 			}
 			// ... and so are their tracebacks (same query constants, per-setting gap costs and result blocks)
 			bool traced = false;
@@ -890,11 +899,16 @@ extern "C" int vx_search_batch(
 				const QueryPlan &pj = plans[(size_t)q * n_aps + group[j]];
 				if (traced) {
 					cudaMemcpyAsync(pj.res + pj.off_n, tks[j].n, sizeof(int32_t), cudaMemcpyDeviceToDevice, c->stream);
+					if (ovf[j]) {
+						cudaMemcpyAsync(pj.res + pj.off_n + 4, ovf[j], sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream);
+					} else {
+						cudaMemsetAsync(pj.res + pj.off_n + 4, 0, sizeof(uint32_t), c->stream);
+					}
 					if (!c->comm) {
 						cudaMemcpyAsync(pj.h_res, pj.res, pj.res_bytes, cudaMemcpyDeviceToHost, c->stream);
 					}
 				} else {
-					rc = multi ? enqueue_finish(c, s, pj, tks[j], false) : enqueue_select(c, s, pj, false);
+					rc = multi ? enqueue_finish(c, s, pj, tks[j], false, ovf[j]) : enqueue_select(c, s, pj, false);
 				}
 				done[group[j]] = 1;
 				live[(size_t)q * n_aps + group[j]] = 1;
@@ -942,6 +956,23 @@ extern "C" int vx_search_batch(
 	}
 	for (const auto &b : mq_buffers) {
 		vx_pool_free(b.first, b.second);
+	}
+	if (rc == VX_OK && e == cudaSuccess) {
+		// pairs whose pruned top-k met more equal scores than its candidate buffer holds (sharded: on any rank -- the merge
+		// ORs the flags, every rank sees the same list): searched again on their own with the radix select
+		bool again = false;
+		for (size_t i = 0; i < n_pairs && rc == VX_OK; i++) {
+			if (live[i] && *(const uint32_t*)(plans[i].h_res + plans[i].off_n + 4) != 0) {
+				rc = enqueue_search(c, sims[i / n_aps], plans[i], false, false);
+				again = true;
+			}
+		}
+		if (again && rc == VX_OK) {
+			if (c->comm) {
+				rc = enqueue_gather_merge(c, host, descs, k);
+			}
+			e = cudaStreamSynchronize(c->stream);
+		}
 	}
 	if (rc != VX_OK) {
 		return rc;

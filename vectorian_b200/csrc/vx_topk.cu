@@ -507,10 +507,31 @@ __device__ __forceinline__ float warp_max(float x) {
 	return x;
 }
 
-// one warp per group of G slots (G a multiple of 32)
-__global__ void __launch_bounds__(256) topk_group_max_kernel(const float *__restrict__ score, int64_t n_slots, int g_slots,
-	float *__restrict__ gmax, int64_t n_groups) {
+struct PrunedState {
+	float tau;
+	unsigned int n_cand;
+	unsigned int ticket;
+	unsigned int overflow;
+};
 
+// up to TOPK_MULTI score arrays over the same slots per launch (blockIdx.y = array): the settings / queries of one
+// vx_search_batch group, or one array for a single search
+struct PrunedMulti {
+	const float *score[8];
+	float *gmax[8];
+	PrunedState *st[8];
+	unsigned long long *cand[8];
+	uint32_t *out_slots[8];
+	float *out_scores[8];
+	int32_t *out_n[8];
+};
+
+// one warp per group of G slots (G a multiple of 32)
+__global__ void __launch_bounds__(256) topk_group_max_kernel(const __grid_constant__ PrunedMulti pm, int64_t n_slots, int g_slots,
+	int64_t n_groups) {
+
+	const float *__restrict__ score = pm.score[blockIdx.y];
+	float *__restrict__ gmax = pm.gmax[blockIdx.y];
 	const int lane = threadIdx.x & 31;
 	const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -535,15 +556,9 @@ __global__ void __launch_bounds__(256) topk_group_max_kernel(const float *__rest
 	}
 }
 
-struct PrunedState {
-	float tau;
-	unsigned int n_cand;
-	unsigned int ticket;
-	unsigned int overflow;
-};
-
-__global__ void __launch_bounds__(1024) topk_tau_kernel(const float *__restrict__ gmax, int64_t n_groups, int k, float min_score,
-	PrunedState *st) {
+__global__ void __launch_bounds__(1024) topk_tau_kernel(const __grid_constant__ PrunedMulti pm, int64_t n_groups, int k, float min_score) {
+	const float *__restrict__ gmax = pm.gmax[blockIdx.x];
+	PrunedState *st = pm.st[blockIdx.x];
 
 	__shared__ unsigned int hist[2048];
 	__shared__ unsigned int sh_prefix, sh_remaining, sh_stop;
@@ -635,11 +650,16 @@ __global__ void __launch_bounds__(1024) topk_tau_kernel(const float *__restrict_
 	}
 }
 
-__global__ void __launch_bounds__(256) topk_collect_sort_kernel(const float *__restrict__ score, const uint32_t *__restrict__ orig,
-	const uint32_t *__restrict__ slot_of, int64_t n_slots, int g_slots, const float *__restrict__ gmax, int64_t n_groups,
-	float min_score, int k, PrunedState *st, unsigned long long *__restrict__ cand,
-	uint32_t *__restrict__ out_slots, float *__restrict__ out_scores, int32_t *__restrict__ out_n) {
+__global__ void __launch_bounds__(256) topk_collect_sort_kernel(const __grid_constant__ PrunedMulti pm, const uint32_t *__restrict__ orig,
+	const uint32_t *__restrict__ slot_of, int64_t n_slots, int g_slots, int64_t n_groups, float min_score, int k) {
 
+	const float *__restrict__ score = pm.score[blockIdx.y];
+	const float *__restrict__ gmax = pm.gmax[blockIdx.y];
+	PrunedState *st = pm.st[blockIdx.y];
+	unsigned long long *__restrict__ cand = pm.cand[blockIdx.y];
+	uint32_t *__restrict__ out_slots = pm.out_slots[blockIdx.y];
+	float *__restrict__ out_scores = pm.out_scores[blockIdx.y];
+	int32_t *__restrict__ out_n = pm.out_n[blockIdx.y];
 	extern __shared__ unsigned long long ps_keys[];   // TOPK_CAP keys (the last block's sort)
 	__shared__ unsigned int is_last;
 	const float tau = st->tau;
@@ -746,11 +766,14 @@ __global__ void __launch_bounds__(256) topk_collect_sort_kernel(const float *__r
 	}
 }
 
-// Returns the number of launches (3), or 0 when the pruned path does not apply.  *overflow_flag_dev receives the
-// device address of the flag the caller must look at after synchronising (copy it with the results).
-int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out, const unsigned int **overflow_flag_dev) {
+// Pruned top-k of n_arrays score arrays over the same slots (work areas `stride` bytes apart).  Returns the number of
+// launches (3), or 0 when the pruned path does not apply.  overflow_flags_dev[i] receives the device address of the flag
+// the caller must look at after synchronising (copy it with the results).
+int vx_launch_topk_pruned_multi(vx_corpus *c, float min_score, int32_t k, void *work, size_t stride, int n_arrays,
+	const float *const *scores, VxTopkOut *outs, const unsigned int **overflow_flags_dev) {
+
 	static const bool off = getenv("VX_TOPK_RADIX") != nullptr;   // A/B switch (read once)
-	if (off || k > TOPK_CAP / 4 || c->n_slots < 1) {
+	if (off || k > TOPK_CAP / 4 || c->n_slots < 1 || n_arrays < 1 || n_arrays > 8) {
 		return 0;
 	}
 	// group size: many more groups than k, at most 1024 slots each
@@ -759,7 +782,8 @@ int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, 
 		g_slots >>= 1;
 	}
 	const int64_t n_groups = (c->n_slots + g_slots - 1) / g_slots;
-	const size_t need = sizeof(float) * (size_t)n_groups;
+	const size_t per_array = (sizeof(float) * (size_t)n_groups + 255) & ~(size_t)255;
+	const size_t need = per_array * 8;
 	if (c->group_max_bytes < need) {
 		cudaFree(c->d_group_max);
 		c->d_group_max = nullptr;
@@ -770,9 +794,20 @@ int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, 
 		}
 		c->group_max_bytes = need;
 	}
-	TopkWork *w;
-	topk_carve(work, k, &w, out);
-	PrunedState *st = reinterpret_cast<PrunedState*>(&w->hist[0][0]);   // the radix histograms are not used by this path
+	PrunedMulti pm;
+	memset(&pm, 0, sizeof(pm));
+	for (int i = 0; i < n_arrays; i++) {
+		TopkWork *w;
+		topk_carve((uint8_t*)work + stride * (size_t)i, k, &w, &outs[i]);
+		pm.score[i] = scores[i];
+		pm.gmax[i] = (float*)((uint8_t*)c->d_group_max + per_array * (size_t)i);
+		pm.st[i] = reinterpret_cast<PrunedState*>(&w->hist[0][0]);   // the radix histograms are not used by this path
+		pm.cand[i] = w->cand;
+		pm.out_slots[i] = outs[i].slots;
+		pm.out_scores[i] = outs[i].scores;
+		pm.out_n[i] = outs[i].n;
+		overflow_flags_dev[i] = &pm.st[i]->overflow;
+	}
 	static int sms = 0;
 	static bool attr = false;
 	if (!sms) {
@@ -785,19 +820,26 @@ int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, 
 	}
 	cudaStream_t st_ = c->stream;
 	int64_t blocks = (n_groups * 32 + 255) / 256;
-	blocks = blocks > (int64_t)sms * 8 ? (int64_t)sms * 8 : blocks < 1 ? 1 : blocks;
-	topk_group_max_kernel<<<(unsigned)blocks, 256, 0, st_>>>(c->d_score, c->n_slots, g_slots, c->d_group_max, n_groups);
-	topk_tau_kernel<<<1, 1024, 0, st_>>>(c->d_group_max, n_groups, k, min_score, st);
+	const int64_t cap = (int64_t)sms * 8 / n_arrays;
+	blocks = blocks > cap ? cap : blocks;
+	blocks = blocks < 1 ? 1 : blocks;
+	topk_group_max_kernel<<<dim3((unsigned)blocks, (unsigned)n_arrays), 256, 0, st_>>>(pm, c->n_slots, g_slots, n_groups);
+	topk_tau_kernel<<<n_arrays, 1024, 0, st_>>>(pm, n_groups, k, min_score);
 	int64_t cblocks = (n_groups + 255) / 256;          // a warp takes 32 groups per step
-	cblocks = cblocks > sms ? sms : cblocks < 1 ? 1 : cblocks;
-	topk_collect_sort_kernel<<<(unsigned)cblocks, 256, smem, st_>>>(c->d_score, c->d_orig, c->d_slot_of, c->n_slots, g_slots,
-		c->d_group_max, n_groups, min_score, k, st, w->cand, out->slots, out->scores, out->n);
+	const int64_t ccap = n_arrays > 1 ? (sms + n_arrays - 1) / n_arrays * 2 : sms;
+	cblocks = cblocks > ccap ? ccap : cblocks < 1 ? 1 : cblocks;
+	topk_collect_sort_kernel<<<dim3((unsigned)cblocks, (unsigned)n_arrays), 256, smem, st_>>>(pm, c->d_orig, c->d_slot_of, c->n_slots, g_slots,
+		n_groups, min_score, k);
 	if (cudaGetLastError() != cudaSuccess) {
 		vx_set_error("pruned top-k launch failed");
 		return -1;
 	}
-	*overflow_flag_dev = &st->overflow;
 	return 3;
+}
+
+int vx_launch_topk_pruned(vx_corpus *c, float min_score, int32_t k, void *work, VxTopkOut *out, const unsigned int **overflow_flag_dev) {
+	const float *scores[1] = {c->d_score};
+	return vx_launch_topk_pruned_multi(c, min_score, k, work, 0, 1, scores, out, overflow_flag_dev);
 }
 
 size_t vx_topk_work_bytes(int32_t k) {
