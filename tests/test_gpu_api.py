@@ -450,3 +450,24 @@ def test_debug_hook_reports_matrix_and_every_slice():
 	big.DEBUG_MAX_WINDOWS = 10
 	with pytest.raises(NotImplementedError, match="debug hook"):
 		big.find("w3 w17", debug=lambda name, data: None)
+
+
+def test_window_emptied_by_a_token_filter_is_not_reported():
+	"""Documented deviation: the token filter is a property of the packed corpus, so a window whose
+	tokens are ALL filtered has no tokens left and is never reported -- the reference aligns the empty window, scores it 0
+	and admits it when min_score < 0 (cpp/slice/static.h:365-416).  With min_score >= 0 (every reference caller: Index.find
+	passes 0.0) the results are identical; this test pins the documented behaviour for min_score < 0."""
+	sents = [["w1", "w2", "w3"], ["w4", "w5"], ["w6", "w1", "w2"]]
+	pos = [["NOUN", "VERB", "NOUN"], ["DET", "DET"], ["NOUN", "DET", "VERB"]]
+	tag = [["NN", "VB", "NN"], ["DT", "DT"], ["NN", "DT", "VB"]]
+	words = [f"w{i}" for i in range(1, 8)]
+	rng = np.random.default_rng(0)
+	emb = KeyedVectors("toy", (words, rng.standard_normal((len(words), 8)).astype(np.float32)))
+	session = Session(Corpus([Document.from_sentences(sents, pos=pos, tag=tag)]), [emb])
+	index = session.partition("sentence").index(
+		OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), LocalAlignment()), nlp=whitespace_nlp)
+	plain = index.find("w1 w2", n=10, min_score=-1.0)
+	assert sorted(m.slice_id for m in plain) == [0, 1, 2]
+	filtered = index.find("w1 w2", n=10, min_score=-1.0, options={"pos_filter": ["DET"]})
+	assert sorted(m.slice_id for m in filtered) == [0, 2]          # slice 1 has only DET tokens
+	assert [m.slice_id for m in index.find("w1 w2", n=10, min_score=0.0, options={"pos_filter": ["DET"]}) if m.slice_id == 1] == []
