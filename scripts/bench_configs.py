@@ -247,6 +247,34 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100, em
 	dc.close()
 
 
+def run_long_query(name, locality, gap, t, n_sent, vocab=50_000, dim=300, k=100, steps=5):
+	"""Queries of more than 16 tokens: S is uploaded (vx_sim_upload), the search takes the TP = 20 .. 32 score kernels."""
+	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED, device=DEV)
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"], on_device=True)
+	del tok
+	emb = synthetic.make_embedding(vocab, dim)
+	ehat = emb / np.linalg.norm(emb, axis=1, keepdims=True)
+	q = synthetic.make_query(t, vocab, seed=123)
+	s_host = np.clip(ehat @ ehat[q].T, 0.0, 1.0).astype(np.float32)
+	s_host[q, np.arange(t)] = 1.0
+	sim = engine.DeviceSim.upload(s_host)
+	r = gaps.resolve_gap_costs(gap, 64, t)
+	kind = r.pop("gap_kind")
+	ap, keep = _cabi.make_align_params(locality, kind, **r)
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
+	tm = []
+	for i in range(2 + steps):
+		t0 = time.perf_counter()
+		hits = dc.search(sim, ap, qp)[0]
+		if i >= 2:
+			tm.append((time.perf_counter() - t0) * 1e3)
+	lt = dc.last_timing()
+	emit({"config": name, "sentences": n_sent, "T": t, "wall_ms": float(np.median(tm)), "ms": lt,
+		"sentences_per_s_e2e": n_sent / float(np.median(tm)) * 1e3, "launches": dc.last_launches(), "top_score": float(hits["score"][0])})
+	sim.close()
+	dc.close()
+
+
 def run_multi_query(name, locality, gap, t, n_sent, vocab, dim, n_queries=8, k=100, reps=5):
 	"""Several queries against ONE linear-gap setting: n_queries single vx_search calls vs one
 	vx_search_batch (score_linear_mq_kernel), same results."""
@@ -312,6 +340,10 @@ def main():
 	if "wsbloc" in which:
 		for loc, nm in ((_cabi.VX_LOCAL, "Local"), (_cabi.VX_GLOBAL, "Global"), (_cabi.VX_SEMIGLOBAL, "Semiglobal")):
 			run_static("WSB %s smooth_gap_cost(5) T=12 10M V=50k" % nm, loc, gaps.smooth_gap_cost(5), 12, 10_000_000, 50_000, 300)
+	if "long" in which:   # a whole sentence as the query: 24 tokens (S assembled from two 16-column similarity launches by the host API; here uploaded)
+		for nm, loc, gap in (("SW Local linear(0.2)", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2)), ("Gotoh Local affine(0.3,0.1)", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1)),
+				("WSB Local smooth_gap_cost(5)", _cabi.VX_LOCAL, gaps.smooth_gap_cost(5))):
+			run_long_query("long query T=24: %s, 2M sentences" % nm, loc, gap, 24, 2_000_000)
 	if "mq" in which:
 		run_multi_query("C2-mq: 8 SW Local linear(0.2) queries, T=8, 20M sentences, V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 20_000_000, 200_000, 300)
 		run_multi_query("C2-mq12: 8 NW Global linear(0.2) queries, T=12, 20M sentences, V=50k", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.2), 12, 20_000_000, 50_000, 300)

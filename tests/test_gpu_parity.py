@@ -264,6 +264,26 @@ def test_many_ties_topk(engine, oracle):
 	assert [(int(h["doc"]), int(h["slice"])) for h in hits] == want
 
 
+@pytest.mark.parametrize("t", [17, 24, 27, 32])
+def test_queries_of_17_to_32_tokens_on_the_score_kernels(engine, oracle, t):
+	"""Queries longer than 16 tokens (a whole sentence as the query) take the linear / affine / general-scratch score kernels
+	(TP = 20 .. 32) instead of the one-thread-per-window scorer: bit-identical scores, identical top-k and tracebacks, for
+	every locality x gap kind, incl. windows longer than 64 tokens and a boost."""
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=900, t=t, seed=90 + t)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	rng = np.random.default_rng(t)
+	boost = rng.uniform(0.5, 1.5, size=len(corpus["span_start"])).astype(np.float32)
+	dc, oc = make_both(engine, oracle, corpus, boost=boost)
+	for locality in LOCALITIES:
+		for gap_name in ("linear0.2", "linear_st", "affine", "smooth5"):
+			run_case(engine, oracle, dc, oc, s, locality, GAPS[gap_name], t)
+	dc.close()
+	dc, oc = make_both(engine, oracle, corpus, window_size=4, window_step=3)     # windows of up to 4 x 64 tokens
+	run_case(engine, oracle, dc, oc, s, _cabi.VX_LOCAL, GAPS["linear0.2"], t)
+	run_case(engine, oracle, dc, oc, s, _cabi.VX_SEMIGLOBAL, GAPS["affine"], t)
+	dc.close()
+
+
 def test_more_ties_than_the_candidate_buffer_holds(engine):
 	"""12 000 identical windows: every score ties, the pruned top-k overflows its 8192-key candidate buffer and the search
 	(single, setting-fused batch, query-fused batch) must fall back to the exact radix select: the order is still

@@ -676,7 +676,12 @@ static int launch_score_tl(vx_corpus *c, const vx_sim *s, const ScoreArgs &a, co
 		default: {
 			// windows up to 64 tokens: shared-memory kernel (vx_wsb.cu); the rest: global scratch
 			int64_t first = 0;
-			const int n_fast = vx_launch_wsb(c, s, ap, qp, &first, a.tok);
+			int n_fast = 0;
+			if (TP <= VX_MAX_T_FAST) {
+				n_fast = vx_launch_wsb(c, s, ap, qp, &first, a.tok);   // (tag weighting: windows <= 64 tokens only, see make_plan)
+			} else {
+				first = c->n_tiles;    // queries of 17 .. 32 tokens: every tile goes to the scratch kernel below
+			}
 			if (n_fast < 0) {
 				return -1;
 			}
@@ -812,6 +817,18 @@ int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 			break;
 		case 16:
 			n = launch_score_t<16>(c, s, a, ap, qp);
+			break;
+		case 20:
+			n = launch_score_t<20>(c, s, a, ap, qp);
+			break;
+		case 24:
+			n = launch_score_t<24>(c, s, a, ap, qp);
+			break;
+		case 28:
+			n = launch_score_t<28>(c, s, a, ap, qp);
+			break;
+		case 32:
+			n = launch_score_t<32>(c, s, a, ap, qp);
 			break;
 		default:
 			vx_set_error("vx_launch_score: query longer than the fast path supports");

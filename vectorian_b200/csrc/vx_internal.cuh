@@ -153,7 +153,8 @@ void vx_pool_free(void *p, size_t bytes);
 cudaStream_t vx_sim_stream();
 
 // Per-query constants handed to the kernels by value.
-constexpr int VX_MAX_T_FAST = 16;    // query lengths with a register-resident fast path
+constexpr int VX_MAX_T_FAST = 16;    // query lengths of the tensor-memory WSB kernel, the similarity kernels, tag weighting, batches
+constexpr int VX_MAX_T_LONG = 32;    // query lengths of the linear / affine / general-scratch score kernels (one DP row in registers)
 constexpr int VX_MAX_T_MASK = 32;    // matched-set bitmask width of the exact kernel
 
 struct VxAlignDev {

@@ -227,7 +227,10 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 		tag_fast = tag_fast && sum > 0.0f && sum < 8192.0f && t <= VX_MAX_T_FAST;
 		tag_fast = tag_fast && !(ap->gap_kind == VX_GAP_GENERAL && c->max_len > 64);
 	}
-	p->fast = (!s->contextual || c->d_iota) && s->tp <= VX_MAX_T_FAST && tag_fast && qp->submatch_weight == 0.0f;
+	// query lengths: up to 16 tokens everywhere; 17 .. 32 tokens on the linear / affine / general-scratch kernels for static
+	// and host-supplied per-token matrices (the contextual similarity kernels and tag weighting stop at 16)
+	const int32_t tp_max = (s->contextual == 1 || s->contextual == 2 || qp->tag_weighted) ? VX_MAX_T_FAST : VX_MAX_T_LONG;
+	p->fast = (!s->contextual || c->d_iota) && s->tp <= tp_max && tag_fast && qp->submatch_weight == 0.0f;
 
 	// ---- workspace layout: [top-k area | block of plan 0 | block of plan 1 | ...] ----
 	const size_t n_ws = ap->gap_kind == VX_GAP_GENERAL ? (size_t)ap->n_w_s : 0;
