@@ -216,7 +216,7 @@ int vx_search_batch(
  * library (held until the process exits).  Returns the same hits (score, score_max, doc, slice; same order) vx_search
  * returns, without tracebacks (no target / dist).
  * Limits: max_matches <= VX_NOALLOC_MAX_K; static or uploaded similarity matrix with at most 16 query tokens; no
- * tag weighting, submatch_weight == 0; general gap costs only with windows of at most 64 tokens (the other paths
+ * tag weighting, submatch_weight == 0; general gap costs only with windows the tensor-memory kernel takes (up to 160 tokens for T <= 12, 144 for T = 16) (the other paths
  * need scratch sized by the input).  Anything beyond fails with VX_ERR_INVALID and a message; nothing is truncated.
  * Every call on a GPU shares the array and finds the last call's contents in it: what must start at zero is cleared
  * at the start of each call.  Calls that overlap on one GPU would race on it; within a process they cannot (the

@@ -247,6 +247,31 @@ def run_sweep(name, n_sent, t=12, vocab=50_000, dim=300, n_queries=64, k=100, em
 	dc.close()
 
 
+def run_windows(name, locality, gap, t, n_sent, window_size, window_step, vocab=50_000, dim=300, k=100, steps=5):
+	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED, device=DEV)
+	dc = engine.DeviceCorpus(tok, tables["doc_tok_off"], tables["span_start"], tables["span_end"], tables["doc_span_off"],
+		window_size=window_size, window_step=window_step, on_device=True)
+	del tok
+	emb = synthetic.make_embedding(vocab, dim)
+	de = engine.DeviceEmbedding(emb)
+	q = synthetic.make_query(t, vocab, seed=123)
+	r = gaps.resolve_gap_costs(gap, dc.max_len, t)
+	kind = r.pop("gap_kind")
+	ap, keep = _cabi.make_align_params(locality, kind, **r)
+	qp, _ = _cabi.make_query_params(max_matches=k, min_score=0.0)
+	tm = []
+	for i in range(2 + steps):
+		t0 = time.perf_counter()
+		sim = engine.DeviceSim.static(de, q, emb[q])
+		hits = dc.search(sim, ap, qp)[0]
+		if i >= 2:
+			tm.append((time.perf_counter() - t0) * 1e3)
+		sim.close()
+	emit({"config": name, "windows": dc.n_windows, "max_len": dc.max_len, "cells": dc.n_cells, "T": t, "wall_ms": float(np.median(tm)), "ms": dc.last_timing(),
+		"windows_per_s_e2e": dc.n_windows / float(np.median(tm)) * 1e3, "gcups": dc.n_cells * t / float(np.median(tm)) / 1e6, "launches": dc.last_launches()})
+	dc.close()
+
+
 def run_long_query(name, locality, gap, t, n_sent, vocab=50_000, dim=300, k=100, steps=5):
 	"""Queries of more than 16 tokens: S is uploaded (vx_sim_upload), the search takes the TP = 20 .. 32 score kernels."""
 	tok, tables = synthetic.make_corpus_device(n_sent, vocab, seed=synthetic.CORPUS_SEED, device=DEV)
@@ -340,6 +365,8 @@ def main():
 	if "wsbloc" in which:
 		for loc, nm in ((_cabi.VX_LOCAL, "Local"), (_cabi.VX_GLOBAL, "Global"), (_cabi.VX_SEMIGLOBAL, "Semiglobal")):
 			run_static("WSB %s smooth_gap_cost(5) T=12 10M V=50k" % nm, loc, gaps.smooth_gap_cost(5), 12, 10_000_000, 50_000, 300)
+	if "win" in which:    # three-sentence windows (~75 tokens, up to 192): general gap costs over windows longer than 64 tokens
+		run_windows("WSB Local smooth_gap_cost(5) T=12, windows of 3 sentences (step 1), 1M sentences", _cabi.VX_LOCAL, gaps.smooth_gap_cost(5), 12, 1_000_000, 3, 1)
 	if "long" in which:   # a whole sentence as the query: 24 tokens (S assembled from two 16-column similarity launches by the host API; here uploaded)
 		for nm, loc, gap in (("SW Local linear(0.2)", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2)), ("Gotoh Local affine(0.3,0.1)", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1)),
 				("WSB Local smooth_gap_cost(5)", _cabi.VX_LOCAL, gaps.smooth_gap_cost(5))):

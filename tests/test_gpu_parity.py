@@ -284,6 +284,27 @@ def test_queries_of_17_to_32_tokens_on_the_score_kernels(engine, oracle, t):
 	dc.close()
 
 
+@pytest.mark.parametrize("t", [5, 12, 16])
+def test_general_gap_costs_over_long_windows(engine, oracle, t):
+	"""Windows of up to five sentences (up to 320 tokens) with general gap costs: the tensor-memory WSB kernel takes
+	windows of up to 160 tokens (fewer warps per SM for the long classes), the scratch kernel the rest -- bit-identical
+	to the oracle for every locality, with and without tag weighting."""
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=700, t=t, seed=60 + t, with_pos=True)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	rng = np.random.default_rng(t)
+	t_pos = rng.integers(0, 17, size=t).astype(np.int8)
+	w = (rng.integers(1, 9, size=t) / 4.0).astype(np.float32)
+	for window_size, window_step in ((3, 2), (5, 3)):
+		dc, oc = make_both(engine, oracle, corpus, window_size=window_size, window_step=window_step, with_pos=True)
+		assert dc.max_len > 64
+		for locality in LOCALITIES:
+			run_case(engine, oracle, dc, oc, s, locality, GAPS["smooth5"], t)
+			run_case(engine, oracle, dc, oc, s, locality, GAPS["mixed"], t)
+		run_case(engine, oracle, dc, oc, s, _cabi.VX_LOCAL, GAPS["log"], t,
+			t_weights=w, t_pos=t_pos, pos_mismatch_penalty=0.4, similarity_threshold=0.1)
+		dc.close()
+
+
 def test_more_ties_than_the_candidate_buffer_holds(engine):
 	"""12 000 identical windows: every score ties, the pruned top-k overflows its 8192-key candidate buffer and the search
 	(single, setting-fused batch, query-fused batch) must fall back to the exact radix select: the order is still

@@ -49,7 +49,8 @@ __host__ __device__ __forceinline__ size_t vx_elem(uint32_t base128, int u, int 
 constexpr int VX_TOK_SLACK = 4 * 128;   // elements readable past the last tile (prefetch runs ahead)
 
 constexpr int VX_TILE = 32;
-constexpr int VX_N_CLASS = 16;       // length classes of 4 tokens: windows up to 64 tokens take the fast WSB kernel
+constexpr int VX_WSB_MAX_LEN = 160;  // longest window the tensor-memory WSB kernel takes (history on chip; fewer warps per SM for long classes)
+constexpr int VX_N_CLASS = VX_WSB_MAX_LEN / 4;   // length classes of 4 tokens
 constexpr uint32_t VX_NO_WINDOW = 0xffffffffu;
 
 struct vx_corpus {
@@ -233,6 +234,7 @@ int vx_launch_score(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const V
 
 // vx_wsb.cu -- general gap cost, windows up to 64 tokens, history in shared memory.  Handles the
 // tiles [*first_tile, n_tiles); the longer ones are left to the scratch kernel of vx_align.cu.
+int vx_wsb_longest(int tp);
 int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQueryDev &qp, int64_t *first_tile, const int32_t *ids);
 
 // vx_trace.cu -- exact DP with traceback for a list of slots (device array), one thread per item.

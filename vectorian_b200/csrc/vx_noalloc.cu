@@ -126,9 +126,9 @@ extern "C" int vx_search_topk_noalloc(
 		if (ap->n_w_s < c->max_len + 1 || ap->n_w_t < t + 1) {
 			VX_FAIL(VX_ERR_INVALID, "gap cost tensor shorter than the longest window / the query");
 		}
-		if (c->max_len > 64) {
-			VX_FAIL(VX_ERR_INVALID, "vx_search_topk_noalloc: general gap costs with windows longer than 64 tokens need "
-				"DP scratch in global memory; use vx_search");
+		if (c->max_len > vx_wsb_longest(s->tp)) {
+			VX_FAIL(VX_ERR_INVALID, "vx_search_topk_noalloc: general gap costs over windows longer than " + std::to_string(vx_wsb_longest(s->tp)) +
+				" tokens need DP scratch in global memory; use vx_search");
 		}
 	}
 	if (t < 1 || c->n_win == 0) {

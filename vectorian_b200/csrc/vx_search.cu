@@ -225,7 +225,7 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 			sum += w;
 		}
 		tag_fast = tag_fast && sum > 0.0f && sum < 8192.0f && t <= VX_MAX_T_FAST;
-		tag_fast = tag_fast && !(ap->gap_kind == VX_GAP_GENERAL && c->max_len > 64);
+		tag_fast = tag_fast && !(ap->gap_kind == VX_GAP_GENERAL && c->max_len > vx_wsb_longest(s->tp));   // the scratch kernel has no tag weighting
 	}
 	// query lengths: up to 16 tokens everywhere; 17 .. 32 tokens on the linear / affine / general-scratch kernels for static
 	// and host-supplied per-token matrices (the contextual similarity kernels and tag weighting stop at 16)

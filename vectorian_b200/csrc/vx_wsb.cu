@@ -32,7 +32,6 @@
 #include <math_constants.h>
 #include <cstring>
 
-constexpr int VX_WSB_MAX_LEN = 64;
 constexpr int VX_WSB_U = 4;
 
 struct WsbArgs {
@@ -50,7 +49,7 @@ struct WsbArgs {
 	int32_t rt;              // rows [0, rt) of the history live in tensor memory (multiple of U)
 	int32_t tmem_cols;       // TMEM columns owned by one warp (256: two warps per lane quarter, 512: one)
 	float total;
-	float ws[VX_WSB_MAX_LEN + 4];   // w_s[0..64], gap cost along the sentence
+	float ws[VX_WSB_MAX_LEN + 4];   // w_s[0..160], gap cost along the sentence
 	float wt[VX_MAX_T_FAST + 4];    // w_t[0..16], gap cost along the query
 	// the same tables negated and paired for the packed adds (add.rn.f32x2 -> FADD2, one issue slot for two
 	// candidates; x - w == x + (-w) bit for bit):
@@ -590,6 +589,19 @@ static void wsb_plan(int tp, int cap, int *warps, int *rt, int *tmem_cols, int *
 	}
 }
 
+// longest window (tokens) whose history fits on chip for queries of row stride tp; longer ones take the scratch kernel
+int vx_wsb_longest(int tp) {
+	static const bool cap64 = getenv("VX_WSB_MAX64") != nullptr;   // A/B switch (read once): the round-1 limit
+	for (int cls = (cap64 ? 64 : VX_WSB_MAX_LEN) / 4; cls >= 1; cls--) {
+		int w, rt, tc, rs;
+		wsb_plan(tp, cls * 4, &w, &rt, &tc, &rs);
+		if (w >= 1) {
+			return cls * 4;
+		}
+	}
+	return 0;
+}
+
 template<int TP, int LOC, bool BORD, bool F2, bool PIPE, bool TAG>
 static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap) {
 	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
@@ -731,7 +743,10 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	unsigned int *counters = (unsigned int*)c->d_counters;
 	cudaMemsetAsync(counters, 0, sizeof(unsigned int) * 16, c->stream);
 	int n_groups = 0;
-	for (int cls = VX_WSB_MAX_LEN / 4; cls >= 1; ) {
+	// the longest class whose history fits on chip at one warp per SM (TP = 12: 42 rows in tensor memory + 147 in shared
+	// memory); longer tiles stay in [0, *first_tile) for the scratch kernel
+	const int cls_start = vx_wsb_longest(s->tp) / 4;
+	for (int cls = cls_start; cls >= 1; ) {
 		if (c->class_first[cls] >= c->class_first[cls - 1]) {
 			cls--;   // no tiles of this length: the next group is sized for the longest length present
 			continue;
