@@ -738,7 +738,8 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	// Measured: overlapping the launches of the short classes is neutral to slightly positive at every size; giving the
 	// last (largest) launch the attribute as well saves 12 % at 1 M sentences (tails overlap) but costs 4 % at
 	// 10 M - 50 M, so it is only done for small corpora.
-	const bool pdl_all = getenv("VX_PDL_ALL") != nullptr || c->n_tiles < 65536;
+	// (re-measured in round 2 with the packed-add kernel: +45 % at 250 k sentences, +9 % at 1 M, -2 % at 2 M, -12 % from 6 M on)
+	const bool pdl_all = getenv("VX_PDL_ALL") != nullptr || c->n_tiles < 49152;
 	int launches = 0;
 	unsigned int *counters = (unsigned int*)c->d_counters;
 	cudaMemsetAsync(counters, 0, sizeof(unsigned int) * 16, c->stream);
