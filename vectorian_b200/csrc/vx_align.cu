@@ -406,21 +406,127 @@ __global__ void __launch_bounds__(128) score_linear_mq_kernel(ScoreArgs a, const
 	m.score[k][slot] = wl < tl.n_valid ? finish_score(raw, m.total[k], boost) : -CUDART_INF_F;
 }
 
+// Packed variant (Local / Global, non-negative gap costs): a lane is a (window, PAIR of queries).  S is interleaved as
+// S_multi[V][K/2][TP][2], so a row load lands in register pairs {S_a[v], S_b[v]} and the three adds of a cell are three
+// FADD2 over the pair -- {diag + S}, {up - g_s}, {left - g_t} -- followed by one FMNMX3 per query: 5 issue slots per
+// cell PAIR (+ the running best) instead of 12.  The multi-query kernel above is issue-bound (84 % issue-active,
+// profiles/r2_mq), so the instruction count is what matters.  Same fp32 operations on the same operands.
+template<int TP, int KP, int LOC, bool ZC>
+__global__ void __launch_bounds__(128) score_linear_mq2_kernel(ScoreArgs a, const __grid_constant__ MqArgs m) {
+	constexpr int W = 32 / KP;       // windows per warp; KP = pairs of queries per window
+	const int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	const int64_t tile = unit / KP;
+	const int sub = (int)(unit - tile * KP);
+	if (tile >= a.n_tiles) {
+		return;
+	}
+	const int lane = threadIdx.x & 31;
+	const int p = lane % KP;
+	const int wl = sub * W + lane / KP;
+	const VxTile tl = a.tiles[tile];
+	const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + wl) * 4;
+	const int len = tl.len;
+	const int ta = m.t[2 * p], tb = m.t[2 * p + 1];
+	const float gs = m.gs, gt = m.gt;
+	const float2 ngs = make_float2(-gs, -gs), ngt = make_float2(-gt, -gt);
+
+	float2 h[TP];   // {V_a[u-1, v], V_b[u-1, v]}
+	#pragma unroll
+	for (int v = 0; v < TP; v++) {
+		const float b = LOC == VX_GLOBAL ? -((float)(v + 1) * gt) : 0.0f;
+		h[v] = make_float2(b, b);
+	}
+	float2 best = make_float2(0.0f, 0.0f);
+
+	float row[2 * TP];
+	IdStream ids(tok);
+	load_row<2 * TP>(m.s_multi, ids.first() * KP + p, row);
+
+	for (int u = 0; u < len; u++) {
+		float2 cur[TP];
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			cur[v] = make_float2(row[2 * v], row[2 * v + 1]);
+		}
+		if (u + 1 < len) {
+			load_row<2 * TP>(m.s_multi, ids.next(u + 1) * KP + p, row);
+		}
+		const float d0 = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
+		const float l0 = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;  // V[u, -1]
+		float2 diag = make_float2(d0, d0), left = make_float2(l0, l0);
+		#pragma unroll
+		for (int v = 0; v < TP; v++) {
+			const float2 up = h[v];
+			const float2 c0 = add2(diag, cur[v]);
+			const float2 c1 = add2(up, ngs);
+			const float2 c2 = add2(left, ngt);
+			float2 x = make_float2(fmax3(c0.x, c1.x, c2.x), fmax3(c0.y, c1.y, c2.y));
+			if (LOC == VX_LOCAL && ZC) {
+				x.x = fmaxf(x.x, 0.0f);   // Local zero; with S >= 0 it never wins: diag + S >= 0 already (ZC = false)
+				x.y = fmaxf(x.y, 0.0f);
+			}
+			diag = up;
+			h[v] = x;
+			left = x;
+		}
+		if (LOC == VX_LOCAL) {
+			// padded columns (v >= t, S = 0) only repeat or lower earlier values (gap costs >= 0): the maximum over all
+			// TP columns is the maximum over the query's own
+			#pragma unroll
+			for (int v = 0; v + 1 < TP; v += 2) {
+				best.x = fmax3(best.x, h[v].x, h[v + 1].x);
+				best.y = fmax3(best.y, h[v].y, h[v + 1].y);
+			}
+		}
+	}
+
+	float ra, rb;
+	if (LOC == VX_LOCAL) {
+		ra = best.x;
+		rb = best.y;
+	} else {
+		ra = h[0].x;   // V[len-1, t-1] of either query; opaque selects keep the row in registers
+		rb = h[0].y;
+		#pragma unroll
+		for (int v = 1; v < TP; v++) {
+			asm("{ .reg .pred q; setp.eq.s32 q, %2, %3; selp.f32 %0, %1, %0, q; }" : "+f"(ra) : "f"(h[v].x), "r"(v), "r"(ta - 1));
+			asm("{ .reg .pred q; setp.eq.s32 q, %2, %3; selp.f32 %0, %1, %0, q; }" : "+f"(rb) : "f"(h[v].y), "r"(v), "r"(tb - 1));
+		}
+	}
+	const int64_t slot = tile * 32 + wl;
+	const float boost = a.boost ? a.boost[slot] : 1.0f;
+	const bool valid = wl < tl.n_valid;
+	m.score[2 * p][slot] = valid ? finish_score(ra, m.total[2 * p], boost) : -CUDART_INF_F;
+	m.score[2 * p + 1][slot] = valid ? finish_score(rb, m.total[2 * p + 1], boost) : -CUDART_INF_F;
+}
+
 // S_multi[row][k][0..TP) = S_k[row][0..tp_k), zero beyond the query's own columns
 struct InterleaveArgs {
 	const float *s[VX_MULTI_MAX];
 	int32_t tp[VX_MULTI_MAX];
 };
 
+// paired: out[row][k / 2][j][k % 2] (the layout of score_linear_mq2_kernel), else out[row][k][j]
 __global__ void __launch_bounds__(256) interleave_sim_kernel(const __grid_constant__ InterleaveArgs g, int64_t rows, int k_n, int tp,
-	float *__restrict__ out) {
+	float *__restrict__ out, bool paired) {
 
 	const int64_t n = rows * k_n * tp;
 	for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-		const int j = (int)(i % tp);
-		const int64_t rk = i / tp;
-		const int k = (int)(rk % k_n);
-		const int64_t r = rk / k_n;
+		int j, k;
+		int64_t r;
+		if (paired) {
+			const int hh = (int)(i & 1);
+			const int64_t q = i >> 1;
+			j = (int)(q % tp);
+			const int64_t rp = q / tp;
+			k = (int)(rp % (k_n / 2)) * 2 + hh;
+			r = rp / (k_n / 2);
+		} else {
+			j = (int)(i % tp);
+			const int64_t rk = i / tp;
+			k = (int)(rk % k_n);
+			r = rk / k_n;
+		}
 		out[i] = j < g.tp[k] ? g.s[k][r * g.tp[k] + j] : 0.0f;
 	}
 }
@@ -858,6 +964,36 @@ static int launch_mq_tk(const ScoreArgs &a, const MqArgs &m, int locality, cudaS
 	}
 }
 
+template<int TP, int KP>
+static int launch_mq2_tk(const ScoreArgs &a, const MqArgs &m, int locality, bool zc, cudaStream_t st) {
+	const int warps = 4;
+	const unsigned grid = (unsigned)((a.n_tiles * KP + warps - 1) / warps);
+	if (locality == VX_LOCAL) {
+		if (zc) {
+			score_linear_mq2_kernel<TP, KP, VX_LOCAL, true><<<grid, warps * 32, 0, st>>>(a, m);
+		} else {
+			score_linear_mq2_kernel<TP, KP, VX_LOCAL, false><<<grid, warps * 32, 0, st>>>(a, m);
+		}
+	} else {
+		score_linear_mq2_kernel<TP, KP, VX_GLOBAL, false><<<grid, warps * 32, 0, st>>>(a, m);
+	}
+	return 1;
+}
+
+template<int TP>
+static int launch_mq2_t(const ScoreArgs &a, const MqArgs &m, int k_n, int locality, bool zc, cudaStream_t st) {
+	switch (k_n) {
+		case 8:
+			return launch_mq2_tk<TP, 4>(a, m, locality, zc, st);
+		case 4:
+			return launch_mq2_tk<TP, 2>(a, m, locality, zc, st);
+		case 2:
+			return launch_mq2_tk<TP, 1>(a, m, locality, zc, st);
+		default:
+			return 0;
+	}
+}
+
 template<int TP>
 static int launch_mq_t(const ScoreArgs &a, const MqArgs &m, int k_n, int locality, cudaStream_t st) {
 	switch (k_n) {
@@ -904,7 +1040,14 @@ int vx_launch_score_mq(vx_corpus *c, const vx_sim *const *sims, int k_n, int loc
 	const int64_t n = rows * k_n * tp;
 	int64_t blocks = (n + 255) / 256;
 	blocks = blocks > 148 * 16 ? 148 * 16 : blocks < 1 ? 1 : blocks;
-	interleave_sim_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(g, rows, k_n, tp, d_s_multi);
+	// packed pairs of queries (FADD2) for Local / Global with non-negative gap costs; VX_MQ_NO_PACK: A/B switch
+	static const bool no_pack = getenv("VX_MQ_NO_PACK") != nullptr;
+	const bool paired = !no_pack && (locality == VX_LOCAL || locality == VX_GLOBAL) && gs >= 0.0f && gt >= 0.0f;
+	bool zc = false;
+	for (int k = 0; k < k_n; k++) {
+		zc = zc || !sims[k]->nonneg;
+	}
+	interleave_sim_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(g, rows, k_n, tp, d_s_multi, paired);
 	ScoreArgs a;
 	a.tiles = c->d_tiles;
 	a.n_tiles = c->n_tiles;
@@ -919,16 +1062,16 @@ int vx_launch_score_mq(vx_corpus *c, const vx_sim *const *sims, int k_n, int loc
 	int launched;
 	switch (tp) {
 		case 4:
-			launched = launch_mq_t<4>(a, m, k_n, locality, c->stream);
+			launched = paired ? launch_mq2_t<4>(a, m, k_n, locality, zc, c->stream) : launch_mq_t<4>(a, m, k_n, locality, c->stream);
 			break;
 		case 8:
-			launched = launch_mq_t<8>(a, m, k_n, locality, c->stream);
+			launched = paired ? launch_mq2_t<8>(a, m, k_n, locality, zc, c->stream) : launch_mq_t<8>(a, m, k_n, locality, c->stream);
 			break;
 		case 12:
-			launched = launch_mq_t<12>(a, m, k_n, locality, c->stream);
+			launched = paired ? launch_mq2_t<12>(a, m, k_n, locality, zc, c->stream) : launch_mq_t<12>(a, m, k_n, locality, c->stream);
 			break;
 		case 16:
-			launched = launch_mq_t<16>(a, m, k_n, locality, c->stream);
+			launched = paired ? launch_mq2_t<16>(a, m, k_n, locality, zc, c->stream) : launch_mq_t<16>(a, m, k_n, locality, c->stream);
 			break;
 		default:
 			launched = 0;
