@@ -43,38 +43,143 @@ __device__ __forceinline__ void load_row(const float *__restrict__ s, int32_t id
 	}
 }
 
-// Token ids of one window (one lane), read as quads: tokens 4q .. 4q+3 of a lane are one 16-byte element of the
-// tiled layout (vx_internal.cuh), so a warp fetches four token positions with one coalesced LDG.128, one quad
-// ahead of its use.  (Reading the ids one by one cost four times the L1 sectors and put the id load on the
-// critical path of every S-row gather.  Used by the linear kernel only: the affine and the multi-setting kernels
-// are register-bound and measured slower with it.)  The stream may run up to two quads past the window: that is the next
-// tile or the slack at the end of the array (VX_TOK_SLACK).
-struct IdStream {
-	const int4 *q;
-	int4 cur, nxt;
-
-	__device__ __forceinline__ explicit IdStream(const int32_t *tok_lane) {
-		q = reinterpret_cast<const int4*>(tok_lane);
-		cur = __ldg(q);
-		nxt = __ldg(q + 32);
-		q += 64;
-	}
-
-	__device__ __forceinline__ int32_t first() const {
-		return cur.x;
-	}
-
-	// id of token u; call with u = 1, 2, 3, ... in order
-	__device__ __forceinline__ int32_t next(int u) {
-		const int k = u & 3;
-		if (k == 0) {
-			cur = nxt;
-			nxt = __ldg(q);
-			q += 32;
+// Row of lane g of G lanes that share a token: the G lanes' rows are interleaved in chunks of one load instruction
+// (CW floats), s[id][NF / CW][G][CW], so that every load instruction of the G lanes covers one contiguous G * CW * 4-byte
+// piece -- with plain [id][G][NF] rows each instruction would touch every 128-byte line of the token's G * NF floats and
+// the gather would cost NF / CW times the L1 wavefronts.  G = 1 is the plain row-major S of a single query.
+template<int NF>
+__device__ __forceinline__ void load_row_g(const float *__restrict__ s, int32_t id, int g_n, int g, float (&row)[NF]) {
+	constexpr int CW = NF % 8 == 0 ? 8 : 4;
+	constexpr int NI = NF / CW;
+	const float *p = s + ((size_t)id * NI * g_n + g) * CW;
+	#pragma unroll
+	for (int i = 0; i < NI; i++) {
+		const float *pi = p + (size_t)i * g_n * CW;
+		if constexpr (CW == 8) {
+			asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+				: "=f"(row[8 * i + 0]), "=f"(row[8 * i + 1]), "=f"(row[8 * i + 2]), "=f"(row[8 * i + 3]),
+				  "=f"(row[8 * i + 4]), "=f"(row[8 * i + 5]), "=f"(row[8 * i + 6]), "=f"(row[8 * i + 7])
+				: "l"(pi));
+		} else {
+			const float4 x = __ldg(reinterpret_cast<const float4*>(pi));
+			row[4 * i + 0] = x.x;
+			row[4 * i + 1] = x.y;
+			row[4 * i + 2] = x.z;
+			row[4 * i + 3] = x.w;
 		}
-		return k == 0 ? cur.x : k == 1 ? cur.y : k == 2 ? cur.z : cur.w;
 	}
-};
+}
+
+// the same row, requested into L1 without a destination register (no scoreboard, nothing for ptxas to move towards the use)
+template<int NF>
+__device__ __forceinline__ void prefetch_row_g(const float *__restrict__ s, int32_t id, int g_n, int g) {
+	constexpr int CW = NF % 8 == 0 ? 8 : 4;
+	constexpr int NI = NF / CW;
+	const float *p = s + ((size_t)id * NI * g_n + g) * CW;
+	#pragma unroll
+	for (int i = 0; i < NI; i++) {
+		asm volatile("prefetch.global.L1 [%0];" :: "l"(p + (size_t)i * g_n * CW));
+	}
+}
+
+// The S rows of one window's tokens, D rows ahead of their use: fn(row, u) is called for u = 0 .. len - 1 in order with
+// the row of lane g of g_n (load_row_g).  Four token positions (one 16-byte quad of ids) per trip over row buffers used
+// in turn: no dynamic select on u & 3 and no register copies between a prefetch buffer and the row in use -- in the
+// one-row-per-trip form those were more than half of the instructions of a DP row (scripts/sass_loop.py).
+// D = 1: loads one row ahead (the single-query kernels: bound by L1 wavefronts, not by latency).  D = 3: in addition an
+// L1 prefetch request three rows ahead -- the multi-query kernels read rows that mostly come from L2 (K times the bytes per
+// token); with one row in flight per warp they stalled on the scoreboard for 8 of 9 issue slots (profiles/r2_mq).
+// The id stream may run up to two quads past the window (the next tile, or VX_TOK_SLACK); S rows are only loaded for
+// u < len.
+template<int NF, int D, class Fn>
+__device__ __forceinline__ void for_each_row(const float *__restrict__ s, const int32_t *tok_lane, int len, int g_n, int g, Fn &&fn) {
+	static_assert(D == 1 || D == 3, "D = 1: loads one row ahead; D = 3: plus L1 prefetch requests three rows ahead");
+	const int4 *q = reinterpret_cast<const int4*>(tok_lane);
+	int4 idq = __ldg(q);
+	int4 idn = __ldg(q + 32);
+	q += 64;
+	int u = 0;
+	if constexpr (D == 1) {
+		float ra[NF], rb[NF];
+		load_row_g<NF>(s, idq.x, g_n, g, ra);
+		#pragma unroll 1
+		for (; u + 4 <= len; u += 4) {
+			load_row_g<NF>(s, idq.y, g_n, g, rb);
+			fn(ra, u);
+			load_row_g<NF>(s, idq.z, g_n, g, ra);
+			fn(rb, u + 1);
+			load_row_g<NF>(s, idq.w, g_n, g, rb);
+			fn(ra, u + 2);
+			idq = idn;
+			idn = __ldg(q);
+			q += 32;
+			if (u + 4 < len) {
+				load_row_g<NF>(s, idq.x, g_n, g, ra);
+			}
+			fn(rb, u + 3);
+		}
+		const int rem = len - u;
+		if (rem > 0) {
+			if (rem > 1) {
+				load_row_g<NF>(s, idq.y, g_n, g, rb);
+			}
+			fn(ra, u);
+			if (rem > 1) {
+				if (rem > 2) {
+					load_row_g<NF>(s, idq.z, g_n, g, ra);
+				}
+				fn(rb, u + 1);
+				if (rem > 2) {
+					fn(ra, u + 2);
+				}
+			}
+		}
+	} else {
+		// demand loads one row ahead as above + an L1 prefetch request two rows further on.  (A four-buffer form with the
+		// demand loads themselves three rows ahead was tried first: ptxas moved the loads back towards their uses and put
+		// them on shared scoreboards -- scripts/sass_sb.py -- and it ran slower than D = 1.)  Rows past the window's end
+		// that get prefetched belong to other windows or are the zero-filled slack: valid ids.
+		float ra[NF], rb[NF];
+		load_row_g<NF>(s, idq.x, g_n, g, ra);
+		prefetch_row_g<NF>(s, idq.z, g_n, g);
+		#pragma unroll 1
+		for (; u + 4 <= len; u += 4) {
+			load_row_g<NF>(s, idq.y, g_n, g, rb);
+			prefetch_row_g<NF>(s, idq.w, g_n, g);
+			fn(ra, u);
+			load_row_g<NF>(s, idq.z, g_n, g, ra);
+			prefetch_row_g<NF>(s, idn.x, g_n, g);
+			fn(rb, u + 1);
+			load_row_g<NF>(s, idq.w, g_n, g, rb);
+			prefetch_row_g<NF>(s, idn.y, g_n, g);
+			fn(ra, u + 2);
+			idq = idn;
+			idn = __ldg(q);
+			q += 32;
+			if (u + 4 < len) {
+				load_row_g<NF>(s, idq.x, g_n, g, ra);
+			}
+			prefetch_row_g<NF>(s, idq.z, g_n, g);
+			fn(rb, u + 3);
+		}
+		const int rem = len - u;
+		if (rem > 0) {
+			if (rem > 1) {
+				load_row_g<NF>(s, idq.y, g_n, g, rb);
+			}
+			fn(ra, u);
+			if (rem > 1) {
+				if (rem > 2) {
+					load_row_g<NF>(s, idq.z, g_n, g, ra);
+				}
+				fn(rb, u + 1);
+				if (rem > 2) {
+					fn(ra, u + 2);
+				}
+			}
+		}
+	}
+}
 
 __device__ __forceinline__ float finish_score(float raw, float total, float boost) {
 	// Score::Score (cpp/match/match.h:302-307) with reference_score == total for submatch_weight == 0.
@@ -118,18 +223,11 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
 	float last_col = 0.0f;
 
-	float row[TP];
-	IdStream ids(tok);
-	load_row<TP>(a.s, ids.first(), row);
-
-	for (int u = 0; u < len; u++) {
+	for_each_row<TP, 1>(a.s, tok, len, 1, 0, [&](const float (&row)[TP], int u) {
 		float cur[TP];
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
 			cur[v] = row[v];
-		}
-		if (u + 1 < len) {
-			load_row<TP>(a.s, ids.next(u + 1), row);
 		}
 		if (a.tag.on) {
 			vx_apply_tag<TP>(a.tag, a.pos[vx_elem(tl.base128, u, lane)], cur);
@@ -157,7 +255,7 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 		if (LOC == VX_SEMIGLOBAL) {
 			best = fmaxf(best, last_col);
 		}
-	}
+	});
 
 	float raw;
 	if (LOC == VX_LOCAL) {
@@ -310,14 +408,14 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 // linear gap cost, several QUERIES at once (vx_search_batch with more than one query and one setting):
 // the reference runs index.find once per query (vectorian/index.py:481-501).  The single-query kernel sits at the
 // L1TEX wavefront limit: its 32 lanes gather 32 different S rows, so every load instruction touches 32 lines.
-// Here the similarity matrices of K queries are interleaved into S_multi[V][K][TP] and a lane is a (window, query)
-// pair: lane = w * K + k.  The K lanes of a window read ONE contiguous K * TP * 4-byte row, an instruction touches
-// 32 / K windows' rows (1-2 lines each) instead of 32, and the per-lane DP state is as small as in the single-query
-// kernel.  A warp takes 32 / K windows of a tile; the cells are the same fp32 maxima of the same candidates.
+// Here the similarity matrices of K queries are interleaved into S_multi (K rows per token, chunked by load instruction:
+// interleave_sim_kernel) and a lane is a (window, query) pair: lane = w * K + k.  Each load instruction of the K lanes of
+// a window reads ONE contiguous K * 16- or 32-byte piece, so it touches 32 / K windows' pieces (1-2 lines each) instead of 32
+// rows, and the per-lane DP state is as small as in the single-query kernel.  A warp takes 32 / K windows of a tile; the cells are the same fp32 maxima of the same candidates.
 // ---------------------------------------------------------------------------
 
 struct MqArgs {
-	const float *s_multi;            // [V][K][TP]
+	const float *s_multi;            // [V][chunk][lane][CW], see interleave_sim_kernel
 	float gs, gt;
 	float *score[VX_MULTI_MAX];      // per query, by slot
 	int32_t t[VX_MULTI_MAX];
@@ -350,25 +448,13 @@ __global__ void __launch_bounds__(128) score_linear_mq_kernel(ScoreArgs a, const
 	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
 	float last_col = 0.0f;
 
-	float row[TP];
-	IdStream ids(tok);
-	load_row<TP>(m.s_multi, ids.first() * K + k, row);
-
-	for (int u = 0; u < len; u++) {
-		float cur[TP];
-		#pragma unroll
-		for (int v = 0; v < TP; v++) {
-			cur[v] = row[v];
-		}
-		if (u + 1 < len) {
-			load_row<TP>(m.s_multi, ids.next(u + 1) * K + k, row);
-		}
+	for_each_row<TP, 1>(m.s_multi, tok, len, K, k, [&](const float (&row)[TP], int u) {
 		float diag = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;
 		float left = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
 			const float up = h[v];
-			float x = fmaxf(fmaxf(diag + cur[v], up - gs), left - gt);
+			float x = fmaxf(fmaxf(diag + row[v], up - gs), left - gt);
 			if (LOC == VX_LOCAL) {
 				x = fmaxf(x, 0.0f);
 				if (v < t) {
@@ -385,7 +471,7 @@ __global__ void __launch_bounds__(128) score_linear_mq_kernel(ScoreArgs a, const
 		if (LOC == VX_SEMIGLOBAL) {
 			best = fmaxf(best, last_col);
 		}
-	}
+	});
 
 	float raw;
 	if (LOC == VX_LOCAL) {
@@ -407,12 +493,12 @@ __global__ void __launch_bounds__(128) score_linear_mq_kernel(ScoreArgs a, const
 }
 
 // Packed variant (Local / Global, non-negative gap costs): a lane is a (window, PAIR of queries).  S is interleaved as
-// S_multi[V][K/2][TP][2], so a row load lands in register pairs {S_a[v], S_b[v]} and the three adds of a cell are three
-// FADD2 over the pair -- {diag + S}, {up - g_s}, {left - g_t} -- followed by one FMNMX3 per query: 5 issue slots per
+// {S_a[v], S_b[v]} pairs (chunked like the rows of the kernel above), so a row load lands in register pairs and the three
+// adds of a cell are three FADD2 over the pair -- {diag + S}, {up - g_s}, {left - g_t} -- followed by one FMNMX3 per query: 5 issue slots per
 // cell PAIR (+ the running best) instead of 12.  The multi-query kernel above is issue-bound (84 % issue-active,
 // profiles/r2_mq), so the instruction count is what matters.  Same fp32 operations on the same operands.
 template<int TP, int KP, int LOC, bool ZC>
-__global__ void __launch_bounds__(128) score_linear_mq2_kernel(ScoreArgs a, const __grid_constant__ MqArgs m) {
+__global__ void __launch_bounds__(128, TP <= 8 ? 6 : TP <= 12 ? 4 : 3) score_linear_mq2_kernel(ScoreArgs a, const __grid_constant__ MqArgs m) {
 	constexpr int W = 32 / KP;       // windows per warp; KP = pairs of queries per window
 	const int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	const int64_t tile = unit / KP;
@@ -438,26 +524,14 @@ __global__ void __launch_bounds__(128) score_linear_mq2_kernel(ScoreArgs a, cons
 	}
 	float2 best = make_float2(0.0f, 0.0f);
 
-	float row[2 * TP];
-	IdStream ids(tok);
-	load_row<2 * TP>(m.s_multi, ids.first() * KP + p, row);
-
-	for (int u = 0; u < len; u++) {
-		float2 cur[TP];
-		#pragma unroll
-		for (int v = 0; v < TP; v++) {
-			cur[v] = make_float2(row[2 * v], row[2 * v + 1]);
-		}
-		if (u + 1 < len) {
-			load_row<2 * TP>(m.s_multi, ids.next(u + 1) * KP + p, row);
-		}
+	for_each_row<2 * TP, 1>(m.s_multi, tok, len, KP, p, [&](const float (&row)[2 * TP], int u) {
 		const float d0 = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
 		const float l0 = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;  // V[u, -1]
 		float2 diag = make_float2(d0, d0), left = make_float2(l0, l0);
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
 			const float2 up = h[v];
-			const float2 c0 = add2(diag, cur[v]);
+			const float2 c0 = add2(diag, make_float2(row[2 * v], row[2 * v + 1]));
 			const float2 c1 = add2(up, ngs);
 			const float2 c2 = add2(left, ngt);
 			float2 x = make_float2(fmax3(c0.x, c1.x, c2.x), fmax3(c0.y, c1.y, c2.y));
@@ -478,7 +552,7 @@ __global__ void __launch_bounds__(128) score_linear_mq2_kernel(ScoreArgs a, cons
 				best.y = fmax3(best.y, h[v].y, h[v + 1].y);
 			}
 		}
-	}
+	});
 
 	float ra, rb;
 	if (LOC == VX_LOCAL) {
@@ -500,33 +574,33 @@ __global__ void __launch_bounds__(128) score_linear_mq2_kernel(ScoreArgs a, cons
 	m.score[2 * p + 1][slot] = valid ? finish_score(rb, m.total[2 * p + 1], boost) : -CUDART_INF_F;
 }
 
-// S_multi[row][k][0..TP) = S_k[row][0..tp_k), zero beyond the query's own columns
+// S_multi: the K queries' similarity rows of one token, interleaved (below); zero beyond a query's own columns
 struct InterleaveArgs {
 	const float *s[VX_MULTI_MAX];
 	int32_t tp[VX_MULTI_MAX];
 };
 
-// paired: out[row][k / 2][j][k % 2] (the layout of score_linear_mq2_kernel), else out[row][k][j]
+// The layout load_row_g reads: out[row][chunk][lane g][CW].  Unpaired: lane g = query k, its row the tp columns of S_k
+// (CW = 8 when tp % 8 == 0, else 4).  Paired (score_linear_mq2_kernel): lane g = queries 2g, 2g + 1, its row the 2 * tp floats
+// {S_2g[j], S_2g+1[j]} for j = 0 .. tp - 1 (CW = 8).
 __global__ void __launch_bounds__(256) interleave_sim_kernel(const __grid_constant__ InterleaveArgs g, int64_t rows, int k_n, int tp,
 	float *__restrict__ out, bool paired) {
 
 	const int64_t n = rows * k_n * tp;
+	const int nf = paired ? 2 * tp : tp;
+	const int cw = nf % 8 == 0 ? 8 : 4;
+	const int ni = nf / cw;
+	const int g_n = paired ? k_n / 2 : k_n;
 	for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-		int j, k;
-		int64_t r;
-		if (paired) {
-			const int hh = (int)(i & 1);
-			const int64_t q = i >> 1;
-			j = (int)(q % tp);
-			const int64_t rp = q / tp;
-			k = (int)(rp % (k_n / 2)) * 2 + hh;
-			r = rp / (k_n / 2);
-		} else {
-			j = (int)(i % tp);
-			const int64_t rk = i / tp;
-			k = (int)(rk % k_n);
-			r = rk / k_n;
-		}
+		const int c = (int)(i % cw);
+		int64_t q = i / cw;
+		const int lane = (int)(q % g_n);
+		q /= g_n;
+		const int chunk = (int)(q % ni);
+		const int64_t r = q / ni;
+		const int e = chunk * cw + c;   // element of the lane's row
+		const int j = paired ? e >> 1 : e;
+		const int k = paired ? 2 * lane + (e & 1) : lane;
 		out[i] = j < g.tp[k] ? g.s[k][r * g.tp[k] + j] : 0.0f;
 	}
 }
@@ -567,19 +641,11 @@ __global__ void __launch_bounds__(128) score_affine_kernel(ScoreArgs a, AffineAr
 	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
 	float last_col = 0.0f;
 
-	float row[TP];
-	int32_t id = tok[0];
-	load_row<TP>(a.s, id, row);
-
-	for (int u = 0; u < len; u++) {
+	for_each_row<TP, 1>(a.s, tok, len, 1, 0, [&](const float (&row)[TP], int u) {
 		float cur[TP];
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
 			cur[v] = row[v];
-		}
-		if (u + 1 < len) {
-			id = tok[vx_elem(0, u + 1, 0)];
-			load_row<TP>(a.s, id, row);
 		}
 		if (a.tag.on) {
 			vx_apply_tag<TP>(a.tag, a.pos[vx_elem(tl.base128, u, lane)], cur);
@@ -611,7 +677,7 @@ __global__ void __launch_bounds__(128) score_affine_kernel(ScoreArgs a, AffineAr
 		if (LOC == VX_SEMIGLOBAL) {
 			best = fmaxf(best, last_col);
 		}
-	}
+	});
 
 	float raw;
 	if (LOC == VX_LOCAL) {
