@@ -70,112 +70,53 @@ __device__ __forceinline__ void load_row_g(const float *__restrict__ s, int32_t 
 	}
 }
 
-// the same row, requested into L1 without a destination register (no scoreboard, nothing for ptxas to move towards the use)
-template<int NF>
-__device__ __forceinline__ void prefetch_row_g(const float *__restrict__ s, int32_t id, int g_n, int g) {
-	constexpr int CW = NF % 8 == 0 ? 8 : 4;
-	constexpr int NI = NF / CW;
-	const float *p = s + ((size_t)id * NI * g_n + g) * CW;
-	#pragma unroll
-	for (int i = 0; i < NI; i++) {
-		asm volatile("prefetch.global.L1 [%0];" :: "l"(p + (size_t)i * g_n * CW));
-	}
-}
-
-// The S rows of one window's tokens, D rows ahead of their use: fn(row, u) is called for u = 0 .. len - 1 in order with
-// the row of lane g of g_n (load_row_g).  Four token positions (one 16-byte quad of ids) per trip over row buffers used
-// in turn: no dynamic select on u & 3 and no register copies between a prefetch buffer and the row in use -- in the
+// The S rows of one window's tokens, one row ahead of their use: fn(row, u) is called for u = 0 .. len - 1 in order with
+// the row of lane g of g_n (load_row_g).  Four token positions (one 16-byte quad of ids) per trip over two row buffers
+// used in turn: no dynamic select on u & 3 and no register copies between a prefetch buffer and the row in use -- in the
 // one-row-per-trip form those were more than half of the instructions of a DP row (scripts/sass_loop.py).
-// D = 1: loads one row ahead (the single-query kernels: bound by L1 wavefronts, not by latency).  D = 3: in addition an
-// L1 prefetch request three rows ahead -- the multi-query kernels read rows that mostly come from L2 (K times the bytes per
-// token); with one row in flight per warp they stalled on the scoreboard for 8 of 9 issue slots (profiles/r2_mq).
+// Deeper prefetching was tried for the multi-query kernels (latency-bound on L2) and dropped: with four buffers ptxas
+// moves the loads back towards their uses and shares scoreboards between them (scripts/sass_sb.py), and L1 prefetch
+// requests (CCTL.E.PF1) cost more than they hide (profiles/r2_mq).
 // The id stream may run up to two quads past the window (the next tile, or VX_TOK_SLACK); S rows are only loaded for
 // u < len.
-template<int NF, int D, class Fn>
+template<int NF, class Fn>
 __device__ __forceinline__ void for_each_row(const float *__restrict__ s, const int32_t *tok_lane, int len, int g_n, int g, Fn &&fn) {
-	static_assert(D == 1 || D == 3, "D = 1: loads one row ahead; D = 3: plus L1 prefetch requests three rows ahead");
 	const int4 *q = reinterpret_cast<const int4*>(tok_lane);
 	int4 idq = __ldg(q);
 	int4 idn = __ldg(q + 32);
 	q += 64;
 	int u = 0;
-	if constexpr (D == 1) {
-		float ra[NF], rb[NF];
-		load_row_g<NF>(s, idq.x, g_n, g, ra);
-		#pragma unroll 1
-		for (; u + 4 <= len; u += 4) {
+	float ra[NF], rb[NF];
+	load_row_g<NF>(s, idq.x, g_n, g, ra);
+	#pragma unroll 1
+	for (; u + 4 <= len; u += 4) {
+		load_row_g<NF>(s, idq.y, g_n, g, rb);
+		fn(ra, u);
+		load_row_g<NF>(s, idq.z, g_n, g, ra);
+		fn(rb, u + 1);
+		load_row_g<NF>(s, idq.w, g_n, g, rb);
+		fn(ra, u + 2);
+		idq = idn;
+		idn = __ldg(q);
+		q += 32;
+		if (u + 4 < len) {
+			load_row_g<NF>(s, idq.x, g_n, g, ra);
+		}
+		fn(rb, u + 3);
+	}
+	const int rem = len - u;
+	if (rem > 0) {
+		if (rem > 1) {
 			load_row_g<NF>(s, idq.y, g_n, g, rb);
-			fn(ra, u);
-			load_row_g<NF>(s, idq.z, g_n, g, ra);
+		}
+		fn(ra, u);
+		if (rem > 1) {
+			if (rem > 2) {
+				load_row_g<NF>(s, idq.z, g_n, g, ra);
+			}
 			fn(rb, u + 1);
-			load_row_g<NF>(s, idq.w, g_n, g, rb);
-			fn(ra, u + 2);
-			idq = idn;
-			idn = __ldg(q);
-			q += 32;
-			if (u + 4 < len) {
-				load_row_g<NF>(s, idq.x, g_n, g, ra);
-			}
-			fn(rb, u + 3);
-		}
-		const int rem = len - u;
-		if (rem > 0) {
-			if (rem > 1) {
-				load_row_g<NF>(s, idq.y, g_n, g, rb);
-			}
-			fn(ra, u);
-			if (rem > 1) {
-				if (rem > 2) {
-					load_row_g<NF>(s, idq.z, g_n, g, ra);
-				}
-				fn(rb, u + 1);
-				if (rem > 2) {
-					fn(ra, u + 2);
-				}
-			}
-		}
-	} else {
-		// demand loads one row ahead as above + an L1 prefetch request two rows further on.  (A four-buffer form with the
-		// demand loads themselves three rows ahead was tried first: ptxas moved the loads back towards their uses and put
-		// them on shared scoreboards -- scripts/sass_sb.py -- and it ran slower than D = 1.)  Rows past the window's end
-		// that get prefetched belong to other windows or are the zero-filled slack: valid ids.
-		float ra[NF], rb[NF];
-		load_row_g<NF>(s, idq.x, g_n, g, ra);
-		prefetch_row_g<NF>(s, idq.z, g_n, g);
-		#pragma unroll 1
-		for (; u + 4 <= len; u += 4) {
-			load_row_g<NF>(s, idq.y, g_n, g, rb);
-			prefetch_row_g<NF>(s, idq.w, g_n, g);
-			fn(ra, u);
-			load_row_g<NF>(s, idq.z, g_n, g, ra);
-			prefetch_row_g<NF>(s, idn.x, g_n, g);
-			fn(rb, u + 1);
-			load_row_g<NF>(s, idq.w, g_n, g, rb);
-			prefetch_row_g<NF>(s, idn.y, g_n, g);
-			fn(ra, u + 2);
-			idq = idn;
-			idn = __ldg(q);
-			q += 32;
-			if (u + 4 < len) {
-				load_row_g<NF>(s, idq.x, g_n, g, ra);
-			}
-			prefetch_row_g<NF>(s, idq.z, g_n, g);
-			fn(rb, u + 3);
-		}
-		const int rem = len - u;
-		if (rem > 0) {
-			if (rem > 1) {
-				load_row_g<NF>(s, idq.y, g_n, g, rb);
-			}
-			fn(ra, u);
-			if (rem > 1) {
-				if (rem > 2) {
-					load_row_g<NF>(s, idq.z, g_n, g, ra);
-				}
-				fn(rb, u + 1);
-				if (rem > 2) {
-					fn(ra, u + 2);
-				}
+			if (rem > 2) {
+				fn(ra, u + 2);
 			}
 		}
 	}
@@ -223,7 +164,7 @@ __global__ void __launch_bounds__(128) score_linear_kernel(ScoreArgs a, float gs
 	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
 	float last_col = 0.0f;
 
-	for_each_row<TP, 1>(a.s, tok, len, 1, 0, [&](const float (&row)[TP], int u) {
+	for_each_row<TP>(a.s, tok, len, 1, 0, [&](const float (&row)[TP], int u) {
 		float cur[TP];
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
@@ -338,20 +279,7 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 		}
 	}
 
-	float row[TP];
-	int32_t id = tok[0];
-	load_row<TP>(a.s, id, row);
-
-	for (int u = 0; u < len; u++) {
-		float2 cur[TP];
-		#pragma unroll
-		for (int v = 0; v < TP; v++) {
-			cur[v] = make_float2(row[v], row[v]);
-		}
-		if (u + 1 < len) {
-			id = tok[vx_elem(0, u + 1, 0)];
-			load_row<TP>(a.s, id, row);
-		}
+	for_each_row<TP>(a.s, tok, len, 1, 0, [&](const float (&row)[TP], int u) {
 		#pragma unroll
 		for (int p = 0; p < NP; p++) {
 			const float2 ngs = make_float2(-m.gs[2 * p], -m.gs[2 * p + 1]);
@@ -362,7 +290,7 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 			#pragma unroll
 			for (int v = 0; v < TP; v++) {
 				const float2 up = h[p][v];
-				const float2 c0 = add2(diag, cur[v]);
+				const float2 c0 = add2(diag, make_float2(row[v], row[v]));
 				const float2 c1 = add2(up, ngs);
 				const float2 c2 = add2(left, ngt);
 				float2 x = make_float2(fmax3(c0.x, c1.x, c2.x), fmax3(c0.y, c1.y, c2.y));
@@ -382,7 +310,7 @@ __global__ void __launch_bounds__(128) score_linear_multi_kernel(ScoreArgs a, co
 				}
 			}
 		}
-	}
+	});
 
 	const int64_t slot = tile * 32 + lane;
 	const float boost = a.boost ? a.boost[slot] : 1.0f;
@@ -448,7 +376,7 @@ __global__ void __launch_bounds__(128) score_linear_mq_kernel(ScoreArgs a, const
 	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
 	float last_col = 0.0f;
 
-	for_each_row<TP, 1>(m.s_multi, tok, len, K, k, [&](const float (&row)[TP], int u) {
+	for_each_row<TP>(m.s_multi, tok, len, K, k, [&](const float (&row)[TP], int u) {
 		float diag = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;
 		float left = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;
 		#pragma unroll
@@ -524,7 +452,7 @@ __global__ void __launch_bounds__(128, TP <= 8 ? 6 : TP <= 12 ? 4 : 3) score_lin
 	}
 	float2 best = make_float2(0.0f, 0.0f);
 
-	for_each_row<2 * TP, 1>(m.s_multi, tok, len, KP, p, [&](const float (&row)[2 * TP], int u) {
+	for_each_row<2 * TP>(m.s_multi, tok, len, KP, p, [&](const float (&row)[2 * TP], int u) {
 		const float d0 = LOC == VX_GLOBAL ? -((float)u * gs) : 0.0f;        // V[u-1, -1]
 		const float l0 = LOC == VX_GLOBAL ? -((float)(u + 1) * gs) : 0.0f;  // V[u, -1]
 		float2 diag = make_float2(d0, d0), left = make_float2(l0, l0);
@@ -641,7 +569,7 @@ __global__ void __launch_bounds__(128) score_affine_kernel(ScoreArgs a, AffineAr
 	float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
 	float last_col = 0.0f;
 
-	for_each_row<TP, 1>(a.s, tok, len, 1, 0, [&](const float (&row)[TP], int u) {
+	for_each_row<TP>(a.s, tok, len, 1, 0, [&](const float (&row)[TP], int u) {
 		float cur[TP];
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
