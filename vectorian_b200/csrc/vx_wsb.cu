@@ -41,11 +41,17 @@ struct WsbArgs {
 	const float *boost;      // by slot or nullptr
 	float *score;            // by slot
 	unsigned int *counter;   // chunk counter of this launch (zeroed by the host)
-	int64_t tile_begin, tile_end;
+	int32_t tile_begin, tile_end;
 	int32_t chunk;           // tiles per reservation for the first n_big reservations, then one tile each
 	uint32_t n_big;
 	int32_t t;
 	int32_t cap;             // rows of history per warp in shared memory (rows rt .. rt+cap-1)
+	// Long queue of the main launch: warps [0, n_long_warps) of every CTA own cap_long >= cap rows and first take the
+	// tiles [long_begin, long_end) -- the next longer length classes -- one at a time, then join the others.
+	int32_t n_long_warps, cap_long;
+	int32_t long_begin;
+	uint32_t n_long_tiles;
+	unsigned int *counter_long;
 	int32_t rt;              // rows [0, rt) of the history live in tensor memory (multiple of U)
 	int32_t tmem_cols;       // TMEM columns owned by one warp (256: two warps per lane quarter, 512: one)
 	float total;
@@ -439,7 +445,8 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 	constexpr int U = VX_WSB_U;
 	const int lane = threadIdx.x & 31;
 	const int warp = threadIdx.x >> 5;
-	float4 *hist = wsb_smem + (size_t)warp * a.cap * Q * 32 + lane;
+	const int hist_row0 = warp < a.n_long_warps ? warp * a.cap_long : a.n_long_warps * a.cap_long + (warp - a.n_long_warps) * a.cap;
+	float4 *hist = wsb_smem + (size_t)hist_row0 * Q * 32 + lane;
 
 	// let the next length class of this query start filling SMs as soon as CTAs of this launch retire
 	// (programmatic dependent launch; there is no data dependency between the launches of one query)
@@ -463,25 +470,37 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 
 	for (;;) {
 		// reserve a chunk of consecutive tiles; their token quads form one contiguous stream
+		// Warps [0, n_long_warps) try the long queue first (stateless: one more atomic per reservation once it is empty;
+		// a flag kept in a register for the whole kernel is what the 249-register variant has no room for).
 		unsigned int got = 0;
 		if (lane == 0) {
-			got = atomicAdd(a.counter, 1u);
+			bool lng = false;
+			if ((threadIdx.x >> 5) < a.n_long_warps) {
+				got = atomicAdd(a.counter_long, 1u);
+				lng = got < a.n_long_tiles;
+			}
+			got = lng ? got | 0x80000000u : atomicAdd(a.counter, 1u);
 		}
 		got = __shfl_sync(0xffffffffu, got, 0);
 		// guided schedule: large reservations first (the pipeline prologue is paid once per reservation), single
 		// tiles at the end (the shortest windows: the warps finish within one short tile of each other)
-		int64_t tile, tile_stop;
-		if (got < a.n_big) {
-			tile = a.tile_begin + (int64_t)got * a.chunk;
-			tile_stop = tile + a.chunk;
-		} else {
-			tile = a.tile_begin + (int64_t)a.n_big * a.chunk + (got - a.n_big);
+		int tile, tile_stop;   // relative to tiles[0]: fewer than 2^26 tiles
+		if (got & 0x80000000u) {
+			tile = a.long_begin + (int)(got & 0x7fffffffu);
 			tile_stop = tile + 1;
+		} else {
+			if (got < a.n_big) {
+				tile = a.tile_begin + (int)got * a.chunk;
+				tile_stop = tile + a.chunk;
+			} else {
+				tile = a.tile_begin + (int)a.n_big * a.chunk + (int)(got - a.n_big);
+				tile_stop = tile + 1;
+			}
+			if (tile >= a.tile_end) {
+				break;
+			}
+			tile_stop = tile_stop < a.tile_end ? tile_stop : a.tile_end;
 		}
-		if (tile >= a.tile_end) {
-			break;
-		}
-		tile_stop = tile_stop < a.tile_end ? tile_stop : a.tile_end;
 		VxTile tl = a.tiles[tile];
 		const int4 *__restrict__ quads = reinterpret_cast<const int4*>(a.tok) + (size_t)tl.base128 * 32 + lane;
 
@@ -551,7 +570,7 @@ __global__ void __launch_bounds__(256, 1) wsb_score_kernel(const __grid_constant
 				}
 				raw = best;
 			}
-			const int64_t slot = tile * 32 + lane;
+			const int64_t slot = (int64_t)tile * 32 + lane;
 			const float boost = a.boost ? a.boost[slot] : 1.0f;
 			a.score[slot] = lane < tl.n_valid ? (raw / a.total) * boost : -CUDART_INF_F;
 			tl = tl_next;
@@ -602,8 +621,15 @@ int vx_wsb_longest(int tp) {
 	return 0;
 }
 
+// long queue of a launch (see WsbArgs): n_warps warps per CTA sized for windows of up to `cap` rows take tiles [begin, end) first
+struct WsbLong {
+	int n_warps, cap;
+	int64_t begin, end;
+	unsigned int *counter;
+};
+
 template<int TP, int LOC, bool BORD, bool F2, bool PIPE, bool TAG>
-static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap) {
+static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap, const WsbLong &lq) {
 	// History placement: rows [0, rt) in tensor memory, the rest in shared memory.  Eight warps per
 	// SM (two per scheduler) when the rest fits; each pair of warps w, w+4 shares a TMEM lane quarter
 	// and gets 256 columns.  Long classes fall back to <= 4 warps with 512 columns each.
@@ -616,6 +642,13 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	a.rt = rt;
 	a.tmem_cols = tmem_cols;
 	a.cap = rows_smem;
+	const bool has_long = lq.n_warps > 0 && lq.end > lq.begin && warps == 8;
+	const int rows_long = has_long ? lq.cap - rt : 0;
+	a.n_long_warps = has_long ? lq.n_warps : 0;
+	a.cap_long = rows_long;
+	a.long_begin = has_long ? (int32_t)lq.begin : 0;
+	a.n_long_tiles = has_long ? (uint32_t)(lq.end - lq.begin) : 0u;
+	a.counter_long = lq.counter;
 	const int64_t n_tiles = a.tile_end - a.tile_begin;
 	// tiles per reservation: large enough to amortise the pipeline prologue, small enough that the
 	// last chunks balance (>= 32 chunks per warp when the class is big)
@@ -628,8 +661,13 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 	a.n_big = (uint32_t)n_big;
 	const int64_t n_chunks = n_big + (n_tiles - n_big * chunk);
 	const int64_t want_blocks = (n_chunks + warps - 1) / warps;
-	const int blocks = (int)(want_blocks < sms ? want_blocks : sms);
-	const size_t smem = (size_t)rows_smem * row_bytes * warps;
+	int64_t need_blocks = want_blocks;
+	if (has_long) {
+		const int64_t long_blocks = (lq.end - lq.begin + lq.n_warps - 1) / lq.n_warps;
+		need_blocks = long_blocks > need_blocks ? long_blocks : need_blocks;
+	}
+	const int blocks = (int)(need_blocks < sms ? need_blocks : sms);
+	const size_t smem = ((size_t)rows_smem * (warps - a.n_long_warps) + (size_t)rows_long * a.n_long_warps) * row_bytes;
 	static bool attr_set = false;
 	if (!attr_set) {
 		cudaFuncSetAttribute(wsb_score_kernel<TP, LOC, BORD, F2, PIPE, TAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024 - 1024));
@@ -656,35 +694,35 @@ static int launch_class(vx_corpus *c, WsbArgs &a, int cap, int sms, bool overlap
 }
 
 template<int TP, bool F2, bool PIPE, bool TAG>
-static int launch_class_f(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
+static int launch_class_f(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap, const WsbLong &lq) {
 	if (loc == VX_LOCAL) {
-		return bord ? launch_class<TP, VX_LOCAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap) : launch_class<TP, VX_LOCAL, false, F2, PIPE, TAG>(c, a, cap, sms, overlap);
+		return bord ? launch_class<TP, VX_LOCAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap, lq) : launch_class<TP, VX_LOCAL, false, F2, PIPE, TAG>(c, a, cap, sms, overlap, lq);
 	}
 	if (loc == VX_GLOBAL) {
-		return launch_class<TP, VX_GLOBAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap);
+		return launch_class<TP, VX_GLOBAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap, lq);
 	}
-	return launch_class<TP, VX_SEMIGLOBAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap);
+	return launch_class<TP, VX_SEMIGLOBAL, true, F2, PIPE, TAG>(c, a, cap, sms, overlap, lq);
 }
 
 template<int TP>
-static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap) {
+static int launch_class_t(vx_corpus *c, WsbArgs &a, int cap, int sms, int loc, bool bord, bool overlap, const WsbLong &lq) {
 	// A/B switches for measurements (read once): VX_WSB_NO_F2 = scalar adds instead of FADD2 (and the round-1 loop
 	// structure), VX_WSB_NO_PIPE = packed adds without the double-buffered history loops
 	static const bool f2 = getenv("VX_WSB_NO_F2") == nullptr;
 	static const bool pipe = getenv("VX_WSB_NO_PIPE") == nullptr;
 	if (a.tag.on) {
-		return launch_class_f<TP, true, false, true>(c, a, cap, sms, loc, bord, overlap);   // tag weighting: packed adds, single-buffered
+		return launch_class_f<TP, true, false, true>(c, a, cap, sms, loc, bord, overlap, lq);   // tag weighting: packed adds, single-buffered
 	}
 	if (!f2) {
-		return launch_class_f<TP, false, false, false>(c, a, cap, sms, loc, bord, overlap);
+		return launch_class_f<TP, false, false, false>(c, a, cap, sms, loc, bord, overlap, lq);
 	}
 	// the second row-pair buffer costs 2 * TP registers: 249 at TP = 12 (fits 8 warps per SM exactly), spills at TP = 16
 	if constexpr (TP <= 12) {
 		if (pipe) {
-			return launch_class_f<TP, true, true, false>(c, a, cap, sms, loc, bord, overlap);
+			return launch_class_f<TP, true, true, false>(c, a, cap, sms, loc, bord, overlap, lq);
 		}
 	}
-	return launch_class_f<TP, true, false, false>(c, a, cap, sms, loc, bord, overlap);
+	return launch_class_f<TP, true, false, false>(c, a, cap, sms, loc, bord, overlap, lq);
 }
 
 // Scores every tile whose windows are at most VX_WSB_MAX_LEN long; *first_tile receives the index of
@@ -747,7 +785,85 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 	// the longest class whose history fits on chip at one warp per SM (TP = 12: 42 rows in tensor memory + 147 in shared
 	// memory); longer tiles stay in [0, *first_tile) for the scratch kernel
 	const int cls_start = vx_wsb_longest(s->tp) / 4;
+
+	// The length classes just above the 8-warp group would run at 7, 6, ... warps per SM in launches of their own (a
+	// fifth of the time at three quarters of the efficiency, plus a tail per launch).  Instead TWO warps of every CTA of
+	// the 8-warp launch get a larger shared-memory slice and take those tiles first, longest first, while the other
+	// six work on the main queue; when the long queue is empty they join them.  Conditions: the launch stays within the
+	// 196 KB shared-memory carve-out (one step more leaves no L1 for the S-row gather: 16 % slower, profiles/r2_wsb_hybrid),
+	// which may mean a shorter main class, and the long tiles hold at most 24 % of the work of the launch (two warps of
+	// eight), so that they never finish last.
+	static const bool hybrid_on = getenv("VX_WSB_NO_HYBRID") == nullptr;   // A/B switch
+	WsbLong lq;
+	memset(&lq, 0, sizeof(lq));
+	int cls_main = 0;   // longest class of the 8-warp group
+	for (int cls = cls_start; cls >= 1 && cls_main == 0; cls--) {
+		int w, rt_, tc_, rs_;
+		wsb_plan(s->tp, cls * 4, &w, &rt_, &tc_, &rs_);
+		if (w == 8) {
+			cls_main = cls;
+		}
+	}
+	int cls_long = cls_main;   // classes (cls_main, cls_long] ride along in the main launch
+	if (hybrid_on && cls_main >= 1 && c->class_first[cls_main] < c->class_first[0]) {
+		int w, rt_main, tc_, rs_;
+		wsb_plan(s->tp, cls_main * 4, &w, &rt_main, &tc_, &rs_);
+		const size_t row_bytes = (size_t)s->tp * 32 * sizeof(float);
+		const int budget_rows = (int)((size_t)192 * 1024 / row_bytes);
+		auto work = [&](int lo_cls, int hi_cls) {   // ~ candidates of the tiles of classes (lo_cls, hi_cls]
+			double sum = 0.0;
+			for (int i = lo_cls + 1; i <= hi_cls; i++) {
+				const double len = 4.0 * i - 1.5;
+				sum += (double)(c->class_first[i - 1] - c->class_first[i]) * (len * len + (qp.t + 3) * len);
+			}
+			return sum;
+		};
+		double best_share = 0.0;
+		int best_main = cls_main, best_n = 0;
+		for (int n_long = 2; n_long <= 4; n_long++) {
+			for (int cm = cls_main; cm >= 1 && cm >= cls_main - 2; cm--) {
+				const int rows_m = cm * 4 > rt_main ? cm * 4 - rt_main : 0;
+				for (int cl = cls_start; cl > cm; cl--) {
+					if (n_long * (cl * 4 - rt_main) + (8 - n_long) * rows_m > budget_rows) {
+						continue;
+					}
+					const double w_long = work(cm, cl), w_all = work(0, cl);
+					// what this choice takes out of the launches with fewer than eight warps
+					const double gain = work(cls_main, cl);
+					if (w_long <= (n_long / 8.0 - 0.02) * w_all) {
+						if (gain > best_share) {
+							best_share = gain;
+							best_main = cm;
+							best_n = n_long;
+							cls_long = cl;
+						}
+						break;   // the longest class that qualifies for this (n_long, cm); shorter ones absorb less
+					}
+				}
+			}
+		}
+		if (best_share > 0.0) {
+			cls_main = best_main;
+			lq.n_warps = best_n;
+			lq.cap = cls_long * 4;
+			lq.begin = c->class_first[cls_long];
+			lq.end = c->class_first[cls_main];
+			lq.counter = counters + (n_groups++ & 15);
+			if (lq.begin < *first_tile) {
+				*first_tile = lq.begin;
+			}
+		} else {
+			cls_long = cls_main;
+		}
+	}
+	WsbLong no_lq;
+	memset(&no_lq, 0, sizeof(no_lq));
+
 	for (int cls = cls_start; cls >= 1; ) {
+		if (cls > cls_main && cls <= cls_long) {
+			cls--;   // these tiles are the long queue of the main launch
+			continue;
+		}
 		if (c->class_first[cls] >= c->class_first[cls - 1]) {
 			cls--;   // no tiles of this length: the next group is sized for the longest length present
 			continue;
@@ -761,8 +877,12 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 			if (w_lo != w_top && w_top < 8) {
 				break;
 			}
+			if (lo - 1 > cls_main && lo - 1 <= cls_long) {
+				break;   // a group does not reach into the long queue's classes
+			}
 			lo--;
 		}
+		const WsbLong &lq_here = w_top == 8 ? lq : no_lq;   // the (one) 8-warp group carries the long queue
 		const int64_t begin = c->class_first[cls];
 		const int64_t end = c->class_first[lo - 1];
 		const int cap = cls * 4;
@@ -774,21 +894,21 @@ int vx_launch_wsb(vx_corpus *c, const vx_sim *s, const VxAlignDev &ap, const VxQ
 			*first_tile = begin;
 		}
 		a.counter = counters + (n_groups++ & 15);
-		a.tile_begin = begin;
-		a.tile_end = end;
+		a.tile_begin = (int32_t)begin;
+		a.tile_end = (int32_t)end;
 		int rc;
 		switch (s->tp) {
 			case 4:
-				rc = launch_class_t<4>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
+				rc = launch_class_t<4>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all), lq_here);
 				break;
 			case 8:
-				rc = launch_class_t<8>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
+				rc = launch_class_t<8>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all), lq_here);
 				break;
 			case 12:
-				rc = launch_class_t<12>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
+				rc = launch_class_t<12>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all), lq_here);
 				break;
 			case 16:
-				rc = launch_class_t<16>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all));
+				rc = launch_class_t<16>(c, a, cap, sms, ap.locality, bord, launches > 0 && pdl && (cls > 0 || pdl_all), lq_here);
 				break;
 			default:
 				vx_set_error("vx_launch_wsb: query longer than the fast path supports");
