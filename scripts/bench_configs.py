@@ -371,6 +371,9 @@ def main():
 		for nm, loc, gap in (("SW Local linear(0.2)", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2)), ("Gotoh Local affine(0.3,0.1)", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1)),
 				("WSB Local smooth_gap_cost(5)", _cabi.VX_LOCAL, gaps.smooth_gap_cost(5))):
 			run_long_query("long query T=24: %s, 2M sentences" % nm, loc, gap, 24, 2_000_000)
+		for t in (40, 64):   # longer than 32 tokens: the linear kernel goes up to 64 query tokens, the affine one to 48
+			run_long_query("long query T=%d: SW Local linear(0.2), 2M sentences" % t, _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), t, 2_000_000)
+		run_long_query("long query T=40: Gotoh Local affine(0.3,0.1), 2M sentences", _cabi.VX_LOCAL, gaps.AffineGapCost(u=0.3, v=0.1), 40, 2_000_000)
 	if "mq" in which:
 		run_multi_query("C2-mq: 8 SW Local linear(0.2) queries, T=8, 20M sentences, V=200k", _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 8, 20_000_000, 200_000, 300)
 		run_multi_query("C2-mq12: 8 NW Global linear(0.2) queries, T=12, 20M sentences, V=50k", _cabi.VX_GLOBAL, gaps.LinearGapCost(0.2), 12, 20_000_000, 50_000, 300)

@@ -264,11 +264,11 @@ def test_many_ties_topk(engine, oracle):
 	assert [(int(h["doc"]), int(h["slice"])) for h in hits] == want
 
 
-@pytest.mark.parametrize("t", [17, 24, 27, 32])
-def test_queries_of_17_to_32_tokens_on_the_score_kernels(engine, oracle, t):
-	"""Queries longer than 16 tokens (a whole sentence as the query) take the linear / affine / general-scratch score kernels
-	(TP = 20 .. 32) instead of the one-thread-per-window scorer: bit-identical scores, identical top-k and tracebacks, for
-	every locality x gap kind, incl. windows longer than 64 tokens and a boost."""
+@pytest.mark.parametrize("t", [17, 24, 27, 32, 33, 47, 50, 64])
+def test_queries_of_17_to_64_tokens_on_the_score_kernels(engine, oracle, t):
+	"""Queries longer than 16 tokens (a whole sentence as the query) take the linear (up to 64 tokens) / affine (up to 48) /
+	general-scratch (up to 32) score kernels instead of the one-thread-per-window scorer, which keeps the rest: bit-identical
+	scores, identical top-k and tracebacks, for every locality x gap kind, incl. windows longer than 64 tokens and a boost."""
 	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=900, t=t, seed=90 + t)
 	s = oracle.sim_static(emb, q_id, q_vec)
 	rng = np.random.default_rng(t)

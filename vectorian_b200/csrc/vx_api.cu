@@ -612,7 +612,7 @@ extern "C" int vx_sim_static(const vx_embedding *e, const int32_t *q_id, const f
 	s->rows = e->v;
 	s->nonneg = true;   // clip01 in the kernel epilogue
 	s->t = t;
-	s->tp = std::max(4, (t + 3) / 4 * 4);
+	s->tp = vx_row_width(t);
 	cudaStream_t st = vx_sim_stream();
 	int rc = sim_alloc_s(s);
 	if (rc == VX_OK) {
@@ -667,7 +667,7 @@ extern "C" int vx_sim_upload(const float *sm, int64_t v, int32_t t, vx_sim **out
 	vx_sim *s = new vx_sim();
 	s->rows = v;
 	s->t = t;
-	s->tp = std::max(4, (t + 3) / 4 * 4);
+	s->tp = vx_row_width(t);
 	s->nonneg = true;
 	for (int64_t i = 0; i < v * t; i++) {
 		if (!(sm[i] >= 0.0f)) {
@@ -720,7 +720,7 @@ extern "C" int vx_sim_upload_tokens(vx_corpus *c, const float *s_tok, int64_t n_
 	s->owner = c;
 	s->rows = c->n_tok_tiled;
 	s->t = t;
-	s->tp = std::max(4, (t + 3) / 4 * 4);
+	s->tp = vx_row_width(t);
 	s->nonneg = true;
 	for (int64_t i = 0; i < n_tok * t; i++) {
 		if (!(s_tok[i] >= 0.0f)) {
@@ -772,7 +772,7 @@ extern "C" int vx_sim_contextual(const float *q_vec, int32_t t, int32_t d, vx_si
 	s->contextual = 1;
 	s->nonneg = true;
 	s->t = t;
-	s->tp = std::max(4, (t + 3) / 4 * 4);
+	s->tp = vx_row_width(t);
 	s->d = d;
 	// staging from the pool: q[t x d] | qhat[t x d]; normalised on the similarity stream, searches wait on ev1
 	// (no cudaMalloc / cudaFree / device-wide synchronisation per query)

@@ -155,7 +155,15 @@ cudaStream_t vx_sim_stream();
 
 // Per-query constants handed to the kernels by value.
 constexpr int VX_MAX_T_FAST = 16;    // query lengths of the tensor-memory WSB kernel, the similarity kernels, tag weighting, batches
-constexpr int VX_MAX_T_LONG = 32;    // query lengths of the linear / affine / general-scratch score kernels (one DP row in registers)
+constexpr int VX_MAX_T_LONG = 32;    // query lengths of the general-scratch score kernel (one DP row + the gap table in registers)
+constexpr int VX_MAX_T_LINEAR = 64;  // query lengths of the linear score kernel (one DP row in registers)
+constexpr int VX_MAX_T_AFFINE = 48;  // ... of the affine score kernel (two DP rows in registers)
+
+// Row width of a similarity matrix for t query tokens: a multiple of 4 up to 32 tokens, of 8 beyond (fewer kernel
+// instances for the long queries; the rows stay 16- resp. 32-byte aligned for the vector loads).
+inline int vx_row_width(int t) {
+	return t <= 32 ? (t < 4 ? 4 : (t + 3) / 4 * 4) : (t + 7) / 8 * 8;
+}
 constexpr int VX_MAX_T_MASK = 32;    // matched-set bitmask width of the exact kernel
 
 struct VxAlignDev {

@@ -227,9 +227,10 @@ static int make_plan(vx_corpus *c, const vx_sim *s, const vx_align_params *ap, c
 		tag_fast = tag_fast && sum > 0.0f && sum < 8192.0f && t <= VX_MAX_T_FAST;
 		tag_fast = tag_fast && !(ap->gap_kind == VX_GAP_GENERAL && c->max_len > vx_wsb_longest(s->tp));   // the scratch kernel has no tag weighting
 	}
-	// query lengths: up to 16 tokens everywhere; 17 .. 32 tokens on the linear / affine / general-scratch kernels for static
-	// and host-supplied per-token matrices (the contextual similarity kernels and tag weighting stop at 16)
-	const int32_t tp_max = (s->contextual == 1 || s->contextual == 2 || qp->tag_weighted) ? VX_MAX_T_FAST : VX_MAX_T_LONG;
+	// query lengths: up to 16 tokens everywhere; for static and host-supplied per-token matrices 17 .. 64 tokens on the linear kernel,
+	// 17 .. 48 on the affine kernel and 17 .. 32 on the general-scratch kernel (the contextual similarity kernels and tag weighting stop at 16)
+	const int32_t tp_max = (s->contextual == 1 || s->contextual == 2 || qp->tag_weighted) ? VX_MAX_T_FAST
+		: ap->gap_kind == VX_GAP_GENERAL ? VX_MAX_T_LONG : ap->gap_kind == VX_GAP_AFFINE ? VX_MAX_T_AFFINE : VX_MAX_T_LINEAR;
 	p->fast = (!s->contextual || c->d_iota) && s->tp <= tp_max && tag_fast && qp->submatch_weight == 0.0f;
 
 	// ---- workspace layout: [top-k area | block of plan 0 | block of plan 1 | ...] ----
