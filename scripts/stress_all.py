@@ -118,6 +118,9 @@ def main():
 		("tag-weighted linear global T=8", dict(), _cabi.VX_GLOBAL, gaps.LinearGapCost(0.2), 8, True),
 		("linear local T=24", dict(), _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 24, False),
 		("wsb local T=24 (scratch kernel)", dict(), _cabi.VX_LOCAL, gaps.smooth_gap_cost(5), 24, False),
+		("linear local T=40 (vx_align_long)", dict(), _cabi.VX_LOCAL, gaps.LinearGapCost(0.2), 40, False),
+		("linear semiglobal T=64", dict(), _cabi.VX_SEMIGLOBAL, gaps.LinearGapCost(0.1), 64, False),
+		("affine global T=48", dict(), _cabi.VX_GLOBAL, gaps.AffineGapCost(u=0.3, v=0.1), 48, False),
 		("wsb local T=12, windows of 3 sentences", dict(window_size=3, window_step=1), _cabi.VX_LOCAL, gaps.smooth_gap_cost(5), 12, False),
 		("wsb semiglobal T=16, windows of 3 sentences", dict(window_size=3, window_step=2), _cabi.VX_SEMIGLOBAL, gaps.smooth_gap_cost(3), 16, False),
 	]
