@@ -191,6 +191,13 @@ int vx_sim_destroy(vx_sim *s);
  *   hits[max_matches], target[max_matches x T] (InjectiveFlow target, -1 = unmatched),
  *   dist[max_matches x T] (ScoreComputer: 1 - unmodified sim, or 1)   cpp/metric/alignment.h:307-347
  * *n_hits receives the number of valid rows.
+ *
+ * Every query length gives the same results; what changes is which kernel scores the windows.  Static and uploaded
+ * similarity matrices: up to 16 query tokens every kernel (general gap costs on the tensor-memory kernel), up to 32 general
+ * gap costs on the global-scratch kernel, up to 48 affine and up to 64 linear gap costs with one DP row in registers.
+ * Contextual vectors (GEMM fused into the DP) and tag weighting: up to 16.  Beyond that, and with submatch_weight != 0
+ * or tag weights that do not sum exactly in fp32, a one-thread-per-window kernel that follows the reference's accumulator
+ * literally (about 100 times slower).
  */
 int vx_search(
 	vx_corpus *c, const vx_sim *s,
