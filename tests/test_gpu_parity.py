@@ -446,6 +446,34 @@ def test_search_batch_several_queries_per_pass(engine, oracle, n_queries):
 	dc.close()
 
 
+def test_search_batch_with_queries_longer_than_the_fused_kernels_take(engine):
+	"""A batch whose queries are 20, 40 and 64 tokens long next to two short ones: the long ones have no fused (multi-query /
+	multi-setting) kernel and run pair by pair inside the same batch; every pair equals its own vx_search."""
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=1500, t=8, seed=31)
+	dc = engine.DeviceCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"], corpus["doc_span_off"], 1, 1)
+	rng = np.random.default_rng(77)
+	sims = [engine.DeviceSim.upload(rng.random((emb.shape[0], t)).astype(np.float32)) for t in (6, 40, 9, 64, 20)]
+	aps, keeps = [], []
+	for locality, gap_name in ((_cabi.VX_LOCAL, "linear0.2"), (_cabi.VX_GLOBAL, "linear_st"), (_cabi.VX_LOCAL, "affine"), (_cabi.VX_LOCAL, "linear_st")):
+		ap, keep = align_params(locality, GAPS[gap_name], dc.max_len, 64)
+		aps.append(ap)
+		keeps.append(keep)
+	qp, _ = _cabi.make_query_params(max_matches=25, min_score=-1e30)
+	batch = dc.search_batch(sims, aps, qp)
+	for q, sim in enumerate(sims):
+		for a, ap in enumerate(aps):
+			hits, target, dist = dc.search(sim, ap, qp)
+			b_hits, b_target, b_dist = batch[q][a]
+			assert len(b_hits) == len(hits) == 25, (q, a)
+			for f in ("score", "score_max", "doc", "slice"):
+				np.testing.assert_array_equal(b_hits[f], hits[f], err_msg=f"{q} {a} {f}")
+			np.testing.assert_array_equal(b_target, target)
+			np.testing.assert_array_equal(b_dist, dist)
+	for sim in sims:
+		sim.close()
+	dc.close()
+
+
 @pytest.mark.parametrize("gap_name", ["linear0.2", "affine", "smooth5", "mixed"])
 def test_gpu_scores_equal_reference_solver(engine, gap_name):
 	"""The CUDA path against the REFERENCE'S OWN solver (oracle/_ref: unmodified pyalign solver.h, oracle/ref/):
