@@ -50,7 +50,10 @@ def ops_per_sentence(lens, t):
 
 
 class ClockSampler:
-	"""nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+	"""nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md: `-lms 200`, started before, killed
+	after).  The polling is not free: on 8 GPUs, where the timed region is 50 ms long, a 100 ms period cost 2-4 % of the
+	end-to-end rate through longer waits in the collective (profiles/r2_final/README.md); hence the recipe's period and the
+	start before the warm-up."""
 
 	def __init__(self, index):
 		self.rows = []
@@ -59,7 +62,7 @@ class ClockSampler:
 			"clocks_event_reasons.sw_power_cap")
 		try:
 			self.p = subprocess.Popen(
-				["nvidia-smi", f"--id={index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+				["nvidia-smi", f"--id={index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200"],
 				stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
 			self.t = threading.Thread(target=self._read, daemon=True)
 			self.t.start()
@@ -69,6 +72,11 @@ class ClockSampler:
 	def _read(self):
 		for line in self.p.stdout:
 			self.rows.append((time.perf_counter(), line.strip()))
+
+	def wait_first(self, timeout_s):
+		t_end = time.perf_counter() + timeout_s
+		while self.p is not None and not self.rows and time.perf_counter() < t_end:
+			time.sleep(0.02)
 
 	def stop(self, t0, t1):
 		if self.p is None:
@@ -316,10 +324,15 @@ def main():
 			dist.barrier()
 		torch.cuda.synchronize()
 
+	# The sampler is a polling nvidia-smi process: start it BEFORE the warm-up and wait for its first line, so that its
+	# start-up (NVML initialisation touches the driver of every GPU of the box) is over when the timed region begins --
+	# at N = 8 that region is only 50 ms long.
+	sampler = ClockSampler(local_rank) if rank == 0 and not args.no_clocks else None
+	if sampler:
+		sampler.wait_first(3.0)
 	for i in range(args.warmup):
 		step(i)
 
-	sampler = ClockSampler(local_rank) if rank == 0 and not args.no_clocks else None
 	barrier()
 	t0 = time.perf_counter()
 	dev_ms_total, dp_ms_total, launches_total = 0.0, 0.0, 0
@@ -351,6 +364,13 @@ def main():
 	if world > 1:
 		dist.all_reduce(times, op=dist.ReduceOp.MAX)
 		dist.all_reduce(counts, op=dist.ReduceOp.SUM)
+	# per-rank means (diagnostic: which rank the others wait for in the collective)
+	mine = torch.tensor([dp_ms_total / args.steps, gather_ms_total / args.steps, dev_ms_total / args.steps, (t1 - t0) * 1e3 / args.steps],
+		dtype=torch.float64, device="cuda")
+	per_rank = [mine.clone() for _ in range(world)]
+	if world > 1:
+		dist.all_gather(per_rank, mine)
+	per_rank = [[round(float(x), 4) for x in r.cpu()] for r in per_rank]
 	wall_s, dev_s, dp_s = [float(x) for x in times.cpu()]
 	n_sent, n_cells, launches_all = [float(x) for x in counts.cpu()]
 
@@ -412,6 +432,7 @@ def main():
 			"hbm_roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
 				"traffic": traffic, "algorithmic_bytes_per_launch": alg_bytes, "peak_source": peak_src},
 			"phases_ms": dict({k: v for k, v in dc.last_timing().items()}, gather_merge_ms_mean=gather_ms_total / args.steps),
+			"per_rank_ms": {"columns": ["dp", "gather_merge (incl. waiting for the slowest rank)", "device", "wall"], "rows": per_rank},
 			"setup_s": setup_s,
 			"top_score": float(last_hits["score"][0]) if len(last_hits) else None,
 		}
