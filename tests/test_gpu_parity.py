@@ -446,6 +446,49 @@ def test_search_batch_several_queries_per_pass(engine, oracle, n_queries):
 	dc.close()
 
 
+def corpus_with_lengths(lens, vocab, seed):
+	"""A one-sentence-per-span corpus with the given sentence lengths (documents of 53 sentences)."""
+	rng = np.random.default_rng(seed)
+	lens = np.asarray(lens, dtype=np.int64)
+	n = len(lens)
+	token_id = rng.integers(0, vocab, size=int(lens.sum())).astype(np.int32)
+	n_doc = (n + 52) // 53
+	doc_span_off = np.minimum(np.arange(n_doc + 1, dtype=np.int64) * 53, n)
+	ends = np.cumsum(lens)
+	starts = ends - lens
+	doc_tok_off = np.concatenate([starts[doc_span_off[:-1]], [int(lens.sum())]]).astype(np.int64)
+	doc_of = np.repeat(np.arange(n_doc), np.diff(doc_span_off))
+	return dict(token_id=token_id, doc_tok_off=doc_tok_off, span_start=(starts - doc_tok_off[doc_of]).astype(np.int32),
+		span_end=(ends - doc_tok_off[doc_of]).astype(np.int32), doc_span_off=doc_span_off)
+
+
+@pytest.mark.parametrize("t", [4, 7, 12, 16])
+def test_wsb_length_class_planner_on_odd_length_distributions(engine, oracle, t):
+	"""The tensor-memory WSB launch plan (groups of length classes, the long queue inside the 8-warp launch, vx_wsb.cu) on
+	corpora whose window lengths sit where the plan changes: only just above the 8-warp classes, two far-apart modes, a long
+	queue that holds too much of the work to be absorbed, every length once, one single long window.  Every window score and
+	the top-k equal the oracle's."""
+	rng = np.random.default_rng(100 + t)
+	emb = rng.standard_normal((300, 16)).astype(np.float32)
+	q_id = rng.choice(300, size=t, replace=False).astype(np.int32)
+	s = oracle.sim_static(emb, q_id, emb[q_id])
+	cases = [
+		rng.integers(33, 41, size=1300),                                                   # nothing at or below 32 tokens
+		np.concatenate([rng.integers(3, 12, size=2500), rng.integers(41, 49, size=160)]),  # two modes
+		np.concatenate([rng.integers(3, 30, size=600), rng.integers(37, 45, size=900)]),   # long classes hold most of the work
+		np.concatenate([np.arange(1, 161), np.arange(1, 161)]),                            # every length up to 160 twice
+		np.concatenate([np.full(2000, 5), [150]]),                                         # one long window among short ones
+		rng.integers(29, 37, size=1500),                                                   # only the top classes of the 8-warp group
+	]
+	for i, lens in enumerate(cases):
+		corpus = corpus_with_lengths(rng.permutation(lens), 300, seed=7 * i + t)
+		dc, oc = make_both(engine, oracle, corpus)
+		for locality in LOCALITIES:
+			run_case(engine, oracle, dc, oc, s, locality, GAPS["smooth5"], t, k=40)
+		run_case(engine, oracle, dc, oc, s, _cabi.VX_LOCAL, GAPS["log"], t, k=40)
+		dc.close()
+
+
 def test_search_batch_with_queries_longer_than_the_fused_kernels_take(engine):
 	"""A batch whose queries are 20, 40 and 64 tokens long next to two short ones: the long ones have no fused (multi-query /
 	multi-setting) kernel and run pair by pair inside the same batch; every pair equals its own vx_search."""
