@@ -360,39 +360,17 @@ __global__ void __launch_bounds__(128) score_general_scratch_kernel(
 		const int32_t *tok = a.tok + ((size_t)tl.base128 * 32 + lane) * 4;
 		const int len = tl.len;
 
-		float top[TP];   // V[-1, v]
+		float prev[TP];  // V[u-1, v]; V[-1, v] = the top border
 		#pragma unroll
 		for (int v = 0; v < TP; v++) {
-			top[v] = LOC == VX_GLOBAL ? -wt[v + 1] : 0.0f;
-		}
-		float prev[TP];  // V[u-1, v]
-		#pragma unroll
-		for (int v = 0; v < TP; v++) {
-			prev[v] = top[v];
+			prev[v] = LOC == VX_GLOBAL ? -wt[v + 1] : 0.0f;
 		}
 		float best = LOC == VX_LOCAL ? 0.0f : -CUDART_INF_F;
 		float last_col = 0.0f;
 
-		for (int u = 0; u < len; u++) {
-			float sim[TP];
-			load_row<TP>(a.s, tok[vx_elem(0, u, 0)], sim);
-
-			// vertical candidates, k = -1 .. u-1
-			float vert[TP];
-			const float w_top = __ldg(w_s + u + 1);
-			#pragma unroll
-			for (int v = 0; v < TP; v++) {
-				vert[v] = top[v] - w_top;
-			}
-			for (int k = 0; k < u; k++) {
-				const float wk = __ldg(w_s + (u - k));
-				const float *hk = hist + (size_t)k * TP * 32;
-				#pragma unroll
-				for (int v = 0; v < TP; v++) {
-					vert[v] = fmaxf(vert[v], hk[v * 32] - wk);
-				}
-			}
-
+		// row u from its vertical candidates (k = -1 .. u-1 folded into vert), the diagonal and the horizontal scan;
+		// leaves the row in prev and in the history
+		auto finish_row = [&](const float (&vert)[TP], const float (&sim)[TP], int u) {
 			const float left_border = LOC == VX_GLOBAL ? -__ldg(w_s + u + 1) : 0.0f;   // V[u, -1]
 			float diag = LOC == VX_GLOBAL ? (u == 0 ? -wt[0] : -__ldg(w_s + u)) : 0.0f;  // V[u-1, -1]
 			float cur[TP];
@@ -425,6 +403,72 @@ __global__ void __launch_bounds__(128) score_general_scratch_kernel(
 			if (LOC == VX_SEMIGLOBAL) {
 				best = fmaxf(best, last_col);
 			}
+		};
+
+		// U rows per pass over the history: every finished row k < u is read once for rows u .. u + U - 1 (the history lives
+		// in L2 and its traffic is what bounds this kernel); a row of the block is folded into the later rows' vertical
+		// candidates from registers as soon as it is finished.  U = 4 up to 24 query columns, 2 beyond (registers).
+		constexpr int U = TP <= 24 ? 4 : 2;
+		int u = 0;
+		for (; u + U <= len; u += U) {
+			float vert[U][TP];
+			#pragma unroll
+			for (int i = 0; i < U; i++) {
+				const float w = __ldg(w_s + u + i + 1);
+				#pragma unroll
+				for (int v = 0; v < TP; v++) {
+					vert[i][v] = (LOC == VX_GLOBAL ? -wt[v + 1] : 0.0f) - w;   // V[-1, v] - w_s[u + i + 1]
+				}
+			}
+			for (int k = 0; k < u; k++) {
+				float wk[U];
+				#pragma unroll
+				for (int i = 0; i < U; i++) {
+					wk[i] = __ldg(w_s + (u + i - k));
+				}
+				const float *hk = hist + (size_t)k * TP * 32;
+				#pragma unroll
+				for (int v = 0; v < TP; v++) {
+					const float h = hk[v * 32];
+					#pragma unroll
+					for (int i = 0; i < U; i++) {
+						vert[i][v] = fmaxf(vert[i][v], h - wk[i]);
+					}
+				}
+			}
+			#pragma unroll
+			for (int i = 0; i < U; i++) {
+				float sim[TP];
+				load_row<TP>(a.s, tok[vx_elem(0, u + i, 0)], sim);
+				finish_row(vert[i], sim, u + i);
+				#pragma unroll
+				for (int j = i + 1; j < U; j++) {
+					const float w = __ldg(w_s + (j - i));
+					#pragma unroll
+					for (int v = 0; v < TP; v++) {
+						vert[j][v] = fmaxf(vert[j][v], prev[v] - w);   // k = u + i, from registers
+					}
+				}
+			}
+		}
+		for (; u < len; u++) {
+			float vert[TP];
+			const float w_top = __ldg(w_s + u + 1);
+			#pragma unroll
+			for (int v = 0; v < TP; v++) {
+				vert[v] = (LOC == VX_GLOBAL ? -wt[v + 1] : 0.0f) - w_top;
+			}
+			for (int k = 0; k < u; k++) {
+				const float wk = __ldg(w_s + (u - k));
+				const float *hk = hist + (size_t)k * TP * 32;
+				#pragma unroll
+				for (int v = 0; v < TP; v++) {
+					vert[v] = fmaxf(vert[v], hk[v * 32] - wk);
+				}
+			}
+			float sim[TP];
+			load_row<TP>(a.s, tok[vx_elem(0, u, 0)], sim);
+			finish_row(vert, sim, u);
 		}
 
 		float raw;
@@ -493,8 +537,10 @@ static int launch_score_tl(vx_corpus *c, const vx_sim *s, const ScoreArgs &a, co
 			}
 			ScoreArgs a_long = a;
 			a_long.n_tiles = first;
-			// persistent: 16 warps per SM
-			const int blocks = sm_count() * 4;
+			// persistent warps: 16 per SM; 12 when every tile comes here (queries of 17 .. 32 tokens: 168 registers, and the
+			// column histories in flight -- warps x window length x TP x 128 bytes -- should stay inside L2): 2 M sentences at
+			// T = 24 take 5.65 ms with 12 warps per SM, 6.2 with 8, 6.4 with 16 (which do not all fit), 7.6 with 4
+			const int blocks = sm_count() * (TP > VX_MAX_T_FAST ? 3 : 4);
 			const size_t need = sizeof(float) * (size_t)blocks * warps * c->max_len * TP * 32;
 			if (c->scratch_bytes < need) {
 				if (c->d_scratch) {
