@@ -314,10 +314,11 @@ def main():
 		j = i % N_QUERIES
 		sim = engine.DeviceSim.static(de, q_ids[j].numpy(), q_vecs[j].numpy())
 		hits, target, distance = dc.search(sim, ap, qp)
-		dev_ms = sim.build_ms + sum(dc.last_timing().values())
+		timing = dc.last_timing()            # read once per step: every read is a handful of cudaEventElapsedTime calls
+		dev_ms = sim.build_ms + sum(timing.values())
 		launches = sim.launches + dc.last_launches()
 		sim.close()
-		return hits, dev_ms, launches
+		return hits, dev_ms, launches, timing
 
 	def barrier():
 		if world > 1:
@@ -339,10 +340,10 @@ def main():
 	last_hits = None
 	gather_ms_total = 0.0
 	for i in range(args.steps):
-		last_hits, dev_ms, launches = step(args.warmup + i)
+		last_hits, dev_ms, launches, timing = step(args.warmup + i)
 		dev_ms_total += dev_ms
-		dp_ms_total += dc.last_timing()["dp_ms"]
-		gather_ms_total += dc.last_timing()["gather_merge_ms"]
+		dp_ms_total += timing["dp_ms"]
+		gather_ms_total += timing["gather_merge_ms"]
 		launches_total += launches
 	barrier()
 	t1 = time.perf_counter()
