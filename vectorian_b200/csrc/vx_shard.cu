@@ -27,6 +27,9 @@ typedef int (*fn_ncclCommInitRank)(NcclComm*, int, NcclUniqueId, int);
 typedef int (*fn_ncclCommDestroy)(NcclComm);
 typedef int (*fn_ncclAllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t);
 typedef const char *(*fn_ncclGetErrorString)(int);
+typedef int (*fn_ncclSend)(const void*, size_t, int, int, NcclComm, cudaStream_t);
+typedef int (*fn_ncclRecv)(void*, size_t, int, int, NcclComm, cudaStream_t);
+typedef int (*fn_ncclGroup)();
 constexpr int NCCL_CHAR = 0;   // ncclInt8 / ncclChar
 
 static struct {
@@ -36,6 +39,9 @@ static struct {
 	fn_ncclCommDestroy comm_destroy = nullptr;
 	fn_ncclAllGather all_gather = nullptr;
 	fn_ncclGetErrorString error_string = nullptr;
+	fn_ncclSend send = nullptr;            // optional (VX_GATHER_P2P experiment)
+	fn_ncclRecv recv = nullptr;
+	fn_ncclGroup group_start = nullptr, group_end = nullptr;
 } g_nccl;
 
 static int nccl_load() {
@@ -57,6 +63,10 @@ static int nccl_load() {
 	g_nccl.comm_destroy = (fn_ncclCommDestroy)dlsym(h, "ncclCommDestroy");
 	g_nccl.all_gather = (fn_ncclAllGather)dlsym(h, "ncclAllGather");
 	g_nccl.error_string = (fn_ncclGetErrorString)dlsym(h, "ncclGetErrorString");
+	g_nccl.send = (fn_ncclSend)dlsym(h, "ncclSend");
+	g_nccl.recv = (fn_ncclRecv)dlsym(h, "ncclRecv");
+	g_nccl.group_start = (fn_ncclGroup)dlsym(h, "ncclGroupStart");
+	g_nccl.group_end = (fn_ncclGroup)dlsym(h, "ncclGroupEnd");
 	if (!g_nccl.get_unique_id || !g_nccl.comm_init_rank || !g_nccl.comm_destroy || !g_nccl.all_gather) {
 		VX_FAIL(VX_ERR_INVALID, "libnccl.so.2 lacks ncclGetUniqueId / ncclCommInitRank / ncclCommDestroy / ncclAllGather");
 	}
@@ -127,6 +137,27 @@ extern "C" int vx_comm_destroy(vx_comm *m) {
 int vx_comm_all_gather(vx_comm *m, const void *send, void *recv, size_t bytes, cudaStream_t st) {
 	if (!m || !m->comm) {
 		VX_FAIL(VX_ERR_INVALID, "no communicator");
+	}
+	// A/B switch (read once): every rank sends its block straight to every peer (grouped ncclSend / ncclRecv: one hop)
+	// instead of the ring all-gather (world - 1 steps)
+	static const bool p2p = getenv("VX_GATHER_P2P") != nullptr;
+	if (p2p && g_nccl.send && g_nccl.recv && g_nccl.group_start && g_nccl.group_end && m->world > 1) {
+		cudaMemcpyAsync((uint8_t*)recv + (size_t)m->rank * bytes, send, bytes, cudaMemcpyDeviceToDevice, st);
+		int rc = g_nccl.group_start();
+		for (int peer = 0; peer < m->world && rc == 0; peer++) {
+			if (peer == m->rank) {
+				continue;
+			}
+			rc = g_nccl.send(send, bytes, NCCL_CHAR, peer, m->comm, st);
+			if (rc == 0) {
+				rc = g_nccl.recv((uint8_t*)recv + (size_t)peer * bytes, bytes, NCCL_CHAR, peer, m->comm, st);
+			}
+		}
+		const int rc_end = g_nccl.group_end();
+		if (rc != 0 || rc_end != 0) {
+			VX_FAIL(VX_ERR_CUDA, "ncclSend / ncclRecv: " + nccl_error(rc != 0 ? rc : rc_end));
+		}
+		return VX_OK;
 	}
 	const int rc = g_nccl.all_gather(send, recv, bytes, NCCL_CHAR, m->comm, st);
 	if (rc != 0) {
