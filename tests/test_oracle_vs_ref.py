@@ -81,6 +81,39 @@ def test_oracle_equals_reference_solver(oracle, locality, gap_name):
 	assert n_ties > 0 and n_flip <= 6   # a last-bit difference may flip a tie; it must stay rare
 
 
+@pytest.mark.parametrize("gap_name", ["linear0.2", "linear_st", "affine", "smooth5"])
+@pytest.mark.parametrize("locality", LOCALITIES)
+def test_oracle_equals_reference_solver_on_long_queries(oracle, locality, gap_name):
+	"""Queries of 17 .. 64 tokens (a whole sentence as the query): the GPU score kernels for these lengths are checked against
+	the oracle (tests/test_gpu_parity.py), so the oracle is pinned to the reference's own solver at these lengths too."""
+	rng = np.random.default_rng(abs(hash((locality, gap_name, "long"))) % (2 ** 31))
+	gap = GAPS[gap_name]
+	max_len_s, max_len_t = 70, 64
+	r = gaps.resolve_gap_costs(gap, max_len_s, max_len_t)
+	solver = ref.RefSolver(locality, r, max_len_s, max_len_t)
+	linspace_border = locality == _cabi.VX_GLOBAL and r["gap_kind"] == 1
+	n_flip = 0
+	for case in range(45):
+		len_s, len_t = int(rng.integers(1, max_len_s + 1)), int(rng.integers(17, max_len_t + 1))
+		if case % 3 == 1:
+			sim = (rng.integers(0, 4, size=(len_s, len_t)) / 3.0).astype(np.float32)      # many exact ties
+		else:
+			sim = np.clip(rng.standard_normal((len_s, len_t)) * 0.5 + 0.2, 0, 1).astype(np.float32)
+		s_ref, t_ref = solver.align(sim)
+		r2 = dict(gaps.resolve_gap_costs(gap, len_s, len_t))
+		kind = r2.pop("gap_kind")
+		ap, keep = _cabi.make_align_params(locality, kind, **r2)
+		s_or, t_or = oracle.align(sim, ap)
+		if linspace_border:
+			assert abs(float(s_or) - float(s_ref)) <= 5e-7 * max(1.0, abs(float(s_ref))), (case, s_or, s_ref)
+			n_flip += list(t_or) != list(t_ref)
+		else:
+			assert np.float32(s_or).tobytes() == np.float32(s_ref).tobytes(), (case, len_s, len_t, s_or, s_ref)
+			assert list(t_or) == list(t_ref), (case, len_s, len_t, list(t_or), list(t_ref))
+	solver.close()
+	assert n_flip <= 4
+
+
 # ---- heap order pinned to the reference's own ResultSet (oracle/ref/resultset_driver.cpp) ----
 
 def tie_problem(n_doc=40, per_doc=37, seed=0):
