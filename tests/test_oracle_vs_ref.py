@@ -114,6 +114,32 @@ def test_oracle_equals_reference_solver_on_long_queries(oracle, locality, gap_na
 	assert n_flip <= 4
 
 
+@pytest.mark.parametrize("gap_name", ["smooth5", "mixed", "log"])
+@pytest.mark.parametrize("locality", LOCALITIES)
+def test_oracle_equals_reference_solver_on_long_windows(oracle, locality, gap_name):
+	"""Windows of up to 320 tokens (several sentences) with general gap costs: the lengths of the long WSB length classes and
+	of the scratch kernel, which the GPU tests check against the oracle."""
+	rng = np.random.default_rng(abs(hash((locality, gap_name, "windows"))) % (2 ** 31))
+	gap = GAPS[gap_name]
+	max_len_s, max_len_t = 320, 16
+	r = gaps.resolve_gap_costs(gap, max_len_s, max_len_t)
+	solver = ref.RefSolver(locality, r, max_len_s, max_len_t)
+	for case in range(16):
+		len_s, len_t = int(rng.integers(65, max_len_s + 1)), int(rng.integers(1, max_len_t + 1))
+		if case % 3 == 1:
+			sim = (rng.integers(0, 4, size=(len_s, len_t)) / 3.0).astype(np.float32)
+		else:
+			sim = np.clip(rng.standard_normal((len_s, len_t)) * 0.5 + 0.2, 0, 1).astype(np.float32)
+		s_ref, t_ref = solver.align(sim)
+		r2 = dict(gaps.resolve_gap_costs(gap, len_s, len_t))
+		kind = r2.pop("gap_kind")
+		ap, keep = _cabi.make_align_params(locality, kind, **r2)
+		s_or, t_or = oracle.align(sim, ap)
+		assert np.float32(s_or).tobytes() == np.float32(s_ref).tobytes(), (case, len_s, len_t, s_or, s_ref)
+		assert list(t_or) == list(t_ref), (case, len_s, len_t, list(t_or), list(t_ref))
+	solver.close()
+
+
 # ---- heap order pinned to the reference's own ResultSet (oracle/ref/resultset_driver.cpp) ----
 
 def tie_problem(n_doc=40, per_doc=37, seed=0):
