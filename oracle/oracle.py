@@ -182,6 +182,16 @@ class OracleCorpus:
 		assert rc == 0
 		return hits[:n.value], target[:n.value, :t], dist[:n.value, :t]
 
+	def window_similarity(self, s, qp, tok, len_s, contextual=False):
+		"""The [len_s x T] similarity matrix the DP sees for the window starting at token `tok` (test hook)."""
+		p, s_keep = self.problem(s, contextual)
+		out = np.zeros((int(len_s), p.t), dtype=np.float32)
+		f = lib().vxo_debug_window_similarity
+		f.restype = None
+		f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]
+		f(C.byref(p), C.byref(qp), int(tok), int(len_s), out.ctypes.data)
+		return out
+
 	def score_all(self, s, ap, qp, n_threads=1, contextual=False):
 		p, s_keep = self.problem(s, contextual)
 		n = len(self.windows()[0])

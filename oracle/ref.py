@@ -150,3 +150,60 @@ def result_set(raw, score_max, doc, slice_id, max_matches, min_score, boost=None
 	_rs_lib.ref_result_set(raw.ctypes.data, score_max.ctypes.data, None if b is None else b.ctypes.data, doc.ctypes.data,
 		slice_id.ctypes.data, len(raw), k, float(min_score), o_doc.ctypes.data, o_slice.ctypes.data, o_score.ctypes.data, C.byref(n))
 	return o_doc[:n.value], o_slice[:n.value], o_score[:n.value]
+
+
+# ---- the reference's own slices (oracle/ref/slice_driver.cpp) ----
+
+SLICE_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libslice_ref.so")
+_slice_lib = None
+
+
+def slices_available():
+	return os.path.exists(SLICE_LIB_PATH)
+
+
+def _slices():
+	global _slice_lib
+	if _slice_lib is None:
+		_slice_lib = C.CDLL(SLICE_LIB_PATH)
+		_slice_lib.ref_slice_similarity.restype = C.c_int
+		_slice_lib.ref_slice_similarity.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p,
+			C.c_int32, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+		_slice_lib.ref_filtered_similarity.restype = C.c_int
+		_slice_lib.ref_filtered_similarity.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+			C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+	return _slice_lib
+
+
+def slice_similarity(s, s_id, s_pos, t_pos, t_weights=None, pos_mismatch_penalty=0.0, similarity_threshold=0.0):
+	"""similarity(i, j), unmodified_similarity(i, j) and max_sum_of_similarities() of the reference's StaticEmbeddingSlice
+	(t_weights None) or TagWeightedSlice<StaticEmbeddingSlice> (cpp/slice/static.h:9-100, 193-288) over a window with token ids
+	s_id / POS ids s_pos and a query with POS ids t_pos."""
+	s = np.ascontiguousarray(s, dtype=np.float32)
+	s_id = np.ascontiguousarray(s_id, dtype=np.int32)
+	s_pos = np.ascontiguousarray(s_pos, dtype=np.int8)
+	t_pos = np.ascontiguousarray(t_pos, dtype=np.int8)
+	t = s.shape[1]
+	sim = np.zeros((len(s_id), t), np.float32)
+	unmod = np.zeros((len(s_id), t), np.float32)
+	max_sum = C.c_float(0.0)
+	w = None if t_weights is None else np.ascontiguousarray(t_weights, dtype=np.float32)
+	_slices().ref_slice_similarity(s.ctypes.data, s.shape[0], t, s_id.ctypes.data, s_pos.ctypes.data, len(s_id), t_pos.ctypes.data,
+		0 if w is None else 1, None if w is None else w.ctypes.data, float(pos_mismatch_penalty), float(similarity_threshold),
+		sim.ctypes.data, unmod.ctypes.data, C.byref(max_sum))
+	return sim, unmod, float(max_sum.value)
+
+
+def filtered_similarity(s, s_id, s_pos, s_tag, pos_mask, tag_mask):
+	"""similarity(i, j) of the FilteredSlice the reference's FilteredSliceFactory::create_slice builds (cpp/slice/static.h:365-416;
+	TokenFilter::pass, cpp/query.h:22-28): rows = the window's tokens that pass the filter, in order."""
+	s = np.ascontiguousarray(s, dtype=np.float32)
+	s_id = np.ascontiguousarray(s_id, dtype=np.int32)
+	s_pos = np.ascontiguousarray(s_pos, dtype=np.int8)
+	s_tag = np.ascontiguousarray(s_tag, dtype=np.int8)
+	t = s.shape[1]
+	sim = np.zeros((len(s_id), t), np.float32)
+	n = C.c_int32(0)
+	_slices().ref_filtered_similarity(s.ctypes.data, s.shape[0], t, s_id.ctypes.data, s_pos.ctypes.data, s_tag.ctypes.data, len(s_id),
+		int(pos_mask), int(tag_mask), sim.ctypes.data, C.byref(n))
+	return sim[:n.value]

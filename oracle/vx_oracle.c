@@ -840,6 +840,13 @@ int vxo_search(const vxo_problem *p, const vx_align_params *ap, const vx_query_p
 	return 0;
 }
 
+/* Test hook: the similarity matrix [len_s x T] of the window of len_s tokens that starts at token `tok`, as the DP
+ * sees it (fill_sim: StaticEmbeddingSlice / TagWeightedSlice ::similarity) -- compared with the reference's own
+ * slice/static.h in tests/test_oracle_vs_ref.py. */
+void vxo_debug_window_similarity(const vxo_problem *p, const vx_query_params *qp, int64_t tok, int32_t len_s, float *out) {
+	fill_sim(p, qp, tok, len_s, out);
+}
+
 int vxo_score_all(const vxo_problem *p, const vx_align_params *ap, const vx_query_params *qp,
 	int32_t n_threads, float *score_out, int64_t n) {
 

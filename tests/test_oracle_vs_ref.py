@@ -176,3 +176,72 @@ def test_oracle_result_set_equals_reference_result_set(oracle, k, min_score):
 	np.testing.assert_array_equal(hits["doc"], want_doc)          # equal scores: the HIGHER document id first
 	np.testing.assert_array_equal(hits["slice"], want_slice)
 	assert k == 1 or np.sum(np.diff(want_score) == 0) > 1       # the winners really are full of ties
+
+
+# ---- slices pinned to the reference's own slice/static.h (oracle/ref/slice_driver.cpp) ----
+
+needs_slices = pytest.mark.skipif(not ref.slices_available(), reason="oracle/_ref/libslice_ref.so not built")
+
+
+@needs_slices
+@pytest.mark.parametrize("weights", ["dyadic", "fractions", "none"])
+def test_oracle_window_similarity_equals_reference_slices(oracle, weights):
+	"""The similarity matrix the oracle's DP sees for a window (fill_sim) against the reference's StaticEmbeddingSlice /
+	TagWeightedSlice::similarity (cpp/slice/static.h:71-75, 236-263): query-token weight, POS-mismatch penalty, threshold --
+	bit for bit; `unmodified_similarity` stays the plain S rows; max_sum_of_similarities is the float sum of the weights."""
+	from tests import helpers
+	corpus, emb, q_id, q_vec = helpers.small_problem(n_sentences=200, t=9, seed=5, with_pos=True)
+	s = oracle.sim_static(emb, q_id, q_vec)
+	t = s.shape[1]
+	rng = np.random.default_rng(11)
+	t_pos = rng.integers(0, 17, size=t).astype(np.int8)
+	w = {"dyadic": (rng.integers(1, 9, size=t) / 4.0).astype(np.float32),
+		"fractions": (0.3 + 0.1 * np.arange(t)).astype(np.float32), "none": None}[weights]
+	oc = oracle.OracleCorpus(corpus["token_id"], corpus["doc_tok_off"], corpus["span_start"], corpus["span_end"],
+		corpus["doc_span_off"], token_pos=corpus["token_pos"])
+	if w is None:
+		qp, keep = _cabi.make_query_params(max_matches=10, min_score=0.0)
+	else:
+		qp, keep = _cabi.make_query_params(max_matches=10, min_score=0.0, t_weights=w, t_pos=t_pos,
+			pos_mismatch_penalty=0.35, similarity_threshold=0.15)
+	doc, sl, tok, ln = oc.windows()
+	n_zeroed = 0
+	for i in rng.choice(len(tok), size=40, replace=False):
+		ids = corpus["token_id"][tok[i]:tok[i] + ln[i]]
+		pos = corpus["token_pos"][tok[i]:tok[i] + ln[i]]
+		o_sim = oc.window_similarity(s, qp, tok[i], ln[i])
+		r_sim, r_unmod, r_max_sum = ref.slice_similarity(s, ids, pos, t_pos, w, 0.35, 0.15)
+		assert o_sim.tobytes() == r_sim.tobytes()
+		assert r_unmod.tobytes() == s[ids].tobytes()
+		if w is not None:
+			acc = np.float32(0.0)
+			for x in w:
+				acc = np.float32(acc + x)
+			assert np.float32(r_max_sum) == acc
+			n_zeroed += int(np.sum((r_sim == 0.0) & (s[ids] > 0.0)))
+		else:
+			assert r_max_sum == float(t)
+	assert w is None or n_zeroed > 0   # the threshold does cut something in this problem
+
+
+@needs_slices
+def test_filter_pass_equals_reference_filtered_slice(oracle):
+	"""Session.filter_pass + the compaction of the token columns (vectorian_b200/session.py) against the reference's
+	FilteredSliceFactory::create_slice (cpp/slice/static.h:365-416, TokenFilter::pass cpp/query.h:22-28): the rows of the
+	FilteredSlice are the S rows of exactly the tokens the product keeps, in order -- also when nothing or everything passes."""
+	from vectorian_b200.session import Session
+	rng = np.random.default_rng(3)
+	s = rng.random((50, 6)).astype(np.float32)
+	for case in range(30):
+		n = int(rng.integers(1, 40))
+		ids = rng.integers(0, 50, size=n).astype(np.int32)
+		pos = rng.integers(0, 20, size=n).astype(np.int8)
+		tag = rng.integers(0, 45, size=n).astype(np.int8)
+		pos_mask = int(rng.integers(0, 2 ** 20)) if case % 5 else 0
+		tag_mask = int(rng.integers(0, 2 ** 45)) if case % 3 else 0
+		if case == 7:
+			pos_mask = 2 ** 20 - 1    # nothing passes
+		keep = Session.filter_pass(pos, tag, (pos_mask, tag_mask))
+		r_sim = ref.filtered_similarity(s, ids, pos, tag, pos_mask, tag_mask)
+		assert r_sim.shape[0] == int(keep.sum())
+		assert r_sim.tobytes() == s[ids[keep]].tobytes()
