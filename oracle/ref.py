@@ -207,3 +207,55 @@ def filtered_similarity(s, s_id, s_pos, s_tag, pos_mask, tag_mask):
 	_slices().ref_filtered_similarity(s.ctypes.data, s.shape[0], t, s_id.ctypes.data, s_pos.ctypes.data, s_tag.ctypes.data, len(s_id),
 		int(pos_mask), int(tag_mask), sim.ctypes.data, C.byref(n))
 	return sim[:n.value]
+
+
+# ---- the reference's own span iteration and booster (oracle/ref/document_driver.cpp) ----
+
+DOC_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libdocument_ref.so")
+_doc_lib = None
+
+
+def document_available():
+	return os.path.exists(DOC_LIB_PATH)
+
+
+def _document():
+	global _doc_lib
+	if _doc_lib is None:
+		_doc_lib = C.CDLL(DOC_LIB_PATH)
+		_doc_lib.ref_iterate_windows.restype = C.c_int64
+		_doc_lib.ref_iterate_windows.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+		_doc_lib.ref_max_len.restype = C.c_int32
+		_doc_lib.ref_max_len.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32]
+		_doc_lib.ref_boost.restype = C.c_float
+		_doc_lib.ref_boost.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+	return _doc_lib
+
+
+def iterate_windows(span_start, span_end, window_size, window_step, n_fixed=None):
+	"""(slice_id, token_at, len_s) of every callback of the reference's Spans::iterate (cpp/document.h:147-169) over
+	VariableSpans built from (span_start, span_end), or over FixedSpans(n_fixed) when the spans are None."""
+	if span_start is None:
+		n, ps, pe = int(n_fixed), None, None
+	else:
+		span_start = np.ascontiguousarray(span_start, dtype=np.int32)
+		span_end = np.ascontiguousarray(span_end, dtype=np.int32)
+		n, ps, pe = len(span_start), span_start.ctypes.data, span_end.ctypes.data
+	cap = n + 1
+	sl = np.zeros((cap,), np.int32)
+	at = np.zeros((cap,), np.int64)
+	ln = np.zeros((cap,), np.int32)
+	k = _document().ref_iterate_windows(ps, pe, n, int(window_size), int(window_step), sl.ctypes.data, at.ctypes.data, ln.ctypes.data, cap)
+	assert k <= cap
+	return sl[:k], at[:k], ln[:k]
+
+
+def spans_max_len(span_start, span_end, window_size):
+	span_start = np.ascontiguousarray(span_start, dtype=np.int32)
+	span_end = np.ascontiguousarray(span_end, dtype=np.int32)
+	return int(_document().ref_max_len(span_start.ctypes.data, span_end.ctypes.data, len(span_start), int(window_size)))
+
+
+def boost(weights, slice_id):
+	w = np.ascontiguousarray(weights, dtype=np.float32)
+	return float(_document().ref_boost(w.ctypes.data, len(w), int(slice_id)))

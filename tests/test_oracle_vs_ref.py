@@ -245,3 +245,53 @@ def test_filter_pass_equals_reference_filtered_slice(oracle):
 		r_sim = ref.filtered_similarity(s, ids, pos, tag, pos_mask, tag_mask)
 		assert r_sim.shape[0] == int(keep.sum())
 		assert r_sim.tobytes() == s[ids[keep]].tobytes()
+
+
+# ---- window enumeration and booster pinned to the reference's own document.h (oracle/ref/document_driver.cpp) ----
+
+needs_document = pytest.mark.skipif(not ref.document_available(), reason="oracle/_ref/libdocument_ref.so not built")
+
+
+@needs_document
+def test_oracle_window_enumeration_equals_reference_spans_iterate(oracle):
+	"""vxo_enumerate_windows against the reference's Spans::iterate over VariableSpans (cpp/document.h:58-104, 147-169):
+	slice ids, token offsets and lengths of every window for a range of window sizes / steps, with empty spans (skipped
+	when the whole window is empty), a single span, steps larger than the window; max_len as the reference computes it."""
+	rng = np.random.default_rng(21)
+	for case in range(40):
+		n = int(rng.integers(1, 60))
+		lens = rng.integers(0 if case % 2 else 1, 12, size=n)
+		ends = np.cumsum(lens)
+		starts = ends - lens
+		n_tok = int(ends[-1])
+		for window_size, window_step in ((1, 1), (2, 1), (3, 2), (5, 3), (2, 5), (7, 7)):
+			r_slice, r_at, r_len = ref.iterate_windows(starts, ends, window_size, window_step)
+			oc = oracle.OracleCorpus(np.zeros(max(n_tok, 1), np.int32), [0, n_tok], starts, ends, [0, n], window_size, window_step)
+			o_doc, o_slice, o_tok, o_len = oc.windows()
+			np.testing.assert_array_equal(o_slice, r_slice)
+			np.testing.assert_array_equal(o_tok, r_at)
+			np.testing.assert_array_equal(o_len, r_len)
+			assert np.all(o_doc == 0)
+			if len(r_len):
+				assert int(r_len.max()) <= ref.spans_max_len(starts, ends, window_size)
+
+
+@needs_document
+def test_boost_lookup_equals_reference_booster():
+	"""Booster::get_boost (cpp/document.h:175-187) is a plain lookup by slice id -- what vx_corpus_set_boost stores."""
+	w = np.random.default_rng(2).uniform(0.25, 2.0, size=37).astype(np.float32)
+	for i in (0, 1, 17, 36):
+		assert np.float32(ref.boost(w, i)) == w[i]
+
+
+@needs_document
+def test_fixed_spans_iterate_like_unit_variable_spans():
+	"""The reference's token-level partition (FixedSpans, cpp/document.h:26-55) enumerates the windows that one-token
+	VariableSpans do -- which is how the host API hands a token-level partition to vx_corpus_create."""
+	for n in (1, 2, 9, 40):
+		unit = np.arange(n, dtype=np.int32)
+		for window_size, window_step in ((1, 1), (3, 1), (4, 2), (2, 3)):
+			a = ref.iterate_windows(None, None, window_size, window_step, n_fixed=n)
+			b = ref.iterate_windows(unit, unit + 1, window_size, window_step)
+			for x, y in zip(a, b):
+				np.testing.assert_array_equal(x, y)
