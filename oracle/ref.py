@@ -259,3 +259,60 @@ def spans_max_len(span_start, span_end, window_size):
 def boost(weights, slice_id):
 	w = np.ascontiguousarray(weights, dtype=np.float32)
 	return float(_document().ref_boost(w.ctypes.data, len(w), int(slice_id)))
+
+
+# ---- the reference's own result rendering (oracle/ref/flow_driver.cpp) ----
+
+FLOW_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libflow_ref.so")
+_flow_lib = None
+
+
+def flow_available():
+	return os.path.exists(FLOW_LIB_PATH)
+
+
+def regions(s_idx, s_len, s_pos, s_tag, t_idx, t_len, t_pos, token_at, slice_len, target, dist, window_size,
+		token_filter=None, gap_s=None, gap_t=None):
+	"""Flow::py_regions / py_omitted of the reference (cpp/match/flow.cpp:8-188 with match.h, region.h) for an injective
+	alignment target[j] (window position of query token j or -1) with distances dist[j], over document tokens given by
+	character offset / length / POS id / tag id and query tokens likewise.  gap_s / gap_t: gap cost by gap length
+	(Matcher::gap_cost_s / gap_cost_t).  Returns (regions, omitted) in the shape of oracle/render.py: regions = dicts with
+	's' (start, end), 'gap_penalty', 'matched' and, if matched, 'pos_s' (POS id) and 'edges' (dicts with 't_slice',
+	't_index', 't_pos' (POS id), 'flow', 'distance'); omitted = [(start, end)]."""
+	global _flow_lib
+	if _flow_lib is None:
+		_flow_lib = C.CDLL(FLOW_LIB_PATH)
+		_flow_lib.ref_regions.restype = C.c_int64
+		_flow_lib.ref_regions.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+			C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+			C.c_int32, C.c_int32, C.c_uint64, C.c_uint64, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]
+	a = lambda x, dt: np.ascontiguousarray(x, dtype=dt)
+	s_idx, s_len, s_pos, s_tag = a(s_idx, np.int32), a(s_len, np.int8), a(s_pos, np.int8), a(s_tag, np.int8)
+	t_idx, t_len, t_pos = a(t_idx, np.int32), a(t_len, np.int8), a(t_pos, np.int8)
+	target, dist = a(target, np.int16), a(dist, np.float32)
+	gap_s = a(gap_s if gap_s is not None else [0.0], np.float32)
+	gap_t = a(gap_t if gap_t is not None else [0.0], np.float32)
+	cap = 64 + 16 * (len(s_idx) + len(t_idx))
+	out = np.zeros((cap,), np.float64)
+	pm, tm = (0, 0) if token_filter is None else token_filter
+	n = _flow_lib.ref_regions(s_idx.ctypes.data, s_len.ctypes.data, s_pos.ctypes.data, s_tag.ctypes.data, len(s_idx),
+		t_idx.ctypes.data, t_len.ctypes.data, t_pos.ctypes.data, len(t_idx), int(token_at), int(slice_len),
+		target.ctypes.data, dist.ctypes.data, int(window_size), 0 if token_filter is None else 1, int(pm), int(tm),
+		gap_s.ctypes.data, len(gap_s), gap_t.ctypes.data, len(gap_t), out.ctypes.data, cap)
+	assert n >= 0
+	it = iter(out[:n])
+	nxt = lambda: next(it)
+	result = []
+	for _ in range(int(nxt())):
+		kind, s0, s1, pen = int(nxt()), int(nxt()), int(nxt()), float(np.float32(nxt()))
+		r = {'s': (s0, s1), 'gap_penalty': pen, 'matched': kind == 1}
+		if kind == 1:
+			r['pos_s'] = int(nxt())
+			edges = []
+			for _ in range(int(nxt())):
+				ti, a0, a1, tp, fl, di = int(nxt()), int(nxt()), int(nxt()), int(nxt()), float(np.float32(nxt())), float(np.float32(nxt()))
+				edges.append({'t_slice': (a0, a1), 't_index': ti, 't_pos': tp, 'flow': fl, 'distance': di})
+			r['edges'] = edges
+		result.append(r)
+	omitted = [(int(nxt()), int(nxt())) for _ in range(int(nxt()))]
+	return result, omitted

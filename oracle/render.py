@@ -10,9 +10,11 @@ Follows, statement by statement:
   CoreMatch.regions / omitted      /root/reference/vectorian/index.py:329-369
   Match.to_json                    /root/reference/vectorian/index.py:249-292
 
-Parity pinned how: no reference test or fixture covers rendering and the C++ cannot be built here (pybind11 / xtensor
-types throughout match.h), so this file is a literal transcription of the control flow above into plain Python over
-plain data; `tests/test_render_oracle.py` drives the product and this checker with the same inputs.
+Parity pinned how: no reference test or fixture covers rendering.  This file is a literal transcription of the control flow
+above into plain Python over plain data; `tests/test_render_oracle.py` drives the product and this checker with the same
+inputs AND checks this file against the reference's own code: `oracle/ref/flow_driver.cpp` compiles the unmodified
+match/flow.cpp, match/match.h and match/region.h (include guards of the pybind11 / xtensor headers pre-defined, stand-in
+types for the few names they touch) and returns the regions / omitted slices the reference builds for the same match.
 
 One reference behaviour worth knowing (kept, because parity is the bar): with a token filter the grouping loop at
 flow.cpp:143 compares the RAW (filtered) target of the next edge with the MAPPED target of the current one, so two

@@ -5,7 +5,7 @@ vectorian/index.py:249-292, 329-369).  Runs without a GPU: matches are built fro
 import numpy as np
 import pytest
 
-from oracle import render
+from oracle import ref, render
 from vectorian_b200 import gaps
 from vectorian_b200._cabi import HIT_DTYPE
 from vectorian_b200.alignment import LocalAlignment
@@ -39,6 +39,34 @@ def make_session(seed=5, n_docs=3, sent_per_doc=12, vocab=60):
 	return Session(Corpus(docs), [emb]), emb, words
 
 
+def check_against_reference_flow(session, pdoc, doc, p_query, token_at, slice_len, target, dist, context, token_filter, gap_fns, want_regions, want_omitted):
+	"""oracle/render.py against the reference's OWN Flow::py_regions / py_omitted (oracle/ref/flow_driver.cpp: the unmodified
+	match/flow.cpp, match/match.h, match/region.h): slices, penalties, matched flags, edges, POS of every region."""
+	pos_id = lambda name: POS.index(name) if name in POS else 99
+	n = doc.n_tokens
+	t_tok = p_query.tokens
+	gap_s = [float(gap_fns[0](k)) for k in range(n + 2)]
+	gap_t = [float(gap_fns[1](k)) for k in range(len(t_tok) + 2)]
+	got, got_omitted = ref.regions(
+		[int(doc.token_idx[i]) for i in range(n)], [int(doc.token_len[i]) for i in range(n)],
+		[int(pdoc.token_pos[i]) for i in range(n)], [int(pdoc.token_tag[i]) for i in range(n)],
+		[t['start'] for t in t_tok], [t['end'] - t['start'] for t in t_tok], [pos_id(t.get('pos', 'X')) for t in t_tok],
+		token_at, slice_len, target, dist, context, token_filter, gap_s, gap_t)
+	assert len(got) == len(want_regions)
+	for g, w in zip(got, want_regions):
+		assert g['s'] == tuple(w['s']) and g['matched'] == w['matched']
+		assert np.float32(g['gap_penalty']) == np.float32(w['gap_penalty'])
+		if g['matched']:
+			assert g['pos_s'] == session._vocab.pos.get(w['pos_s'])
+			assert len(g['edges']) == len(w['edges'])
+			for ge, we in zip(g['edges'], w['edges']):
+				assert ge['t_slice'] == tuple(we['t_slice']) and ge['t_index'] == we['t_index']
+				assert np.float32(ge['flow']) == np.float32(we['flow']) and np.float32(ge['distance']) == np.float32(we['distance'])
+				assert ge['t_pos'] == pos_id(we['t_pos'])
+	assert got_omitted == [tuple(x) for x in want_omitted]
+	return 1
+
+
 def random_target(rng, n_s, n_t, p_match):
 	"""A monotone injective alignment: target[j] strictly increasing over the matched query tokens, -1 elsewhere."""
 	target = np.full((n_t,), -1, dtype=np.int16)
@@ -59,7 +87,7 @@ def test_regions_omitted_to_json_equal_the_reference_restatement(window, step, f
 	index = partition.index(OptimizedSpanSim(EmbeddingTokenSim(emb, CosineSim()), LocalAlignment(gap=gap)), nlp=whitespace_nlp)
 	rng = np.random.default_rng(window * 100 + step * 10 + int(filtered))
 	options = {"pos_filter": ["DET", "ADP"]} if filtered else {}
-	n_cases = n_grouped = n_filtered_changes = 0
+	n_cases = n_grouped = n_filtered_changes = n_ref_checked = 0
 	for case in range(120):
 		n_t = int(rng.integers(1, 8))
 		text = " ".join(words[i] for i in rng.integers(0, len(words), size=n_t))
@@ -97,6 +125,9 @@ def test_regions_omitted_to_json_equal_the_reference_restatement(window, step, f
 		edges = [(int(u), j, 1.0, float(dist[j])) for j, u in enumerate(target) if u >= 0]
 		want_regions = render.py_regions(s_tokens, t_tokens, token_at, slice_len, edges, context,
 			filter_pass=None if keep is None else [bool(x) for x in keep], gap_cost_s=gap_fns[0], gap_cost_t=gap_fns[1])
+		if ref.flow_available():
+			n_ref_checked += check_against_reference_flow(session, pdoc, doc, p_query, token_at, slice_len, target, dist, context, token_filter, gap_fns,
+				want_regions, render.py_omitted(t_tokens, target))
 		want = render.render(doc.text_str, p_query.text_str, want_regions, "toy-cosine")
 		got = [(r.s, None if r.match is None else (r.match.pos_s, [((e.t.text, e.t.index, e.t.pos), e.flow, e.distance, e.metric) for e in r.match.edges]),
 			r.gap_penalty) for r in match.regions(context)]
@@ -108,6 +139,7 @@ def test_regions_omitted_to_json_equal_the_reference_restatement(window, step, f
 		n_grouped += sum(1 for r in want_regions if r['matched'] and len(r['edges']) > 1)
 		n_cases += 1
 	assert n_cases > 80
+	assert n_ref_checked == n_cases or not ref.flow_available()
 	if filtered:
 		assert n_filtered_changes > 20          # the filter really removed tokens
 		assert n_grouped > 0                    # ... and the reference's raw-vs-mapped grouping (flow.cpp:143) occurred
